@@ -1,0 +1,162 @@
+// k1_tail.cuh — the part of one pair after the two Viterbi halves: back-trace
+// (ObservationModelFB.cpp:1148-1165) and the alignment summary (reportVariants, cpp:1351-1463).
+// Warp-cooperative; shared by the generic and the register-tiled K1 kernels, which differ only in
+// how a back-pointer code is fetched (functor `Bt`).
+//
+// Back-pointer code of one state column x at one row: code0 = winner among the plane-0 ("not in
+// insertion") candidates in reference source order, bit1 = 1 when the plane-1 state was reached
+// from plane 0 instead of staying in the insertion.
+//   left half  (passMessageTwoDec, cpp:1775): x in 1..H: code0 = y-1 (from x-y, clamped to 0),
+//              J = from plane-1 x-1;  x == 0: 0;  x == RO: 0 RO, 1 H, 2 S+RO, 3 S+H
+//              plane 1: bit1 -> from plane-0 x
+//   right half (passMessageTwoInc, cpp:1715): x in 1..H: code0 = y-1 (to x+y, clamped to RO),
+//              J = plane-1 x;  x == 0: 0 -> 0, 1 -> 1, J -> S;  x == RO: 0 RO, J S+RO
+//              plane 1: bit1 -> plane-0 min(x+1, RO)  (x == 0: plane-0 0)
+#pragma once
+#include "k1_common.cuh"
+
+__device__ __forceinline__ int k1_prev_state_dec(int s, int code0, int bit1, int S, int H, int J)
+{
+    int RO = H + 1;
+    if (s >= S) return bit1 ? (s - S) : s;
+    if (s == 0) return 0;
+    if (s == RO) return (code0 == 0) ? RO : (code0 == 1) ? H : (code0 == 2) ? S + RO : S + H;
+    if (code0 >= J) return S + s - 1;
+    int nx = s - code0 - 1;
+    return nx < 0 ? 0 : nx;
+}
+
+__device__ __forceinline__ int k1_next_state_inc(int s, int code0, int bit1, int S, int H, int J)
+{
+    int RO = H + 1;
+    if (s >= S) {
+        int x = s - S;
+        if (!bit1) return s;
+        if (x == 0) return 0;
+        return (x + 1 > RO) ? RO : x + 1;
+    }
+    if (s == 0) return (code0 == 0) ? 0 : (code0 == 1) ? 1 : S;
+    if (s == RO) return (code0 == 0) ? RO : S + RO;
+    if (code0 >= J) return S + s;
+    int nx = s + code0 + 1;
+    return nx > H ? RO : nx;
+}
+
+// Everything after ms[bMid] is known.  `bt(row, x)` returns code0 | bit1 << 7 of state column x;
+// rows 1..bMid hold the left half (btf[b]), rows bMid+1..R-1 hold btb[row-1].
+// sm_ms: int16[R] scratch; sm_ch / sm_ph: the read's bases and phred bytes; sm_acc: double[R].
+template <class Bt>
+__device__ __forceinline__ void k1_tail(const Bt &bt, int lane, int R, int H, int J, int bMid,
+                                        int msMid, const uint8_t *hap, const uint8_t *sm_ch,
+                                        const uint8_t *sm_ph, int16_t *sm_ms, double *sm_acc,
+                                        const K1Luts *__restrict__ L, double ll, double llOn,
+                                        double llOff, int offHap, int offHapHMQ,
+                                        dindel_pair_out *out, int16_t *hpos_out)
+{
+    const int S = H + 2;
+    // --- back-trace, cpp:1148-1165: lane 0 walks left, lane 1 walks right ---
+    if (lane == 0) {
+        int s = msMid;
+        sm_ms[bMid] = (int16_t)s;
+        for (int b = bMid; b > 0; b--) {
+            int x = s >= S ? s - S : s;
+            int c = bt(b, x);
+            s = k1_prev_state_dec(s, c & 127, c >> 7, S, H, J);
+            sm_ms[b - 1] = (int16_t)s;
+        }
+    } else if (lane == 1) {
+        int s = msMid;
+        for (int b = bMid; b < R - 1; b++) {
+            int x = s >= S ? s - S : s;
+            int c = bt(b + 1, x);
+            s = k1_next_state_inc(s, c & 127, c >> 7, S, H, J);
+            sm_ms[b + 1] = (int16_t)s;
+        }
+    }
+    __syncwarp();
+    // --- summary, cpp:1351-1463, one read base per lane ---
+    int first = 0x7fffffff, last = -1;
+    int nInd = 0, nMis = 0, nBQT = 0, nmmBQT = 0, nL = 0, nR = 0;
+    for (int b = lane; b < R; b += 32) {
+        int s = sm_ms[b];
+        int plane1 = s >= S;
+        int x = plane1 ? s - S : s;
+        bool on = (x > 0) && (x <= H);
+        int hp;
+        double acc = 0.0;
+        if (!on) {
+            hp = (x == 0) ? DINDEL_HPOS_LO : DINDEL_HPOS_RO;
+        } else if (plane1) {
+            hp = DINDEL_HPOS_INS;
+            if (b == 0 || sm_ms[b - 1] < S) nInd++; // one event per insertion run (cpp:1379-1395)
+        } else {
+            hp = x - 1;
+            first = min(first, hp);
+            last = max(last, hp);
+            int ph = sm_ph[b];
+            int qf = L->qflag[ph];
+            if (qf & 1) {
+                nBQT++;
+                acc = L->log10q[ph];
+            }
+            if (sm_ch[b] != hap[x - 1]) { // cpp:1410-1430
+                if (qf & 1) nmmBQT++;
+                if (b < 6) nL++;
+                if (b > R - 6) nR++;
+                if (qf & 2) nMis++;
+            }
+            if (b < R - 1) { // deletion, cpp:1437-1453
+                int ns = sm_ms[b + 1];
+                if (ns < S && ns - s > 1) nInd++;
+            }
+        }
+        sm_acc[b] = acc;
+        if (hpos_out) hpos_out[b] = (int16_t)hp;
+    }
+    first = __reduce_min_sync(0xffffffffu, first);
+    last = __reduce_max_sync(0xffffffffu, last);
+    nInd = __reduce_add_sync(0xffffffffu, nInd);
+    nMis = __reduce_add_sync(0xffffffffu, nMis);
+    nBQT = __reduce_add_sync(0xffffffffu, nBQT);
+    nmmBQT = __reduce_add_sync(0xffffffffu, nmmBQT);
+    nL = __reduce_add_sync(0xffffffffu, nL);
+    nR = __reduce_add_sync(0xffffffffu, nR);
+    __syncwarp();
+    if (lane == 0) {
+        // mLogBQ is a left-to-right FP64 sum in the reference (cpp:1406); adding +0.0 for the
+        // bases that do not count leaves every partial sum bit-identical.
+        double m = 0.0;
+        for (int b = 0; b < R; b++) m += sm_acc[b];
+        __align__(16) dindel_pair_out o;
+        o.ll = ll; o.llOn = llOn; o.llOff = llOff; o.mLogBQ = m;
+        o.firstBase = (last < 0) ? -1 : first;
+        o.lastBase = last;
+        o.numIndels = (uint16_t)nInd; o.numMismatch = (uint16_t)nMis;
+        o.nBQT = (uint16_t)nBQT; o.nmmBQT = (uint16_t)nmmBQT;
+        o.nMMLeft = (uint16_t)nL; o.nMMRight = (uint16_t)nR;
+        o.offHap = (uint8_t)offHap; o.offHapHMQ = (uint8_t)offHapHMQ;
+        o.bMid = (int16_t)bMid;
+        // cpp DInDel.cpp:1722-1735: ll > 0.1 is fatal, NaN/Inf skips the window
+        o.status = (ll > 0.1) ? DINDEL_WIN_LL_POSITIVE
+                              : ((ll != ll || ll - ll != 0.0) ? DINDEL_WIN_NAN : DINDEL_WIN_OK);
+        for (int i = 0; i < 7; i++) o.pad[i] = 0;
+        const int4 *src = reinterpret_cast<const int4 *>(&o);
+        int4 *dst = reinterpret_cast<int4 *>(out);
+        dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2]; dst[3] = src[3];
+    }
+    __syncwarp();
+}
+
+// A pair that the reference refuses with "hapSize error." (cpp:47).
+__device__ __forceinline__ void k1_write_hapsize_error(dindel_pair_out *out, int lane)
+{
+    if (lane == 0) {
+        dindel_pair_out o;
+        o.ll = 0.0; o.llOn = 0.0; o.llOff = 0.0; o.mLogBQ = 0.0;
+        o.firstBase = -1; o.lastBase = -1;
+        o.numIndels = 0; o.numMismatch = 0; o.nBQT = 0; o.nmmBQT = 0; o.nMMLeft = 0; o.nMMRight = 0;
+        o.offHap = 0; o.offHapHMQ = 0; o.bMid = 0; o.status = DINDEL_WIN_HAPSIZE;
+        for (int i = 0; i < 7; i++) o.pad[i] = 0;
+        *out = o;
+    }
+}

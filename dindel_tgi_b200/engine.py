@@ -1,0 +1,315 @@
+"""ctypes binding of libdindel_b200.so (include/dindel_b200.h) + numpy batch containers.
+
+This is a test / bench driver over the C ABI, not a compute path: every number comes from the
+CUDA library.  There is no CPU fallback; loading fails loudly when the library is missing and
+`Engine()` raises when no CUDA device is usable.
+
+Host-side mirror of the reference interface (same names and argument meaning):
+  Engine.compute_likelihoods(batch)  ~  DetInDel::computeLikelihoods  (DInDel.cpp:1707-1739)
+  PairResults fields                 ~  MLAlignment                   (MLAlignment.hpp:50-70)
+  Params                             ~  ObservationModelParameters    (ObservationModel.hpp:28-99)
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdindel_b200.so")
+
+WIN_OK, WIN_HAPSIZE, WIN_NAN, WIN_LL_POSITIVE = 0, 1, 2, 3
+HPOS_INS, HPOS_LO, HPOS_RO = -1, -3, -4
+READ_UNMAPPED, READ_REVERSE = 1, 2
+
+
+class Params(C.Structure):
+    _fields_ = [(n, C.c_double) for n in
+                ("pError", "pMut", "mapQualThreshold", "pFirstgLO", "checkBaseQualThreshold")] + \
+               [(n, C.c_int32) for n in ("maxLengthDel", "padCover", "bMid", "forceReadOnHaplotype")]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class _BatchIn(C.Structure):
+    _fields_ = [("n_windows", C.c_int32), ("n_haps", C.c_int32), ("n_reads", C.c_int32),
+                ("reserved", C.c_int32),
+                ("hap_start", C.c_void_p), ("win_hap", C.c_void_p), ("win_read", C.c_void_p),
+                ("hap_off", C.c_void_p), ("hap_seq", C.c_void_p), ("read_off", C.c_void_p),
+                ("read_seq", C.c_void_p), ("read_qual", C.c_void_p), ("read_mapq", C.c_void_p),
+                ("read_start", C.c_void_p), ("read_flags", C.c_void_p)]
+
+
+class _BatchOut(C.Structure):
+    _fields_ = [("n_pairs", C.c_int64), ("pairs", C.c_void_p), ("hpos", C.c_void_p),
+                ("hpos_stride", C.c_int32), ("reserved", C.c_int32), ("win_pair", C.c_void_p),
+                ("win_status", C.c_void_p), ("read_on_hap", C.c_void_p)]
+
+
+class Timing(C.Structure):
+    _fields_ = [("h2d_ms", C.c_float), ("prep_ms", C.c_float), ("k1_ms", C.c_float),
+                ("d2h_ms", C.c_float), ("total_ms", C.c_float), ("k1_launches", C.c_int32),
+                ("prep_launches", C.c_int32), ("n_pairs", C.c_int64), ("n_cells", C.c_int64)]
+
+
+PAIR_DTYPE = np.dtype([
+    ("ll", "<f8"), ("llOn", "<f8"), ("llOff", "<f8"), ("mLogBQ", "<f8"),
+    ("firstBase", "<i4"), ("lastBase", "<i4"),
+    ("numIndels", "<u2"), ("numMismatch", "<u2"), ("nBQT", "<u2"), ("nmmBQT", "<u2"),
+    ("nMMLeft", "<u2"), ("nMMRight", "<u2"),
+    ("offHap", "u1"), ("offHapHMQ", "u1"), ("bMid", "<i2"), ("status", "u1"), ("pad", "u1", (7,)),
+])
+assert PAIR_DTYPE.itemsize == 64
+
+EXPORTS = [
+    "dindel_b200_default_params", "dindel_b200_cli_params", "dindel_b200_abi_version",
+    "dindel_b200_strerror", "dindel_b200_last_error", "dindel_b200_create", "dindel_b200_destroy",
+    "dindel_b200_count_pairs", "dindel_b200_count_cells", "dindel_b200_submit",
+    "dindel_b200_upload", "dindel_b200_run", "dindel_b200_download", "dindel_b200_sync",
+    "dindel_b200_get_timing", "dindel_b200_hpos_stride", "dindel_b200_alloc_pinned",
+    "dindel_b200_free_pinned", "dindel_b200_measure_fp64_peak",
+]
+
+_lib = None
+
+
+def load_library():
+    """dlopen the CUDA library; raises (no fallback) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  There is no CPU fallback for this path.")
+    lib = C.CDLL(LIB_PATH)
+    lib.dindel_b200_strerror.restype = C.c_char_p
+    lib.dindel_b200_last_error.restype = C.c_char_p
+    lib.dindel_b200_last_error.argtypes = [C.c_void_p]
+    lib.dindel_b200_create.argtypes = [C.POINTER(Params), C.c_int, C.POINTER(C.c_void_p)]
+    lib.dindel_b200_destroy.argtypes = [C.c_void_p]
+    lib.dindel_b200_count_pairs.restype = C.c_int64
+    lib.dindel_b200_count_pairs.argtypes = [C.POINTER(_BatchIn)]
+    lib.dindel_b200_count_cells.restype = C.c_int64
+    lib.dindel_b200_count_cells.argtypes = [C.POINTER(_BatchIn)]
+    lib.dindel_b200_submit.argtypes = [C.c_void_p, C.POINTER(_BatchIn), C.POINTER(_BatchOut)]
+    lib.dindel_b200_upload.argtypes = [C.c_void_p, C.POINTER(_BatchIn), C.c_int]
+    lib.dindel_b200_run.argtypes = [C.c_void_p]
+    lib.dindel_b200_sync.argtypes = [C.c_void_p]
+    lib.dindel_b200_download.argtypes = [C.c_void_p, C.POINTER(_BatchOut)]
+    lib.dindel_b200_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
+    lib.dindel_b200_hpos_stride.argtypes = [C.c_void_p]
+    lib.dindel_b200_alloc_pinned.restype = C.c_void_p
+    lib.dindel_b200_alloc_pinned.argtypes = [C.c_size_t]
+    lib.dindel_b200_free_pinned.argtypes = [C.c_void_p]
+    lib.dindel_b200_measure_fp64_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+    _lib = lib
+    return lib
+
+
+def default_params():
+    p = Params()
+    load_library().dindel_b200_default_params(C.byref(p))
+    return p
+
+
+def cli_params():
+    p = Params()
+    load_library().dindel_b200_cli_params(C.byref(p))
+    return p
+
+
+class Batch:
+    """A batch of realignment windows in the C ABI's SoA/CSR layout (numpy, host memory)."""
+
+    def __init__(self, hap_start, win_hap, win_read, hap_off, hap_seq, read_off, read_seq,
+                 read_qual, read_mapq, read_start, read_flags):
+        self.hap_start = np.ascontiguousarray(hap_start, dtype=np.uint32)
+        self.win_hap = np.ascontiguousarray(win_hap, dtype=np.int32)
+        self.win_read = np.ascontiguousarray(win_read, dtype=np.int32)
+        self.hap_off = np.ascontiguousarray(hap_off, dtype=np.int64)
+        self.hap_seq = np.ascontiguousarray(hap_seq, dtype=np.uint8)
+        self.read_off = np.ascontiguousarray(read_off, dtype=np.int64)
+        self.read_seq = np.ascontiguousarray(read_seq, dtype=np.uint8)
+        self.read_qual = np.ascontiguousarray(read_qual, dtype=np.uint8)
+        self.read_mapq = np.ascontiguousarray(read_mapq, dtype=np.uint8)
+        self.read_start = np.ascontiguousarray(read_start, dtype=np.uint32)
+        self.read_flags = np.ascontiguousarray(read_flags, dtype=np.uint8)
+
+    @property
+    def n_windows(self):
+        return len(self.hap_start)
+
+    @property
+    def n_haps(self):
+        return len(self.hap_off) - 1
+
+    @property
+    def n_reads(self):
+        return len(self.read_off) - 1
+
+    def pair_offsets(self):
+        nh = np.diff(self.win_hap).astype(np.int64)
+        nr = np.diff(self.win_read).astype(np.int64)
+        return np.concatenate([[0], np.cumsum(nh * nr)]).astype(np.int64)
+
+    def n_pairs(self):
+        return int(self.pair_offsets()[-1])
+
+    def n_cells(self):
+        """sum over pairs of R*(H+2): the GCUPS numerator."""
+        cols = (self.hap_off[self.win_hap[1:]] - self.hap_off[self.win_hap[:-1]]) + \
+            2 * np.diff(self.win_hap).astype(np.int64)
+        rows = self.read_off[self.win_read[1:]] - self.read_off[self.win_read[:-1]]
+        return int(np.sum(cols * rows))
+
+    def input_bytes(self):
+        return sum(a.nbytes for a in (self.hap_start, self.win_hap, self.win_read, self.hap_off,
+                                      self.hap_seq, self.read_off, self.read_seq, self.read_qual,
+                                      self.read_mapq, self.read_start, self.read_flags))
+
+    def _c(self):
+        b = _BatchIn()
+        b.n_windows, b.n_haps, b.n_reads = self.n_windows, self.n_haps, self.n_reads
+        for n in ("hap_start", "win_hap", "win_read", "hap_off", "hap_seq", "read_off", "read_seq",
+                  "read_qual", "read_mapq", "read_start", "read_flags"):
+            setattr(b, n, getattr(self, n).ctypes.data)
+        return b
+
+    def window(self, w):
+        """(haps list[bytes], reads list[(seq bytes, qual array, mapq, start, flags)], hapStart)."""
+        haps = [bytes(self.hap_seq[self.hap_off[h]:self.hap_off[h + 1]])
+                for h in range(self.win_hap[w], self.win_hap[w + 1])]
+        reads = []
+        for r in range(self.win_read[w], self.win_read[w + 1]):
+            a, b = self.read_off[r], self.read_off[r + 1]
+            reads.append((bytes(self.read_seq[a:b]), self.read_qual[a:b].copy(), int(self.read_mapq[r]),
+                          int(self.read_start[r]), int(self.read_flags[r])))
+        return haps, reads, int(self.hap_start[w])
+
+    def slice_windows(self, w0, w1):
+        """Sub-batch of windows [w0, w1) (copies)."""
+        h0, h1 = int(self.win_hap[w0]), int(self.win_hap[w1])
+        r0, r1 = int(self.win_read[w0]), int(self.win_read[w1])
+        hb0, hb1 = int(self.hap_off[h0]), int(self.hap_off[h1])
+        rb0, rb1 = int(self.read_off[r0]), int(self.read_off[r1])
+        return Batch(self.hap_start[w0:w1], self.win_hap[w0:w1 + 1] - h0, self.win_read[w0:w1 + 1] - r0,
+                     self.hap_off[h0:h1 + 1] - hb0, self.hap_seq[hb0:hb1], self.read_off[r0:r1 + 1] - rb0,
+                     self.read_seq[rb0:rb1], self.read_qual[rb0:rb1], self.read_mapq[r0:r1],
+                     self.read_start[r0:r1], self.read_flags[r0:r1])
+
+    @staticmethod
+    def from_windows(windows):
+        """windows: iterable of (hapStart, [hap bytes...], [(seq, qual, mapq, start, flags)...])."""
+        hs, wh, wr, ho, hseq, ro, rseq, rq, mq, rs, rf = [], [0], [0], [0], [], [0], [], [], [], [], []
+        for hap_start, haps, reads in windows:
+            hs.append(hap_start)
+            for h in haps:
+                hseq.append(np.frombuffer(bytes(h), dtype=np.uint8))
+                ho.append(ho[-1] + len(h))
+            for seq, qual, mapq, start, flags in reads:
+                rseq.append(np.frombuffer(bytes(seq), dtype=np.uint8))
+                rq.append(np.asarray(qual, dtype=np.uint8))
+                assert len(seq) == len(rq[-1])
+                ro.append(ro[-1] + len(seq))
+                mq.append(mapq)
+                rs.append(start & 0xffffffff)
+                rf.append(flags)
+            wh.append(len(ho) - 1)
+            wr.append(len(ro) - 1)
+        cat = lambda l: np.concatenate(l) if l else np.zeros(0, dtype=np.uint8)
+        return Batch(hs, wh, wr, ho, cat(hseq), ro, cat(rseq), cat(rq), mq, rs, rf)
+
+
+class PairResults:
+    def __init__(self, pairs, win_pair, win_status, read_on_hap, hpos, timing):
+        self.pairs, self.win_pair, self.win_status = pairs, win_pair, win_status
+        self.read_on_hap, self.hpos, self.timing = read_on_hap, hpos, timing
+
+
+class Engine:
+    """One context on one device (dindel_b200_create)."""
+
+    def __init__(self, params=None, device=0):
+        self.lib = load_library()
+        self.params = params if params is not None else cli_params()
+        h = C.c_void_p()
+        rc = self.lib.dindel_b200_create(C.byref(self.params), device, C.byref(h))
+        if rc != 0:
+            raise RuntimeError("dindel_b200_create failed: %s" % self.lib.dindel_b200_strerror(rc).decode())
+        self.h = h
+        self._resident = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.dindel_b200_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise RuntimeError("%s failed: %s (%s)" % (what, self.lib.dindel_b200_strerror(rc).decode(),
+                                                       self.lib.dindel_b200_last_error(self.h).decode()))
+
+    def _alloc_out(self, batch, want_hpos, stride=None):
+        n = batch.n_pairs()
+        pairs = np.zeros(n, dtype=PAIR_DTYPE)
+        win_pair = np.zeros(batch.n_windows + 1, dtype=np.int64)
+        win_status = np.zeros(batch.n_windows, dtype=np.int32)
+        on_hap = np.zeros(batch.n_reads, dtype=np.uint8)
+        hpos = None
+        o = _BatchOut()
+        o.n_pairs = n
+        o.pairs = pairs.ctypes.data
+        o.win_pair = win_pair.ctypes.data
+        o.win_status = win_status.ctypes.data
+        o.read_on_hap = on_hap.ctypes.data
+        if want_hpos:
+            if stride is None:
+                maxr = int(np.max(np.diff(batch.read_off))) if batch.n_reads else 0
+                stride = max(8, (maxr + 7) & ~7)
+            hpos = np.full((n, stride), -32768, dtype=np.int16)
+            o.hpos = hpos.ctypes.data
+            o.hpos_stride = stride
+        return o, pairs, win_pair, win_status, on_hap, hpos
+
+    def timing(self):
+        t = Timing()
+        self.lib.dindel_b200_get_timing(self.h, C.byref(t))
+        return t
+
+    def compute_likelihoods(self, batch, want_hpos=True):
+        """Host buffers in, host buffers out: dindel_b200_submit."""
+        o, pairs, win_pair, win_status, on_hap, hpos = self._alloc_out(batch, want_hpos)
+        cb = batch._c()
+        self._check(self.lib.dindel_b200_submit(self.h, C.byref(cb), C.byref(o)), "submit")
+        return PairResults(pairs, win_pair, win_status, on_hap, hpos, self.timing())
+
+    # resident-batch API (bench: kernel-only timing with inputs already in HBM)
+    def upload(self, batch, want_hpos=False):
+        cb = batch._c()
+        self._check(self.lib.dindel_b200_upload(self.h, C.byref(cb), int(want_hpos)), "upload")
+        self._resident = (batch, want_hpos)
+
+    def run(self, sync=True):
+        self._check(self.lib.dindel_b200_run(self.h), "run")
+        if sync:
+            self._check(self.lib.dindel_b200_sync(self.h), "sync")
+        return self.timing()
+
+    def download(self):
+        batch, want_hpos = self._resident
+        stride = self.lib.dindel_b200_hpos_stride(self.h) if want_hpos else None
+        o, pairs, win_pair, win_status, on_hap, hpos = self._alloc_out(batch, want_hpos, stride)
+        self._check(self.lib.dindel_b200_download(self.h, C.byref(o)), "download")
+        return PairResults(pairs, win_pair, win_status, on_hap, hpos, self.timing())
+
+    def measure_fp64_peak(self):
+        v = C.c_double()
+        self._check(self.lib.dindel_b200_measure_fp64_peak(self.h, C.byref(v)), "measure_fp64_peak")
+        return v.value

@@ -1,0 +1,149 @@
+/* include/dindel_b200.h — C ABI of the B200 read x candidate-haplotype likelihood engine.
+ *
+ * Drop-in boundary for the path DetInDel::empiricalDistributionMethod drives in the reference
+ * (all citations relative to the reference tree):
+ *   - DetInDel::computeLikelihoods (DInDel.cpp:1707-1739), i.e. for every (hap, read) of a window
+ *     ObservationModelFBMaxErr(hap, read, leftPos, obsParams).calcLikelihood()
+ *     (ObservationModelFB.hpp:160,133; ObservationModelFB.cpp:1068)         -> dindel_b200_submit
+ *   - the pair-marginalisation core of DetInDel::diploidGLF (DInDel.cpp:3085-3113,3349-3390)
+ *                                                                            -> dindel_b200_diploid
+ *   - the variational-Bayes EM core of DetInDel::estimateHaplotypeFrequenciesBayesEM
+ *     (DInDel.cpp:2431-2543)                                                 -> dindel_b200_bayes_em
+ * Plain C, POD only, caller-owned buffers, no exceptions: every entry returns 0 or a negative
+ * DINDEL_E_* code (dindel_b200_strerror).  There is NO CPU fallback: without a CUDA device every
+ * compute entry fails with DINDEL_E_NO_DEVICE.
+ */
+#ifndef DINDEL_B200_H
+#define DINDEL_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DINDEL_B200_ABI_VERSION 1
+
+/* error codes (batch-fatal) */
+#define DINDEL_OK 0
+#define DINDEL_E_INVALID (-1)    /* bad argument / inconsistent batch */
+#define DINDEL_E_NO_DEVICE (-2)  /* no usable CUDA device */
+#define DINDEL_E_CUDA (-3)       /* CUDA runtime error (see dindel_b200_last_error) */
+#define DINDEL_E_NOMEM (-4)
+#define DINDEL_E_UNSUPPORTED (-5) /* shape outside what the kernels are built for */
+
+/* per-window status, mirrors the reference's per-window skip reasons (DInDel.cpp:1361-1408) */
+#define DINDEL_WIN_OK 0
+#define DINDEL_WIN_HAPSIZE 1     /* throw "hapSize error."  (ObservationModelFB.cpp:47) */
+#define DINDEL_WIN_NAN 2         /* throw "Nan detected"    (DInDel.cpp:1732-1735) */
+#define DINDEL_WIN_LL_POSITIVE 3 /* ll > 0.1 -> exit(1)     (DInDel.cpp:1722-1731) */
+
+/* hpos codes (MLAlignment.hpp:31-34) */
+#define DINDEL_HPOS_INS (-1)
+#define DINDEL_HPOS_LO (-3)
+#define DINDEL_HPOS_RO (-4)
+
+/* read flag bits */
+#define DINDEL_READ_UNMAPPED 1u /* Read::isUnmapped() (Read.hpp:200) */
+#define DINDEL_READ_REVERSE 2u  /* Read::onReverseStrand */
+
+/* Replaces ObservationModelParameters (ObservationModel.hpp:28-99): the fields the path reads.
+ * dindel_b200_default_params() fills the struct defaults (ObservationModel.hpp:39-62);
+ * dindel_b200_cli_params() fills the `dindel` CLI defaults (DInDel.cpp:4122-4157,3943-3948). */
+typedef struct dindel_params {
+    double pError, pMut, mapQualThreshold, pFirstgLO, checkBaseQualThreshold;
+    int32_t maxLengthDel, padCover, bMid, forceReadOnHaplotype;
+} dindel_params;
+
+/* One batch of realignment windows, SoA with CSR offsets.  Replaces the (haps, reads, leftPos)
+ * arguments of DetInDel::computeLikelihoods (DInDel.cpp:1707).
+ * Sequences are the bytes Haplotype::seq / Read::seq hold (ASCII; emission test is plain char
+ * equality or hap=='N', ObservationModelFB.cpp:246).  Qualities are the phred bytes of the BAM
+ * record (Read.hpp:127,143): the library converts them exactly as Read's ctor does. */
+typedef struct dindel_batch_in {
+    int32_t n_windows;
+    int32_t n_haps;             /* total over windows */
+    int32_t n_reads;            /* total over windows */
+    int32_t reserved;
+    const uint32_t *hap_start;  /* [n_windows]   leftPos of the window (hapStart of Init, cpp:35) */
+    const int32_t *win_hap;     /* [n_windows+1] window -> first haplotype */
+    const int32_t *win_read;    /* [n_windows+1] window -> first read */
+    const int64_t *hap_off;     /* [n_haps+1]    haplotype -> first base in hap_seq */
+    const char *hap_seq;        /* [hap_off[n_haps]] */
+    const int64_t *read_off;    /* [n_reads+1]   read -> first base in read_seq/read_qual */
+    const char *read_seq;       /* [read_off[n_reads]] */
+    const uint8_t *read_qual;   /* [read_off[n_reads]] phred */
+    const uint8_t *read_mapq;   /* [n_reads] phred mapping quality (bam core.qual) */
+    const uint32_t *read_start; /* [n_reads] uint32_t(read.posStat.first) (cpp:52) */
+    const uint8_t *read_flags;  /* [n_reads] DINDEL_READ_* */
+} dindel_batch_in;
+
+/* Flat image of one MLAlignment (MLAlignment.hpp:50-70), 64 bytes.  The AlignedVariant maps
+ * (indels/snps/hapIndelCovered/hapSNPCovered) are pure functions of hpos / firstBase / lastBase
+ * and the sequences; the host adapter rebuilds them on demand. */
+typedef struct dindel_pair_out {
+    double ll, llOn, llOff, mLogBQ;
+    int32_t firstBase, lastBase;
+    uint16_t numIndels, numMismatch, nBQT, nmmBQT, nMMLeft, nMMRight;
+    uint8_t offHap, offHapHMQ;
+    int16_t bMid;
+    uint8_t status; /* DINDEL_WIN_* of this pair */
+    uint8_t pad[7];
+} dindel_pair_out;
+
+/* Results, caller-allocated.  Pair (w, h, r) lives at win_pair[w] + r*nh(w) + h  (r-major, like
+ * rl[r*nh+h] at DInDel.cpp:2129).  win_pair is filled by the library ([n_windows+1]). */
+typedef struct dindel_batch_out {
+    int64_t n_pairs;            /* capacity of pairs[] (>= dindel_b200_count_pairs) */
+    dindel_pair_out *pairs;     /* [n_pairs] */
+    int16_t *hpos;              /* optional [n_pairs * hpos_stride]: MLAlignment::hpos */
+    int32_t hpos_stride;        /* >= longest read when hpos != NULL */
+    int32_t reserved;
+    int64_t *win_pair;          /* [n_windows+1] */
+    int32_t *win_status;        /* [n_windows] DINDEL_WIN_* (first failing pair's reason) */
+    uint8_t *read_on_hap;       /* optional [n_reads]: onHap[r] (DInDel.cpp:1720) */
+} dindel_batch_out;
+
+/* timings of the last submit/run on the context's stream, CUDA events, milliseconds */
+typedef struct dindel_timing {
+    float h2d_ms, prep_ms, k1_ms, d2h_ms, total_ms;
+    int32_t k1_launches, prep_launches;
+    int64_t n_pairs, n_cells; /* cells = sum over pairs R*(H+2) */
+} dindel_timing;
+
+typedef struct dindel_ctx dindel_ctx;
+
+void dindel_b200_default_params(dindel_params *p);
+void dindel_b200_cli_params(dindel_params *p);
+int dindel_b200_abi_version(void);
+const char *dindel_b200_strerror(int code);
+const char *dindel_b200_last_error(const dindel_ctx *ctx);
+
+/* one context = one device + one stream; use from one host thread at a time */
+int dindel_b200_create(const dindel_params *p, int device, dindel_ctx **out);
+int dindel_b200_destroy(dindel_ctx *ctx);
+
+int64_t dindel_b200_count_pairs(const dindel_batch_in *in);
+int64_t dindel_b200_count_cells(const dindel_batch_in *in);
+
+/* computeLikelihoods for a whole batch: host buffers in, host buffers out (H2D + kernels + D2H). */
+int dindel_b200_submit(dindel_ctx *ctx, const dindel_batch_in *in, dindel_batch_out *out);
+
+/* the same split in three for callers that keep a batch resident in HBM */
+int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos);
+int dindel_b200_run(dindel_ctx *ctx);                         /* kernels only, device resident */
+int dindel_b200_download(dindel_ctx *ctx, dindel_batch_out *out);
+int dindel_b200_sync(dindel_ctx *ctx);                        /* wait for run(); updates timing */
+int dindel_b200_get_timing(const dindel_ctx *ctx, dindel_timing *t);
+int dindel_b200_hpos_stride(const dindel_ctx *ctx);           /* stride of the resident hpos rows */
+
+/* pinned host memory for the caller's buffers */
+void *dindel_b200_alloc_pinned(size_t bytes);
+void dindel_b200_free_pinned(void *p);
+
+/* FP64 add-issue peak of the context's device (ops/s), register-resident DADD microbenchmark:
+ * the denominator of the K1 roofline. */
+int dindel_b200_measure_fp64_peak(dindel_ctx *ctx, double *dadd_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

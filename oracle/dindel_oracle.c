@@ -1,0 +1,403 @@
+/* oracle/dindel_oracle.c — TEST INFRASTRUCTURE ONLY.
+ *
+ * Plain-C CPU restatement of Dindel's read x candidate-haplotype likelihood path
+ * (ObservationModelFBMaxErr, a two-sided max-product HMM) and, further down, of the numeric cores
+ * of the diploid marginalisation and the Bayesian EM that consume its output.  It is the checker
+ * for the CUDA path: only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may
+ * load it; the product library never links or calls it.
+ *
+ * Parity status: PINNED for K1.  tests/test_oracle.py checks this file against
+ *   (1) the four smain() known-answer fixtures (DInDel.cpp:3993-4066, values in SURVEY.md 8c), and
+ *   (2) the reference's own ObservationModelFB.cpp compiled here into oracle/_ref (bit-equal ll /
+ *       llOn / llOff / mLogBQ, identical Viterbi path, hpos and counters on randomised pairs), and
+ *   (3) golden vectors produced by that compiled reference, committed under tests/golden/.
+ * K2 (diploid) is a restatement of libm-only arithmetic; K3's digamma is a third-party function
+ * (Boost.Math, version unpinned by the reference) => "parity unpinned" for that one function.
+ *
+ * Every function cites the reference lines (relative to /root/reference) it follows.
+ */
+#include "dindel_oracle.h"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+int ora_sizeof_params(void) { return (int)sizeof(ora_params); }
+int ora_sizeof_pair_out(void) { return (int)sizeof(ora_pair_out); }
+
+/* Read.hpp:127-131 (mapping quality) and :143-148 (base quality): phred byte -> probability. */
+double ora_phred_to_prob(int phred)
+{
+    double ph = (double)phred;
+    double q = (1.0 - pow(10.0, -ph / 10.0));
+    if (q < 1e-16) q = 1e-16;
+    if (q > 1.0 - 1e-16) q = 1.0 - 1e-16;
+    return q;
+}
+
+/* ReadIndelErrorModel.hpp:28-50: homopolymer run length -> per-base indel error probability. */
+static double hp_error(int hpLen)
+{
+    static const double base[10] = {2.9e-5, 2.9e-5, 2.9e-5, 2.9e-5, 4.3e-5,
+                                    1.1e-4, 2.4e-4, 5.7e-4, 1.0e-3, 1.4e-3};
+    int len = hpLen < 1 ? 1 : hpLen;
+    double pbe = (len <= 10) ? base[len - 1] : base[9] + 4.3e-4 * (double)(len - 10);
+    pbe *= (double)hpLen;
+    if (pbe > 0.99) pbe = 0.99;
+    return pbe;
+}
+
+/* ObservationModelFB.cpp:877-888 (EPS = 1e-10, ObservationModelFB.hpp:25). */
+static inline void upd(double *dv, int *di, double nv, int ni)
+{
+    if (nv > *dv + 1e-10) {
+        *dv = nv;
+        *di = ni;
+    } else if (nv >= *dv && nv <= *dv + 1e-5 && *di > ni) {
+        *dv = nv;
+        *di = ni;
+    }
+}
+
+typedef struct {
+    int H, R, S, RO, T; /* S = numS = H+2, T = numT = maxLengthDel+2 */
+    double lLOgLO, lFirstgLO, lInsgIns, lNoInsgIns, lInsgNoIns, lNoInsgNoIns;
+    double *lpe, *lpn; /* logProbError / logProbNoError, H+2 each */
+} hmm_t;
+
+/* ObservationModelFB.cpp:1641-1713: transition constants and the homopolymer tables. */
+static void setup_transitions(hmm_t *m, const char *hap, const ora_params *p)
+{
+    int H = m->H, b, len;
+    double perr;
+    m->lLOgLO = log(1.0 - p->pFirstgLO);
+    m->lFirstgLO = log(p->pFirstgLO);
+    m->T = p->maxLengthDel + 2;
+    m->lInsgIns = -.5;
+    m->lNoInsgIns = log(1.0 - exp(m->lInsgIns));
+    m->lInsgNoIns = log(p->pError);
+    m->lNoInsgNoIns = log(1 - p->pError);
+    for (b = 0; b < H + 2; b++) {
+        m->lpe[b] = log(1e-5);
+        m->lpn[b] = log(1 - 1e-5);
+    }
+    len = 1;
+    perr = hp_error(1);
+    m->lpe[1] = log(perr);
+    m->lpn[1] = log(1.0 - perr);
+    for (b = 1; b < H; b++) {
+        if (hap[b] == hap[b - 1]) {
+            len++;
+        } else {
+            perr = hp_error(len);
+            m->lpe[b] = log(perr);
+            m->lpn[b] = log(1.0 - perr);
+            len = 1;
+        }
+    }
+    perr = hp_error(len);
+    m->lpe[H - 1] = log(perr);
+    m->lpn[H - 1] = log(1.0 - perr);
+}
+
+/* ObservationModelFB.cpp:1775-1829: one left-half step, row b from row b-1. */
+static void step_dec(const hmm_t *m, double *A, const double *P, const double *O, int *bt)
+{
+    int H = m->H, S = m->S, RO = m->RO, T = m->T, x, y;
+    A[RO] = -HUGE_VAL;
+    upd(&A[RO], &bt[RO], O[RO] + P[RO] + m->lLOgLO + m->lNoInsgNoIns, RO);
+    upd(&A[RO], &bt[RO], O[H] + P[H] + m->lFirstgLO + m->lNoInsgNoIns, H);
+    for (x = 1; x <= H; x++) {
+        double lpt = m->lpe[x], lpn = m->lpn[x];
+        A[x] = -HUGE_VAL;
+        for (y = 1; y < T; y++) {
+            int nx = x - y;
+            double lp;
+            if (nx < 0) nx = 0;
+            lp = (y == 1) ? lpn : (lpt + (double)(y - 1) * m->lInsgIns);
+            upd(&A[x], &bt[x], O[nx] + lp + P[nx] + lpn, nx);
+        }
+    }
+    A[0] = O[0] + P[0] + m->lNoInsgNoIns;
+    bt[0] = 0;
+    upd(&A[RO], &bt[RO], O[S + RO] + P[S + RO] + m->lLOgLO + m->lpe[RO], S + RO);
+    upd(&A[RO], &bt[RO], O[S + H] + P[S + H] + m->lFirstgLO + m->lpe[H], S + H);
+    for (x = 1; x <= H; x++) {
+        int nx = x - 1;
+        upd(&A[x], &bt[x], O[S + nx] + P[S + nx] + m->lpe[x], S + nx);
+    }
+    for (x = 0; x <= H + 1; x++) {
+        A[S + x] = O[S + x] + P[S + x] + m->lInsgIns;
+        bt[S + x] = S + x;
+    }
+    for (x = 1; x <= H + 1; x++) upd(&A[S + x], &bt[S + x], O[x] + P[x] + m->lNoInsgIns, x);
+}
+
+/* ObservationModelFB.cpp:1715-1773: one right-half step, row b-1 from row b. */
+static void step_inc(const hmm_t *m, double *B, const double *P, const double *O, int *bt)
+{
+    int H = m->H, S = m->S, RO = m->RO, T = m->T, x, y;
+    B[0] = -HUGE_VAL;
+    upd(&B[0], &bt[0], O[0] + P[0] + m->lLOgLO + m->lNoInsgNoIns, 0);
+    upd(&B[0], &bt[0], O[1] + P[1] + m->lFirstgLO + m->lNoInsgNoIns, 1);
+    for (x = 1; x <= H; x++) {
+        B[x] = -HUGE_VAL;
+        for (y = 1; y < T; y++) {
+            int nx = x + y;
+            double lpn, lpt, lp;
+            if (nx > H) nx = RO;
+            lpn = m->lpn[nx];
+            lpt = m->lpe[nx];
+            lp = (y == 1) ? lpn : (lpt + (double)(y - 1) * m->lInsgIns);
+            upd(&B[x], &bt[x], lp + lpn + P[nx] + O[nx], nx);
+        }
+    }
+    B[RO] = -HUGE_VAL;
+    upd(&B[RO], &bt[RO], O[RO] + P[RO] + m->lpn[RO], RO);
+    for (x = 0; x <= H; x++) upd(&B[x], &bt[x], O[S + x] + P[S + x] + m->lpe[x + 1], S + x);
+    x = H + 1;
+    upd(&B[x], &bt[x], O[S + x] + P[S + x], S + x);
+    for (x = 0; x <= H + 1; x++) {
+        B[S + x] = O[S + x] + P[S + x] + m->lInsgIns;
+        bt[S + x] = S + x;
+    }
+    upd(&B[S], &bt[S], O[0] + P[0] + m->lNoInsgIns, 0);
+    for (x = 1; x <= H + 1; x++) {
+        int nx = x + 1;
+        if (nx > RO) nx = RO;
+        upd(&B[S + x], &bt[S + x], O[nx] + P[nx] + m->lNoInsgIns, nx);
+    }
+}
+
+/* ObservationModelFB.cpp:268-305 with pinsert == 0 (no --libFile). */
+static void bmid_prior(const hmm_t *m, double *prior, double mapQual, double mapQualThreshold)
+{
+    int S = m->S, H = m->H, RO = m->RO, i, x;
+    double mq = 1.0 - mapQual, pOff;
+    if (-10.0 * log10(mq) > mapQualThreshold) mq = pow(10.0, -mapQualThreshold / 10.0);
+    pOff = mq;
+    for (i = 0; i < 2; i++) {
+        double lIns = (i == 1) ? m->lInsgNoIns : log(1.0 - exp(m->lInsgNoIns));
+        prior[i * S + 0] = log(pOff) + lIns + 0.0;
+        prior[i * S + RO] = -100.0;
+        for (x = 1; x < H + 1; x++) prior[i * S + x] = 0.0 + log((1.0 - pOff)) + lIns;
+    }
+}
+
+/* ObservationModelFB.cpp:35-102: the anchor base. */
+static int compute_bmid(int H, int R, double posStatFirst, int unmapped, uint32_t hapStart,
+                        const ora_params *p)
+{
+    uint32_t hapEnd = hapStart + (uint32_t)H;
+    uint32_t mReadStart = (uint32_t)posStatFirst;
+    uint32_t readEnd = mReadStart + (uint32_t)R - 1;
+    int bMid;
+    if (unmapped) {
+        bMid = R / 2;
+    } else if (mReadStart > hapEnd) {
+        bMid = R / 2;
+    } else if (readEnd < hapStart) {
+        bMid = R / 2;
+    } else {
+        uint32_t olStart = (hapStart > mReadStart) ? hapStart : mReadStart;
+        uint32_t olEnd = (hapEnd > readEnd) ? readEnd : hapEnd;
+        int mid = ((int)olEnd - (int)olStart) / 2 + (int)olStart;
+        bMid = mid - (int)mReadStart;
+    }
+    if (p->bMid != -1) bMid = p->bMid;
+    if (bMid < 0) bMid = 0;
+    if (bMid >= R) bMid = R - 1;
+    return bMid;
+}
+
+int ora_pair(const char *hap, int H, const char *read, int R, const double *qual, double mapQual,
+             double posStatFirst, int unmapped, uint32_t hapStart, const ora_params *p,
+             ora_pair_out *out, int32_t *hpos_out, int32_t *mapState_out)
+{
+    hmm_t m;
+    int S = H + 2, W = 2 * S, RO = H + 1, b, x, s, bMid;
+    double *obs, *alpha, *beta, *priorR, *priorH;
+    int *btf, *btb, *ms;
+    memset(out, 0, sizeof(*out));
+    /* ObservationModelFB.cpp:47 */
+    if (p->maxLengthDel > H) {
+        out->status = 1;
+        return 1;
+    }
+    bMid = compute_bmid(H, R, posStatFirst, unmapped, hapStart, p);
+    m.H = H; m.R = R; m.S = S; m.RO = RO;
+    m.lpe = (double *)malloc(sizeof(double) * S);
+    m.lpn = (double *)malloc(sizeof(double) * S);
+    setup_transitions(&m, hap, p);
+    obs = (double *)malloc(sizeof(double) * (size_t)R * W);
+    alpha = (double *)malloc(sizeof(double) * (size_t)R * W);
+    beta = (double *)malloc(sizeof(double) * (size_t)R * W);
+    btf = (int *)calloc((size_t)R * W, sizeof(int));
+    btb = (int *)calloc((size_t)R * W, sizeof(int));
+    ms = (int *)calloc(R, sizeof(int));
+    priorR = (double *)malloc(sizeof(double) * W);
+    priorH = (double *)malloc(sizeof(double) * W);
+
+    /* ObservationModelFB.cpp:335-338 */
+    for (x = 0; x < W; x++) {
+        alpha[x] = 0.0;
+        beta[(size_t)(R - 1) * W + x] = 0.0;
+    }
+    /* ObservationModelFB.cpp:220-266: emissions */
+    for (b = 0; b < R; b++) {
+        double *o = obs + (size_t)b * W;
+        double pr = qual[b] * (1.0 - p->pMut);
+        double eq = log(.25 + .75 * pr);
+        double uq = log(.75 + 1e-10 - .75 * pr);
+        char nuc = read[b];
+        o[S + 0] = eq; o[S + H + 1] = eq; o[0] = eq; o[H + 1] = eq;
+        for (x = 0; x < H; x++) {
+            o[S + x + 1] = eq;
+            o[x + 1] = (hap[x] == 'N' || hap[x] == nuc) ? eq : uq;
+        }
+        if (p->forceReadOnHaplotype) { /* :307-316 */
+            o[0] = -1000.0; o[RO] = -1000.0; o[S] = -1000.0; o[RO + S] = -1000.0;
+        }
+    }
+    /* ObservationModelFB.cpp:1569-1581 */
+    for (b = 1; b <= bMid; b++)
+        step_dec(&m, alpha + (size_t)b * W, alpha + (size_t)(b - 1) * W, obs + (size_t)(b - 1) * W,
+                 btf + (size_t)b * W);
+    for (b = R - 1; b > bMid; b--)
+        step_inc(&m, beta + (size_t)(b - 1) * W, beta + (size_t)b * W, obs + (size_t)b * W,
+                 btb + (size_t)(b - 1) * W);
+
+    /* ObservationModelFB.cpp:1075-1144 */
+    {
+        const double *a = alpha + (size_t)bMid * W, *be = beta + (size_t)bMid * W,
+                     *o = obs + (size_t)bMid * W;
+        double ll = -HUGE_VAL, llHMQ = -HUGE_VAL, off = -HUGE_VAL, on = -HUGE_VAL;
+        int msR = 0;
+        bmid_prior(&m, priorR, mapQual, p->mapQualThreshold);
+        bmid_prior(&m, priorH, 1.0 - 1e-10, p->mapQualThreshold);
+        for (s = 0; s < W; s++) {
+            double v = a[s] + o[s] + be[s] + priorR[s];
+            if (v > ll + 1e-10) { ll = v; msR = s; }
+            if ((s % S) == 0) { if (v > off) off = v; }
+            else if ((s % S) != RO) { if (v > on) on = v; }
+            v = a[s] + o[s] + be[s] + priorH[s];
+            if (v > llHMQ + 1e-10) { llHMQ = v; ms[bMid] = s; }
+        }
+        out->ll = ll; out->llOff = off; out->llOn = on;
+        out->offHapHMQ = ((ms[bMid] % S) == 0 || (ms[bMid] % S) == RO);
+        out->offHap = ((msR % S) == 0 || (msR % S) == RO);
+    }
+    /* ObservationModelFB.cpp:1148-1165 */
+    for (b = bMid; b > 0; b--) ms[b - 1] = btf[(size_t)b * W + ms[b]];
+    for (b = bMid; b < R - 1; b++) ms[b + 1] = btb[(size_t)b * W + ms[b]];
+
+    /* ObservationModelFB.cpp:1351-1463 (the integer/FP summaries; the std::map / std::string
+     * AlignedVariant records are rebuilt on the host from hpos when a caller needs them) */
+    {
+        int first = -1, last = -1;
+        out->nBQT = 0; out->nmmBQT = 0; out->mLogBQ = 0.0; out->nMMRight = 0; out->nMMLeft = 0;
+        out->numIndels = 0; out->numMismatch = 0;
+        b = 0;
+        while (b < R) {
+            int hp;
+            s = ms[b];
+            if ((s % S) > 0 && (s % S) <= H) {
+                if (s >= S) {
+                    while (b < R && ms[b] >= S) {
+                        if (hpos_out) hpos_out[b] = -1;
+                        b++;
+                    }
+                    out->numIndels++;
+                    b--;
+                } else {
+                    hp = s - 1;
+                    if (hpos_out) hpos_out[b] = hp;
+                    if (first == -1) first = hp; else if (hp < first) first = hp;
+                    if (last == -1) last = hp; else if (hp > last) last = hp;
+                    if (qual[b] > p->checkBaseQualThreshold) {
+                        out->nBQT++;
+                        out->mLogBQ += log10(1.0 - qual[b]);
+                    }
+                    if (read[b] != hap[s - 1]) {
+                        if (qual[b] > p->checkBaseQualThreshold) out->nmmBQT++;
+                        if (b < 6) out->nMMLeft++;
+                        if (b > R - 6) out->nMMRight++;
+                        if (qual[b] > 0.95) out->numMismatch++;
+                    }
+                    if (b < R - 1) {
+                        int ns = ms[b + 1];
+                        if (ns < S && ns - s > 1) out->numIndels++;
+                    }
+                }
+            } else {
+                if (hpos_out) hpos_out[b] = ((s % S) == 0) ? -3 : -4;
+            }
+            b++;
+        }
+        out->firstBase = first;
+        out->lastBase = last;
+    }
+    out->bMid = bMid;
+    out->status = 0;
+    if (mapState_out) for (b = 0; b < R; b++) mapState_out[b] = ms[b];
+    free(m.lpe); free(m.lpn); free(obs); free(alpha); free(beta); free(btf); free(btb); free(ms);
+    free(priorR); free(priorH);
+    return 0;
+}
+
+/* The double loop of DetInDel::computeLikelihoods (DInDel.cpp:1715-1737) over flat buffers;
+ * results r-major like rl[] (DInDel.cpp:2129). */
+int ora_window(const char *hap_seq, const int32_t *hap_off, int nh, const char *read_seq,
+               const uint8_t *read_qual, const int32_t *read_off, const uint8_t *mapq,
+               const uint32_t *mReadStart, const uint8_t *flags, int nr, uint32_t hapStart,
+               const ora_params *p, ora_pair_out *out, int32_t *hpos, int hpos_stride)
+{
+    int h, r, b, n = 0, maxR = 0;
+    double *q;
+    for (r = 0; r < nr; r++)
+        if (read_off[r + 1] - read_off[r] > maxR) maxR = read_off[r + 1] - read_off[r];
+    q = (double *)malloc(sizeof(double) * (maxR + 1));
+    for (h = 0; h < nh; h++)
+        for (r = 0; r < nr; r++) {
+            int R = read_off[r + 1] - read_off[r];
+            size_t pi = (size_t)r * nh + h;
+            for (b = 0; b < R; b++) q[b] = ora_phred_to_prob(read_qual[read_off[r] + b]);
+            if (ora_pair(hap_seq + hap_off[h], hap_off[h + 1] - hap_off[h], read_seq + read_off[r], R,
+                         q, ora_phred_to_prob(mapq[r]), (double)mReadStart[r], flags[r] & 1, hapStart,
+                         p, &out[pi], hpos ? hpos + pi * hpos_stride : 0, 0)) {
+                free(q);
+                return -1;
+            }
+            n++;
+        }
+    free(q);
+    return n;
+}
+
+/* Utils.hpp:29-38 */
+double ora_addlogs(double l1, double l2)
+{
+    if (l1 > l2) {
+        double diff = l2 - l1;
+        return l1 + log(1.0 + exp(diff));
+    } else {
+        double diff = l1 - l2;
+        return l2 + log(1.0 + exp(diff));
+    }
+}
+
+/* Digamma for x > 0.  The reference calls boost::math::digamma (DInDel.cpp:2466,2472), a
+ * third-party function absent from /root/reference and unpinned in version ("parity unpinned").
+ * Published algorithm restated: upward recurrence psi(x) = psi(x+1) - 1/x to x >= 10, then the
+ * asymptotic series ln x - 1/(2x) - sum B_2k / (2k x^2k).  The CUDA K3 mirrors this exactly. */
+double ora_digamma(double x)
+{
+    double r = 0.0, f, t;
+    while (x < 10.0) {
+        r -= 1.0 / x;
+        x += 1.0;
+    }
+    f = 1.0 / (x * x);
+    t = f * (-1.0 / 12.0 + f * (1.0 / 120.0 + f * (-1.0 / 252.0 + f * (1.0 / 240.0 + f * (-1.0 / 132.0
+        + f * (691.0 / 32760.0 + f * (-1.0 / 12.0)))))));
+    return r + log(x) - 0.5 / x + t;
+}

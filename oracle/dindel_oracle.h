@@ -1,0 +1,43 @@
+/* oracle/dindel_oracle.h — TEST INFRASTRUCTURE ONLY (see dindel_oracle.c). */
+#ifndef DINDEL_ORACLE_H
+#define DINDEL_ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* The subset of ObservationModelParameters (ObservationModel.hpp:28-99) the path reads. */
+typedef struct ora_params {
+    double pError, pMut, mapQualThreshold, pFirstgLO, checkBaseQualThreshold;
+    int32_t maxLengthDel, padCover, bMid, forceReadOnHaplotype;
+} ora_params;
+
+/* Flat image of the MLAlignment fields (MLAlignment.hpp:50-70) a pair produces. */
+typedef struct ora_pair_out {
+    double ll, llOn, llOff, mLogBQ;
+    int32_t firstBase, lastBase;
+    int32_t numIndels, numMismatch, nBQT, nmmBQT, nMMLeft, nMMRight;
+    int32_t offHap, offHapHMQ;
+    int32_t bMid, status; /* status: 0 ok, 1 "hapSize error." */
+} ora_pair_out;
+
+int ora_sizeof_params(void);
+int ora_sizeof_pair_out(void);
+double ora_phred_to_prob(int phred);
+
+int ora_pair(const char *hap, int H, const char *read, int R, const double *qual, double mapQual,
+             double posStatFirst, int unmapped, uint32_t hapStart, const ora_params *p,
+             ora_pair_out *out, int32_t *hpos, int32_t *mapState);
+
+int ora_window(const char *hap_seq, const int32_t *hap_off, int nh, const char *read_seq,
+               const uint8_t *read_qual, const int32_t *read_off, const uint8_t *mapq,
+               const uint32_t *mReadStart, const uint8_t *flags, int nr, uint32_t hapStart,
+               const ora_params *p, ora_pair_out *out, int32_t *hpos, int hpos_stride);
+
+double ora_addlogs(double a, double b);
+double ora_digamma(double x);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,100 @@
+"""oracle/pyoracle.py — TEST INFRASTRUCTURE ONLY: ctypes loader for the two CPU checkers.
+
+  Oracle("port")      -> oracle/libdindel_oracle.so    (plain-C restatement, dindel_oracle.c)
+  Oracle("reference") -> oracle/_ref/libdindel_ref.so  (the reference's own ObservationModelFB.cpp)
+Both export the same entry points (prefix ora_ / ref_) and the same POD layouts.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PORT_SO = os.path.join(HERE, "libdindel_oracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libdindel_ref.so")
+
+
+class OraParams(C.Structure):
+    _fields_ = [(n, C.c_double) for n in
+                ("pError", "pMut", "mapQualThreshold", "pFirstgLO", "checkBaseQualThreshold")] + \
+               [(n, C.c_int32) for n in ("maxLengthDel", "padCover", "bMid", "forceReadOnHaplotype")]
+
+
+ORA_DTYPE = np.dtype([
+    ("ll", "<f8"), ("llOn", "<f8"), ("llOff", "<f8"), ("mLogBQ", "<f8"),
+    ("firstBase", "<i4"), ("lastBase", "<i4"), ("numIndels", "<i4"), ("numMismatch", "<i4"),
+    ("nBQT", "<i4"), ("nmmBQT", "<i4"), ("nMMLeft", "<i4"), ("nMMRight", "<i4"),
+    ("offHap", "<i4"), ("offHapHMQ", "<i4"), ("bMid", "<i4"), ("status", "<i4")])
+assert ORA_DTYPE.itemsize == 80
+
+
+def build(which="port"):
+    subprocess.check_call(["make", "-s", "-C", HERE, "oracle" if which == "port" else "ref"])
+
+
+def params_from(p):
+    """engine.Params (or any object with the same fields) -> OraParams."""
+    o = OraParams()
+    for n, _ in OraParams._fields_:
+        setattr(o, n, getattr(p, n))
+    return o
+
+
+class Oracle:
+    def __init__(self, kind="port"):
+        self.kind = kind
+        path = PORT_SO if kind == "port" else REF_SO
+        if kind == "port" and not os.path.exists(path):
+            build("port")
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        self.lib = C.CDLL(path)
+        pre = "ora_" if kind == "port" else "ref_"
+        self._pair = getattr(self.lib, pre + "pair")
+        self._window = getattr(self.lib, pre + "window")
+        self._p2p = getattr(self.lib, pre + "phred_to_prob")
+        self._p2p.restype = C.c_double
+        assert getattr(self.lib, pre + "sizeof_params")() == C.sizeof(OraParams)
+        assert getattr(self.lib, pre + "sizeof_pair_out")() == ORA_DTYPE.itemsize
+
+    def phred_to_prob(self, ph):
+        return self._p2p(int(ph))
+
+    def pair(self, hap, read, qual, map_qual, pos_stat_first, unmapped, hap_start, params):
+        """qual: probabilities (float64 array); map_qual: probability."""
+        hap, read = bytes(hap), bytes(read)
+        R = len(read)
+        q = np.ascontiguousarray(qual, dtype=np.float64)
+        out = np.zeros(1, dtype=ORA_DTYPE)
+        hpos = np.zeros(max(R, 1), dtype=np.int32)
+        ms = np.zeros(max(R, 1), dtype=np.int32)
+        self._pair(hap, len(hap), read, R, q.ctypes.data_as(C.c_void_p), C.c_double(map_qual),
+                   C.c_double(pos_stat_first), int(unmapped), C.c_uint32(hap_start & 0xffffffff),
+                   C.byref(params), out.ctypes.data_as(C.c_void_p), hpos.ctypes.data_as(C.c_void_p),
+                   ms.ctypes.data_as(C.c_void_p))
+        return out[0], hpos[:R], ms[:R]
+
+    def window(self, batch, w, params, want_hpos=True):
+        """All pairs of window w of an engine.Batch -> (records r-major [nr*nh], hpos [nr*nh, stride])."""
+        h0, h1 = int(batch.win_hap[w]), int(batch.win_hap[w + 1])
+        r0, r1 = int(batch.win_read[w]), int(batch.win_read[w + 1])
+        nh, nr = h1 - h0, r1 - r0
+        hb, rb = int(batch.hap_off[h0]), int(batch.read_off[r0])
+        hap_off = (batch.hap_off[h0:h1 + 1] - hb).astype(np.int32)
+        read_off = (batch.read_off[r0:r1 + 1] - rb).astype(np.int32)
+        hap_seq = np.ascontiguousarray(batch.hap_seq[hb:int(batch.hap_off[h1])])
+        read_seq = np.ascontiguousarray(batch.read_seq[rb:int(batch.read_off[r1])])
+        read_qual = np.ascontiguousarray(batch.read_qual[rb:int(batch.read_off[r1])])
+        mapq = np.ascontiguousarray(batch.read_mapq[r0:r1])
+        start = np.ascontiguousarray(batch.read_start[r0:r1])
+        flags = np.ascontiguousarray(batch.read_flags[r0:r1])
+        out = np.zeros(nh * nr, dtype=ORA_DTYPE)
+        stride = int(np.max(np.diff(read_off))) if nr else 1
+        stride = max(stride, 1)
+        hpos = np.full((max(nh * nr, 1), stride), -32768, dtype=np.int32) if want_hpos else None
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        n = self._window(vp(hap_seq), vp(hap_off), nh, vp(read_seq), vp(read_qual), vp(read_off), vp(mapq),
+                         vp(start), vp(flags), nr, C.c_uint32(int(batch.hap_start[w])), C.byref(params),
+                         vp(out), vp(hpos) if want_hpos else None, stride)
+        return n, out, hpos
