@@ -16,7 +16,8 @@ extern "C" cudaError_t k1_generic_launch(const K1Batch *B, int grid, int warps_p
                                          int bt_in_smem, size_t smem_bytes, cudaStream_t stream);
 extern "C" int k1_tiled_supported(int maxS, int maxR, int J);
 extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream_t stream,
-                                       int *launches);
+                                       int *launches, unsigned class_mask);
+extern "C" unsigned k1_tiled_class_of(int S);
 
 // ------------------------------------------------------------------------------------------
 // small device kernels owned by the API layer
@@ -136,6 +137,8 @@ struct dindel_ctx {
     std::vector<long long> win_pair, win_unit;
     dindel_timing timing;
     int force_generic = 0;
+    unsigned class_mask = 0;   // shape classes (state columns per lane) present in the batch
+    bool alphabet_ok = true;   // every sequence byte in [A-Z=] (needed by the tiled kernel)
 };
 
 static int fail(dindel_ctx *c, int code, const std::string &msg)
@@ -370,10 +373,24 @@ int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos
         ctx->win_unit[w + 1] = ctx->win_unit[w] + a * ((b + K1_READ_CHUNK - 1) / K1_READ_CHUNK);
     }
     int maxH = 0, maxR = 0;
+    ctx->class_mask = 0;
     for (int h = 0; h < nh; h++) {
         long long l = in->hap_off[h + 1] - in->hap_off[h];
         if (l > 32000) return fail(ctx, DINDEL_E_UNSUPPORTED, "haplotype longer than 32000");
         if (l > maxH) maxH = (int)l;
+        unsigned cls = k1_tiled_class_of((int)l + 2);
+        if (cls < 32) ctx->class_mask |= 1u << cls;
+    }
+    {
+        // the tiled kernel encodes symbols as one-hot masks over (byte & 31): exact for [A-Z=]
+        bool ok[256];
+        for (int i = 0; i < 256; i++) ok[i] = (i >= 'A' && i <= 'Z') || i == '=';
+        unsigned bad = 0;
+        const unsigned char *hs = (const unsigned char *)in->hap_seq, *rs = (const unsigned char *)in->read_seq;
+        const long long hb = nh ? in->hap_off[nh] : 0, rbytes = nr ? in->read_off[nr] : 0;
+        for (long long i = 0; i < hb; i++) bad |= !ok[hs[i]];
+        for (long long i = 0; i < rbytes; i++) bad |= !ok[rs[i]];
+        ctx->alphabet_ok = (bad == 0);
     }
     for (int r = 0; r < nr; r++) {
         long long l = in->read_off[r + 1] - in->read_off[r];
@@ -462,9 +479,9 @@ int dindel_b200_run(dindel_ctx *ctx)
     int launches = 0;
     if (B.n_units > 0) {
         const int J = ctx->luts.numT - 1;
-        if (!ctx->force_generic && k1_tiled_supported(B.max_S, B.max_R, J)) {
-            CU(cudaMemsetAsync(B.counter, 0, 64, st));
-            CU(k1_tiled_launch(&B, ctx->num_sms, st, &launches));
+        if (!ctx->force_generic && ctx->alphabet_ok && !ctx->luts.force &&
+            k1_tiled_supported(B.max_S, B.max_R, J)) {
+            CU(k1_tiled_launch(&B, ctx->num_sms, st, &launches, ctx->class_mask));
         } else {
             // generic kernel: pick the shared-memory plan
             const size_t budget = ctx->smem_optin;

@@ -1,8 +1,561 @@
-// k1_tiled.cu — K1, register-tiled variant (placeholder until the tiled kernel lands).
+// k1_tiled.cu — K1, register-tiled variant: the production kernel for the common shapes.
+//
+// One warp owns one (read, haplotype) pair.  The 2*(H+2) states of a row live in registers:
+// lane l holds C consecutive state columns x = l*C .. l*C+C-1 of both planes (plane 0 "not in
+// insertion", plane 1 "in insertion"); row b depends only on row b-1, so a row is data-parallel
+// and the J-wide look-back (left half) / look-ahead (right half) window is exchanged with warp
+// shuffles.  Per-haplotype transition tables sit in registers for the duration of a half;
+// back-pointers go to shared memory as 4-bit (J <= 7) or 8-bit codes; the meeting-row scan, the
+// back-trace and the alignment summary follow (k1_tail.cuh).
+//
+// Bit-exactness: the reference's updateMax (ObservationModelFB.cpp:877-888) is order dependent.
+// Inside each state the candidates are offered in the reference's source order and every sum is
+// associated as written there; the two-branch rule is specialised per call site using only facts
+// about the candidate index order (derivations in DESIGN.md "updateMax specialisation"):
+//   * offered index below every index seen so far  ->  take iff new >= dest
+//   * offered index above every index seen so far  ->  take iff new >  dest + 1e-10
+//   * clamped duplicates of LO / RO can never be taken -> offered as -inf
+// Requires: sequence bytes in [A-Z=] (one-hot accept masks), forceReadOnHaplotype off; other
+// batches take the generic kernel (k1_generic.cu).
 #include "k1_common.cuh"
-extern "C" int k1_tiled_supported(int maxS, int maxR, int J) { (void)maxS; (void)maxR; (void)J; return 0; }
-extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream_t stream, int *launches)
+#include "k1_tail.cuh"
+
+#define K1_EPS 1e-10
+#define FULLMASK 0xffffffffu
+
+template <int C, int J>
+struct TiledCfg {
+    static constexpr bool NIB = (J <= 7);
+    static constexpr int U16 = NIB ? (C + 3) / 4 : (C + 1) / 2; // 16-bit back-pointer units per lane-row
+};
+
+__host__ __device__ inline size_t tiled_smem_per_warp(int C, int U16, int maxR)
 {
-    (void)B; (void)num_sms; (void)stream; (void)launches;
-    return cudaErrorNotSupported;
+    size_t b = (size_t)maxR * U16 * 64   // back-pointers
+               + (size_t)maxR * 16       // eq / uq
+               + (size_t)2 * 32 * C * 8  // alpha[bMid]+obs[bMid]
+               + (size_t)maxR * 2        // map state
+               + (size_t)maxR * 2;       // read chars + phreds
+    return (b + 15) & ~(size_t)15;
+}
+
+__device__ __forceinline__ double shfl_up_d(double v, int d) { return __shfl_up_sync(FULLMASK, v, d); }
+__device__ __forceinline__ double shfl_down_d(double v, int d) { return __shfl_down_sync(FULLMASK, v, d); }
+
+__device__ __forceinline__ double warp_max_d(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        double w = __shfl_xor_sync(FULLMASK, v, o);
+        v = (w > v) ? w : v;
+    }
+    return v;
+}
+
+// accept mask of a state column: which read symbols (bit = char & 31) emit "match"
+// (ObservationModelFB.cpp:237-250: LO, RO and hap 'N' always match).
+__device__ __forceinline__ uint32_t accept_mask(const uint8_t *hap, int x, int H)
+{
+    if (x < 1 || x > H) return 0xffffffffu;
+    uint8_t c = hap[x - 1];
+    return (c == 'N') ? 0xffffffffu : (1u << (c & 31));
+}
+
+// Sequential "v > best + EPS, first wins" scan over all 2S states (cpp:1096-1116), done exactly
+// without serialising over the states: only states within 1e-9 of the maximum can ever be taken
+// once the first of them has been seen (and that one is taken, provided nothing lies in the
+// guard band [M-2e-9, M-1e-9)); those few are then replayed in state order.  If the guard band
+// is populated every state is replayed.
+template <int C>
+__device__ __forceinline__ void scan_first_wins(const double (&v0)[C], const double (&v1)[C], int lane,
+                                                int S, double &best, int &bestState)
+{
+    double m = K1_NEG_INF;
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+        m = (v0[c] > m) ? v0[c] : m;
+        m = (v1[c] > m) ? v1[c] : m;
+    }
+    m = warp_max_d(m);
+    const double tNear = m - 1e-9, tGuard = m - 2e-9;
+    uint32_t near = 0, guard = 0, valid = 0;
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+        const bool ok = (lane * C + c) < S;
+        if (ok) valid |= (1u << c) | (1u << (C + c));
+        if (ok && v0[c] >= tNear) near |= 1u << c;
+        if (ok && v1[c] >= tNear) near |= 1u << (C + c);
+        if (ok && v0[c] < tNear && v0[c] >= tGuard) guard |= 1u << c;
+        if (ok && v1[c] < tNear && v1[c] >= tGuard) guard |= 1u << (C + c);
+    }
+    if (__any_sync(FULLMASK, guard != 0)) near = valid;
+    best = K1_NEG_INF;
+    bestState = 0;
+    for (;;) {
+        int bit = near ? (__ffs(near) - 1) : -1;
+        int key = 0x7fffffff;
+        if (bit >= 0) key = (bit < C) ? (lane * C + bit) : (S + lane * C + (bit - C));
+        const int kmin = __reduce_min_sync(FULLMASK, key);
+        if (kmin == 0x7fffffff) break;
+        double vv = 0.0;
+#pragma unroll
+        for (int c = 0; c < C; c++) {
+            if (bit == c) vv = v0[c];
+            if (bit == C + c) vv = v1[c];
+        }
+        const int owner = __ffs(__ballot_sync(FULLMASK, key == kmin)) - 1;
+        vv = __shfl_sync(FULLMASK, vv, owner);
+        if (vv > best + K1_EPS) {
+            best = vv;
+            bestState = kmin;
+        }
+        if (lane == owner) near &= near - 1;
+    }
+}
+
+template <int C, int J>
+__global__ void __launch_bounds__(128, 3) k1_tiled_kernel(K1Batch B, int Slo, int Shi)
+{
+    using Cfg = TiledCfg<C, J>;
+    constexpr int U16 = Cfg::U16;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ double s_hp_lpe[K1_HP_LUT], s_hp_lpn[K1_HP_LUT];
+    const int lane = threadIdx.x & 31;
+    const int wib = threadIdx.x >> 5;
+    const K1Luts *__restrict__ L = B.luts;
+    const int maxR = B.max_R;
+    for (int i = threadIdx.x; i < K1_HP_LUT; i += blockDim.x) {
+        s_hp_lpe[i] = L->hp_lpe[i];
+        s_hp_lpn[i] = L->hp_lpn[i];
+    }
+    __syncthreads();
+    unsigned char *base = smem_raw + tiled_smem_per_warp(C, U16, maxR) * wib;
+    uint16_t *sm_bt = reinterpret_cast<uint16_t *>(base);
+    double *sm_eq = reinterpret_cast<double *>(base + (size_t)maxR * U16 * 64);
+    double *sm_uq = sm_eq + maxR;
+    double *sm_ao = sm_uq + maxR; // [2][32*C]
+    int16_t *sm_ms = reinterpret_cast<int16_t *>(sm_ao + 2 * 32 * C);
+    uint8_t *sm_ch = reinterpret_cast<uint8_t *>(sm_ms + maxR);
+    uint8_t *sm_ph = sm_ch + maxR;
+
+    const double lLOgLO = L->lLOgLO, lFirstgLO = L->lFirstgLO, lInsgIns = L->lInsgIns,
+                 lNoInsgIns = L->lNoInsgIns, lNoInsgNoIns = L->lNoInsgNoIns;
+    const int c0 = lane * C;
+
+    for (;;) {
+        long long unit = 0;
+        if (lane == 0) unit = (long long)atomicAdd(B.counter, 1ULL);
+        unit = __shfl_sync(FULLMASK, unit, 0);
+        if (unit >= B.n_units) break;
+        const int w = k1_find_window(B.win_unit, B.n_windows, unit);
+        const int h0 = B.win_hap[w], nh = B.win_hap[w + 1] - h0;
+        const int r0 = B.win_read[w], nr = B.win_read[w + 1] - r0;
+        const int nchunk = (nr + K1_READ_CHUNK - 1) / K1_READ_CHUNK;
+        const int local = (int)(unit - B.win_unit[w]);
+        const int h = local / nchunk, chunk = local - h * nchunk;
+        const long long hoff = B.hap_off[h0 + h];
+        const int H = (int)(B.hap_off[h0 + h + 1] - hoff);
+        const int S = H + 2, RO = H + 1;
+        if (S <= Slo || S > Shi) continue; // another launch owns this shape class
+        const uint8_t *hap = B.hap_seq + hoff;
+        const uint8_t *hp = B.hap_hp + hoff + 2LL * (h0 + h);
+        const uint32_t hapStart = B.hap_start[w];
+        const bool hapsize_err = L->maxLengthDel > H;
+        const int rb = r0 + chunk * K1_READ_CHUNK;
+        const int re = min(rb + K1_READ_CHUNK, r0 + nr);
+
+        for (int r = rb; r < re; r++) {
+            const long long pair = B.win_pair[w] + (long long)(r - r0) * nh + h;
+            dindel_pair_out *out = B.pairs + pair;
+            if (hapsize_err) {
+                k1_write_hapsize_error(out, lane);
+                continue;
+            }
+            const long long roff = B.read_off[r];
+            const int R = (int)(B.read_off[r + 1] - roff);
+            if (R <= 0) {
+                if (lane == 0) {
+                    k1_write_hapsize_error(out, 0);
+                    out->status = DINDEL_WIN_NAN;
+                }
+                continue;
+            }
+            const int mapq = B.read_mapq[r];
+            const bool unmapped = (B.read_flags[r] & DINDEL_READ_UNMAPPED) != 0;
+            const int bMid = k1_bmid(hapStart, H, R, B.read_start[r], unmapped, L->bMidOverride);
+            __syncwarp();
+            for (int b = lane; b < R; b += 32) {
+                int ph = B.read_qual[roff + b];
+                sm_ch[b] = B.read_seq[roff + b];
+                sm_ph[b] = (uint8_t)ph;
+                sm_eq[b] = L->eq[ph];
+                sm_uq[b] = L->uq[ph];
+            }
+            __syncwarp();
+
+            double P0[C], P1[C];
+            uint32_t am[C];
+#pragma unroll
+            for (int c = 0; c < C; c++) am[c] = accept_mask(hap, c0 + c, H);
+
+            // =================== left half: rows 1..bMid (passMessageTwoDec) ===================
+            {
+                double lpn[C], lpe[C], lpD[C][J - 1];
+                uint32_t amL[J];
+#pragma unroll
+                for (int c = 0; c < C; c++) {
+                    const int x = c0 + c;
+                    const int code = hp[x <= RO ? x : RO];
+                    lpe[c] = s_hp_lpe[code];
+                    lpn[c] = s_hp_lpn[code];
+#pragma unroll
+                    for (int y = 2; y <= J; y++) lpD[c][y - 2] = lpe[c] + (double)(y - 1) * lInsgIns; // cpp:1791
+                    P0[c] = 0.0; // alpha[0] = 0 (cpp:335-338)
+                    P1[c] = 0.0;
+                }
+                // lpe of the column left of this lane's first (RO's "from S+H" candidate, cpp:1805)
+                const double lpeLm1 = s_hp_lpe[hp[(c0 >= 1 && c0 - 1 <= RO) ? c0 - 1 : 0]];
+#pragma unroll
+                for (int j = 1; j <= J; j++) amL[j - 1] = accept_mask(hap, c0 - j, H);
+
+                for (int b = 1; b <= bMid; b++) {
+                    const double eq = sm_eq[b - 1], uq = sm_uq[b - 1];
+                    const uint32_t rbit = 1u << (sm_ch[b - 1] & 31);
+                    double Os[C], u[C], t1[C], hP[J], hO[J];
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
+                        Os[c] = (am[c] & rbit) ? eq : uq;
+                        u[c] = Os[c] + P0[c];
+                        t1[c] = eq + P1[c];
+                    }
+#pragma unroll
+                    for (int j = 1; j <= J; j++) {
+                        constexpr int dummy = 0;
+                        (void)dummy;
+                        const int d = (j + C - 1) / C;
+                        const int ci = d * C - j;
+                        double v = shfl_up_d(P0[ci], d);
+                        hP[j - 1] = (lane >= d) ? v : K1_NEG_INF;
+                        hO[j - 1] = (amL[j - 1] & rbit) ? eq : uq;
+                    }
+                    double t1h = shfl_up_d(t1[C - 1], 1);
+                    if (lane == 0) t1h = K1_NEG_INF;
+
+                    double N0[C], N1[C];
+                    uint32_t nib[C];
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
+                        const int x = c0 + c;
+                        // jumps y = 1..J from column x-y (cpp:1784-1795)
+                        const double O1s = (c >= 1) ? Os[c - 1] : hO[0];
+                        const double P1s = (c >= 1) ? P0[c - 1] : hP[0];
+                        double best = ((O1s + lpn[c]) + P1s) + lpn[c];
+                        uint32_t code = 0;
+#pragma unroll
+                        for (int y = 2; y <= J; y++) {
+                            const double Oy = (c - y >= 0) ? Os[(c - y >= 0) ? c - y : 0] : hO[(y - c - 1 >= 0) ? y - c - 1 : 0];
+                            const double Py = (c - y >= 0) ? P0[(c - y >= 0) ? c - y : 0] : hP[(y - c - 1 >= 0) ? y - c - 1 : 0];
+                            const double v = ((Oy + lpD[c][y - 2]) + Py) + lpn[c];
+                            if (v >= best) { best = v; code = y - 1; }
+                        }
+                        // from plane-1 x-1 (cpp:1807-1811)
+                        const double t1s = (c >= 1) ? t1[c - 1] : t1h;
+                        const double vi = t1s + lpe[c];
+                        if (vi > best + K1_EPS) { best = vi; code = J; }
+                        // plane 1 (cpp:1816-1826)
+                        const double stay = t1[c] + lInsgIns;
+                        const double f = u[c] + lNoInsgIns;
+                        uint32_t bit1 = (f >= stay) ? 1u : 0u;
+                        double a1 = bit1 ? f : stay;
+                        if (c == 0 && lane == 0) { // LO (cpp:1798-1799); plane 1 only stays (loop from x=1)
+                            best = u[c] + lNoInsgNoIns;
+                            code = 0;
+                            a1 = stay;
+                            bit1 = 0;
+                        }
+                        if (x == RO) { // cpp:1780-1782, 1804-1805
+                            double rv = (u[c] + lLOgLO) + lNoInsgNoIns;
+                            uint32_t rcode = 0;
+                            const double v2 = ((O1s + P1s) + lFirstgLO) + lNoInsgNoIns;
+                            if (v2 >= rv) { rv = v2; rcode = 1; }
+                            const double v3 = (t1[c] + lLOgLO) + lpe[c];
+                            if (v3 > rv + K1_EPS) { rv = v3; rcode = 2; }
+                            const double lpeH = (c >= 1) ? lpe[(c >= 1) ? c - 1 : 0] : lpeLm1;
+                            const double v4 = (t1s + lFirstgLO) + lpeH;
+                            const bool take = (rcode == 2) ? (v4 >= rv) : (v4 > rv + K1_EPS);
+                            if (take) { rv = v4; rcode = 3; }
+                            best = rv;
+                            code = rcode;
+                        }
+                        N0[c] = best;
+                        N1[c] = a1;
+                        nib[c] = Cfg::NIB ? (code | (bit1 << 3)) : (code | (bit1 << 7));
+                    }
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
+                        P0[c] = N0[c];
+                        P1[c] = N1[c];
+                    }
+                    uint16_t *row = sm_bt + (size_t)b * U16 * 32;
+#pragma unroll
+                    for (int k = 0; k < U16; k++) {
+                        uint32_t v = 0;
+                        if (Cfg::NIB) {
+#pragma unroll
+                            for (int q = 0; q < 4; q++)
+                                if (4 * k + q < C) v |= nib[(4 * k + q < C) ? 4 * k + q : 0] << (4 * q);
+                        } else {
+#pragma unroll
+                            for (int q = 0; q < 2; q++)
+                                if (2 * k + q < C) v |= nib[(2 * k + q < C) ? 2 * k + q : 0] << (8 * q);
+                        }
+                        row[k * 32 + lane] = (uint16_t)v;
+                    }
+                }
+            }
+            // alpha[bMid] + obs[bMid] (first add of cpp:1098) -> shared, by state column
+            {
+                const double eq = sm_eq[bMid], uq = sm_uq[bMid];
+                const uint32_t rbit = 1u << (sm_ch[bMid] & 31);
+#pragma unroll
+                for (int c = 0; c < C; c++) {
+                    sm_ao[c0 + c] = P0[c] + ((am[c] & rbit) ? eq : uq);
+                    sm_ao[32 * C + c0 + c] = P1[c] + eq;
+                }
+            }
+            // =================== right half: rows R-2..bMid (passMessageTwoInc) ===================
+            {
+                double cI[C][J], lpeN[C];
+                uint32_t amR[J];
+#pragma unroll
+                for (int c = 0; c < C; c++) {
+                    const int x = c0 + c;
+#pragma unroll
+                    for (int y = 1; y <= J; y++) {
+                        const int nx = (x + y <= RO) ? x + y : RO; // cpp:1728-1729
+                        const int code = hp[nx];
+                        const double lpn_s = s_hp_lpn[code], lpe_s = s_hp_lpe[code];
+                        const double lp = (y == 1) ? lpn_s : (lpe_s + (double)(y - 1) * lInsgIns); // cpp:1732
+                        cI[c][y - 1] = lp + lpn_s;
+                        if (y == 1) lpeN[c] = lpe_s; // logProbError[x+1] (cpp:1748)
+                    }
+                    P0[c] = (x <= RO) ? 0.0 : K1_NEG_INF; // beta[R-1] = 0; columns beyond RO never win
+                    P1[c] = (x <= RO) ? 0.0 : K1_NEG_INF;
+                }
+                const double lpnRO = s_hp_lpn[hp[RO]];
+#pragma unroll
+                for (int j = 1; j <= J; j++) amR[j - 1] = accept_mask(hap, c0 + C - 1 + j, H);
+
+                for (int b = R - 1; b > bMid; b--) {
+                    const double eq = sm_eq[b], uq = sm_uq[b];
+                    const uint32_t rbit = 1u << (sm_ch[b] & 31);
+                    double Os[C], u[C], t1[C], hP[J], hO[J];
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
+                        Os[c] = (am[c] & rbit) ? eq : uq;
+                        u[c] = Os[c] + P0[c];
+                        t1[c] = eq + P1[c];
+                    }
+#pragma unroll
+                    for (int j = 1; j <= J; j++) {
+                        const int d = (C - 1 + j) / C;
+                        const int ci = (C - 1 + j) % C;
+                        double v = shfl_down_d(P0[ci], d);
+                        hP[j - 1] = (lane + d <= 31) ? v : K1_NEG_INF;
+                        hO[j - 1] = (amR[j - 1] & rbit) ? eq : uq;
+                    }
+                    double uh = shfl_down_d(u[0], 1);
+                    if (lane == 31) uh = K1_NEG_INF;
+
+                    double N0[C], N1[C];
+                    uint32_t nib[C];
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
+                        const int x = c0 + c;
+                        // jumps y = 1..J to column x+y (cpp:1724-1737)
+                        const double O1s = (c + 1 < C) ? Os[(c + 1 < C) ? c + 1 : 0] : hO[0];
+                        const double P1s = (c + 1 < C) ? P0[(c + 1 < C) ? c + 1 : 0] : hP[0];
+                        double best = (cI[c][0] + P1s) + O1s;
+                        uint32_t code = 0;
+#pragma unroll
+                        for (int y = 2; y <= J; y++) {
+                            const double Oy = (c + y < C) ? Os[(c + y < C) ? c + y : 0] : hO[(c + y - C >= 0) ? c + y - C : 0];
+                            const double Py = (c + y < C) ? P0[(c + y < C) ? c + y : 0] : hP[(c + y - C >= 0) ? c + y - C : 0];
+                            const double v = (cI[c][y - 1] + Py) + Oy;
+                            if (v > best + K1_EPS) { best = v; code = y - 1; }
+                        }
+                        // from plane-1 x (cpp:1746-1749)
+                        const double vi = t1[c] + lpeN[c];
+                        if (vi > best + K1_EPS) { best = vi; code = J; }
+                        // plane 1 (cpp:1754-1767)
+                        const double stay = t1[c] + lInsgIns;
+                        const double un = (c + 1 < C) ? u[(c + 1 < C) ? c + 1 : 0] : uh;
+                        double f = un + lNoInsgIns;
+                        if (c == 0 && lane == 0) { // LO (cpp:1720-1722, 1748, 1762)
+                            double rv = (u[c] + lLOgLO) + lNoInsgNoIns;
+                            uint32_t rcode = 0;
+                            const double v2 = (un + lFirstgLO) + lNoInsgNoIns;
+                            if (v2 > rv + K1_EPS) { rv = v2; rcode = 1; }
+                            if (vi > rv + K1_EPS) { rv = vi; rcode = J; }
+                            best = rv;
+                            code = rcode;
+                            f = u[c] + lNoInsgIns;
+                        }
+                        if (x == RO) { // cpp:1741-1742, 1750, 1764
+                            double rv = u[c] + lpnRO;
+                            uint32_t rcode = 0;
+                            if (t1[c] > rv + K1_EPS) { rv = t1[c]; rcode = J; }
+                            best = rv;
+                            code = rcode;
+                            f = u[c] + lNoInsgIns;
+                        }
+                        const uint32_t bit1 = (f >= stay) ? 1u : 0u;
+                        N0[c] = best;
+                        N1[c] = bit1 ? f : stay;
+                        nib[c] = Cfg::NIB ? (code | (bit1 << 3)) : (code | (bit1 << 7));
+                    }
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
+                        P0[c] = N0[c];
+                        P1[c] = N1[c];
+                    }
+                    uint16_t *row = sm_bt + (size_t)b * U16 * 32; // btb[b-1] stored at row b
+#pragma unroll
+                    for (int k = 0; k < U16; k++) {
+                        uint32_t v = 0;
+                        if (Cfg::NIB) {
+#pragma unroll
+                            for (int q = 0; q < 4; q++)
+                                if (4 * k + q < C) v |= nib[(4 * k + q < C) ? 4 * k + q : 0] << (4 * q);
+                        } else {
+#pragma unroll
+                            for (int q = 0; q < 2; q++)
+                                if (2 * k + q < C) v |= nib[(2 * k + q < C) ? 2 * k + q : 0] << (8 * q);
+                        }
+                        row[k * 32 + lane] = (uint16_t)v;
+                    }
+                }
+            }
+            __syncwarp();
+            // =================== meeting row (cpp:1075-1144) ===================
+            double vR0[C], vR1[C], vH0[C], vH1[C];
+            double onMax = K1_NEG_INF;
+            {
+                const double pLO0 = L->priorLO[0][mapq], pLO1 = L->priorLO[1][mapq];
+                const double pOn0 = L->priorOn[0][mapq], pOn1 = L->priorOn[1][mapq];
+                const double hLO0 = L->priorLO_H[0], hLO1 = L->priorLO_H[1];
+                const double hOn0 = L->priorOn_H[0], hOn1 = L->priorOn_H[1];
+#pragma unroll
+                for (int c = 0; c < C; c++) {
+                    const int x = c0 + c;
+                    const double t0 = sm_ao[x] + P0[c];
+                    const double t1v = sm_ao[32 * C + x] + P1[c];
+                    const bool lo = (x == 0), ro = (x == RO), pad = (x > RO);
+                    vR0[c] = pad ? K1_NEG_INF : t0 + (lo ? pLO0 : ro ? -100.0 : pOn0);
+                    vR1[c] = pad ? K1_NEG_INF : t1v + (lo ? pLO1 : ro ? -100.0 : pOn1);
+                    vH0[c] = pad ? K1_NEG_INF : t0 + (lo ? hLO0 : ro ? -100.0 : hOn0);
+                    vH1[c] = pad ? K1_NEG_INF : t1v + (lo ? hLO1 : ro ? -100.0 : hOn1);
+                    if (x >= 1 && x <= H) {
+                        onMax = (vR0[c] > onMax) ? vR0[c] : onMax;
+                        onMax = (vR1[c] > onMax) ? vR1[c] : onMax;
+                    }
+                }
+            }
+            double ll, llH;
+            int msR, msH;
+            scan_first_wins<C>(vR0, vR1, lane, S, ll, msR);
+            scan_first_wins<C>(vH0, vH1, lane, S, llH, msH);
+            const double llOn = warp_max_d(onMax);
+            double llOff = (vR0[0] > vR1[0]) ? vR0[0] : vR1[0]; // states 0 and S, plain '>' (cpp:1104-1105)
+            llOff = __shfl_sync(FULLMASK, llOff, 0);
+            const int xr = msR >= S ? msR - S : msR, xh = msH >= S ? msH - S : msH;
+            const int offHap = (xr == 0 || xr == RO), offHapHMQ = (xh == 0 || xh == RO);
+
+            const uint16_t *btp = sm_bt;
+            auto btf = [btp](int row, int x) -> int {
+                const int ln = x / C, c = x - ln * C;
+                if (Cfg::NIB) {
+                    const uint32_t u16 = btp[((size_t)row * U16 + (c >> 2)) * 32 + ln];
+                    const uint32_t v = (u16 >> (4 * (c & 3))) & 15u;
+                    return (int)((v & 7u) | ((v >> 3) << 7));
+                } else {
+                    const uint32_t u16 = btp[((size_t)row * U16 + (c >> 1)) * 32 + ln];
+                    return (int)((u16 >> (8 * (c & 1))) & 255u);
+                }
+            };
+            k1_tail(btf, lane, R, H, J, bMid, msH, hap, sm_ch, sm_ph, sm_ms, sm_eq, L, ll, llOn, llOff,
+                    offHap, offHapHMQ, out, B.hpos ? B.hpos + pair * (long long)B.hpos_stride : nullptr);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side: shape classes and launches
+// ------------------------------------------------------------------------------------------
+template <int C, int J>
+static cudaError_t launch_one(const K1Batch *B, int num_sms, int Slo, int Shi, cudaStream_t st)
+{
+    constexpr int U16 = TiledCfg<C, J>::U16;
+    const int warps = 4;
+    const size_t smem = tiled_smem_per_warp(C, U16, B->max_R) * warps;
+    cudaError_t e = cudaFuncSetAttribute(k1_tiled_kernel<C, J>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_tiled_kernel<C, J>, warps * 32, smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorInvalidConfiguration;
+    long long grid = (long long)num_sms * per_sm;
+    long long need = (B->n_units + warps - 1) / warps;
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+    k1_tiled_kernel<C, J><<<(int)grid, warps * 32, smem, st>>>(*B, Slo, Shi);
+    return cudaGetLastError();
+}
+
+static const int kClassC[] = {2, 3, 4, 5, 6, 8};
+static const int kNumClass = 6;
+
+extern "C" int k1_tiled_supported(int maxS, int maxR, int J)
+{
+    if (J != 6) return 0;
+    if (maxS > 32 * kClassC[kNumClass - 1]) return 0;
+    // back-pointers of the largest class must fit one CTA of 4 warps in shared memory
+    int C = kClassC[kNumClass - 1];
+    for (int i = 0; i < kNumClass; i++)
+        if (maxS <= 32 * kClassC[i]) { C = kClassC[i]; break; }
+    int U16 = (C + 3) / 4;
+    return tiled_smem_per_warp(C, U16, maxR) * 4 <= 200 * 1024;
+}
+
+// One launch per shape class present (class = state columns per lane).  `class_mask` bit i set
+// when some haplotype of the batch falls in class i.
+extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream_t st, int *launches,
+                                       unsigned class_mask)
+{
+    int n = 0;
+    cudaError_t e = cudaSuccess;
+    for (int i = 0; i < kNumClass && e == cudaSuccess; i++) {
+        if (!(class_mask & (1u << i))) continue;
+        const int Slo = (i == 0) ? 0 : 32 * kClassC[i - 1], Shi = 32 * kClassC[i];
+        e = cudaMemsetAsync(B->counter, 0, sizeof(unsigned long long), st);
+        if (e != cudaSuccess) break;
+        switch (kClassC[i]) {
+        case 2: e = launch_one<2, 6>(B, num_sms, Slo, Shi, st); break;
+        case 3: e = launch_one<3, 6>(B, num_sms, Slo, Shi, st); break;
+        case 4: e = launch_one<4, 6>(B, num_sms, Slo, Shi, st); break;
+        case 5: e = launch_one<5, 6>(B, num_sms, Slo, Shi, st); break;
+        case 6: e = launch_one<6, 6>(B, num_sms, Slo, Shi, st); break;
+        case 8: e = launch_one<8, 6>(B, num_sms, Slo, Shi, st); break;
+        }
+        n++;
+    }
+    if (launches) *launches = n;
+    return e;
+}
+
+extern "C" unsigned k1_tiled_class_of(int S)
+{
+    for (int i = 0; i < kNumClass; i++)
+        if (S <= 32 * kClassC[i]) return (unsigned)i;
+    return 0xffffffffu;
 }
