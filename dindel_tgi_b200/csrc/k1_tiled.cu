@@ -21,6 +21,9 @@
 #include "k1_tail.cuh"
 
 #define K1_EPS 1e-10
+#ifndef K1_TILED_MINB
+#define K1_TILED_MINB 4
+#endif
 #define FULLMASK 0xffffffffu
 
 template <int C, int J>
@@ -114,7 +117,7 @@ __device__ __forceinline__ void scan_first_wins(const double (&v0)[C], const dou
 }
 
 template <int C, int J>
-__global__ void __launch_bounds__(128, 3) k1_tiled_kernel(K1Batch B, int Slo, int Shi)
+__global__ void __launch_bounds__(128, K1_TILED_MINB) k1_tiled_kernel(K1Batch B, int Slo, int Shi)
 {
     using Cfg = TiledCfg<C, J>;
     constexpr int U16 = Cfg::U16;
@@ -209,7 +212,8 @@ __global__ void __launch_bounds__(128, 3) k1_tiled_kernel(K1Batch B, int Slo, in
                     lpe[c] = s_hp_lpe[code];
                     lpn[c] = s_hp_lpn[code];
 #pragma unroll
-                    for (int y = 2; y <= J; y++) lpD[c][y - 2] = lpe[c] + (double)(y - 1) * lInsgIns; // cpp:1791
+                    for (int y = 2; y <= J; y++) // cpp:1791; a source left of LO can never win -> -inf
+                        lpD[c][y - 2] = (x - y >= 0) ? lpe[c] + (double)(y - 1) * lInsgIns : K1_NEG_INF;
                     P0[c] = 0.0; // alpha[0] = 0 (cpp:335-338)
                     P1[c] = 0.0;
                 }
@@ -230,16 +234,12 @@ __global__ void __launch_bounds__(128, 3) k1_tiled_kernel(K1Batch B, int Slo, in
                     }
 #pragma unroll
                     for (int j = 1; j <= J; j++) {
-                        constexpr int dummy = 0;
-                        (void)dummy;
                         const int d = (j + C - 1) / C;
                         const int ci = d * C - j;
-                        double v = shfl_up_d(P0[ci], d);
-                        hP[j - 1] = (lane >= d) ? v : K1_NEG_INF;
+                        hP[j - 1] = shfl_up_d(P0[ci], d); // lanes without a left neighbour: table entry is -inf
                         hO[j - 1] = (amL[j - 1] & rbit) ? eq : uq;
                     }
-                    double t1h = shfl_up_d(t1[C - 1], 1);
-                    if (lane == 0) t1h = K1_NEG_INF;
+                    const double t1h = shfl_up_d(t1[C - 1], 1); // lane 0: only LO would use it (overridden)
 
                     double N0[C], N1[C];
                     uint32_t nib[C];
@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(128, 3) k1_tiled_kernel(K1Batch B, int Slo, in
                         const int code = hp[nx];
                         const double lpn_s = s_hp_lpn[code], lpe_s = s_hp_lpe[code];
                         const double lp = (y == 1) ? lpn_s : (lpe_s + (double)(y - 1) * lInsgIns); // cpp:1732
-                        cI[c][y - 1] = lp + lpn_s;
+                        cI[c][y - 1] = (x + y <= RO) ? lp + lpn_s : K1_NEG_INF; // duplicates of RO never win
                         if (y == 1) lpeN[c] = lpe_s; // logProbError[x+1] (cpp:1748)
                     }
                     P0[c] = (x <= RO) ? 0.0 : K1_NEG_INF; // beta[R-1] = 0; columns beyond RO never win
@@ -360,12 +360,10 @@ __global__ void __launch_bounds__(128, 3) k1_tiled_kernel(K1Batch B, int Slo, in
                     for (int j = 1; j <= J; j++) {
                         const int d = (C - 1 + j) / C;
                         const int ci = (C - 1 + j) % C;
-                        double v = shfl_down_d(P0[ci], d);
-                        hP[j - 1] = (lane + d <= 31) ? v : K1_NEG_INF;
+                        hP[j - 1] = shfl_down_d(P0[ci], d); // beyond lane 31: table entry is -inf
                         hO[j - 1] = (amR[j - 1] & rbit) ? eq : uq;
                     }
-                    double uh = shfl_down_d(u[0], 1);
-                    if (lane == 31) uh = K1_NEG_INF;
+                    const double uh = shfl_down_d(u[0], 1); // lane 31: column is RO or padding (overridden)
 
                     double N0[C], N1[C];
                     uint32_t nib[C];
