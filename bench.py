@@ -310,7 +310,7 @@ def main():
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-            nwin = args.cpu_windows or max(8, int(6 * cores))
+            nwin = args.cpu_windows or max(8, int(100 * cores))
             r = cpu_baseline(batch, params, nwin, cores)
             line["cpu_baseline"] = {"value": r["pairs"] / r["wall_s"], "unit": UNIT, "cores": r["cores"],
                                     "kind": r["kind"],

@@ -10,6 +10,7 @@
 #include <string>
 #include <vector>
 #include "k1_common.cuh"
+#include "k23.cuh"
 
 extern "C" size_t k1_generic_smem_per_warp(int maxS, int maxR, int bt_in_smem);
 extern "C" cudaError_t k1_generic_launch(const K1Batch *B, int grid, int warps_per_cta,
@@ -18,6 +19,9 @@ extern "C" int k1_tiled_supported(int maxS, int maxR, int J);
 extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream_t stream,
                                        int *launches, unsigned class_mask);
 extern "C" unsigned k1_tiled_class_of(int S);
+extern "C" cudaError_t k2_launch(const K2Args *a, cudaStream_t st);
+extern "C" cudaError_t k3_launch(const K3Args *a, cudaStream_t st);
+extern "C" int k3_max_haps(void);
 
 // ------------------------------------------------------------------------------------------
 // small device kernels owned by the API layer
@@ -130,11 +134,12 @@ struct dindel_ctx {
     std::string err;
     DevBuf d_luts, d_counter, d_hap_start, d_win_hap, d_win_read, d_win_pair, d_win_unit, d_hap_off,
         d_hap_seq, d_hap_hp, d_read_off, d_read_seq, d_read_qual, d_read_mapq, d_read_start,
-        d_read_flags, d_pairs, d_hpos, d_win_status, d_on_hap, d_bt;
+        d_read_flags, d_pairs, d_hpos, d_win_status, d_on_hap, d_bt, d_x[8];
     // resident batch
     bool resident = false, ran = false;
     K1Batch B;
     std::vector<long long> win_pair, win_unit;
+    std::vector<int> win_nh;
     dindel_timing timing;
     int force_generic = 0;
     unsigned class_mask = 0;   // shape classes (state columns per lane) present in the batch
@@ -304,6 +309,7 @@ int dindel_b200_destroy(dindel_ctx *ctx)
                       &ctx->d_read_start, &ctx->d_read_flags, &ctx->d_pairs, &ctx->d_hpos,
                       &ctx->d_win_status, &ctx->d_on_hap, &ctx->d_bt};
     for (DevBuf *b : bufs) b->release();
+    for (int i = 0; i < 8; i++) ctx->d_x[i].release();
     for (int i = 0; i < 6; i++) cudaEventDestroy(ctx->ev[i]);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -367,7 +373,9 @@ int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos
     // host-side indexing: pair / work-unit prefix sums, extreme shapes
     ctx->win_pair.assign((size_t)nw + 1, 0);
     ctx->win_unit.assign((size_t)nw + 1, 0);
+    ctx->win_nh.assign((size_t)nw, 0);
     for (int w = 0; w < nw; w++) {
+        ctx->win_nh[w] = in->win_hap[w + 1] - in->win_hap[w];
         long long a = in->win_hap[w + 1] - in->win_hap[w], b = in->win_read[w + 1] - in->win_read[w];
         ctx->win_pair[w + 1] = ctx->win_pair[w] + a * b;
         ctx->win_unit[w + 1] = ctx->win_unit[w] + a * ((b + K1_READ_CHUNK - 1) / K1_READ_CHUNK);
@@ -592,6 +600,89 @@ int dindel_b200_get_timing(const dindel_ctx *ctx, dindel_timing *t)
 {
     if (!ctx || !t) return DINDEL_E_INVALID;
     *t = ctx->timing;
+    return DINDEL_OK;
+}
+
+int dindel_b200_pair_sums(dindel_ctx *ctx, const dindel_pairsum_in *in, double *out)
+{
+    if (!ctx || !in || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "pair_sums needs a resident, computed batch");
+    if (in->n_jobs < 0) return fail(ctx, DINDEL_E_INVALID, "n_jobs");
+    if (in->n_jobs == 0) return DINDEL_OK;
+    if (!in->job_window || !in->job_group || !in->job_off || !in->start || !out) return fail(ctx, DINDEL_E_INVALID, "null array");
+    const K1Batch &B = ctx->B;
+    for (int j = 0; j < in->n_jobs; j++) {
+        int w = in->job_window[j];
+        if (w < 0 || w >= B.n_windows) return fail(ctx, DINDEL_E_INVALID, "job_window out of range");
+        const long long nh = ctx->win_nh[w];
+        if (in->job_off[j + 1] - in->job_off[j] != nh * (nh + 1) / 2) return fail(ctx, DINDEL_E_INVALID, "job_off does not match nh*(nh+1)/2");
+    }
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const size_t nj = (size_t)in->n_jobs, nv = (size_t)in->job_off[in->n_jobs];
+    CU(ctx->d_x[0].ensure(nj * 4)); CU(ctx->d_x[1].ensure(nj * 4)); CU(ctx->d_x[2].ensure((nj + 1) * 8));
+    CU(ctx->d_x[3].ensure(nv * 8 + 8)); CU(ctx->d_x[4].ensure(nv * 8 + 8));
+    CU(cudaMemcpyAsync(ctx->d_x[0].p, in->job_window, nj * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(ctx->d_x[1].p, in->job_group, nj * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(ctx->d_x[2].p, in->job_off, (nj + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (nv) CU(cudaMemcpyAsync(ctx->d_x[3].p, in->start, nv * 8, cudaMemcpyHostToDevice, st));
+    if (in->read_group) {
+        CU(ctx->d_x[5].ensure((size_t)B.n_reads * 4 + 8));
+        if (B.n_reads) CU(cudaMemcpyAsync(ctx->d_x[5].p, in->read_group, (size_t)B.n_reads * 4, cudaMemcpyHostToDevice, st));
+    }
+    K2Args a;
+    a.n_jobs = in->n_jobs;
+    a.job_window = (const int32_t *)ctx->d_x[0].p; a.job_group = (const int32_t *)ctx->d_x[1].p;
+    a.job_off = (const long long *)ctx->d_x[2].p; a.start = (const double *)ctx->d_x[3].p;
+    a.read_group = in->read_group ? (const int32_t *)ctx->d_x[5].p : nullptr;
+    a.out = (double *)ctx->d_x[4].p;
+    a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.pairs = B.pairs;
+    volatile double half = 0.5;
+    a.log_half = log(half); // DInDel.cpp:3091 log(0.5), host libm
+    CU(k2_launch(&a, st));
+    if (nv) CU(cudaMemcpyAsync(out, a.out, nv * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return DINDEL_OK;
+}
+
+int dindel_b200_bayes_em(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out *out)
+{
+    if (!ctx || !in || !out || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "bayes_em needs a resident, computed batch");
+    if (in->n_sets < 0) return fail(ctx, DINDEL_E_INVALID, "n_sets");
+    if (in->n_sets == 0) return DINDEL_OK;
+    if (!in->set_window || !in->set_off || !in->compatible || !out->loglik || !out->iters || !out->pi || !out->freqs)
+        return fail(ctx, DINDEL_E_INVALID, "null array");
+    const K1Batch &B = ctx->B;
+    for (int s = 0; s < in->n_sets; s++) {
+        int w = in->set_window[s];
+        if (w < 0 || w >= B.n_windows) return fail(ctx, DINDEL_E_INVALID, "set_window out of range");
+        if (in->set_off[s + 1] - in->set_off[s] != ctx->win_nh[w]) return fail(ctx, DINDEL_E_INVALID, "set_off does not match nh");
+        if (in->set_off[s + 1] - in->set_off[s] > k3_max_haps()) return fail(ctx, DINDEL_E_UNSUPPORTED, "more than 64 haplotypes in a window");
+    }
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const size_t ns = (size_t)in->n_sets, nv = (size_t)in->set_off[in->n_sets];
+    CU(ctx->d_x[0].ensure(ns * 4)); CU(ctx->d_x[1].ensure((ns + 1) * 8)); CU(ctx->d_x[2].ensure(nv + 8));
+    CU(ctx->d_x[3].ensure(ns * 8)); CU(ctx->d_x[4].ensure(ns * 4)); CU(ctx->d_x[5].ensure(nv * 8 + 8));
+    CU(ctx->d_x[6].ensure(nv * 8 + 8));
+    CU(cudaMemcpyAsync(ctx->d_x[0].p, in->set_window, ns * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(ctx->d_x[1].p, in->set_off, (ns + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (nv) CU(cudaMemcpyAsync(ctx->d_x[2].p, in->compatible, nv, cudaMemcpyHostToDevice, st));
+    K3Args a;
+    a.n_sets = in->n_sets;
+    a.set_window = (const int32_t *)ctx->d_x[0].p; a.set_off = (const long long *)ctx->d_x[1].p;
+    a.compatible = (const uint8_t *)ctx->d_x[2].p;
+    a.a0 = in->a0; a.tol = in->tol;
+    a.loglik = (double *)ctx->d_x[3].p; a.iters = (int32_t *)ctx->d_x[4].p;
+    a.pi = (double *)ctx->d_x[5].p; a.freqs = (double *)ctx->d_x[6].p;
+    a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.pairs = B.pairs;
+    CU(k3_launch(&a, st));
+    CU(cudaMemcpyAsync(out->loglik, a.loglik, ns * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out->iters, a.iters, ns * 4, cudaMemcpyDeviceToHost, st));
+    if (nv) {
+        CU(cudaMemcpyAsync(out->pi, a.pi, nv * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(out->freqs, a.freqs, nv * 8, cudaMemcpyDeviceToHost, st));
+    }
+    CU(cudaStreamSynchronize(st));
     return DINDEL_OK;
 }
 

@@ -52,6 +52,21 @@ class Timing(C.Structure):
                 ("prep_launches", C.c_int32), ("n_pairs", C.c_int64), ("n_cells", C.c_int64)]
 
 
+class _PairSumIn(C.Structure):
+    _fields_ = [("n_jobs", C.c_int32), ("reserved", C.c_int32), ("job_window", C.c_void_p),
+                ("job_group", C.c_void_p), ("job_off", C.c_void_p), ("start", C.c_void_p),
+                ("read_group", C.c_void_p)]
+
+
+class _EmIn(C.Structure):
+    _fields_ = [("n_sets", C.c_int32), ("reserved", C.c_int32), ("set_window", C.c_void_p),
+                ("set_off", C.c_void_p), ("compatible", C.c_void_p), ("a0", C.c_double), ("tol", C.c_double)]
+
+
+class _EmOut(C.Structure):
+    _fields_ = [("loglik", C.c_void_p), ("iters", C.c_void_p), ("pi", C.c_void_p), ("freqs", C.c_void_p)]
+
+
 PAIR_DTYPE = np.dtype([
     ("ll", "<f8"), ("llOn", "<f8"), ("llOff", "<f8"), ("mLogBQ", "<f8"),
     ("firstBase", "<i4"), ("lastBase", "<i4"),
@@ -67,7 +82,8 @@ EXPORTS = [
     "dindel_b200_count_pairs", "dindel_b200_count_cells", "dindel_b200_submit",
     "dindel_b200_upload", "dindel_b200_run", "dindel_b200_download", "dindel_b200_sync",
     "dindel_b200_get_timing", "dindel_b200_hpos_stride", "dindel_b200_alloc_pinned",
-    "dindel_b200_free_pinned", "dindel_b200_measure_fp64_peak",
+    "dindel_b200_free_pinned", "dindel_b200_measure_fp64_peak", "dindel_b200_pair_sums",
+    "dindel_b200_bayes_em",
 ]
 
 _lib = None
@@ -103,6 +119,8 @@ def load_library():
     lib.dindel_b200_alloc_pinned.argtypes = [C.c_size_t]
     lib.dindel_b200_free_pinned.argtypes = [C.c_void_p]
     lib.dindel_b200_measure_fp64_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+    lib.dindel_b200_pair_sums.argtypes = [C.c_void_p, C.POINTER(_PairSumIn), C.c_void_p]
+    lib.dindel_b200_bayes_em.argtypes = [C.c_void_p, C.POINTER(_EmIn), C.POINTER(_EmOut)]
     _lib = lib
     return lib
 
@@ -313,3 +331,35 @@ class Engine:
         v = C.c_double()
         self._check(self.lib.dindel_b200_measure_fp64_peak(self.h, C.byref(v)), "measure_fp64_peak")
         return v.value
+
+    # ---- inference kernels over the resident likelihood matrix ----
+    def pair_sums(self, job_window, starts, job_group=None, read_group=None):
+        """K2 (diploidGLF / pooled genotype sums).  starts: list of float64 arrays, one per job, each
+        nh*(nh+1)/2 long (h1 <= h2 row-major).  Returns the list of summed arrays."""
+        nj = len(job_window)
+        jw = np.ascontiguousarray(job_window, dtype=np.int32)
+        jg = np.full(nj, -1, dtype=np.int32) if job_group is None else np.ascontiguousarray(job_group, dtype=np.int32)
+        off = np.concatenate([[0], np.cumsum([len(x) for x in starts])]).astype(np.int64)
+        st = np.ascontiguousarray(np.concatenate(starts) if nj else np.zeros(0), dtype=np.float64)
+        out = np.zeros_like(st)
+        rg = None if read_group is None else np.ascontiguousarray(read_group, dtype=np.int32)
+        a = _PairSumIn()
+        a.n_jobs, a.job_window, a.job_group, a.job_off, a.start = nj, jw.ctypes.data, jg.ctypes.data, off.ctypes.data, st.ctypes.data
+        a.read_group = rg.ctypes.data if rg is not None else None
+        self._check(self.lib.dindel_b200_pair_sums(self.h, C.byref(a), out.ctypes.data), "pair_sums")
+        return [out[off[j]:off[j + 1]] for j in range(nj)]
+
+    def bayes_em(self, set_window, compatible, a0=0.001, tol=1e-4):
+        """K3 (estimateHaplotypeFrequenciesBayesEM core).  compatible: list of uint8 arrays (nh each).
+        Returns (loglik[n], iters[n], [pi arrays], [freq arrays])."""
+        ns = len(set_window)
+        sw = np.ascontiguousarray(set_window, dtype=np.int32)
+        off = np.concatenate([[0], np.cumsum([len(x) for x in compatible])]).astype(np.int64)
+        comp = np.ascontiguousarray(np.concatenate(compatible) if ns else np.zeros(0), dtype=np.uint8)
+        ll, it = np.zeros(ns), np.zeros(ns, dtype=np.int32)
+        pi, fr = np.zeros(len(comp)), np.zeros(len(comp))
+        a, o = _EmIn(), _EmOut()
+        a.n_sets, a.set_window, a.set_off, a.compatible, a.a0, a.tol = ns, sw.ctypes.data, off.ctypes.data, comp.ctypes.data, a0, tol
+        o.loglik, o.iters, o.pi, o.freqs = ll.ctypes.data, it.ctypes.data, pi.ctypes.data, fr.ctypes.data
+        self._check(self.lib.dindel_b200_bayes_em(self.h, C.byref(a), C.byref(o)), "bayes_em")
+        return ll, it, [pi[off[j]:off[j + 1]] for j in range(ns)], [fr[off[j]:off[j + 1]] for j in range(ns)]

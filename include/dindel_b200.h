@@ -135,6 +135,45 @@ int dindel_b200_sync(dindel_ctx *ctx);                        /* wait for run();
 int dindel_b200_get_timing(const dindel_ctx *ctx, dindel_timing *t);
 int dindel_b200_hpos_stride(const dindel_ctx *ctx);           /* stride of the resident hpos rows */
 
+/* ---- K2: haplotype-pair sums over the RESIDENT likelihood matrix (after run/submit) ----------
+ * Replaces the inner loops of DetInDel::diploidGLF (DInDel.cpp:3085-3113: start = 0;
+ * :3349-3390: start = prior - sitePrior) and the pooled genotype likelihoods (DInDel.cpp:2683-2694:
+ * reads of one pool member).  Job j on window job_window[j]:
+ *   out[job_off[j] + q] = start[job_off[j] + q] (+)= log(0.5) + addLogs(rl[r,h1], rl[r,h2])
+ * summed over the window's reads r in order (only those with read_group[r] == job_group[j] when
+ * job_group[j] >= 0); q enumerates h1 <= h2 row-major: (0,0),(0,1)..(0,nh-1),(1,1).. */
+typedef struct dindel_pairsum_in {
+    int32_t n_jobs;
+    int32_t reserved;
+    const int32_t *job_window; /* [n_jobs] */
+    const int32_t *job_group;  /* [n_jobs] -1 = all reads */
+    const int64_t *job_off;    /* [n_jobs+1]; job_off[j+1]-job_off[j] == nh*(nh+1)/2 of its window */
+    const double *start;       /* [job_off[n_jobs]] */
+    const int32_t *read_group; /* optional [n_reads] (Read::poolID) */
+} dindel_pairsum_in;
+int dindel_b200_pair_sums(dindel_ctx *ctx, const dindel_pairsum_in *in, double *out);
+
+/* ---- K3: variational-Bayes EM over haplotype frequencies (DInDel.cpp:2431-2545) --------------
+ * One EM run per set of active variants: set s on window set_window[s] with compatible[] flags
+ * (DInDel.cpp:2395-2411) for its nh haplotypes at set_off[s].  Outputs per set: loglik (logliks[th],
+ * :2542), iterations, and per haplotype pi (log, :2473) and freqs = exp(pi)/sum (:2539). */
+typedef struct dindel_em_in {
+    int32_t n_sets;
+    int32_t reserved;
+    const int32_t *set_window;  /* [n_sets] */
+    const int64_t *set_off;     /* [n_sets+1] */
+    const uint8_t *compatible;  /* [set_off[n_sets]] */
+    double a0;                  /* params.bayesa0 (CLI default 0.001, DInDel.cpp:4142) */
+    double tol;                 /* params.EMtol  (1e-4, DInDel.hpp:244) */
+} dindel_em_in;
+typedef struct dindel_em_out {
+    double *loglik;  /* [n_sets] */
+    int32_t *iters;  /* [n_sets] */
+    double *pi;      /* [set_off[n_sets]] */
+    double *freqs;   /* [set_off[n_sets]] */
+} dindel_em_out;
+int dindel_b200_bayes_em(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out *out);
+
 /* pinned host memory for the caller's buffers */
 void *dindel_b200_alloc_pinned(size_t bytes);
 void dindel_b200_free_pinned(void *p);

@@ -401,3 +401,96 @@ double ora_digamma(double x)
         + f * (691.0 / 32760.0 + f * (-1.0 / 12.0)))))));
     return r + log(x) - 0.5 / x + t;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * K2: haplotype-pair sums.  DInDel.cpp:3085-3093 (start 0.0, `ll+=log(0.5)+addLogs(...)`),
+ * :3378-3381 (start `pr`), :2683-2690 (reads of one pool member).  rl is r-major [nr*nh].
+ * q enumerates h1 <= h2 row-major.  group < 0: all reads.
+ * ------------------------------------------------------------------------------------------ */
+void ora_pair_sums(const double *rl, int nr, int nh, const int32_t *read_group, int group,
+                   const double *start, double *out)
+{
+    int h1, h2, r, q = 0;
+    double log5 = log(0.5);
+    for (h1 = 0; h1 < nh; h1++)
+        for (h2 = h1; h2 < nh; h2++, q++) {
+            double ll = start[q];
+            for (r = 0; r < nr; r++) {
+                if (group >= 0 && read_group && read_group[r] != group) continue;
+                ll += log5 + ora_addlogs(rl[r * nh + h1], rl[r * nh + h2]);
+            }
+            out[q] = ll;
+        }
+}
+
+/* ------------------------------------------------------------------------------------------
+ * K3: one variational-Bayes EM run, DInDel.cpp:2413-2542 statement by statement (z, nk, lpi, pi,
+ * eNew, convergence `fabs(eOld-eNew)<tol || iter>25`), digamma = ora_digamma (Boost's is absent:
+ * parity unpinned for that function).  Outputs loglik (:2542), pi (log), freqs (:2539), iters.
+ * ------------------------------------------------------------------------------------------ */
+int ora_bayes_em(const double *rl, int nr, int nh, const uint8_t *compatible, double a0, double tol,
+                 double *loglik_out, double *pi_out, double *freqs_out)
+{
+    double *z = (double *)malloc(sizeof(double) * (size_t)nr * nh);
+    double *pi = (double *)malloc(sizeof(double) * nh), *lpi = (double *)malloc(sizeof(double) * nh);
+    double *nk = (double *)malloc(sizeof(double) * nh), *ak = (double *)malloc(sizeof(double) * nh);
+    int h, r, idx, numah = 0, iter = 0, converged = 0;
+    double eOld = -HUGE_VAL, eNew, loglik = 0.0, zs;
+    for (h = 0; h < nh; h++) if (compatible[h]) numah++;
+    for (h = 0; h < nh; h++) lpi[h] = compatible[h] ? log(1.0 / (double)numah) : -100;
+    while (!converged) {
+        double ahat = 0.0, dahat;
+        for (h = 0; h < nh; h++) nk[h] = 0.0;
+        loglik = 0.0;
+        idx = 0;
+        for (r = 0; r < nr; r++) {
+            double lognorm = -HUGE_VAL;
+            for (h = 0; h < nh; h++) {
+                z[idx] = lpi[h] + (rl[idx]);
+                lognorm = ora_addlogs(lognorm, z[idx]);
+                idx++;
+            }
+            idx -= nh;
+            for (h = 0; h < nh; h++) {
+                z[idx] -= lognorm;
+                z[idx] = exp(z[idx]);
+                nk[h] += z[idx];
+                idx++;
+            }
+            loglik += lognorm;
+        }
+        for (h = 0; h < nh; h++) if (compatible[h]) {
+            ak[h] = nk[h] + a0;
+            ahat += ak[h];
+        }
+        dahat = ora_digamma(ahat);
+        for (h = 0; h < nh; h++) {
+            if (compatible[h]) {
+                lpi[h] = ora_digamma(ak[h]) - dahat;
+                pi[h] = log((a0 + nk[h]) / ((double)numah * a0 + (double)nr));
+            } else {
+                lpi[h] = -100;
+                pi[h] = -100;
+            }
+        }
+        idx = 0;
+        eNew = 0.0;
+        for (r = 0; r < nr; r++)
+            for (h = 0; h < nh; h++) {
+                eNew += z[idx] * (pi[h] + rl[idx]);
+                idx++;
+            }
+        converged = (fabs(eOld - eNew)) < tol || iter > 25;
+        eOld = eNew;
+        iter++;
+    }
+    zs = 0.0;
+    for (h = 0; h < nh; h++) zs += exp(pi[h]);
+    for (h = 0; h < nh; h++) {
+        pi_out[h] = pi[h];
+        freqs_out[h] = exp(pi[h]) / zs;
+    }
+    *loglik_out = loglik;
+    free(z); free(pi); free(lpi); free(nk); free(ak);
+    return iter;
+}

@@ -34,6 +34,10 @@ int ora_window(const char *hap_seq, const int32_t *hap_off, int nh, const char *
                const uint32_t *mReadStart, const uint8_t *flags, int nr, uint32_t hapStart,
                const ora_params *p, ora_pair_out *out, int32_t *hpos, int hpos_stride);
 
+void ora_pair_sums(const double *rl, int nr, int nh, const int32_t *read_group, int group,
+                   const double *start, double *out);
+int ora_bayes_em(const double *rl, int nr, int nh, const uint8_t *compatible, double a0, double tol,
+                 double *loglik_out, double *pi_out, double *freqs_out);
 double ora_addlogs(double a, double b);
 double ora_digamma(double x);
 

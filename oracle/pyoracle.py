@@ -98,3 +98,30 @@ class Oracle:
                          vp(start), vp(flags), nr, C.c_uint32(int(batch.hap_start[w])), C.byref(params),
                          vp(out), vp(hpos) if want_hpos else None, stride)
         return n, out, hpos
+
+
+    # ---- K2 / K3 restatements (port only) ----
+    def pair_sums(self, rl, nh, start, read_group=None, group=-1):
+        rl = np.ascontiguousarray(rl, dtype=np.float64)
+        nr = len(rl) // nh
+        start = np.ascontiguousarray(start, dtype=np.float64)
+        out = np.zeros(nh * (nh + 1) // 2, dtype=np.float64)
+        rg = None if read_group is None else np.ascontiguousarray(read_group, dtype=np.int32)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        self.lib.ora_pair_sums(vp(rl), nr, nh, vp(rg) if rg is not None else None, int(group), vp(start), vp(out))
+        return out
+
+    def bayes_em(self, rl, nh, compatible, a0=0.001, tol=1e-4):
+        rl = np.ascontiguousarray(rl, dtype=np.float64)
+        nr = len(rl) // nh
+        comp = np.ascontiguousarray(compatible, dtype=np.uint8)
+        ll = C.c_double()
+        pi = np.zeros(nh)
+        fr = np.zeros(nh)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        it = self.lib.ora_bayes_em(vp(rl), nr, nh, vp(comp), C.c_double(a0), C.c_double(tol), C.byref(ll), vp(pi), vp(fr))
+        return ll.value, it, pi, fr
+
+    def digamma(self, x):
+        self.lib.ora_digamma.restype = C.c_double
+        return self.lib.ora_digamma(C.c_double(x))
