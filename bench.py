@@ -145,8 +145,9 @@ def run_reference(args, rank, world):
     params = engine.Params(5e-4, 1e-5, 100.0, 0.01, 0.95, 5, 2, -1, 0) if args.cfg != 4 else \
         engine.Params(5e-4, 1e-5, 100.0, 0.01, 0.95, 10, 2, -1, 0)
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    # bounded sample per step: ~2.5 windows per core (about 1.3k pairs per core-step at ~2k pairs/s/core)
-    nwin = args.cpu_windows or max(8, int(2.5 * cores))
+    # bounded sample per step: ~60 windows per core (about 16k pairs = 4-5 s per core-step at ~4k
+    # pairs/s/core), so that process start-up is amortised and K+W steps still end within minutes
+    nwin = args.cpu_windows or max(8, int(60 * cores))
     batch = synth.make_batch(args.cfg, nwin)
     times, pairs, kind = [], 0, "port"
     for i in range(args.warmup + args.steps):

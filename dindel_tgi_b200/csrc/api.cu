@@ -362,6 +362,30 @@ int64_t dindel_b200_count_cells(const dindel_batch_in *in)
     return n;
 }
 
+int dindel_b200_plan_shards(const dindel_batch_in *in, int n_shards, int32_t *first_window)
+{
+    if (validate(in) != DINDEL_OK || n_shards < 1 || !first_window) return DINDEL_E_INVALID;
+    const int nw = in->n_windows;
+    std::vector<long long> pre((size_t)nw + 1, 0); // prefix sums of the per-window K1 cost
+    for (int w = 0; w < nw; w++) {
+        int h0 = in->win_hap[w], h1 = in->win_hap[w + 1], r0 = in->win_read[w], r1 = in->win_read[w + 1];
+        long long cols = (in->hap_off[h1] - in->hap_off[h0]) + 2LL * (h1 - h0);
+        long long rows = in->read_off[r1] - in->read_off[r0];
+        pre[w + 1] = pre[w] + cols * rows + 1; // +1: empty windows still cost a slot
+    }
+    first_window[0] = 0;
+    int w = 0;
+    for (int k = 1; k < n_shards; k++) {
+        // first boundary whose prefix reaches k/n of the total (rounded to the nearer side)
+        const long long target = (long long)(((__int128)pre[nw] * k) / n_shards);
+        while (w < nw && pre[w + 1] <= target) w++;
+        if (w < nw && target - pre[w] > pre[w + 1] - target) w++;
+        first_window[k] = w;
+    }
+    first_window[n_shards] = nw;
+    return DINDEL_OK;
+}
+
 int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos)
 {
     if (!ctx) return DINDEL_E_INVALID;

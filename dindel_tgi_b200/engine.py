@@ -15,7 +15,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdindel_b200.so")
+# DINDEL_B200_LIB selects another build of the same library (kernel-variant experiments)
+LIB_PATH = os.environ.get("DINDEL_B200_LIB") or os.path.join(_HERE, "libdindel_b200.so")
 
 WIN_OK, WIN_HAPSIZE, WIN_NAN, WIN_LL_POSITIVE = 0, 1, 2, 3
 HPOS_INS, HPOS_LO, HPOS_RO = -1, -3, -4
@@ -83,7 +84,7 @@ EXPORTS = [
     "dindel_b200_upload", "dindel_b200_run", "dindel_b200_download", "dindel_b200_sync",
     "dindel_b200_get_timing", "dindel_b200_hpos_stride", "dindel_b200_alloc_pinned",
     "dindel_b200_free_pinned", "dindel_b200_measure_fp64_peak", "dindel_b200_pair_sums",
-    "dindel_b200_bayes_em",
+    "dindel_b200_bayes_em", "dindel_b200_plan_shards",
 ]
 
 _lib = None
@@ -121,8 +122,20 @@ def load_library():
     lib.dindel_b200_measure_fp64_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
     lib.dindel_b200_pair_sums.argtypes = [C.c_void_p, C.POINTER(_PairSumIn), C.c_void_p]
     lib.dindel_b200_bayes_em.argtypes = [C.c_void_p, C.POINTER(_EmIn), C.POINTER(_EmOut)]
+    lib.dindel_b200_plan_shards.argtypes = [C.POINTER(_BatchIn), C.c_int, C.c_void_p]
     _lib = lib
     return lib
+
+
+def plan_shards(batch, n_shards):
+    """Window scheduler (dindel_b200_plan_shards): boundaries of n_shards contiguous window ranges of
+    near-equal K1 cost; shard k = batch.slice_windows(b[k], b[k+1]).  Host only."""
+    out = np.zeros(n_shards + 1, dtype=np.int32)
+    cb = batch._c()
+    rc = load_library().dindel_b200_plan_shards(C.byref(cb), n_shards, out.ctypes.data)
+    if rc != 0:
+        raise RuntimeError("dindel_b200_plan_shards failed: %s" % load_library().dindel_b200_strerror(rc).decode())
+    return out
 
 
 def default_params():

@@ -124,6 +124,13 @@ int dindel_b200_destroy(dindel_ctx *ctx);
 int64_t dindel_b200_count_pairs(const dindel_batch_in *in);
 int64_t dindel_b200_count_cells(const dindel_batch_in *in);
 
+/* Window scheduler, host only (no device needed): split the batch into n_shards contiguous window
+ * ranges of near-equal K1 cost (cells = sum R*(H+2) per window), one per GPU / process.  Windows are
+ * independent (DInDel.cpp:1310-1411), so shards need no collective; this replaces the per-file
+ * window split of makeWindows.py (python/makeWindows.py:48-55).  first_window[n_shards+1] receives
+ * the range boundaries: shard k owns windows [first_window[k], first_window[k+1]). */
+int dindel_b200_plan_shards(const dindel_batch_in *in, int n_shards, int32_t *first_window);
+
 /* computeLikelihoods for a whole batch: host buffers in, host buffers out (H2D + kernels + D2H). */
 int dindel_b200_submit(dindel_ctx *ctx, const dindel_batch_in *in, dindel_batch_out *out);
 
