@@ -201,10 +201,18 @@ __global__ void __launch_bounds__(128, K1_TILED_MINB) k1_tiled_kernel(K1Batch B,
 #pragma unroll
             for (int c = 0; c < C; c++) am[c] = accept_mask(hap, c0 + c, H);
 
+            // Column RO = H+1 sits at a warp-uniform register slot cRO of lane lRO; its special
+            // transitions are evaluated once per row under a warp-uniform test.
+            const int lRO = RO / C, cRO = RO - lRO * C;
+            const bool isLane0 = (lane == 0), isLaneRO = (lane == lRO);
+
             // =================== left half: rows 1..bMid (passMessageTwoDec) ===================
+            // Per row: a window W*[k] of the previous row over columns c0-J .. c0+C-1 (own columns at
+            // k = J+c, the J columns to the left fetched from the neighbour lanes), then the C cells'
+            // candidate chains advanced in lock step (y outer, c inner) so that the chains of the C
+            // cells interleave in the instruction stream.
             {
                 double lpn[C], lpe[C], lpD[C][J - 1];
-                uint32_t amL[J];
 #pragma unroll
                 for (int c = 0; c < C; c++) {
                     const int x = c0 + c;
@@ -219,82 +227,92 @@ __global__ void __launch_bounds__(128, K1_TILED_MINB) k1_tiled_kernel(K1Batch B,
                 }
                 // lpe of the column left of this lane's first (RO's "from S+H" candidate, cpp:1805)
                 const double lpeLm1 = s_hp_lpe[hp[(c0 >= 1 && c0 - 1 <= RO) ? c0 - 1 : 0]];
-#pragma unroll
-                for (int j = 1; j <= J; j++) amL[j - 1] = accept_mask(hap, c0 - j, H);
 
                 for (int b = 1; b <= bMid; b++) {
                     const double eq = sm_eq[b - 1], uq = sm_uq[b - 1];
                     const uint32_t rbit = 1u << (sm_ch[b - 1] & 31);
-                    double Os[C], u[C], t1[C], hP[J], hO[J];
+                    double WO[C + J], WP[C + J], u[C], t1w[C + 1];
 #pragma unroll
                     for (int c = 0; c < C; c++) {
-                        Os[c] = (am[c] & rbit) ? eq : uq;
-                        u[c] = Os[c] + P0[c];
-                        t1[c] = eq + P1[c];
+                        WO[J + c] = (am[c] & rbit) ? eq : uq;
+                        WP[J + c] = P0[c];
+                        u[c] = WO[J + c] + P0[c];
+                        t1w[c + 1] = eq + P1[c];
                     }
 #pragma unroll
-                    for (int j = 1; j <= J; j++) {
+                    for (int j = 1; j <= J; j++) { // lanes without a left neighbour: table entry is -inf
                         const int d = (j + C - 1) / C;
                         const int ci = d * C - j;
-                        hP[j - 1] = shfl_up_d(P0[ci], d); // lanes without a left neighbour: table entry is -inf
-                        hO[j - 1] = (amL[j - 1] & rbit) ? eq : uq;
+                        WP[J - j] = shfl_up_d(WP[J + ci], d);
+                        WO[J - j] = shfl_up_d(WO[J + ci], d);
                     }
-                    const double t1h = shfl_up_d(t1[C - 1], 1); // lane 0: only LO would use it (overridden)
+                    t1w[0] = shfl_up_d(t1w[C], 1); // lane 0: only LO would use it (overridden)
 
-                    double N0[C], N1[C];
-                    uint32_t nib[C];
+                    double best[C], a1[C];
+                    uint32_t code[C], bit1[C];
+                    // jumps y = 1..J from column x-y (cpp:1784-1795)
 #pragma unroll
                     for (int c = 0; c < C; c++) {
-                        const int x = c0 + c;
-                        // jumps y = 1..J from column x-y (cpp:1784-1795)
-                        const double O1s = (c >= 1) ? Os[c - 1] : hO[0];
-                        const double P1s = (c >= 1) ? P0[c - 1] : hP[0];
-                        double best = ((O1s + lpn[c]) + P1s) + lpn[c];
-                        uint32_t code = 0;
+                        best[c] = ((WO[J + c - 1] + lpn[c]) + WP[J + c - 1]) + lpn[c];
+                        code[c] = 0;
+                    }
 #pragma unroll
-                        for (int y = 2; y <= J; y++) {
-                            const double Oy = (c - y >= 0) ? Os[(c - y >= 0) ? c - y : 0] : hO[(y - c - 1 >= 0) ? y - c - 1 : 0];
-                            const double Py = (c - y >= 0) ? P0[(c - y >= 0) ? c - y : 0] : hP[(y - c - 1 >= 0) ? y - c - 1 : 0];
-                            const double v = ((Oy + lpD[c][y - 2]) + Py) + lpn[c];
-                            if (v >= best) { best = v; code = y - 1; }
+                    for (int y = 2; y <= J; y++) {
+#pragma unroll
+                        for (int c = 0; c < C; c++) {
+                            const double v = ((WO[J + c - y] + lpD[c][y - 2]) + WP[J + c - y]) + lpn[c];
+                            const bool p = (v >= best[c]);
+                            best[c] = p ? v : best[c];
+                            code[c] = p ? (uint32_t)(y - 1) : code[c];
                         }
-                        // from plane-1 x-1 (cpp:1807-1811)
-                        const double t1s = (c >= 1) ? t1[c - 1] : t1h;
-                        const double vi = t1s + lpe[c];
-                        if (vi > best + K1_EPS) { best = vi; code = J; }
-                        // plane 1 (cpp:1816-1826)
-                        const double stay = t1[c] + lInsgIns;
+                    }
+                    // from plane-1 x-1 (cpp:1807-1811)
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
+                        const double vi = t1w[c] + lpe[c];
+                        const bool p = (vi > best[c] + K1_EPS);
+                        best[c] = p ? vi : best[c];
+                        code[c] = p ? (uint32_t)J : code[c];
+                    }
+                    // plane 1 (cpp:1816-1826)
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
+                        const double stay = t1w[c + 1] + lInsgIns;
                         const double f = u[c] + lNoInsgIns;
-                        uint32_t bit1 = (f >= stay) ? 1u : 0u;
-                        double a1 = bit1 ? f : stay;
-                        if (c == 0 && lane == 0) { // LO (cpp:1798-1799); plane 1 only stays (loop from x=1)
-                            best = u[c] + lNoInsgNoIns;
-                            code = 0;
-                            a1 = stay;
-                            bit1 = 0;
+                        const bool p = (f >= stay);
+                        a1[c] = p ? f : stay;
+                        bit1[c] = p ? 1u : 0u;
+                        if (c == 0) { // LO (cpp:1798-1799); plane 1 only stays (loop from x=1)
+                            const double lo = u[0] + lNoInsgNoIns;
+                            best[0] = isLane0 ? lo : best[0];
+                            code[0] = isLane0 ? 0u : code[0];
+                            a1[0] = isLane0 ? stay : a1[0];
+                            bit1[0] = isLane0 ? 0u : bit1[0];
                         }
-                        if (x == RO) { // cpp:1780-1782, 1804-1805
+                    }
+                    // RO (cpp:1780-1782, 1804-1805)
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
+                        if (c == cRO) {
+                            const double uH = WO[J + c - 1] + WP[J + c - 1];
                             double rv = (u[c] + lLOgLO) + lNoInsgNoIns;
                             uint32_t rcode = 0;
-                            const double v2 = ((O1s + P1s) + lFirstgLO) + lNoInsgNoIns;
+                            const double v2 = (uH + lFirstgLO) + lNoInsgNoIns;
                             if (v2 >= rv) { rv = v2; rcode = 1; }
-                            const double v3 = (t1[c] + lLOgLO) + lpe[c];
+                            const double v3 = (t1w[c + 1] + lLOgLO) + lpe[c];
                             if (v3 > rv + K1_EPS) { rv = v3; rcode = 2; }
                             const double lpeH = (c >= 1) ? lpe[(c >= 1) ? c - 1 : 0] : lpeLm1;
-                            const double v4 = (t1s + lFirstgLO) + lpeH;
+                            const double v4 = (t1w[c] + lFirstgLO) + lpeH;
                             const bool take = (rcode == 2) ? (v4 >= rv) : (v4 > rv + K1_EPS);
                             if (take) { rv = v4; rcode = 3; }
-                            best = rv;
-                            code = rcode;
+                            best[c] = isLaneRO ? rv : best[c];
+                            code[c] = isLaneRO ? rcode : code[c];
                         }
-                        N0[c] = best;
-                        N1[c] = a1;
-                        nib[c] = Cfg::NIB ? (code | (bit1 << 3)) : (code | (bit1 << 7));
                     }
 #pragma unroll
                     for (int c = 0; c < C; c++) {
-                        P0[c] = N0[c];
-                        P1[c] = N1[c];
+                        P0[c] = best[c];
+                        P1[c] = a1[c];
                     }
                     uint16_t *row = sm_bt + (size_t)b * U16 * 32;
 #pragma unroll
@@ -303,11 +321,17 @@ __global__ void __launch_bounds__(128, K1_TILED_MINB) k1_tiled_kernel(K1Batch B,
                         if (Cfg::NIB) {
 #pragma unroll
                             for (int q = 0; q < 4; q++)
-                                if (4 * k + q < C) v |= nib[(4 * k + q < C) ? 4 * k + q : 0] << (4 * q);
+                                if (4 * k + q < C) {
+                                    const int cc = (4 * k + q < C) ? 4 * k + q : 0;
+                                    v += (code[cc] + 8u * bit1[cc]) << (4 * q);
+                                }
                         } else {
 #pragma unroll
                             for (int q = 0; q < 2; q++)
-                                if (2 * k + q < C) v |= nib[(2 * k + q < C) ? 2 * k + q : 0] << (8 * q);
+                                if (2 * k + q < C) {
+                                    const int cc = (2 * k + q < C) ? 2 * k + q : 0;
+                                    v += (code[cc] + 128u * bit1[cc]) << (8 * q);
+                                }
                         }
                         row[k * 32 + lane] = (uint16_t)v;
                     }
@@ -324,9 +348,10 @@ __global__ void __launch_bounds__(128, K1_TILED_MINB) k1_tiled_kernel(K1Batch B,
                 }
             }
             // =================== right half: rows R-2..bMid (passMessageTwoInc) ===================
+            // Window W*[k] over columns c0 .. c0+C-1+J (own at k = c, the J columns to the right
+            // from the neighbour lanes).
             {
                 double cI[C][J], lpeN[C];
-                uint32_t amR[J];
 #pragma unroll
                 for (int c = 0; c < C; c++) {
                     const int x = c0 + c;
@@ -343,79 +368,93 @@ __global__ void __launch_bounds__(128, K1_TILED_MINB) k1_tiled_kernel(K1Batch B,
                     P1[c] = (x <= RO) ? 0.0 : K1_NEG_INF;
                 }
                 const double lpnRO = s_hp_lpn[hp[RO]];
-#pragma unroll
-                for (int j = 1; j <= J; j++) amR[j - 1] = accept_mask(hap, c0 + C - 1 + j, H);
 
                 for (int b = R - 1; b > bMid; b--) {
                     const double eq = sm_eq[b], uq = sm_uq[b];
                     const uint32_t rbit = 1u << (sm_ch[b] & 31);
-                    double Os[C], u[C], t1[C], hP[J], hO[J];
+                    double WO[C + J], WP[C + J], uw[C + 1], t1[C];
 #pragma unroll
                     for (int c = 0; c < C; c++) {
-                        Os[c] = (am[c] & rbit) ? eq : uq;
-                        u[c] = Os[c] + P0[c];
+                        WO[c] = (am[c] & rbit) ? eq : uq;
+                        WP[c] = P0[c];
+                        uw[c] = WO[c] + P0[c];
                         t1[c] = eq + P1[c];
                     }
 #pragma unroll
-                    for (int j = 1; j <= J; j++) {
+                    for (int j = 1; j <= J; j++) { // beyond lane 31: table entry is -inf
                         const int d = (C - 1 + j) / C;
                         const int ci = (C - 1 + j) % C;
-                        hP[j - 1] = shfl_down_d(P0[ci], d); // beyond lane 31: table entry is -inf
-                        hO[j - 1] = (amR[j - 1] & rbit) ? eq : uq;
+                        WP[C - 1 + j] = shfl_down_d(WP[ci], d);
+                        WO[C - 1 + j] = shfl_down_d(WO[ci], d);
                     }
-                    const double uh = shfl_down_d(u[0], 1); // lane 31: column is RO or padding (overridden)
+                    uw[C] = shfl_down_d(uw[0], 1); // lane 31: column is RO or padding (overridden)
 
-                    double N0[C], N1[C];
-                    uint32_t nib[C];
+                    double best[C], a1[C];
+                    uint32_t code[C], bit1[C];
+                    // jumps y = 1..J to column x+y (cpp:1724-1737)
 #pragma unroll
                     for (int c = 0; c < C; c++) {
-                        const int x = c0 + c;
-                        // jumps y = 1..J to column x+y (cpp:1724-1737)
-                        const double O1s = (c + 1 < C) ? Os[(c + 1 < C) ? c + 1 : 0] : hO[0];
-                        const double P1s = (c + 1 < C) ? P0[(c + 1 < C) ? c + 1 : 0] : hP[0];
-                        double best = (cI[c][0] + P1s) + O1s;
-                        uint32_t code = 0;
+                        best[c] = (cI[c][0] + WP[c + 1]) + WO[c + 1];
+                        code[c] = 0;
+                    }
 #pragma unroll
-                        for (int y = 2; y <= J; y++) {
-                            const double Oy = (c + y < C) ? Os[(c + y < C) ? c + y : 0] : hO[(c + y - C >= 0) ? c + y - C : 0];
-                            const double Py = (c + y < C) ? P0[(c + y < C) ? c + y : 0] : hP[(c + y - C >= 0) ? c + y - C : 0];
-                            const double v = (cI[c][y - 1] + Py) + Oy;
-                            if (v > best + K1_EPS) { best = v; code = y - 1; }
+                    for (int y = 2; y <= J; y++) {
+#pragma unroll
+                        for (int c = 0; c < C; c++) {
+                            const double v = (cI[c][y - 1] + WP[c + y]) + WO[c + y];
+                            const bool p = (v > best[c] + K1_EPS);
+                            best[c] = p ? v : best[c];
+                            code[c] = p ? (uint32_t)(y - 1) : code[c];
                         }
-                        // from plane-1 x (cpp:1746-1749)
+                    }
+                    // from plane-1 x (cpp:1746-1749); LO's candidates (cpp:1720-1722, 1748)
+                    double vi0 = 0.0;
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
                         const double vi = t1[c] + lpeN[c];
-                        if (vi > best + K1_EPS) { best = vi; code = J; }
-                        // plane 1 (cpp:1754-1767)
-                        const double stay = t1[c] + lInsgIns;
-                        const double un = (c + 1 < C) ? u[(c + 1 < C) ? c + 1 : 0] : uh;
-                        double f = un + lNoInsgIns;
-                        if (c == 0 && lane == 0) { // LO (cpp:1720-1722, 1748, 1762)
-                            double rv = (u[c] + lLOgLO) + lNoInsgNoIns;
-                            uint32_t rcode = 0;
-                            const double v2 = (un + lFirstgLO) + lNoInsgNoIns;
-                            if (v2 > rv + K1_EPS) { rv = v2; rcode = 1; }
-                            if (vi > rv + K1_EPS) { rv = vi; rcode = J; }
-                            best = rv;
-                            code = rcode;
-                            f = u[c] + lNoInsgIns;
-                        }
-                        if (x == RO) { // cpp:1741-1742, 1750, 1764
-                            double rv = u[c] + lpnRO;
+                        if (c == 0) vi0 = vi;
+                        const bool p = (vi > best[c] + K1_EPS);
+                        best[c] = p ? vi : best[c];
+                        code[c] = p ? (uint32_t)J : code[c];
+                    }
+                    double f[C];
+#pragma unroll
+                    for (int c = 0; c < C; c++) f[c] = uw[c + 1] + lNoInsgIns;
+                    { // LO (cpp:1720-1722, 1748, 1762)
+                        double rv = (uw[0] + lLOgLO) + lNoInsgNoIns;
+                        uint32_t rcode = 0;
+                        const double v2 = (uw[1] + lFirstgLO) + lNoInsgNoIns;
+                        if (v2 > rv + K1_EPS) { rv = v2; rcode = 1; }
+                        if (vi0 > rv + K1_EPS) { rv = vi0; rcode = J; }
+                        const double f0 = uw[0] + lNoInsgIns;
+                        best[0] = isLane0 ? rv : best[0];
+                        code[0] = isLane0 ? rcode : code[0];
+                        f[0] = isLane0 ? f0 : f[0];
+                    }
+#pragma unroll
+                    for (int c = 0; c < C; c++) { // RO (cpp:1741-1742, 1750, 1764)
+                        if (c == cRO) {
+                            double rv = uw[c] + lpnRO;
                             uint32_t rcode = 0;
                             if (t1[c] > rv + K1_EPS) { rv = t1[c]; rcode = J; }
-                            best = rv;
-                            code = rcode;
-                            f = u[c] + lNoInsgIns;
+                            const double fr = uw[c] + lNoInsgIns;
+                            best[c] = isLaneRO ? rv : best[c];
+                            code[c] = isLaneRO ? rcode : code[c];
+                            f[c] = isLaneRO ? fr : f[c];
                         }
-                        const uint32_t bit1 = (f >= stay) ? 1u : 0u;
-                        N0[c] = best;
-                        N1[c] = bit1 ? f : stay;
-                        nib[c] = Cfg::NIB ? (code | (bit1 << 3)) : (code | (bit1 << 7));
+                    }
+                    // plane 1 (cpp:1754-1767)
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
+                        const double stay = t1[c] + lInsgIns;
+                        const bool p = (f[c] >= stay);
+                        a1[c] = p ? f[c] : stay;
+                        bit1[c] = p ? 1u : 0u;
                     }
 #pragma unroll
                     for (int c = 0; c < C; c++) {
-                        P0[c] = N0[c];
-                        P1[c] = N1[c];
+                        P0[c] = best[c];
+                        P1[c] = a1[c];
                     }
                     uint16_t *row = sm_bt + (size_t)b * U16 * 32; // btb[b-1] stored at row b
 #pragma unroll
@@ -424,11 +463,17 @@ __global__ void __launch_bounds__(128, K1_TILED_MINB) k1_tiled_kernel(K1Batch B,
                         if (Cfg::NIB) {
 #pragma unroll
                             for (int q = 0; q < 4; q++)
-                                if (4 * k + q < C) v |= nib[(4 * k + q < C) ? 4 * k + q : 0] << (4 * q);
+                                if (4 * k + q < C) {
+                                    const int cc = (4 * k + q < C) ? 4 * k + q : 0;
+                                    v += (code[cc] + 8u * bit1[cc]) << (4 * q);
+                                }
                         } else {
 #pragma unroll
                             for (int q = 0; q < 2; q++)
-                                if (2 * k + q < C) v |= nib[(2 * k + q < C) ? 2 * k + q : 0] << (8 * q);
+                                if (2 * k + q < C) {
+                                    const int cc = (2 * k + q < C) ? 2 * k + q : 0;
+                                    v += (code[cc] + 128u * bit1[cc]) << (8 * q);
+                                }
                         }
                         row[k * 32 + lane] = (uint16_t)v;
                     }
