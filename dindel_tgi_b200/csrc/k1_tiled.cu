@@ -24,6 +24,9 @@
 #ifndef K1_TILED_MINB
 #define K1_TILED_MINB 4
 #endif
+#ifndef K1_TILED_WPC
+#define K1_TILED_WPC 4 // warps per CTA
+#endif
 #define FULLMASK 0xffffffffu
 
 template <int C, int J>
@@ -44,6 +47,14 @@ __host__ __device__ inline size_t tiled_smem_per_warp(int C, int U16, int maxR)
 
 __device__ __forceinline__ double shfl_up_d(double v, int d) { return __shfl_up_sync(FULLMASK, v, d); }
 __device__ __forceinline__ double shfl_down_d(double v, int d) { return __shfl_down_sync(FULLMASK, v, d); }
+
+// Opaque copy: keeps a loop-invariant table entry in its register (the optimiser otherwise sinks
+// the entry's construction -- an add and a select -- into the row loop to save registers).
+__device__ __forceinline__ double pin_d(double v)
+{
+    asm volatile("" : "+d"(v));
+    return v;
+}
 
 __device__ __forceinline__ double warp_max_d(double v)
 {
@@ -117,7 +128,7 @@ __device__ __forceinline__ void scan_first_wins(const double (&v0)[C], const dou
 }
 
 template <int C, int J>
-__global__ void __launch_bounds__(128, K1_TILED_MINB) k1_tiled_kernel(K1Batch B, int Slo, int Shi)
+__global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_kernel(K1Batch B, int Slo, int Shi)
 {
     using Cfg = TiledCfg<C, J>;
     constexpr int U16 = Cfg::U16;
@@ -221,7 +232,7 @@ __global__ void __launch_bounds__(128, K1_TILED_MINB) k1_tiled_kernel(K1Batch B,
                     lpn[c] = s_hp_lpn[code];
 #pragma unroll
                     for (int y = 2; y <= J; y++) // cpp:1791; a source left of LO can never win -> -inf
-                        lpD[c][y - 2] = (x - y >= 0) ? lpe[c] + (double)(y - 1) * lInsgIns : K1_NEG_INF;
+                        lpD[c][y - 2] = pin_d((x - y >= 0) ? lpe[c] + (double)(y - 1) * lInsgIns : K1_NEG_INF);
                     P0[c] = 0.0; // alpha[0] = 0 (cpp:335-338)
                     P1[c] = 0.0;
                 }
@@ -361,7 +372,7 @@ __global__ void __launch_bounds__(128, K1_TILED_MINB) k1_tiled_kernel(K1Batch B,
                         const int code = hp[nx];
                         const double lpn_s = s_hp_lpn[code], lpe_s = s_hp_lpe[code];
                         const double lp = (y == 1) ? lpn_s : (lpe_s + (double)(y - 1) * lInsgIns); // cpp:1732
-                        cI[c][y - 1] = (x + y <= RO) ? lp + lpn_s : K1_NEG_INF; // duplicates of RO never win
+                        cI[c][y - 1] = pin_d((x + y <= RO) ? lp + lpn_s : K1_NEG_INF); // duplicates of RO never win
                         if (y == 1) lpeN[c] = lpe_s; // logProbError[x+1] (cpp:1748)
                     }
                     P0[c] = (x <= RO) ? 0.0 : K1_NEG_INF; // beta[R-1] = 0; columns beyond RO never win
@@ -539,7 +550,7 @@ template <int C, int J>
 static cudaError_t launch_one(const K1Batch *B, int num_sms, int Slo, int Shi, cudaStream_t st)
 {
     constexpr int U16 = TiledCfg<C, J>::U16;
-    const int warps = 4;
+    const int warps = K1_TILED_WPC;
     const size_t smem = tiled_smem_per_warp(C, U16, B->max_R) * warps;
     cudaError_t e = cudaFuncSetAttribute(k1_tiled_kernel<C, J>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -567,7 +578,7 @@ extern "C" int k1_tiled_supported(int maxS, int maxR, int J)
     for (int i = 0; i < kNumClass; i++)
         if (maxS <= 32 * kClassC[i]) { C = kClassC[i]; break; }
     int U16 = (C + 3) / 4;
-    return tiled_smem_per_warp(C, U16, maxR) * 4 <= 200 * 1024;
+    return tiled_smem_per_warp(C, U16, maxR) * K1_TILED_WPC <= 200 * 1024;
 }
 
 // One launch per shape class present (class = state columns per lane).  `class_mask` bit i set
