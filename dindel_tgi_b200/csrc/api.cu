@@ -19,6 +19,7 @@ extern "C" int k1_tiled_supported(int maxS, int maxR, int J);
 extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream_t stream,
                                        int *launches, unsigned class_mask);
 extern "C" unsigned k1_tiled_class_of(int S);
+extern "C" cudaError_t k1_tiled_prepare(const K1Batch *B, cudaStream_t stream, int *launches);
 extern "C" cudaError_t k2_launch(const K2Args *a, cudaStream_t st);
 extern "C" cudaError_t k3_launch(const K3Args *a, cudaStream_t st);
 extern "C" int k3_max_haps(void);
@@ -134,7 +135,7 @@ struct dindel_ctx {
     std::string err;
     DevBuf d_luts, d_counter, d_hap_start, d_win_hap, d_win_read, d_win_pair, d_win_unit, d_hap_off,
         d_hap_seq, d_hap_hp, d_read_off, d_read_seq, d_read_qual, d_read_mapq, d_read_start,
-        d_read_flags, d_pairs, d_hpos, d_win_status, d_on_hap, d_bt, d_x[8];
+        d_read_flags, d_pairs, d_hpos, d_win_status, d_on_hap, d_bt, d_units, d_buckets, d_x[8];
     // resident batch
     bool resident = false, ran = false;
     K1Batch B;
@@ -144,6 +145,7 @@ struct dindel_ctx {
     int force_generic = 0;
     unsigned class_mask = 0;   // shape classes (state columns per lane) present in the batch
     bool alphabet_ok = true;   // every sequence byte in [A-Z=] (needed by the tiled kernel)
+    bool use_tiled = false;    // the resident batch runs on the register-tiled kernel
 };
 
 static int fail(dindel_ctx *c, int code, const std::string &msg)
@@ -307,7 +309,7 @@ int dindel_b200_destroy(dindel_ctx *ctx)
                       &ctx->d_win_pair, &ctx->d_win_unit, &ctx->d_hap_off, &ctx->d_hap_seq, &ctx->d_hap_hp,
                       &ctx->d_read_off, &ctx->d_read_seq, &ctx->d_read_qual, &ctx->d_read_mapq,
                       &ctx->d_read_start, &ctx->d_read_flags, &ctx->d_pairs, &ctx->d_hpos,
-                      &ctx->d_win_status, &ctx->d_on_hap, &ctx->d_bt};
+                      &ctx->d_win_status, &ctx->d_on_hap, &ctx->d_bt, &ctx->d_units, &ctx->d_buckets};
     for (DevBuf *b : bufs) b->release();
     for (int i = 0; i < 8; i++) ctx->d_x[i].release();
     for (int i = 0; i < 6; i++) cudaEventDestroy(ctx->ev[i]);
@@ -468,7 +470,6 @@ int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos
                                                        (uint8_t *)ctx->d_hap_hp.p);
         CU(cudaGetLastError());
     }
-    CU(cudaEventRecord(ctx->ev[2], st));
 
     K1Batch &B = ctx->B;
     memset(&B, 0, sizeof(B));
@@ -497,6 +498,24 @@ int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos
     ctx->timing.n_pairs = n_pairs;
     ctx->timing.n_cells = dindel_b200_count_cells(in);
     ctx->timing.prep_launches = nh > 0 ? 1 : 0;
+    // work-unit lists of the tiled kernel (bucketed by shape class and RO slot)
+    ctx->use_tiled = !ctx->force_generic && ctx->alphabet_ok && !ctx->luts.force &&
+                     k1_tiled_supported(B.max_S, B.max_R, ctx->luts.numT - 1);
+    for (int w = 0; w < nw && ctx->use_tiled; w++) // unit descriptors hold hap and chunk in 16 bits each
+        if (ctx->win_nh[w] > 65535 || (in->win_read[w + 1] - in->win_read[w]) / K1_READ_CHUNK >= 65535 ||
+            B.n_units >= 0xffffffffLL)
+            ctx->use_tiled = false;
+    if (ctx->use_tiled && B.n_units > 0) {
+        CU(ctx->d_units.ensure((size_t)B.n_units * sizeof(uint2) + 16));
+        CU(ctx->d_buckets.ensure(sizeof(unsigned) * (3 * K1_TILED_BUCKETS + 1)));
+        B.units = (uint2 *)ctx->d_units.p;
+        B.bucket_start = (unsigned *)ctx->d_buckets.p;
+        B.bucket_work = B.bucket_start + K1_TILED_BUCKETS + 1;
+        int pl = 0;
+        CU(k1_tiled_prepare(&B, st, &pl));
+        ctx->timing.prep_launches += pl;
+    }
+    CU(cudaEventRecord(ctx->ev[2], st));
     ctx->resident = true;
     return DINDEL_OK;
 }
@@ -511,8 +530,8 @@ int dindel_b200_run(dindel_ctx *ctx)
     int launches = 0;
     if (B.n_units > 0) {
         const int J = ctx->luts.numT - 1;
-        if (!ctx->force_generic && ctx->alphabet_ok && !ctx->luts.force &&
-            k1_tiled_supported(B.max_S, B.max_R, J)) {
+        (void)J;
+        if (ctx->use_tiled) {
             CU(k1_tiled_launch(&B, ctx->num_sms, st, &launches, ctx->class_mask));
         } else {
             // generic kernel: pick the shared-memory plan

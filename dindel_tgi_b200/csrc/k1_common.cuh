@@ -15,6 +15,8 @@
 
 #define K1_HP_LUT 64     // homopolymer run-length codes 0 (default) .. 63 (>= 63, capped 0.99)
 #define K1_READ_CHUNK 16 // reads per work unit (window, hap, chunk)
+#define K1_TILED_SLOTS 8    // RO slots per shape class (columns per lane <= 8)
+#define K1_TILED_BUCKETS 48 // 6 shape classes x 8 slots
 
 struct K1Luts {
     // ObservationModelFB.cpp:232-234 by base phred (Read.hpp:143-148 conversion included)
@@ -48,7 +50,12 @@ struct K1Batch {
     const uint32_t *read_start;
     dindel_pair_out *pairs;
     int16_t *hpos;
-    unsigned long long *counter; // work-queue head
+    unsigned long long *counter; // work-queue heads (generic kernel: [0]; tiled kernel: one per class)
+    // tiled kernel: work units (window, hap, read chunk) bucketed by shape class and RO slot
+    // (k1_tiled_prepare); bucket b = class * K1_TILED_SLOTS + slot owns units[bucket_start[b] .. [b+1])
+    uint2 *units;
+    unsigned *bucket_start;      // [K1_TILED_BUCKETS + 1]
+    unsigned *bucket_work;       // [2 * K1_TILED_BUCKETS] counts, then fill cursors
     const K1Luts *luts;
     uint8_t *bt_scratch;         // generic kernel: per-warp back-pointer slots when smem is short
     long long bt_slot_bytes;

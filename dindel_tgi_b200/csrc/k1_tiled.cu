@@ -17,6 +17,7 @@
 //   * clamped duplicates of LO / RO can never be taken -> offered as -inf
 // Requires: sequence bytes in [A-Z=] (one-hot accept masks), forceReadOnHaplotype off; other
 // batches take the generic kernel (k1_generic.cu).
+#include <type_traits>
 #include "k1_common.cuh"
 #include "k1_tail.cuh"
 
@@ -27,7 +28,20 @@
 #ifndef K1_TILED_WPC
 #define K1_TILED_WPC 4 // warps per CTA
 #endif
+#ifndef K1_TILED_CRO_MAXC
+#define K1_TILED_CRO_MAXC 5
+#endif
 #define FULLMASK 0xffffffffu
+
+// call f(integral_constant<int, cro>) for the run-time value cro in [0, C)
+template <int C, int I = 0, class F>
+__device__ __forceinline__ void static_for_cro(int cro, F &f)
+{
+    if constexpr (I < C) {
+        if (cro == I) f(std::integral_constant<int, I>{});
+        else static_for_cro<C, I + 1>(cro, f);
+    }
+}
 
 template <int C, int J>
 struct TiledCfg {
@@ -128,7 +142,7 @@ __device__ __forceinline__ void scan_first_wins(const double (&v0)[C], const dou
 }
 
 template <int C, int J>
-__global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_kernel(K1Batch B, int Slo, int Shi)
+__global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_kernel(K1Batch B, int cls)
 {
     using Cfg = TiledCfg<C, J>;
     constexpr int U16 = Cfg::U16;
@@ -156,21 +170,22 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
                  lNoInsgIns = L->lNoInsgIns, lNoInsgNoIns = L->lNoInsgNoIns;
     const int c0 = lane * C;
 
+    // Units of this class, sorted by RO slot: the warps of the GPU walk the list together, so at
+    // any time (nearly) all of them run the same instantiation of the row loops (I-cache).
+    const unsigned u_begin = B.bucket_start[cls * K1_TILED_SLOTS];
+    const unsigned u_end = B.bucket_start[(cls + 1) * K1_TILED_SLOTS];
     for (;;) {
-        long long unit = 0;
-        if (lane == 0) unit = (long long)atomicAdd(B.counter, 1ULL);
-        unit = __shfl_sync(FULLMASK, unit, 0);
-        if (unit >= B.n_units) break;
-        const int w = k1_find_window(B.win_unit, B.n_windows, unit);
+        unsigned ui = 0;
+        if (lane == 0) ui = u_begin + (unsigned)atomicAdd(B.counter + 1 + cls, 1ULL);
+        ui = __shfl_sync(FULLMASK, ui, 0);
+        if (ui >= u_end) break;
+        const uint2 ud = B.units[ui];
+        const int w = (int)ud.x, h = (int)(ud.y >> 16), chunk = (int)(ud.y & 0xffffu);
         const int h0 = B.win_hap[w], nh = B.win_hap[w + 1] - h0;
         const int r0 = B.win_read[w], nr = B.win_read[w + 1] - r0;
-        const int nchunk = (nr + K1_READ_CHUNK - 1) / K1_READ_CHUNK;
-        const int local = (int)(unit - B.win_unit[w]);
-        const int h = local / nchunk, chunk = local - h * nchunk;
         const long long hoff = B.hap_off[h0 + h];
         const int H = (int)(B.hap_off[h0 + h + 1] - hoff);
         const int S = H + 2, RO = H + 1;
-        if (S <= Slo || S > Shi) continue; // another launch owns this shape class
         const uint8_t *hap = B.hap_seq + hoff;
         const uint8_t *hp = B.hap_hp + hoff + 2LL * (h0 + h);
         const uint32_t hapStart = B.hap_start[w];
@@ -217,6 +232,9 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
             const int lRO = RO / C, cRO = RO - lRO * C;
             const bool isLane0 = (lane == 0), isLaneRO = (lane == lRO);
 
+            // The row loops are instantiated once per RO slot (K1_TILED_CRO_MAXC: classes up to that
+            // many columns per lane), so RO's transitions are straight-line code inside the cells'
+            // basic block; wider classes test the slot at run time (CRO = -1).
             // =================== left half: rows 1..bMid (passMessageTwoDec) ===================
             // Per row: a window W*[k] of the previous row over columns c0-J .. c0+C-1 (own columns at
             // k = J+c, the J columns to the left fetched from the neighbour lanes), then the C cells'
@@ -239,6 +257,8 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
                 // lpe of the column left of this lane's first (RO's "from S+H" candidate, cpp:1805)
                 const double lpeLm1 = s_hp_lpe[hp[(c0 >= 1 && c0 - 1 <= RO) ? c0 - 1 : 0]];
 
+                auto left_rows = [&](auto cro_tag) {
+                constexpr int CRO = decltype(cro_tag)::value;
                 for (int b = 1; b <= bMid; b++) {
                     const double eq = sm_eq[b - 1], uq = sm_uq[b - 1];
                     const uint32_t rbit = 1u << (sm_ch[b - 1] & 31);
@@ -304,7 +324,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
                     // RO (cpp:1780-1782, 1804-1805)
 #pragma unroll
                     for (int c = 0; c < C; c++) {
-                        if (c == cRO) {
+                        if (CRO < 0 ? (c == cRO) : (c == CRO)) {
                             const double uH = WO[J + c - 1] + WP[J + c - 1];
                             double rv = (u[c] + lLOgLO) + lNoInsgNoIns;
                             uint32_t rcode = 0;
@@ -347,6 +367,9 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
                         row[k * 32 + lane] = (uint16_t)v;
                     }
                 }
+                }; // left_rows
+                if (C <= K1_TILED_CRO_MAXC) static_for_cro<C>(cRO, left_rows);
+                else left_rows(std::integral_constant<int, -1>{});
             }
             // alpha[bMid] + obs[bMid] (first add of cpp:1098) -> shared, by state column
             {
@@ -380,6 +403,8 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
                 }
                 const double lpnRO = s_hp_lpn[hp[RO]];
 
+                auto right_rows = [&](auto cro_tag) {
+                constexpr int CRO = decltype(cro_tag)::value;
                 for (int b = R - 1; b > bMid; b--) {
                     const double eq = sm_eq[b], uq = sm_uq[b];
                     const uint32_t rbit = 1u << (sm_ch[b] & 31);
@@ -444,7 +469,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
                     }
 #pragma unroll
                     for (int c = 0; c < C; c++) { // RO (cpp:1741-1742, 1750, 1764)
-                        if (c == cRO) {
+                        if (CRO < 0 ? (c == cRO) : (c == CRO)) {
                             double rv = uw[c] + lpnRO;
                             uint32_t rcode = 0;
                             if (t1[c] > rv + K1_EPS) { rv = t1[c]; rcode = J; }
@@ -489,6 +514,9 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
                         row[k * 32 + lane] = (uint16_t)v;
                     }
                 }
+                }; // right_rows
+                if (C <= K1_TILED_CRO_MAXC) static_for_cro<C>(cRO, right_rows);
+                else right_rows(std::integral_constant<int, -1>{});
             }
             __syncwarp();
             // =================== meeting row (cpp:1075-1144) ===================
@@ -546,8 +574,71 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
 // ------------------------------------------------------------------------------------------
 // host side: shape classes and launches
 // ------------------------------------------------------------------------------------------
+static const int kClassC[] = {2, 3, 4, 5, 6, 8};
+static const int kNumClass = 6;
+__constant__ int d_kClassC[6] = {2, 3, 4, 5, 6, 8};
+
+__device__ __forceinline__ int tiled_class_of_dev(int S)
+{
+#pragma unroll
+    for (int i = 0; i < 6; i++)
+        if (S <= 32 * d_kClassC[i]) return i;
+    return -1;
+}
+
+// Work-unit lists: count (pass 0) and fill (pass 1), one thread per window; in between one thread
+// turns the counts into bucket offsets.  A haplotype outside every class (S > 256) is never listed:
+// such batches take the generic kernel.
+__global__ void k1_tiled_units(K1Batch B, int pass)
+{
+    const int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= B.n_windows) return;
+    const int h0 = B.win_hap[w], nh = B.win_hap[w + 1] - h0;
+    const int nr = B.win_read[w + 1] - B.win_read[w];
+    const unsigned nchunk = (unsigned)((nr + K1_READ_CHUNK - 1) / K1_READ_CHUNK);
+    if (nchunk == 0) return;
+    for (int h = 0; h < nh; h++) {
+        const int H = (int)(B.hap_off[h0 + h + 1] - B.hap_off[h0 + h]);
+        const int cls = tiled_class_of_dev(H + 2);
+        if (cls < 0) continue;
+        const int bkt = cls * K1_TILED_SLOTS + (H + 1) % d_kClassC[cls];
+        if (pass == 0) {
+            atomicAdd(&B.bucket_work[bkt], nchunk);
+        } else {
+            const unsigned at = B.bucket_start[bkt] + atomicAdd(&B.bucket_work[K1_TILED_BUCKETS + bkt], nchunk);
+            for (unsigned ch = 0; ch < nchunk; ch++) B.units[at + ch] = make_uint2((unsigned)w, ((unsigned)h << 16) | ch);
+        }
+    }
+}
+__global__ void k1_tiled_units_scan(K1Batch B)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned acc = 0;
+    for (int b = 0; b < K1_TILED_BUCKETS; b++) {
+        B.bucket_start[b] = acc;
+        acc += B.bucket_work[b];
+        B.bucket_work[K1_TILED_BUCKETS + b] = 0;
+    }
+    B.bucket_start[K1_TILED_BUCKETS] = acc;
+}
+
+// Builds the bucketed unit lists of the resident batch (once per upload).  3 launches.
+extern "C" cudaError_t k1_tiled_prepare(const K1Batch *B, cudaStream_t st, int *launches)
+{
+    if (launches) *launches = 0;
+    if (B->n_windows <= 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(B->bucket_work, 0, sizeof(unsigned) * 2 * K1_TILED_BUCKETS, st);
+    if (e != cudaSuccess) return e;
+    const int threads = 128, blocks = (B->n_windows + threads - 1) / threads;
+    k1_tiled_units<<<blocks, threads, 0, st>>>(*B, 0);
+    k1_tiled_units_scan<<<1, 32, 0, st>>>(*B);
+    k1_tiled_units<<<blocks, threads, 0, st>>>(*B, 1);
+    if (launches) *launches = 3;
+    return cudaGetLastError();
+}
+
 template <int C, int J>
-static cudaError_t launch_one(const K1Batch *B, int num_sms, int Slo, int Shi, cudaStream_t st)
+static cudaError_t launch_one(const K1Batch *B, int num_sms, int cls, cudaStream_t st)
 {
     constexpr int U16 = TiledCfg<C, J>::U16;
     const int warps = K1_TILED_WPC;
@@ -562,12 +653,10 @@ static cudaError_t launch_one(const K1Batch *B, int num_sms, int Slo, int Shi, c
     long long need = (B->n_units + warps - 1) / warps;
     if (grid > need) grid = need;
     if (grid < 1) grid = 1;
-    k1_tiled_kernel<C, J><<<(int)grid, warps * 32, smem, st>>>(*B, Slo, Shi);
+    k1_tiled_kernel<C, J><<<(int)grid, warps * 32, smem, st>>>(*B, cls);
     return cudaGetLastError();
 }
 
-static const int kClassC[] = {2, 3, 4, 5, 6, 8};
-static const int kNumClass = 6;
 
 extern "C" int k1_tiled_supported(int maxS, int maxR, int J)
 {
@@ -590,16 +679,17 @@ extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream
     cudaError_t e = cudaSuccess;
     for (int i = 0; i < kNumClass && e == cudaSuccess; i++) {
         if (!(class_mask & (1u << i))) continue;
-        const int Slo = (i == 0) ? 0 : 32 * kClassC[i - 1], Shi = 32 * kClassC[i];
-        e = cudaMemsetAsync(B->counter, 0, sizeof(unsigned long long), st);
-        if (e != cudaSuccess) break;
+        if (n == 0) {
+            e = cudaMemsetAsync(B->counter, 0, 8 * sizeof(unsigned long long), st);
+            if (e != cudaSuccess) break;
+        }
         switch (kClassC[i]) {
-        case 2: e = launch_one<2, 6>(B, num_sms, Slo, Shi, st); break;
-        case 3: e = launch_one<3, 6>(B, num_sms, Slo, Shi, st); break;
-        case 4: e = launch_one<4, 6>(B, num_sms, Slo, Shi, st); break;
-        case 5: e = launch_one<5, 6>(B, num_sms, Slo, Shi, st); break;
-        case 6: e = launch_one<6, 6>(B, num_sms, Slo, Shi, st); break;
-        case 8: e = launch_one<8, 6>(B, num_sms, Slo, Shi, st); break;
+        case 2: e = launch_one<2, 6>(B, num_sms, i, st); break;
+        case 3: e = launch_one<3, 6>(B, num_sms, i, st); break;
+        case 4: e = launch_one<4, 6>(B, num_sms, i, st); break;
+        case 5: e = launch_one<5, 6>(B, num_sms, i, st); break;
+        case 6: e = launch_one<6, 6>(B, num_sms, i, st); break;
+        case 8: e = launch_one<8, 6>(B, num_sms, i, st); break;
         }
         n++;
     }
