@@ -31,11 +31,11 @@ extern "C" int k3_max_haps(void);
 // K0: homopolymer run-length code per state column of every haplotype
 // (ObservationModelFBMaxErr::setupTransitionProbs, ObservationModelFB.cpp:1678-1703: which
 // logProbError / logProbNoError entry gets which run length; the log() values are in K1Luts).
-__global__ void k0_hap_tables(int n_haps, const long long *hap_off, const uint8_t *hap_seq,
+__global__ void k0_hap_tables(int h_begin, int h_end, const long long *hap_off, const uint8_t *hap_seq,
                               uint8_t *hap_hp)
 {
-    int h = blockIdx.x * blockDim.x + threadIdx.x;
-    if (h >= n_haps) return;
+    int h = h_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (h >= h_end) return;
     long long off = hap_off[h];
     int H = (int)(hap_off[h + 1] - off);
     const uint8_t *seq = hap_seq + off;
@@ -57,13 +57,13 @@ __global__ void k0_hap_tables(int n_haps, const long long *hap_off, const uint8_
 
 // Per-window status (first failing pair in the reference's h-outer / r-inner loop order,
 // DInDel.cpp:1715-1737) and onHap[r] (DInDel.cpp:1720).  One warp per window.
-__global__ void k1_window_summary(int n_windows, const int32_t *win_hap, const int32_t *win_read,
+__global__ void k1_window_summary(int w_begin, int w_end, const int32_t *win_hap, const int32_t *win_read,
                                   const long long *win_pair, const dindel_pair_out *pairs,
                                   int32_t *win_status, uint8_t *read_on_hap)
 {
-    int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int w = w_begin + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     int lane = threadIdx.x & 31;
-    if (w >= n_windows) return;
+    if (w >= w_end) return;
     int h0 = win_hap[w], nh = win_hap[w + 1] - h0;
     int r0 = win_read[w], nr = win_read[w + 1] - r0;
     const dindel_pair_out *p = pairs + win_pair[w];
@@ -125,27 +125,69 @@ struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
+// pinned host array of long long
+struct HostBuf {
+    long long *p = nullptr;
+    size_t cap = 0;
+    bool assign(size_t n)
+    {
+        if (n > cap) {
+            if (p) cudaFreeHost(p);
+            p = nullptr; cap = 0;
+            size_t want = n + n / 8 + 16;
+            if (cudaHostAlloc((void **)&p, want * sizeof(long long), cudaHostAllocDefault) != cudaSuccess) {
+                cudaGetLastError();
+                return false;
+            }
+            cap = want;
+        }
+        memset(p, 0, n * sizeof(long long));
+        return true;
+    }
+    long long *data() { return p; }
+    long long &operator[](size_t i) { return p[i]; }
+    const long long &operator[](size_t i) const { return p[i]; }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+// One compute stream with its own work-queue state.  Lane 0 runs on the context's main stream (the
+// resident upload/run/download API); a pipelined submit alternates its chunks over both lanes so
+// that the tail of one chunk's kernels overlaps the head of the next.
+struct Lane {
+    cudaStream_t st = nullptr;
+    DevBuf d_counter, d_units, d_buckets, d_bt;
+};
+#define DINDEL_NUM_LANES 2
+
+// A contiguous window range of the resident batch with its slices of every CSR array.
+struct Range {
+    int w0, w1, h0, h1, r0, r1;
+    long long hb0, hb1, rb0, rb1, p0, p1, u0, u1;
+    bool use_tiled;
+    unsigned class_mask;
+};
+
 struct dindel_ctx {
     int device = 0, num_sms = 0;
     size_t smem_optin = 0;
     dindel_params params;
     K1Luts luts;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, s_in = nullptr, s_out = nullptr;
+    Lane lane[DINDEL_NUM_LANES];
     cudaEvent_t ev[6];
+    std::vector<cudaEvent_t> evpool; // per-chunk events of a pipelined submit
     std::string err;
-    DevBuf d_luts, d_counter, d_hap_start, d_win_hap, d_win_read, d_win_pair, d_win_unit, d_hap_off,
+    DevBuf d_luts, d_hap_start, d_win_hap, d_win_read, d_win_pair, d_win_unit, d_hap_off,
         d_hap_seq, d_hap_hp, d_read_off, d_read_seq, d_read_qual, d_read_mapq, d_read_start,
-        d_read_flags, d_pairs, d_hpos, d_win_status, d_on_hap, d_bt, d_units, d_buckets, d_x[8];
+        d_read_flags, d_pairs, d_hpos, d_win_status, d_on_hap, d_x[8];
     // resident batch
     bool resident = false, ran = false;
     K1Batch B;
-    std::vector<long long> win_pair, win_unit;
+    HostBuf win_pair, win_unit; // [n_windows+1] prefix sums (pinned: uploaded by async copies)
     std::vector<int> win_nh;
     dindel_timing timing;
-    int force_generic = 0;
-    unsigned class_mask = 0;   // shape classes (state columns per lane) present in the batch
-    bool alphabet_ok = true;   // every sequence byte in [A-Z=] (needed by the tiled kernel)
-    bool use_tiled = false;    // the resident batch runs on the register-tiled kernel
+    int force_generic = 0, force_chunks = 0, force_lanes = 0;
+    Range all;                 // the whole resident batch (resident API)
 };
 
 static int fail(dindel_ctx *c, int code, const std::string &msg)
@@ -280,6 +322,11 @@ int dindel_b200_create(const dindel_params *p, int device, dindel_ctx **out)
     cudaDeviceProp prop;
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking);
+    ctx->lane[0].st = ctx->stream;
+    for (int i = 1; i < DINDEL_NUM_LANES && e == cudaSuccess; i++)
+        e = cudaStreamCreateWithFlags(&ctx->lane[i].st, cudaStreamNonBlocking);
     for (int i = 0; i < 6 && e == cudaSuccess; i++) e = cudaEventCreate(&ctx->ev[i]);
     if (e != cudaSuccess) {
         delete ctx;
@@ -288,13 +335,21 @@ int dindel_b200_create(const dindel_params *p, int device, dindel_ctx **out)
     ctx->num_sms = prop.multiProcessorCount;
     ctx->smem_optin = prop.sharedMemPerBlockOptin;
     build_luts(*p, ctx->luts);
-    if (ctx->d_luts.ensure(sizeof(K1Luts)) != cudaSuccess || ctx->d_counter.ensure(64) != cudaSuccess ||
-        cudaMemcpy(ctx->d_luts.p, &ctx->luts, sizeof(K1Luts), cudaMemcpyHostToDevice) != cudaSuccess) {
+    bool ok = ctx->d_luts.ensure(sizeof(K1Luts)) == cudaSuccess &&
+              cudaMemcpy(ctx->d_luts.p, &ctx->luts, sizeof(K1Luts), cudaMemcpyHostToDevice) == cudaSuccess;
+    for (int i = 0; i < DINDEL_NUM_LANES && ok; i++)
+        ok = ctx->lane[i].d_counter.ensure(64) == cudaSuccess &&
+             ctx->lane[i].d_buckets.ensure(sizeof(unsigned) * (3 * K1_TILED_BUCKETS + 1)) == cudaSuccess;
+    if (!ok) {
         delete ctx;
         return DINDEL_E_CUDA;
     }
     const char *fg = getenv("DINDEL_B200_FORCE_GENERIC");
     ctx->force_generic = (fg && fg[0] == '1');
+    const char *fc = getenv("DINDEL_B200_CHUNKS"); // pipelined submit: number of chunks (0 = auto)
+    ctx->force_chunks = fc ? atoi(fc) : 0;
+    const char *fl = getenv("DINDEL_B200_LANES");
+    ctx->force_lanes = fl ? atoi(fl) : 0;
     memset(&ctx->timing, 0, sizeof(ctx->timing));
     *out = ctx;
     return DINDEL_OK;
@@ -304,15 +359,25 @@ int dindel_b200_destroy(dindel_ctx *ctx)
 {
     if (!ctx) return DINDEL_E_INVALID;
     cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
-    DevBuf *bufs[] = {&ctx->d_luts, &ctx->d_counter, &ctx->d_hap_start, &ctx->d_win_hap, &ctx->d_win_read,
+    cudaDeviceSynchronize();
+    DevBuf *bufs[] = {&ctx->d_luts, &ctx->d_hap_start, &ctx->d_win_hap, &ctx->d_win_read,
                       &ctx->d_win_pair, &ctx->d_win_unit, &ctx->d_hap_off, &ctx->d_hap_seq, &ctx->d_hap_hp,
                       &ctx->d_read_off, &ctx->d_read_seq, &ctx->d_read_qual, &ctx->d_read_mapq,
                       &ctx->d_read_start, &ctx->d_read_flags, &ctx->d_pairs, &ctx->d_hpos,
-                      &ctx->d_win_status, &ctx->d_on_hap, &ctx->d_bt, &ctx->d_units, &ctx->d_buckets};
+                      &ctx->d_win_status, &ctx->d_on_hap};
     for (DevBuf *b : bufs) b->release();
     for (int i = 0; i < 8; i++) ctx->d_x[i].release();
+    for (int i = 0; i < DINDEL_NUM_LANES; i++) {
+        Lane &ln = ctx->lane[i];
+        ln.d_counter.release(); ln.d_units.release(); ln.d_buckets.release(); ln.d_bt.release();
+        if (i > 0 && ln.st) cudaStreamDestroy(ln.st);
+    }
     for (int i = 0; i < 6; i++) cudaEventDestroy(ctx->ev[i]);
+    for (cudaEvent_t e : ctx->evpool) cudaEventDestroy(e);
+    ctx->win_pair.release();
+    ctx->win_unit.release();
+    cudaStreamDestroy(ctx->s_in);
+    cudaStreamDestroy(ctx->s_out);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return DINDEL_OK;
@@ -388,17 +453,19 @@ int dindel_b200_plan_shards(const dindel_batch_in *in, int n_shards, int32_t *fi
     return DINDEL_OK;
 }
 
-int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos)
+// ------------------------------------------------------------------------------------------
+// batch plumbing: host indexing + device allocation (prepare_batch), then per window range:
+// host scan (which kernel), H2D of the range's slices, prep kernels, K1 + summary, D2H.
+// ------------------------------------------------------------------------------------------
+static int prepare_batch(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos, int hstride_req)
 {
-    if (!ctx) return DINDEL_E_INVALID;
     if (validate(in) != DINDEL_OK) return fail(ctx, DINDEL_E_INVALID, "inconsistent batch");
     CU(cudaSetDevice(ctx->device));
     ctx->resident = false;
     ctx->ran = false;
     const int nw = in->n_windows, nh = in->n_haps, nr = in->n_reads;
-    // host-side indexing: pair / work-unit prefix sums, extreme shapes
-    ctx->win_pair.assign((size_t)nw + 1, 0);
-    ctx->win_unit.assign((size_t)nw + 1, 0);
+    if (!ctx->win_pair.assign((size_t)nw + 1) || !ctx->win_unit.assign((size_t)nw + 1))
+        return fail(ctx, DINDEL_E_NOMEM, "pinned host index arrays");
     ctx->win_nh.assign((size_t)nw, 0);
     for (int w = 0; w < nw; w++) {
         ctx->win_nh[w] = in->win_hap[w + 1] - in->win_hap[w];
@@ -407,74 +474,46 @@ int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos
         ctx->win_unit[w + 1] = ctx->win_unit[w] + a * ((b + K1_READ_CHUNK - 1) / K1_READ_CHUNK);
     }
     int maxH = 0, maxR = 0;
-    ctx->class_mask = 0;
     for (int h = 0; h < nh; h++) {
         long long l = in->hap_off[h + 1] - in->hap_off[h];
         if (l > 32000) return fail(ctx, DINDEL_E_UNSUPPORTED, "haplotype longer than 32000");
         if (l > maxH) maxH = (int)l;
-        unsigned cls = k1_tiled_class_of((int)l + 2);
-        if (cls < 32) ctx->class_mask |= 1u << cls;
-    }
-    {
-        // the tiled kernel encodes symbols as one-hot masks over (byte & 31): exact for [A-Z=]
-        bool ok[256];
-        for (int i = 0; i < 256; i++) ok[i] = (i >= 'A' && i <= 'Z') || i == '=';
-        unsigned bad = 0;
-        const unsigned char *hs = (const unsigned char *)in->hap_seq, *rs = (const unsigned char *)in->read_seq;
-        const long long hb = nh ? in->hap_off[nh] : 0, rbytes = nr ? in->read_off[nr] : 0;
-        for (long long i = 0; i < hb; i++) bad |= !ok[hs[i]];
-        for (long long i = 0; i < rbytes; i++) bad |= !ok[rs[i]];
-        ctx->alphabet_ok = (bad == 0);
     }
     for (int r = 0; r < nr; r++) {
         long long l = in->read_off[r + 1] - in->read_off[r];
         if (l > 32000) return fail(ctx, DINDEL_E_UNSUPPORTED, "read longer than 32000");
         if (l > maxR) maxR = (int)l;
     }
-    const long long n_pairs = ctx->win_pair[nw];
+    const long long n_pairs = ctx->win_pair[nw], n_units = ctx->win_unit[nw];
     const long long hap_bytes = nh ? in->hap_off[nh] : 0, read_bytes = nr ? in->read_off[nr] : 0;
     int hstride = 0;
-    if (want_hpos) hstride = (maxR + 7) & ~7;
-
-    cudaStream_t st = ctx->stream;
-    CU(cudaEventRecord(ctx->ev[0], st));
-#define UP(buf, src, bytes)                                                                \
-    do {                                                                                   \
-        CU(ctx->buf.ensure((size_t)(bytes) + 16));                                         \
-        if ((bytes) > 0) CU(cudaMemcpyAsync(ctx->buf.p, (src), (size_t)(bytes), cudaMemcpyHostToDevice, st)); \
-    } while (0)
-    UP(d_hap_start, in->hap_start, (size_t)nw * 4);
-    UP(d_win_hap, in->win_hap, ((size_t)nw + 1) * 4);
-    UP(d_win_read, in->win_read, ((size_t)nw + 1) * 4);
-    UP(d_win_pair, ctx->win_pair.data(), ((size_t)nw + 1) * 8);
-    UP(d_win_unit, ctx->win_unit.data(), ((size_t)nw + 1) * 8);
-    UP(d_hap_off, in->hap_off, ((size_t)nh + 1) * 8);
-    UP(d_hap_seq, in->hap_seq, hap_bytes);
-    UP(d_read_off, in->read_off, ((size_t)nr + 1) * 8);
-    UP(d_read_seq, in->read_seq, read_bytes);
-    UP(d_read_qual, in->read_qual, read_bytes);
-    UP(d_read_mapq, in->read_mapq, (size_t)nr);
-    UP(d_read_start, in->read_start, (size_t)nr * 4);
-    UP(d_read_flags, in->read_flags, (size_t)nr);
-#undef UP
+    if (want_hpos) {
+        hstride = hstride_req > 0 ? hstride_req : ((maxR + 7) & ~7);
+        if (hstride < maxR) return fail(ctx, DINDEL_E_INVALID, "hpos_stride shorter than the longest read");
+    }
+    CU(ctx->d_hap_start.ensure((size_t)nw * 4 + 16));
+    CU(ctx->d_win_hap.ensure(((size_t)nw + 1) * 4 + 16));
+    CU(ctx->d_win_read.ensure(((size_t)nw + 1) * 4 + 16));
+    CU(ctx->d_win_pair.ensure(((size_t)nw + 1) * 8 + 16));
+    CU(ctx->d_win_unit.ensure(((size_t)nw + 1) * 8 + 16));
+    CU(ctx->d_hap_off.ensure(((size_t)nh + 1) * 8 + 16));
+    CU(ctx->d_hap_seq.ensure((size_t)hap_bytes + 16));
+    CU(ctx->d_read_off.ensure(((size_t)nr + 1) * 8 + 16));
+    CU(ctx->d_read_seq.ensure((size_t)read_bytes + 16));
+    CU(ctx->d_read_qual.ensure((size_t)read_bytes + 16));
+    CU(ctx->d_read_mapq.ensure((size_t)nr + 16));
+    CU(ctx->d_read_start.ensure((size_t)nr * 4 + 16));
+    CU(ctx->d_read_flags.ensure((size_t)nr + 16));
     CU(ctx->d_hap_hp.ensure((size_t)hap_bytes + 2 * (size_t)nh + 16));
     CU(ctx->d_pairs.ensure((size_t)n_pairs * sizeof(dindel_pair_out) + 64));
     CU(ctx->d_win_status.ensure((size_t)nw * 4 + 16));
     CU(ctx->d_on_hap.ensure((size_t)nr + 16));
     if (want_hpos) CU(ctx->d_hpos.ensure((size_t)n_pairs * hstride * 2 + 16));
-    CU(cudaEventRecord(ctx->ev[1], st));
-    // prep: homopolymer codes per hap column
-    if (nh > 0) {
-        k0_hap_tables<<<(nh + 127) / 128, 128, 0, st>>>(nh, (const long long *)ctx->d_hap_off.p,
-                                                       (const uint8_t *)ctx->d_hap_seq.p,
-                                                       (uint8_t *)ctx->d_hap_hp.p);
-        CU(cudaGetLastError());
-    }
 
     K1Batch &B = ctx->B;
     memset(&B, 0, sizeof(B));
     B.n_windows = nw; B.n_haps = nh; B.n_reads = nr; B.hpos_stride = hstride;
-    B.n_units = ctx->win_unit[nw]; B.n_pairs = n_pairs;
+    B.n_units = n_units; B.n_pairs = n_pairs;
     B.hap_start = (const uint32_t *)ctx->d_hap_start.p;
     B.win_hap = (const int32_t *)ctx->d_win_hap.p;
     B.win_read = (const int32_t *)ctx->d_win_read.p;
@@ -491,30 +530,227 @@ int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos
     B.read_start = (const uint32_t *)ctx->d_read_start.p;
     B.pairs = (dindel_pair_out *)ctx->d_pairs.p;
     B.hpos = want_hpos ? (int16_t *)ctx->d_hpos.p : nullptr;
-    B.counter = (unsigned long long *)ctx->d_counter.p;
     B.luts = (const K1Luts *)ctx->d_luts.p;
     B.max_R = maxR > 0 ? maxR : 1;
     B.max_S = maxH + 2;
+    memset(&ctx->timing, 0, sizeof(ctx->timing));
     ctx->timing.n_pairs = n_pairs;
-    ctx->timing.n_cells = dindel_b200_count_cells(in);
-    ctx->timing.prep_launches = nh > 0 ? 1 : 0;
-    // work-unit lists of the tiled kernel (bucketed by shape class and RO slot)
-    ctx->use_tiled = !ctx->force_generic && ctx->alphabet_ok && !ctx->luts.force &&
-                     k1_tiled_supported(B.max_S, B.max_R, ctx->luts.numT - 1);
-    for (int w = 0; w < nw && ctx->use_tiled; w++) // unit descriptors hold hap and chunk in 16 bits each
-        if (ctx->win_nh[w] > 65535 || (in->win_read[w + 1] - in->win_read[w]) / K1_READ_CHUNK >= 65535 ||
-            B.n_units >= 0xffffffffLL)
-            ctx->use_tiled = false;
-    if (ctx->use_tiled && B.n_units > 0) {
-        CU(ctx->d_units.ensure((size_t)B.n_units * sizeof(uint2) + 16));
-        CU(ctx->d_buckets.ensure(sizeof(unsigned) * (3 * K1_TILED_BUCKETS + 1)));
-        B.units = (uint2 *)ctx->d_units.p;
-        B.bucket_start = (unsigned *)ctx->d_buckets.p;
-        B.bucket_work = B.bucket_start + K1_TILED_BUCKETS + 1;
-        int pl = 0;
-        CU(k1_tiled_prepare(&B, st, &pl));
-        ctx->timing.prep_launches += pl;
+    long long cells = 0;
+    for (int w = 0; w < nw; w++) {
+        int h0 = in->win_hap[w], h1 = in->win_hap[w + 1], r0 = in->win_read[w], r1 = in->win_read[w + 1];
+        cells += ((in->hap_off[h1] - in->hap_off[h0]) + 2LL * (h1 - h0)) * (in->read_off[r1] - in->read_off[r0]);
     }
+    ctx->timing.n_cells = cells;
+    return DINDEL_OK;
+}
+
+// any byte outside [A-Z=] ?  (branch-free so that the host compiler vectorises it)
+static unsigned outside_alphabet(const unsigned char *p, long long n)
+{
+    unsigned char bad = 0;
+    for (long long i = 0; i < n; i++) {
+        const unsigned char c = p[i];
+        bad |= (unsigned char)(((unsigned char)(c - 'A') > 25) & (c != '='));
+    }
+    return bad;
+}
+
+// Slices of the CSR arrays that windows [w0, w1) own, and which kernel the range takes: the
+// register-tiled kernel needs every sequence byte in [A-Z=] (one-hot symbol masks), unit
+// descriptors that fit 16+16 bits, and a shape inside its classes.
+static void scan_range(dindel_ctx *ctx, const dindel_batch_in *in, int w0, int w1, Range &g)
+{
+    g.w0 = w0; g.w1 = w1;
+    g.h0 = in->win_hap[w0]; g.h1 = in->win_hap[w1];
+    g.r0 = in->win_read[w0]; g.r1 = in->win_read[w1];
+    g.hb0 = in->n_haps ? in->hap_off[g.h0] : 0; g.hb1 = in->n_haps ? in->hap_off[g.h1] : 0;
+    g.rb0 = in->n_reads ? in->read_off[g.r0] : 0; g.rb1 = in->n_reads ? in->read_off[g.r1] : 0;
+    g.p0 = ctx->win_pair[w0]; g.p1 = ctx->win_pair[w1];
+    g.u0 = ctx->win_unit[w0]; g.u1 = ctx->win_unit[w1];
+    g.class_mask = 0;
+    for (int h = g.h0; h < g.h1; h++) {
+        unsigned cls = k1_tiled_class_of((int)(in->hap_off[h + 1] - in->hap_off[h]) + 2);
+        if (cls < 32) g.class_mask |= 1u << cls;
+    }
+    const unsigned char *hs = (const unsigned char *)in->hap_seq, *rs = (const unsigned char *)in->read_seq;
+    const unsigned bad = outside_alphabet(hs + g.hb0, g.hb1 - g.hb0) | outside_alphabet(rs + g.rb0, g.rb1 - g.rb0);
+    g.use_tiled = !ctx->force_generic && bad == 0 && !ctx->luts.force &&
+                  k1_tiled_supported(ctx->B.max_S, ctx->B.max_R, ctx->luts.numT - 1) &&
+                  (g.u1 - g.u0) < 0xffffffffLL;
+    for (int w = w0; w < w1 && g.use_tiled; w++)
+        if (ctx->win_nh[w] > 65535 || (in->win_read[w + 1] - in->win_read[w]) / K1_READ_CHUNK >= 65535)
+            g.use_tiled = false;
+}
+
+static int copy_in_range(dindel_ctx *ctx, const dindel_batch_in *in, const Range &g, cudaStream_t st)
+{
+#define UPR(buf, src, first, count, esz)                                                        \
+    do {                                                                                        \
+        if ((count) > 0)                                                                        \
+            CU(cudaMemcpyAsync((char *)ctx->buf.p + (size_t)(first) * (esz),                    \
+                               (const char *)(src) + (size_t)(first) * (esz),                   \
+                               (size_t)(count) * (esz), cudaMemcpyHostToDevice, st));           \
+    } while (0)
+    const int nwr = g.w1 - g.w0, nhr = g.h1 - g.h0, nrr = g.r1 - g.r0;
+    if (nwr <= 0) return DINDEL_OK;
+    UPR(d_hap_start, in->hap_start, g.w0, nwr, 4);
+    UPR(d_win_hap, in->win_hap, g.w0, nwr + 1, 4);
+    UPR(d_win_read, in->win_read, g.w0, nwr + 1, 4);
+    UPR(d_win_pair, ctx->win_pair.data(), g.w0, nwr + 1, 8);
+    UPR(d_win_unit, ctx->win_unit.data(), g.w0, nwr + 1, 8);
+    UPR(d_hap_off, in->hap_off, g.h0, nhr + 1, 8);
+    UPR(d_hap_seq, in->hap_seq, g.hb0, g.hb1 - g.hb0, 1);
+    UPR(d_read_off, in->read_off, g.r0, nrr + 1, 8);
+    UPR(d_read_seq, in->read_seq, g.rb0, g.rb1 - g.rb0, 1);
+    UPR(d_read_qual, in->read_qual, g.rb0, g.rb1 - g.rb0, 1);
+    UPR(d_read_mapq, in->read_mapq, g.r0, nrr, 1);
+    UPR(d_read_start, in->read_start, g.r0, nrr, 4);
+    UPR(d_read_flags, in->read_flags, g.r0, nrr, 1);
+#undef UPR
+    return DINDEL_OK;
+}
+
+// K1Batch of one range on one lane (work-queue state of that lane).
+static K1Batch range_batch(dindel_ctx *ctx, const Range &g, Lane &ln)
+{
+    K1Batch b = ctx->B;
+    b.w_begin = g.w0; b.w_end = g.w1;
+    b.unit_begin = g.u0; b.unit_end = g.u1;
+    b.counter = (unsigned long long *)ln.d_counter.p;
+    b.units = (uint2 *)ln.d_units.p;
+    b.bucket_start = (unsigned *)ln.d_buckets.p;
+    b.bucket_work = b.bucket_start + K1_TILED_BUCKETS + 1;
+    return b;
+}
+
+// lane buffers large enough for any range of up to max_units work units
+static int ensure_lane(dindel_ctx *ctx, Lane &ln, long long max_units)
+{
+    CU(ln.d_units.ensure((size_t)max_units * sizeof(uint2) + 16));
+    return DINDEL_OK;
+}
+
+// prep kernels of a range: homopolymer codes per hap column (K0) and, for the tiled kernel, the
+// bucketed work-unit lists
+static int prep_range(dindel_ctx *ctx, const Range &g, Lane &ln, int *launches)
+{
+    cudaStream_t st = ln.st;
+    const int nhr = g.h1 - g.h0;
+    if (nhr > 0) {
+        k0_hap_tables<<<(nhr + 127) / 128, 128, 0, st>>>(g.h0, g.h1, ctx->B.hap_off, ctx->B.hap_seq,
+                                                         (uint8_t *)ctx->d_hap_hp.p);
+        CU(cudaGetLastError());
+        (*launches)++;
+    }
+    if (g.use_tiled && g.u1 > g.u0) {
+        K1Batch b = range_batch(ctx, g, ln);
+        int pl = 0;
+        CU(k1_tiled_prepare(&b, st, &pl));
+        *launches += pl;
+    }
+    return DINDEL_OK;
+}
+
+// K1 over a range + per-window status / onHap
+static int k1_range(dindel_ctx *ctx, const Range &g, Lane &ln, int *launches)
+{
+    cudaStream_t st = ln.st;
+    K1Batch b = range_batch(ctx, g, ln);
+    if (g.u1 > g.u0) {
+        if (g.use_tiled) {
+            int n = 0;
+            CU(k1_tiled_launch(&b, ctx->num_sms, st, &n, g.class_mask));
+            *launches += n;
+        } else {
+            // generic kernel: pick the shared-memory plan
+            const size_t budget = ctx->smem_optin;
+            int bt_in_smem = 1, warps = 4;
+            size_t pw = k1_generic_smem_per_warp(b.max_S, b.max_R, 1);
+            while (warps > 1 && pw * warps > budget) warps >>= 1;
+            if (pw * warps > budget) {
+                bt_in_smem = 0;
+                warps = 4;
+                pw = k1_generic_smem_per_warp(b.max_S, b.max_R, 0);
+                while (warps > 1 && pw * warps > budget) warps >>= 1;
+                if (pw * warps > budget) return fail(ctx, DINDEL_E_UNSUPPORTED, "shape exceeds shared memory");
+            }
+            size_t smem = pw * warps;
+            int ctas_per_sm = (int)((size_t)(228 * 1024 - 1024) / (smem + 1024));
+            if (ctas_per_sm < 1) ctas_per_sm = 1;
+            if (ctas_per_sm * warps > 32) ctas_per_sm = 32 / warps;
+            int grid = ctx->num_sms * ctas_per_sm;
+            long long need = (g.u1 - g.u0 + warps - 1) / warps;
+            if (grid > need) grid = (int)need;
+            if (!bt_in_smem) {
+                b.bt_slot_bytes = (((long long)b.max_S * b.max_R) + 255) & ~255LL;
+                // allocated at full-grid size up front, so a later range never reallocates it
+                CU(ln.d_bt.ensure((size_t)b.bt_slot_bytes * ctx->num_sms * ctas_per_sm * warps));
+                b.bt_scratch = (uint8_t *)ln.d_bt.p;
+            }
+            CU(cudaMemsetAsync(b.counter, 0, 64, st));
+            CU(k1_generic_launch(&b, grid, warps, bt_in_smem, smem, st));
+            (*launches)++;
+        }
+    }
+    if (g.w1 > g.w0) {
+        int threads = 128, wpb = threads / 32;
+        k1_window_summary<<<(g.w1 - g.w0 + wpb - 1) / wpb, threads, 0, st>>>(
+            g.w0, g.w1, b.win_hap, b.win_read, b.win_pair, b.pairs, (int32_t *)ctx->d_win_status.p,
+            (uint8_t *)ctx->d_on_hap.p);
+        CU(cudaGetLastError());
+        (*launches)++;
+    }
+    return DINDEL_OK;
+}
+
+static int copy_out_range(dindel_ctx *ctx, dindel_batch_out *out, const Range &g, cudaStream_t st)
+{
+    const K1Batch &B = ctx->B;
+    const long long np = g.p1 - g.p0;
+    if (np > 0)
+        CU(cudaMemcpyAsync(out->pairs + g.p0, B.pairs + g.p0, (size_t)np * sizeof(dindel_pair_out),
+                           cudaMemcpyDeviceToHost, st));
+    if (out->hpos && np > 0)
+        CU(cudaMemcpyAsync(out->hpos + g.p0 * B.hpos_stride, B.hpos + g.p0 * B.hpos_stride,
+                           (size_t)np * B.hpos_stride * 2, cudaMemcpyDeviceToHost, st));
+    if (out->win_status && g.w1 > g.w0)
+        CU(cudaMemcpyAsync(out->win_status + g.w0, (int32_t *)ctx->d_win_status.p + g.w0,
+                           (size_t)(g.w1 - g.w0) * 4, cudaMemcpyDeviceToHost, st));
+    if (out->read_on_hap && g.r1 > g.r0)
+        CU(cudaMemcpyAsync(out->read_on_hap + g.r0, (uint8_t *)ctx->d_on_hap.p + g.r0, (size_t)(g.r1 - g.r0),
+                           cudaMemcpyDeviceToHost, st));
+    return DINDEL_OK;
+}
+
+static int check_out(dindel_ctx *ctx, dindel_batch_out *out)
+{
+    const K1Batch &B = ctx->B;
+    if (!out) return fail(ctx, DINDEL_E_INVALID, "null out");
+    if (out->n_pairs < B.n_pairs || (B.n_pairs > 0 && !out->pairs))
+        return fail(ctx, DINDEL_E_INVALID, "pairs[] too small");
+    if (out->hpos && (!B.hpos || out->hpos_stride != B.hpos_stride))
+        return fail(ctx, DINDEL_E_INVALID, "hpos requested but batch uploaded without it (or stride mismatch)");
+    return DINDEL_OK;
+}
+
+int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos)
+{
+    if (!ctx) return DINDEL_E_INVALID;
+    int rc = prepare_batch(ctx, in, want_hpos, 0);
+    if (rc != DINDEL_OK) return rc;
+    Lane &ln = ctx->lane[0];
+    cudaStream_t st = ln.st;
+    scan_range(ctx, in, 0, in->n_windows, ctx->all);
+    rc = ensure_lane(ctx, ln, ctx->B.n_units);
+    if (rc != DINDEL_OK) return rc;
+    CU(cudaEventRecord(ctx->ev[0], st));
+    rc = copy_in_range(ctx, in, ctx->all, st);
+    if (rc != DINDEL_OK) return rc;
+    CU(cudaEventRecord(ctx->ev[1], st));
+    int pl = 0;
+    rc = prep_range(ctx, ctx->all, ln, &pl);
+    if (rc != DINDEL_OK) return rc;
+    ctx->timing.prep_launches = pl;
     CU(cudaEventRecord(ctx->ev[2], st));
     ctx->resident = true;
     return DINDEL_OK;
@@ -524,54 +760,12 @@ int dindel_b200_run(dindel_ctx *ctx)
 {
     if (!ctx || !ctx->resident) return fail(ctx, DINDEL_E_INVALID, "no resident batch (call upload first)");
     CU(cudaSetDevice(ctx->device));
-    cudaStream_t st = ctx->stream;
-    K1Batch &B = ctx->B;
-    CU(cudaEventRecord(ctx->ev[3], st));
+    Lane &ln = ctx->lane[0];
+    CU(cudaEventRecord(ctx->ev[3], ln.st));
     int launches = 0;
-    if (B.n_units > 0) {
-        const int J = ctx->luts.numT - 1;
-        (void)J;
-        if (ctx->use_tiled) {
-            CU(k1_tiled_launch(&B, ctx->num_sms, st, &launches, ctx->class_mask));
-        } else {
-            // generic kernel: pick the shared-memory plan
-            const size_t budget = ctx->smem_optin;
-            int bt_in_smem = 1, warps = 4;
-            size_t pw = k1_generic_smem_per_warp(B.max_S, B.max_R, 1);
-            while (warps > 1 && pw * warps > budget) warps >>= 1;
-            if (pw * warps > budget) {
-                bt_in_smem = 0;
-                warps = 4;
-                pw = k1_generic_smem_per_warp(B.max_S, B.max_R, 0);
-                while (warps > 1 && pw * warps > budget) warps >>= 1;
-                if (pw * warps > budget) return fail(ctx, DINDEL_E_UNSUPPORTED, "shape exceeds shared memory");
-            }
-            size_t smem = pw * warps;
-            int ctas_per_sm = (int)((size_t)(228 * 1024 - 1024) / (smem + 1024));
-            if (ctas_per_sm < 1) ctas_per_sm = 1;
-            if (ctas_per_sm * warps > 32) ctas_per_sm = 32 / warps;
-            int grid = ctx->num_sms * ctas_per_sm;
-            long long need = (B.n_units + warps - 1) / warps;
-            if (grid > need) grid = (int)need;
-            if (!bt_in_smem) {
-                B.bt_slot_bytes = (((long long)B.max_S * B.max_R) + 255) & ~255LL;
-                CU(ctx->d_bt.ensure((size_t)B.bt_slot_bytes * grid * warps));
-                B.bt_scratch = (uint8_t *)ctx->d_bt.p;
-            }
-            CU(cudaMemsetAsync(B.counter, 0, 64, st));
-            CU(k1_generic_launch(&B, grid, warps, bt_in_smem, smem, st));
-            launches = 1;
-        }
-    }
-    if (B.n_windows > 0) {
-        int threads = 128, wpb = threads / 32;
-        k1_window_summary<<<(B.n_windows + wpb - 1) / wpb, threads, 0, st>>>(
-            B.n_windows, B.win_hap, B.win_read, B.win_pair, B.pairs, (int32_t *)ctx->d_win_status.p,
-            (uint8_t *)ctx->d_on_hap.p);
-        CU(cudaGetLastError());
-        launches++;
-    }
-    CU(cudaEventRecord(ctx->ev[4], st));
+    int rc = k1_range(ctx, ctx->all, ln, &launches);
+    if (rc != DINDEL_OK) return rc;
+    CU(cudaEventRecord(ctx->ev[4], ln.st));
     ctx->timing.k1_launches = launches;
     ctx->ran = true;
     return DINDEL_OK;
@@ -580,26 +774,15 @@ int dindel_b200_run(dindel_ctx *ctx)
 int dindel_b200_download(dindel_ctx *ctx, dindel_batch_out *out)
 {
     if (!ctx || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "nothing to download");
-    if (!out) return fail(ctx, DINDEL_E_INVALID, "null out");
+    int rc = check_out(ctx, out);
+    if (rc != DINDEL_OK) return rc;
     CU(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
-    K1Batch &B = ctx->B;
-    if (out->n_pairs < B.n_pairs || (B.n_pairs > 0 && !out->pairs))
-        return fail(ctx, DINDEL_E_INVALID, "pairs[] too small");
-    if (out->hpos && (!B.hpos || out->hpos_stride != B.hpos_stride))
-        return fail(ctx, DINDEL_E_INVALID, "hpos requested but batch uploaded without it (or stride mismatch)");
-    if (B.n_pairs > 0)
-        CU(cudaMemcpyAsync(out->pairs, B.pairs, (size_t)B.n_pairs * sizeof(dindel_pair_out),
-                           cudaMemcpyDeviceToHost, st));
-    if (out->hpos && B.n_pairs > 0)
-        CU(cudaMemcpyAsync(out->hpos, B.hpos, (size_t)B.n_pairs * B.hpos_stride * 2, cudaMemcpyDeviceToHost, st));
-    if (out->win_status && B.n_windows > 0)
-        CU(cudaMemcpyAsync(out->win_status, ctx->d_win_status.p, (size_t)B.n_windows * 4, cudaMemcpyDeviceToHost, st));
-    if (out->read_on_hap && B.n_reads > 0)
-        CU(cudaMemcpyAsync(out->read_on_hap, ctx->d_on_hap.p, (size_t)B.n_reads, cudaMemcpyDeviceToHost, st));
+    rc = copy_out_range(ctx, out, ctx->all, st);
+    if (rc != DINDEL_OK) return rc;
     CU(cudaEventRecord(ctx->ev[5], st));
     CU(cudaStreamSynchronize(st));
-    if (out->win_pair) memcpy(out->win_pair, ctx->win_pair.data(), ((size_t)B.n_windows + 1) * 8);
+    if (out->win_pair) memcpy(out->win_pair, ctx->win_pair.data(), ((size_t)ctx->B.n_windows + 1) * 8);
     dindel_timing &t = ctx->timing;
     cudaEventElapsedTime(&t.h2d_ms, ctx->ev[0], ctx->ev[1]);
     cudaEventElapsedTime(&t.prep_ms, ctx->ev[1], ctx->ev[2]);
@@ -611,21 +794,104 @@ int dindel_b200_download(dindel_ctx *ctx, dindel_batch_out *out)
 
 int dindel_b200_hpos_stride(const dindel_ctx *ctx) { return ctx && ctx->resident ? ctx->B.hpos_stride : 0; }
 
+// computeLikelihoods for a whole batch, host buffers in and out, as a pipeline over chunks of
+// windows (cost-balanced contiguous ranges): chunk c+1's H2D copies (stream s_in) run under
+// chunk c's kernels (compute lanes, alternating) and chunk c-1's D2H copies (stream s_out).
+// With pinned host buffers (dindel_b200_alloc_pinned) the copies are truly asynchronous.
 int dindel_b200_submit(dindel_ctx *ctx, const dindel_batch_in *in, dindel_batch_out *out)
 {
     if (!ctx || !out) return DINDEL_E_INVALID;
-    int rc = dindel_b200_upload(ctx, in, out->hpos != nullptr);
+    int rc = prepare_batch(ctx, in, out->hpos != nullptr, out->hpos ? out->hpos_stride : 0);
     if (rc != DINDEL_OK) return rc;
-    if (out->hpos) {
-        if (out->hpos_stride < ctx->B.max_R) return fail(ctx, DINDEL_E_INVALID, "hpos_stride shorter than the longest read");
-        // device rows use the caller's stride so one copy brings them back
-        ctx->B.hpos_stride = out->hpos_stride;
-        CU(ctx->d_hpos.ensure((size_t)ctx->B.n_pairs * out->hpos_stride * 2 + 16));
-        ctx->B.hpos = (int16_t *)ctx->d_hpos.p;
+    rc = check_out(ctx, out);
+    if (rc != DINDEL_OK) return rc;
+    const int nw = in->n_windows;
+    // chunk plan: about 8e9 cells (~30 ms of K1) per chunk, at most 64 chunks
+    int n_chunks = ctx->force_chunks > 0 ? ctx->force_chunks : (int)(ctx->timing.n_cells / 8000000000LL);
+    if (n_chunks > 64) n_chunks = 64;
+    if (n_chunks > nw) n_chunks = nw;
+    if (n_chunks < 1) n_chunks = 1;
+    std::vector<int32_t> bounds((size_t)n_chunks + 1, 0);
+    if (dindel_b200_plan_shards(in, n_chunks, bounds.data()) != DINDEL_OK)
+        return fail(ctx, DINDEL_E_INVALID, "chunk plan");
+    long long max_units = 0;
+    for (int c = 0; c < n_chunks; c++) {
+        long long u = ctx->win_unit[bounds[c + 1]] - ctx->win_unit[bounds[c]];
+        if (u > max_units) max_units = u;
     }
-    rc = dindel_b200_run(ctx);
+    int n_lanes = n_chunks > 1 ? DINDEL_NUM_LANES : 1;
+    if (ctx->force_lanes >= 1 && ctx->force_lanes < n_lanes) n_lanes = ctx->force_lanes;
+    for (int i = 0; i < n_lanes; i++) {
+        rc = ensure_lane(ctx, ctx->lane[i], max_units);
+        if (rc != DINDEL_OK) return rc;
+    }
+    while ((int)ctx->evpool.size() < 4 * n_chunks) {
+        cudaEvent_t e;
+        CU(cudaEventCreate(&e));
+        ctx->evpool.push_back(e);
+    }
+    cudaStream_t s_in = n_chunks > 1 ? ctx->s_in : ctx->stream;
+    cudaStream_t s_out = n_chunks > 1 ? ctx->s_out : ctx->stream;
+    CU(cudaEventRecord(ctx->ev[0], s_in));
+    int launches = 0, prep_launches = 0;
+    std::vector<Range> rg((size_t)n_chunks);
+    for (int c = 0; c < n_chunks; c++) {
+        Range &g = rg[c];
+        Lane &ln = ctx->lane[c % n_lanes];
+        cudaEvent_t e_in = ctx->evpool[4 * c], e_k0 = ctx->evpool[4 * c + 1], e_k1 = ctx->evpool[4 * c + 2];
+        scan_range(ctx, in, bounds[c], bounds[c + 1], g); // host work, overlaps the GPU's earlier chunks
+        rc = copy_in_range(ctx, in, g, s_in);
+        if (rc != DINDEL_OK) return rc;
+        CU(cudaEventRecord(e_in, s_in));
+        CU(cudaStreamWaitEvent(ln.st, e_in, 0));
+        CU(cudaEventRecord(e_k0, ln.st));
+        rc = prep_range(ctx, g, ln, &prep_launches);
+        if (rc == DINDEL_OK) rc = k1_range(ctx, g, ln, &launches);
+        if (rc != DINDEL_OK) return rc;
+        CU(cudaEventRecord(e_k1, ln.st));
+        CU(cudaStreamWaitEvent(s_out, e_k1, 0));
+        rc = copy_out_range(ctx, out, g, s_out);
+        if (rc != DINDEL_OK) return rc;
+    }
+    CU(cudaEventRecord(ctx->ev[5], s_out));
+    CU(cudaStreamSynchronize(s_out));
+    for (int i = 0; i < n_lanes; i++) CU(cudaStreamSynchronize(ctx->lane[i].st));
+    CU(cudaStreamSynchronize(s_in));
+    if (out->win_pair) memcpy(out->win_pair, ctx->win_pair.data(), ((size_t)nw + 1) * 8);
+    dindel_timing &t = ctx->timing;
+    t.k1_ms = 0.f;
+    for (int c = 0; c < n_chunks; c++) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, ctx->evpool[4 * c + 1], ctx->evpool[4 * c + 2]);
+        t.k1_ms += ms; // sum of the chunks' kernel spans (spans of the two lanes overlap)
+    }
+    cudaEventElapsedTime(&t.total_ms, ctx->ev[0], ctx->ev[5]);
+    t.h2d_ms = t.prep_ms = t.d2h_ms = 0.f; // overlapped: not separable in a pipelined submit
+    t.k1_launches = launches;
+    t.prep_launches = prep_launches;
+    // the batch stays resident for K2 / K3 and for run()/download()
+    ctx->all = rg[0];
+    for (int c = 1; c < n_chunks; c++) {
+        ctx->all.use_tiled = ctx->all.use_tiled && rg[c].use_tiled;
+        ctx->all.class_mask |= rg[c].class_mask;
+    }
+    {
+        const Range &z = rg[n_chunks - 1];
+        ctx->all.w1 = z.w1; ctx->all.h1 = z.h1; ctx->all.r1 = z.r1; ctx->all.hb1 = z.hb1; ctx->all.rb1 = z.rb1;
+        ctx->all.p1 = z.p1; ctx->all.u1 = z.u1;
+        if (ctx->all.u1 - ctx->all.u0 >= 0xffffffffLL) ctx->all.use_tiled = false;
+    }
+    rc = ensure_lane(ctx, ctx->lane[0], ctx->B.n_units);
     if (rc != DINDEL_OK) return rc;
-    return dindel_b200_download(ctx, out);
+    if (n_chunks > 1 && ctx->all.use_tiled) { // run() on the whole batch needs whole-batch unit lists
+        int pl = 0;
+        rc = prep_range(ctx, ctx->all, ctx->lane[0], &pl);
+        if (rc != DINDEL_OK) return rc;
+        CU(cudaStreamSynchronize(ctx->lane[0].st));
+    }
+    ctx->resident = true;
+    ctx->ran = true;
+    return DINDEL_OK;
 }
 
 int dindel_b200_sync(dindel_ctx *ctx)
@@ -634,7 +900,9 @@ int dindel_b200_sync(dindel_ctx *ctx)
     CU(cudaSetDevice(ctx->device));
     CU(cudaStreamSynchronize(ctx->stream));
     if (ctx->ran) {
-        cudaEventElapsedTime(&ctx->timing.k1_ms, ctx->ev[3], ctx->ev[4]);
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ctx->ev[3], ctx->ev[4]) == cudaSuccess) ctx->timing.k1_ms = ms;
+        else cudaGetLastError();
     }
     return DINDEL_OK;
 }
@@ -749,7 +1017,7 @@ int dindel_b200_measure_fp64_peak(dindel_ctx *ctx, double *dadd_per_s)
     double best = 0.0;
     for (int rep = 0; rep < 4; rep++) {
         CU(cudaEventRecord(ctx->ev[0], st));
-        fp64_peak_kernel<<<blocks, threads, 0, st>>>((double *)ctx->d_counter.p + 1, 1.0 + rep, iters);
+        fp64_peak_kernel<<<blocks, threads, 0, st>>>((double *)ctx->lane[0].d_counter.p + 7, 1.0 + rep, iters);
         CU(cudaGetLastError());
         CU(cudaEventRecord(ctx->ev[1], st));
         CU(cudaStreamSynchronize(st));

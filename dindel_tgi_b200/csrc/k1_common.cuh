@@ -14,7 +14,9 @@
 #include "../../include/dindel_b200.h"
 
 #define K1_HP_LUT 64     // homopolymer run-length codes 0 (default) .. 63 (>= 63, capped 0.99)
-#define K1_READ_CHUNK 16 // reads per work unit (window, hap, chunk)
+#ifndef K1_READ_CHUNK
+#define K1_READ_CHUNK 4 // reads per work unit (window, hap, chunk): small units keep launch tails short
+#endif
 #define K1_TILED_SLOTS 8    // RO slots per shape class (columns per lane <= 8)
 #define K1_TILED_BUCKETS 48 // 6 shape classes x 8 slots
 
@@ -39,6 +41,9 @@ struct K1Luts {
 struct K1Batch {
     int32_t n_windows, n_haps, n_reads, hpos_stride;
     long long n_units, n_pairs;
+    // the window range this launch set works on (a whole batch, or one chunk of a pipelined submit)
+    int32_t w_begin, w_end;
+    long long unit_begin, unit_end; // generic kernel: units of that range (win_unit numbering)
     const uint32_t *hap_start;
     const int32_t *win_hap, *win_read;
     const long long *win_pair, *win_unit;

@@ -89,9 +89,9 @@ __global__ void __launch_bounds__(128) k1_generic_kernel(K1Batch B, int bt_in_sm
 
     for (;;) {
         long long unit = 0;
-        if (lane == 0) unit = (long long)atomicAdd(B.counter, 1ULL);
+        if (lane == 0) unit = B.unit_begin + (long long)atomicAdd(B.counter, 1ULL);
         unit = __shfl_sync(0xffffffffu, unit, 0);
-        if (unit >= B.n_units) break;
+        if (unit >= B.unit_end) break;
         const int w = k1_find_window(B.win_unit, B.n_windows, unit);
         const int h0 = B.win_hap[w], nh = B.win_hap[w + 1] - h0;
         const int r0 = B.win_read[w], nr = B.win_read[w + 1] - r0;

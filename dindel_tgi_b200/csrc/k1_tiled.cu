@@ -591,8 +591,8 @@ __device__ __forceinline__ int tiled_class_of_dev(int S)
 // such batches take the generic kernel.
 __global__ void k1_tiled_units(K1Batch B, int pass)
 {
-    const int w = blockIdx.x * blockDim.x + threadIdx.x;
-    if (w >= B.n_windows) return;
+    const int w = B.w_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= B.w_end) return;
     const int h0 = B.win_hap[w], nh = B.win_hap[w + 1] - h0;
     const int nr = B.win_read[w + 1] - B.win_read[w];
     const unsigned nchunk = (unsigned)((nr + K1_READ_CHUNK - 1) / K1_READ_CHUNK);
@@ -626,10 +626,10 @@ __global__ void k1_tiled_units_scan(K1Batch B)
 extern "C" cudaError_t k1_tiled_prepare(const K1Batch *B, cudaStream_t st, int *launches)
 {
     if (launches) *launches = 0;
-    if (B->n_windows <= 0) return cudaSuccess;
+    if (B->w_end <= B->w_begin) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(B->bucket_work, 0, sizeof(unsigned) * 2 * K1_TILED_BUCKETS, st);
     if (e != cudaSuccess) return e;
-    const int threads = 128, blocks = (B->n_windows + threads - 1) / threads;
+    const int threads = 128, blocks = (B->w_end - B->w_begin + threads - 1) / threads;
     k1_tiled_units<<<blocks, threads, 0, st>>>(*B, 0);
     k1_tiled_units_scan<<<1, 32, 0, st>>>(*B);
     k1_tiled_units<<<blocks, threads, 0, st>>>(*B, 1);
@@ -650,7 +650,7 @@ static cudaError_t launch_one(const K1Batch *B, int num_sms, int cls, cudaStream
     if (e != cudaSuccess) return e;
     if (per_sm < 1) return cudaErrorInvalidConfiguration;
     long long grid = (long long)num_sms * per_sm;
-    long long need = (B->n_units + warps - 1) / warps;
+    long long need = (B->unit_end - B->unit_begin + warps - 1) / warps;
     if (grid > need) grid = need;
     if (grid < 1) grid = 1;
     k1_tiled_kernel<C, J><<<(int)grid, warps * 32, smem, st>>>(*B, cls);
