@@ -139,7 +139,9 @@ __device__ __forceinline__ void k1_tail(const Bt &bt, int lane, int R, int H, in
         // cpp DInDel.cpp:1722-1735: ll > 0.1 is fatal, NaN/Inf skips the window
         o.status = (ll > 0.1) ? DINDEL_WIN_LL_POSITIVE
                               : ((ll != ll || ll - ll != 0.0) ? DINDEL_WIN_NAN : DINDEL_WIN_OK);
-        for (int i = 0; i < 7; i++) o.pad[i] = 0;
+        o.pad0 = 0;
+        o.mapState0 = (uint16_t)sm_ms[0];
+        for (int i = 0; i < 4; i++) o.pad[i] = 0;
         const int4 *src = reinterpret_cast<const int4 *>(&o);
         int4 *dst = reinterpret_cast<int4 *>(out);
         dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2]; dst[3] = src[3];
@@ -156,7 +158,9 @@ __device__ __forceinline__ void k1_write_hapsize_error(dindel_pair_out *out, int
         o.firstBase = -1; o.lastBase = -1;
         o.numIndels = 0; o.numMismatch = 0; o.nBQT = 0; o.nmmBQT = 0; o.nMMLeft = 0; o.nMMRight = 0;
         o.offHap = 0; o.offHapHMQ = 0; o.bMid = 0; o.status = DINDEL_WIN_HAPSIZE;
-        for (int i = 0; i < 7; i++) o.pad[i] = 0;
+        o.pad0 = 0;
+        o.mapState0 = 0;
+        for (int i = 0; i < 4; i++) o.pad[i] = 0;
         *out = o;
     }
 }

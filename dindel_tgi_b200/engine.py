@@ -73,7 +73,7 @@ PAIR_DTYPE = np.dtype([
     ("firstBase", "<i4"), ("lastBase", "<i4"),
     ("numIndels", "<u2"), ("numMismatch", "<u2"), ("nBQT", "<u2"), ("nmmBQT", "<u2"),
     ("nMMLeft", "<u2"), ("nMMRight", "<u2"),
-    ("offHap", "u1"), ("offHapHMQ", "u1"), ("bMid", "<i2"), ("status", "u1"), ("pad", "u1", (7,)),
+    ("offHap", "u1"), ("offHapHMQ", "u1"), ("bMid", "<i2"), ("status", "u1"), ("pad0", "u1"), ("mapState0", "<u2"), ("pad", "u1", (4,)),
 ])
 assert PAIR_DTYPE.itemsize == 64
 

@@ -86,7 +86,10 @@ typedef struct dindel_pair_out {
     uint8_t offHap, offHapHMQ;
     int16_t bMid;
     uint8_t status; /* DINDEL_WIN_* of this pair */
-    uint8_t pad[7];
+    uint8_t pad0;
+    uint16_t mapState0; /* Viterbi state of read base 0 (x, or S+x in an insertion; S = H+2): with hpos it
+                           determines every state, so the AlignedVariant maps can be rebuilt exactly */
+    uint8_t pad[4];
 } dindel_pair_out;
 
 /* Results, caller-allocated.  Pair (w, h, r) lives at win_pair[w] + r*nh(w) + h  (r-major, like

@@ -1,0 +1,237 @@
+// include/dindel_b200.hpp — C++ host adapter over the C ABI (include/dindel_b200.h).
+//
+// Source-level drop-in for the one loop of the reference that drives the likelihood engine,
+//   DetInDel::computeLikelihoods(haps, reads, liks, leftPos, rightPos, onHap)   (DInDel.cpp:1707-1739)
+// i.e. for every (hap, read): ObservationModelFBMaxErr(hap, read, leftPos, obsParams).calcLikelihood()
+// (ObservationModelFB.hpp:160,133).  Header only, duck typed: it is written against the *names* the
+// reference's value types expose, so it compiles unchanged against the reference's own
+// Haplotype / Read / MLAlignment / AlignedVariant (Haplotype.hpp:40, Read.hpp:31,
+// MLAlignment.hpp:28, Variant.hpp:78) and against any test double with the same members:
+//   HapT : std::string seq;  std::map<int, AV> indels, snps;  (AV::isCovered(pad, first, last))
+//   MLA  : ll llOn llOff offHap offHapHMQ firstBase lastBase numIndels numMismatch nBQT nmmBQT
+//          mLogBQ nMMLeft nMMRight align hpos indels snps hapIndelCovered hapSNPCovered
+//          (mapped_type of MLA::indels constructible from (string, hapStart, hapEnd, readStart, readEnd))
+//   ReadT: read through ReadTraits<ReadT> (specialise it for other read types); the default reads the
+//          reference's Read: seq.seq, getBam() -> phred bytes / mapping quality / BAM_FUNMAP,
+//          posStat.first, onReverseStrand.
+// The GPU computes the Viterbi path and the per-pair record; this header only re-expands that record
+// into the reference's containers (reportVariants, ObservationModelFB.cpp:1351-1463) and reproduces
+// computeLikelihoods' guards.  There is no CPU fallback: without a CUDA device Engine() throws.
+#ifndef DINDEL_B200_HPP
+#define DINDEL_B200_HPP
+#include <stdint.h>
+#include <stdlib.h>
+#include <iostream>
+#include <map>
+#include <string>
+#include <vector>
+#include "dindel_b200.h"
+
+namespace dindel_b200 {
+
+// How the adapter reads one read.  Default = the reference's Read (Read.hpp); needs samtools' bam.h
+// (bam1_qual, BAM_FUNMAP) to be included before this header, as DInDel.cpp does.
+template <class ReadT>
+struct ReadTraits {
+    static const std::string &seq(const ReadT &r) { return r.seq.seq; }
+#ifdef BAM_BAM_H
+    static const uint8_t *phred(const ReadT &r) { return (const uint8_t *)bam1_qual(r.getBam()); } // Read.hpp:143
+    static uint8_t mapq(const ReadT &r) { return (uint8_t)r.getBam()->core.qual; }                   // Read.hpp:127
+    static bool unmapped(const ReadT &r) { return (r.getBam()->core.flag & BAM_FUNMAP) != 0; }       // Read.hpp:200
+#endif
+    static uint32_t start(const ReadT &r) { return uint32_t(r.posStat.first); }                      // ObservationModelFB.cpp:52
+    static bool reverse(const ReadT &r) { return r.onReverseStrand; }
+};
+
+// RAII owner of one dindel_ctx (one device).  Construct from anything with the fields of
+// ObservationModelParameters (ObservationModel.hpp:28-99) that the path reads.
+class Engine {
+public:
+    template <class ObsParams>
+    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0)
+    {
+        dindel_b200_default_params(&p_);
+        p_.pError = op.pError; p_.pMut = op.pMut; p_.mapQualThreshold = op.mapQualThreshold;
+        p_.pFirstgLO = op.pFirstgLO; p_.checkBaseQualThreshold = op.checkBaseQualThreshold;
+        p_.maxLengthDel = op.maxLengthDel; p_.padCover = op.padCover; p_.bMid = op.bMid;
+        p_.forceReadOnHaplotype = op.forceReadOnHaplotype ? 1 : 0;
+        int rc = dindel_b200_create(&p_, device, &ctx_);
+        if (rc != DINDEL_OK) throw std::string("dindel_b200: ") + dindel_b200_strerror(rc);
+    }
+    ~Engine() { if (ctx_) dindel_b200_destroy(ctx_); }
+    dindel_ctx *ctx() const { return ctx_; }
+    const dindel_params &params() const { return p_; }
+
+    template <class HapT, class ReadT, class MLA>
+    void computeLikelihoods(const std::vector<HapT> &haps, const std::vector<ReadT> &reads,
+                            std::vector<std::vector<MLA> > &liks, uint32_t leftPos, uint32_t rightPos,
+                            std::vector<int> &onHap);
+
+private:
+    Engine(const Engine &);
+    Engine &operator=(const Engine &);
+    dindel_params p_;
+    dindel_ctx *ctx_;
+};
+
+// mapped types of MLA::indels and HapT::indels (C++98-friendly, the reference builds as gnu++98)
+template <class M> struct map_value;
+template <class K, class V, class C, class A> struct map_value<std::map<K, V, C, A> > { typedef V type; };
+template <class MLA> struct MLA_indel_type {
+    static MLA &ref();
+    typedef typename map_value<__typeof__(ref().indels)>::type type;
+};
+template <class HapT> struct HapT_variant {
+    static HapT &ref();
+    typedef typename map_value<__typeof__(ref().indels)>::type type;
+};
+
+// Re-expands one GPU pair record into the reference's MLAlignment exactly as reportVariants does
+// (ObservationModelFB.cpp:1351-1463).  The Viterbi states are recovered from hpos + mapState0:
+// an on-haplotype base at hap index p is state x = p+1, LO is x = 0, RO is x = H+1, and a base inside
+// an insertion keeps the column of the base before it (plane 1 is entered from plane 0 of the same
+// column, cpp:1754/:1823) or, when the read starts inside the insertion, the column in mapState0.
+template <class HapT, class MLA>
+inline void expandAlignment(const dindel_pair_out &rec, const int16_t *hpos, const HapT &hap,
+                            const std::string &readSeq, int padCover, MLA &ml)
+{
+    typedef typename MLA_indel_type<MLA>::type AV;
+    const std::string &hseq = hap.seq;
+    const int H = (int)hseq.size(), S = H + 2, R = (int)readSeq.size();
+    ml.ll = rec.ll; ml.llOn = rec.llOn; ml.llOff = rec.llOff;                    // cpp:1120-1135
+    ml.offHap = rec.offHap != 0; ml.offHapHMQ = rec.offHapHMQ != 0;
+    ml.align = std::string((size_t)H, 'R');                                      // cpp:1353-1372
+    ml.indels.clear(); ml.snps.clear();
+    ml.hapIndelCovered.clear(); ml.hapSNPCovered.clear();
+    ml.firstBase = rec.firstBase; ml.lastBase = rec.lastBase;
+    ml.nBQT = rec.nBQT; ml.nmmBQT = rec.nmmBQT; ml.mLogBQ = rec.mLogBQ;
+    ml.nMMRight = rec.nMMRight; ml.nMMLeft = rec.nMMLeft;
+    ml.numIndels = rec.numIndels; ml.numMismatch = rec.numMismatch;
+    ml.hpos.assign((size_t)R, 0);
+    for (int b = 0; b < R; b++) ml.hpos[b] = hpos[b];
+
+    // plane-0 column of read base b, or -1 inside an insertion
+    struct Col {
+        static int of(int hp, int H) { return hp >= 0 ? hp + 1 : (hp == DINDEL_HPOS_LO ? 0 : (hp == DINDEL_HPOS_RO ? H + 1 : -1)); }
+    };
+    int b = 0;
+    while (b < R) {
+        const int hp = hpos[b];
+        if (hp == DINDEL_HPOS_INS) {                                             // cpp:1377-1396
+            int pos;
+            if (b > 0) pos = Col::of(hpos[b - 1], H);
+            else pos = (int)rec.mapState0 - S;
+            const int rpos = b;
+            int len = 0;
+            while (b < R && hpos[b] == DINDEL_HPOS_INS) { b++; len++; }
+            ml.indels[pos] = AV(std::string("+").append(readSeq.substr(rpos, len)), pos, pos, rpos, b - 1);
+            continue; // b already sits on the base after the run (the reference does b--, b++)
+        }
+        if (hp >= 0) {
+            const int s = hp + 1;
+            if (readSeq[b] != hseq[s - 1]) {                                     // cpp:1410-1433
+                std::string snp;
+                snp += hseq[s - 1];
+                snp.append("=>");
+                snp += readSeq[b];
+                ml.snps[s - 1] = AV(snp, s - 1, s - 1, b, b);
+                ml.align[s - 1] = readSeq[b];
+            }
+            if (b < R - 1 && hpos[b + 1] != DINDEL_HPOS_INS) {                    // cpp:1436-1453
+                const int ns = Col::of(hpos[b + 1], H);
+                if (ns - s > 1) {
+                    const int pos = s, dlen = ns - s - 1;
+                    for (int y = pos; y < dlen + pos; y++) ml.align[y] = 'D';
+                    ml.indels[pos] = AV(std::string("-").append(hseq.substr(pos, dlen)), pos, pos + dlen - 1, b, b + 1);
+                }
+            }
+        }
+        b++;
+    }
+    for (typename std::map<int, typename HapT_variant<HapT>::type>::const_iterator it = hap.indels.begin();
+         it != hap.indels.end(); ++it)                                           // cpp:1465-1468
+        ml.hapIndelCovered[it->first] = it->second.isCovered(padCover, ml.firstBase, ml.lastBase);
+    for (typename std::map<int, typename HapT_variant<HapT>::type>::const_iterator it = hap.snps.begin();
+         it != hap.snps.end(); ++it)                                             // cpp:1469-1472
+        ml.hapSNPCovered[it->first] = it->second.isCovered(padCover, ml.firstBase, ml.lastBase);
+}
+
+// DetInDel::computeLikelihoods (DInDel.cpp:1707-1739) for one window: packs the window into the C
+// ABI's batch layout, runs the GPU engine, re-expands every pair.  Guards as in the reference, in
+// its h-outer / r-inner order: a haplotype shorter than maxLengthDel throws "hapSize error."
+// (ObservationModelFB.cpp:47), ll > 0.1 prints "Likelihood>0" and exits (DInDel.cpp:1722-1731),
+// NaN / Inf throws "Nan detected" (DInDel.cpp:1732-1735).
+template <class HapT, class ReadT, class MLA>
+void Engine::computeLikelihoods(const std::vector<HapT> &haps, const std::vector<ReadT> &reads,
+                                std::vector<std::vector<MLA> > &liks, uint32_t leftPos, uint32_t /*rightPos*/,
+                                std::vector<int> &onHap)
+{
+    typedef ReadTraits<ReadT> RT;
+    const size_t nh = haps.size(), nr = reads.size();
+    onHap = std::vector<int>(nr, 0);
+    liks = std::vector<std::vector<MLA> >(nh, std::vector<MLA>(nr));
+    if (nh == 0 || nr == 0) return;
+    std::vector<int64_t> hap_off(1, 0), read_off(1, 0);
+    std::string hap_seq, read_seq;
+    std::vector<uint8_t> qual, mapq, flags;
+    std::vector<uint32_t> start;
+    size_t maxR = 0;
+    for (size_t h = 0; h < nh; h++) { hap_seq += haps[h].seq; hap_off.push_back((int64_t)hap_seq.size()); }
+    for (size_t r = 0; r < nr; r++) {
+        const std::string &sq = RT::seq(reads[r]);
+        const uint8_t *ph = RT::phred(reads[r]);
+        read_seq += sq; read_off.push_back((int64_t)read_seq.size());
+        qual.insert(qual.end(), ph, ph + sq.size());
+        mapq.push_back(RT::mapq(reads[r]));
+        start.push_back(RT::start(reads[r]));
+        flags.push_back((uint8_t)((RT::unmapped(reads[r]) ? DINDEL_READ_UNMAPPED : 0) |
+                                  (RT::reverse(reads[r]) ? DINDEL_READ_REVERSE : 0)));
+        if (sq.size() > maxR) maxR = sq.size();
+    }
+    int32_t win_hap[2] = {0, (int32_t)nh}, win_read[2] = {0, (int32_t)nr};
+    static const uint8_t none = 0;
+    dindel_batch_in in;
+    in.n_windows = 1; in.n_haps = (int32_t)nh; in.n_reads = (int32_t)nr; in.reserved = 0;
+    in.hap_start = &leftPos; in.win_hap = win_hap; in.win_read = win_read;
+    in.hap_off = &hap_off[0]; in.hap_seq = hap_seq.data();
+    in.read_off = &read_off[0]; in.read_seq = read_seq.data();
+    in.read_qual = qual.empty() ? &none : &qual[0];
+    in.read_mapq = &mapq[0]; in.read_start = &start[0]; in.read_flags = &flags[0];
+
+    const size_t np = nh * nr;
+    const int stride = (int)((maxR + 7) & ~(size_t)7) > 0 ? (int)((maxR + 7) & ~(size_t)7) : 8;
+    std::vector<dindel_pair_out> pairs(np);
+    std::vector<int16_t> hpos(np * (size_t)stride);
+    std::vector<uint8_t> on(nr);
+    int64_t win_pair[2];
+    int32_t status = 0;
+    dindel_batch_out out;
+    out.n_pairs = (int64_t)np; out.pairs = &pairs[0]; out.hpos = &hpos[0]; out.hpos_stride = stride;
+    out.reserved = 0; out.win_pair = win_pair; out.win_status = &status; out.read_on_hap = &on[0];
+    int rc = dindel_b200_submit(ctx_, &in, &out);
+    if (rc != DINDEL_OK)
+        throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx_) + ")";
+
+    for (size_t h = 0; h < nh; h++) {
+        for (size_t r = 0; r < nr; r++) {
+            const size_t i = r * nh + h; // pairs are r-major inside a window
+            const dindel_pair_out &rec = pairs[i];
+            if (rec.status == DINDEL_WIN_HAPSIZE) throw std::string("hapSize error.");
+            expandAlignment(rec, &hpos[i * (size_t)stride], haps[h], RT::seq(reads[r]), p_.padCover, liks[h][r]);
+            if (!liks[h][r].offHapHMQ) onHap[r] = 1;
+            if (rec.status == DINDEL_WIN_LL_POSITIVE) {
+                std::cout << std::string(25, ' ') << haps[h].seq << std::endl;
+                std::cout << "hidx: " << h << " r: " << r << std::endl;
+                std::cerr << "Likelihood>0" << std::endl;
+                exit(1);
+            }
+            if (rec.status == DINDEL_WIN_NAN) {
+                std::cout << "NAN/Inf error" << std::endl;
+                throw std::string("Nan detected");
+            }
+        }
+    }
+}
+
+} // namespace dindel_b200
+#endif

@@ -1,0 +1,138 @@
+// tests/cpp/adapter_mock_test.cpp — include/dindel_b200.hpp against test doubles that expose the same
+// member names as the reference's Haplotype / Read / MLAlignment / AlignedVariant (no reference code
+// needed).  Exit codes: 0 = all checks passed on a CUDA device, 2 = no CUDA device (the adapter has
+// no CPU path and must say so), 1 = a check failed.
+#include <stdio.h>
+#include <string.h>
+#include <map>
+#include <string>
+#include <vector>
+#include "dindel_b200.hpp"
+
+struct MockAV { // Variant.hpp:78-175: the members this path touches
+    std::string str;
+    int startHap, endHap, startRead, endRead;
+    MockAV() : startHap(0), endHap(0), startRead(0), endRead(0) {}
+    MockAV(const std::string &s, int sh, int eh, int sr, int er) : str(s), startHap(sh), endHap(eh), startRead(sr), endRead(er) {}
+    bool isCovered(int pad, int firstBase, int lastBase) const { return firstBase + pad <= startRead && lastBase - pad >= endRead; }
+};
+struct MockHap { // Haplotype.hpp:40-70
+    std::string seq;
+    std::map<int, MockAV> indels, snps;
+};
+struct MockRead {
+    std::string seq;
+    std::vector<uint8_t> phred;
+    uint8_t mapq;
+    uint32_t start;
+    bool unmapped, reverse;
+};
+struct MockMLA { // MLAlignment.hpp:28-76
+    int relPos, firstBase, lastBase, hl, hr, numIndels, numMismatch, nBQT, nmmBQT, nMMLeft, nMMRight;
+    std::map<int, MockAV> indels, snps;
+    std::map<int, bool> hapIndelCovered, hapSNPCovered;
+    double ll, llOn, llOff, mLogBQ;
+    bool offHap, offHapHMQ;
+    std::string align;
+    std::vector<int> hpos;
+    MockMLA() : relPos(-1), firstBase(0), lastBase(0), hl(-1), hr(-1), numIndels(0), numMismatch(0), nBQT(0), nmmBQT(0),
+                nMMLeft(0), nMMRight(0), ll(0), llOn(0), llOff(0), mLogBQ(0), offHap(false), offHapHMQ(false) {}
+};
+namespace dindel_b200 {
+template <> struct ReadTraits<MockRead> {
+    static const std::string &seq(const MockRead &r) { return r.seq; }
+    static const uint8_t *phred(const MockRead &r) { return r.phred.empty() ? (const uint8_t *)"" : &r.phred[0]; }
+    static uint8_t mapq(const MockRead &r) { return r.mapq; }
+    static bool unmapped(const MockRead &r) { return r.unmapped; }
+    static uint32_t start(const MockRead &r) { return r.start; }
+    static bool reverse(const MockRead &r) { return r.reverse; }
+};
+}
+struct Params { // ObservationModel.hpp:28-99, CLI values (DInDel.cpp:4122-4157)
+    double pError, pMut, mapQualThreshold, pFirstgLO, checkBaseQualThreshold;
+    int maxLengthDel, padCover, bMid;
+    bool forceReadOnHaplotype;
+};
+
+static MockRead mk(const std::string &s, uint32_t start)
+{
+    MockRead r;
+    r.seq = s; r.phred.assign(s.size(), 30); r.mapq = 60; r.start = start; r.unmapped = false; r.reverse = false;
+    return r;
+}
+#define CHECK(c) do { if (!(c)) { fprintf(stderr, "adapter_mock_test: check failed at line %d: %s\n", __LINE__, #c); return 1; } } while (0)
+
+int main()
+{
+    Params p = {5e-4, 1e-5, 100.0, 0.01, 0.95, 5, 2, -1, false};
+    dindel_b200::Engine *eng = 0;
+    try {
+        eng = new dindel_b200::Engine(p, 0);
+    } catch (std::string &s) {
+        printf("no engine: %s\n", s.c_str());
+        return strstr(s.c_str(), "no usable CUDA device") ? 2 : 1;
+    }
+    const std::string ref = "ACGTTGCAAGGCTTAGCATCGGATACCGTTAGGCATCAAGTTCGGATCCATGCAAGTCGGCTAAGCTTGCAGGTCCATAGGCTAACGGTTACGATCGGA";
+    const uint32_t leftPos = 7000;
+    std::vector<MockHap> haps(2);
+    haps[0].seq = ref;
+    haps[1].seq = ref.substr(0, 50) + ref.substr(53); // 3-bp deletion after hap base 49
+    haps[1].indels[50] = MockAV("-" + ref.substr(50, 3), 50, 52, 50, 50);
+    std::vector<MockRead> reads;
+    reads.push_back(mk(ref.substr(10, 60), leftPos + 10));                          // 0: plain reference read
+    reads.push_back(mk(ref.substr(20, 30) + ref.substr(53, 30), leftPos + 20));     // 1: carries the deletion
+    reads.push_back(mk(ref.substr(15, 25) + "TT" + ref.substr(40, 35), leftPos + 15)); // 2: 2-bp insertion before hap base 40
+    std::string snp = ref.substr(30, 50);
+    snp[20] = (snp[20] == 'A') ? 'C' : 'A';
+    reads.push_back(mk(snp, leftPos + 30));                                         // 3: one mismatch at hap base 50
+    std::vector<std::vector<MockMLA> > liks;
+    std::vector<int> onHap;
+    eng->computeLikelihoods(haps, reads, liks, leftPos, leftPos + 100, onHap);
+    CHECK(liks.size() == 2 && liks[0].size() == 4 && onHap.size() == 4);
+    for (int r = 0; r < 4; r++) CHECK(onHap[r] == 1);
+    { // read 0 on the reference haplotype: ungapped, no variants
+        const MockMLA &m = liks[0][0];
+        CHECK(m.ll < 0 && m.ll > -1.0 && m.numIndels == 0 && m.indels.empty() && m.snps.empty());
+        CHECK(m.firstBase == 10 && m.lastBase == 69 && m.hpos.size() == 60);
+        for (int b = 0; b < 60; b++) CHECK(m.hpos[b] == 10 + b);
+        CHECK(m.align == std::string(ref.size(), 'R') && !m.offHap && !m.offHapHMQ && m.nBQT == 60);
+    }
+    { // read 1: deletion against hap 0, clean against hap 1, and it covers hap 1's indel
+        const MockMLA &a = liks[0][1], &b = liks[1][1];
+        CHECK(a.numIndels == 1 && a.indels.size() == 1 && a.indels.begin()->second.str[0] == '-');
+        CHECK(a.indels.begin()->second.str.size() == 4 && a.indels.begin()->second.endHap - a.indels.begin()->second.startHap == 2);
+        CHECK(a.align.find("DDD") != std::string::npos);
+        CHECK(b.numIndels == 0 && b.indels.empty() && b.ll > a.ll);
+        CHECK(b.hapIndelCovered.size() == 1 && b.hapIndelCovered.begin()->first == 50 && b.hapIndelCovered.begin()->second);
+        CHECK(liks[1][0].hapIndelCovered.size() == 1); // every read reports every hap indel, covered or not
+    }
+    { // read 2: insertion "+TT" recorded before hap base 40 with its read coordinates
+        const MockMLA &m = liks[0][2];
+        CHECK(m.numIndels == 1 && m.indels.size() == 1);
+        const MockAV &v = m.indels.begin()->second;
+        CHECK(v.str == "+TT" && v.startHap == v.endHap && v.endRead - v.startRead == 1);
+        CHECK(m.hpos[v.startRead] == DINDEL_HPOS_INS && m.hpos[v.endRead] == DINDEL_HPOS_INS);
+        CHECK(m.hpos[v.startRead - 1] + 1 == m.indels.begin()->first && m.hpos[v.endRead + 1] == m.indels.begin()->first);
+    }
+    { // read 3: one SNP at hap base 50, "X=>Y" with X the haplotype's base
+        const MockMLA &m = liks[0][3];
+        CHECK(m.snps.size() == 1 && m.snps.begin()->first == 50 && m.numMismatch == 1 && m.nmmBQT == 1);
+        CHECK(m.snps.begin()->second.str[0] == ref[50] && m.snps.begin()->second.str.substr(1, 2) == "=>");
+        CHECK(m.align[50] == snp[20]);
+    }
+    { // a haplotype shorter than maxLengthDel: "hapSize error." (ObservationModelFB.cpp:47)
+        std::vector<MockHap> bad(2);
+        bad[0].seq = ref; bad[1].seq = "ACG";
+        std::string err;
+        try { eng->computeLikelihoods(bad, reads, liks, leftPos, leftPos + 100, onHap); } catch (std::string &s) { err = s; }
+        CHECK(err == "hapSize error.");
+    }
+    { // empty window
+        std::vector<MockHap> none;
+        eng->computeLikelihoods(none, reads, liks, leftPos, leftPos + 100, onHap);
+        CHECK(liks.empty() && onHap.size() == 4);
+    }
+    delete eng;
+    printf("adapter_mock_test ok\n");
+    return 0;
+}
