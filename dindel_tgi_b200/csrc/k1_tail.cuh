@@ -54,23 +54,37 @@ __device__ __forceinline__ void k1_tail(const Bt &bt, int lane, int R, int H, in
                                         dindel_pair_out *out, int16_t *hpos_out)
 {
     const int S = H + 2;
-    // --- back-trace, cpp:1148-1165: lane 0 walks left, lane 1 walks right ---
-    if (lane == 0) {
-        int s = msMid;
-        sm_ms[bMid] = (int16_t)s;
-        for (int b = bMid; b > 0; b--) {
-            int x = s >= S ? s - S : s;
-            int c = bt(b, x);
-            s = k1_prev_state_dec(s, c & 127, c >> 7, S, H, J);
-            sm_ms[b - 1] = (int16_t)s;
-        }
-    } else if (lane == 1) {
-        int s = msMid;
-        for (int b = bMid; b < R - 1; b++) {
-            int x = s >= S ? s - S : s;
-            int c = bt(b + 1, x);
-            s = k1_next_state_inc(s, c & 127, c >> 7, S, H, J);
-            sm_ms[b + 1] = (int16_t)s;
+    // --- back-trace, cpp:1148-1165: lane 0 walks left (btf), lane 1 walks right (btb), in the same
+    //     instruction stream (one loop, both decodes evaluated, the lane's own one selected) ---
+    if (lane < 2) {
+        const bool left = (lane == 0);
+        const int RO = H + 1;
+        const int n = left ? bMid : (R - 1 - bMid);
+        int s = msMid, b = bMid;
+        if (left) sm_ms[bMid] = (int16_t)s;
+        for (int i = 0; i < n; i++) {
+            const bool plane1 = s >= S;
+            const int x = plane1 ? s - S : s;
+            const int c = bt(left ? b : b + 1, x);
+            const int code = c & 127;
+            const bool bit1 = (c >> 7) != 0;
+            // plane 1 (k1_prev_state_dec / k1_next_state_inc, s >= S)
+            const int p1d = bit1 ? x : s;
+            const int xi = (x + 1 > RO) ? RO : x + 1;
+            const int p1i = !bit1 ? s : (x == 0 ? 0 : xi);
+            // plane 0, interior column
+            const int jd0 = x - code - 1, ji0 = x + code + 1;
+            const int gd = (code >= J) ? S + x - 1 : (jd0 < 0 ? 0 : jd0);
+            const int gi = (code >= J) ? S + x : (ji0 > H ? RO : ji0);
+            // plane 0, LO and RO
+            const int i0 = (code == 0) ? 0 : (code == 1) ? 1 : S;
+            const int dR = (code == 0) ? RO : (code == 1) ? H : (code == 2) ? S + RO : S + H;
+            const int iR = (code == 0) ? RO : S + RO;
+            const int d = plane1 ? p1d : (x == 0 ? 0 : (x == RO ? dR : gd));
+            const int u = plane1 ? p1i : (x == 0 ? i0 : (x == RO ? iR : gi));
+            s = left ? d : u;
+            b += left ? -1 : 1;
+            sm_ms[b] = (int16_t)s;
         }
     }
     __syncwarp();
