@@ -1,0 +1,132 @@
+#!/usr/bin/env python
+"""oracle/e2e/run_e2e.py — TEST INFRASTRUCTURE ONLY.
+
+End-to-end check of BASELINE.json configs[0] (`dindel --analysis indels --doDiploid` on a synthetic
+chr20 BAM, 30x 100-bp reads, ~120-bp windows from makeWindows): the reference's own pipeline is run
+twice over the same window files,
+  arm "cpu": oracle/_ref/dindel_ref   (stock reference binary)
+  arm "gpu": oracle/_ref/dindel_b200  (same sources + INTEGRATION.md's two-line patch: K1 on the B200)
+and the `.glf.txt` files and the merged VCFs are compared byte for byte.
+
+  stage 1  dindel_ref --analysis getCIGARindels          (README.md pipeline; GetCandidates.cpp:387)
+  stage 2  make_windows.py (selectCandidates --minCount 2, makeWindows; window files = unit of parallelism)
+  stage 3  <arm binary> --analysis indels --doDiploid    one process per window file, `procs` at a time
+  stage 4  merge_diploid.py -> VCF
+
+    python oracle/e2e/run_e2e.py --work /tmp/e2e --length 60000 --arms cpu,gpu
+prints one JSON line with counts, wall times and the comparison verdict.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REFDIR = os.path.join(os.path.dirname(HERE), "_ref")
+sys.path.insert(0, HERE)
+import make_windows  # noqa: E402
+import merge_diploid  # noqa: E402
+
+BIN = {"cpu": os.path.join(REFDIR, "dindel_ref"), "gpu": os.path.join(REFDIR, "dindel_b200")}
+BAMTOOL = os.path.join(REFDIR, "bamtool")
+
+
+def have_binaries(arms=("cpu",)):
+    return os.path.exists(BAMTOOL) and all(os.path.exists(BIN[a]) for a in arms)
+
+
+def sh(cmd, log):
+    with open(log, "w") as f:
+        rc = subprocess.call(cmd, stdout=f, stderr=subprocess.STDOUT)
+    if rc != 0:
+        raise RuntimeError("%s failed (rc %d), see %s:\n%s" % (cmd[0], rc, log, open(log).read()[-2000:]))
+
+
+def prepare(work, length, seed, coverage=30.0, per_file=1000, min_count=2):
+    """synthetic genome -> BAM -> candidates -> window files.  Returns dict of paths."""
+    os.makedirs(work, exist_ok=True)
+    sh([sys.executable, os.path.join(HERE, "synth_genome.py"), "--out", work, "--length", str(length),
+        "--coverage", str(coverage), "--seed", str(seed)], os.path.join(work, "synth.log"))
+    ref, sam, bam = (os.path.join(work, n) for n in ("ref.fa", "sample.sam", "sample.bam"))
+    sh([BAMTOOL, "faidx", ref], os.path.join(work, "faidx.log"))
+    sh([BAMTOOL, "sam2bam", sam, bam], os.path.join(work, "sam2bam.log"))
+    s1 = os.path.join(work, "s1")
+    sh([BIN["cpu"], "--analysis", "getCIGARindels", "--bamFile", bam, "--ref", ref, "--outputFile", s1],
+       os.path.join(work, "stage1.log"))
+    sel = os.path.join(work, "win.selected.txt")
+    make_windows.select_candidates(s1 + ".variants.txt", sel, min_count)
+    files = make_windows.split_and_merge(sel, os.path.join(work, "win"), 20, per_file)
+    n_win = sum(1 for f in files for _ in open(f))
+    return {"ref": ref, "bam": bam, "window_files": files, "n_windows": n_win,
+            "n_candidates": sum(1 for _ in open(sel))}
+
+
+def run_arm(arm, prep, work, procs, extra=()):
+    """stage 3 + 4 for one arm.  Returns (glf paths, vcf path, wall seconds of stage 3)."""
+    def one(k_f):
+        k, wf = k_f
+        out = os.path.join(work, "%s.%d" % (arm, k))
+        sh([BIN[arm], "--analysis", "indels", "--doDiploid", "--bamFile", prep["bam"], "--ref", prep["ref"],
+            "--varFile", wf, "--outputFile", out] + list(extra), out + ".log")
+        return out + ".glf.txt"
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max(1, procs)) as ex:
+        glfs = list(ex.map(one, enumerate(prep["window_files"], 1)))
+    wall = time.perf_counter() - t0
+    vcf = os.path.join(work, arm + ".vcf")
+    n_calls = merge_diploid.merge_output(glfs, prep["ref"], vcf)
+    return glfs, vcf, wall, n_calls
+
+
+def glf_stats(glfs):
+    ok = err = 0
+    for g in glfs:
+        with open(g) as f:
+            f.readline()
+            seen = set()
+            for line in f:
+                d = line.split(" ", 2)
+                if d[1] in seen:
+                    continue
+                seen.add(d[1])
+                if d[0] == "ok":
+                    ok += 1
+                else:
+                    err += 1
+    return ok, err
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--work", required=True)
+    ap.add_argument("--length", type=int, default=60000)
+    ap.add_argument("--coverage", type=float, default=30.0)
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--arms", default="cpu,gpu")
+    ap.add_argument("--procs", type=int, default=0, help="concurrent stage-3 processes (0 = host cores)")
+    ap.add_argument("--windows-per-file", type=int, default=1000)
+    a = ap.parse_args()
+    arms = a.arms.split(",")
+    procs = a.procs or len(os.sched_getaffinity(0))
+    prep = prepare(a.work, a.length, a.seed, a.coverage, a.windows_per_file)
+    res = {"length": a.length, "coverage": a.coverage, "n_candidates": prep["n_candidates"],
+           "n_windows": prep["n_windows"], "window_files": len(prep["window_files"]), "procs": procs}
+    out = {}
+    for arm in arms:
+        glfs, vcf, wall, n_calls = run_arm(arm, prep, a.work, procs if arm == "cpu" else 1)
+        ok, err = glf_stats(glfs)
+        out[arm] = (glfs, vcf)
+        res[arm] = {"stage3_wall_s": round(wall, 3), "vcf_calls": n_calls, "windows_ok": ok, "windows_skipped": err}
+    if "cpu" in out and "gpu" in out:
+        same_glf = all(open(x, "rb").read() == open(y, "rb").read() for x, y in zip(out["cpu"][0], out["gpu"][0]))
+        same_vcf = open(out["cpu"][1], "rb").read() == open(out["gpu"][1], "rb").read()
+        res["glf_identical"], res["vcf_identical"] = same_glf, same_vcf
+    print(json.dumps(res))
+    return 0 if res.get("glf_identical", True) and res.get("vcf_identical", True) else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,125 @@
+"""End-to-end check on the reference's own pipeline (BASELINE.json configs[0], SURVEY.md 8d "G1"):
+synthetic chr20 FASTA + 30x BAM -> `--analysis getCIGARindels` -> windows -> `--analysis indels
+--doDiploid` -> `.glf.txt` -> VCF.
+
+  * CPU: the window scripts' restatements (oracle/e2e/make_windows.py, merge_diploid.py), and the stock
+    reference binary (oracle/_ref/dindel_ref, built where /root/reference exists) recovering the planted
+    indels from the synthetic BAM -- this pins the fixture generator and the harness.
+  * GPU: the reference binary with INTEGRATION.md's two-line patch (oracle/_ref/dindel_b200: K1 runs on
+    the B200 through include/dindel_b200.hpp) produces `.glf.txt` files and a VCF that are byte-identical
+    to the stock CPU binary's (north star: "final VCF indel calls and genotypes must be bit-exact").
+"""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+E2E = os.path.join(ROOT, "oracle", "e2e")
+sys.path.insert(0, E2E)
+import make_windows  # noqa: E402
+import merge_diploid  # noqa: E402
+import run_e2e  # noqa: E402
+
+
+def test_select_and_make_windows(tmp_path):
+    src = tmp_path / "v.txt"
+    src.write_text("20 100 +A # 1\n20 100 +A -CG # 2 3\n20 105 -T # 2\n20 400 +GG # 1\n20 900 -AAAA # 5\n")
+    sel = tmp_path / "sel.txt"
+    make_windows.select_candidates(str(src), str(sel), 2)
+    assert sel.read_text() == "20 100 +A # 3\n20 100 -CG # 3\n20 105 -T # 2\n20 900 -AAAA # 5\n"
+    files = make_windows.split_and_merge(str(sel), str(tmp_path / "w"), 20, 1000)
+    assert len(files) == 1
+    lines = open(files[0]).read().splitlines()
+    # 100 and 105 cluster (<= minDist apart); window = [min refStart - 60, max refEnd + 60]
+    assert lines[0] == "20 40 165 100,+A 100,-CG 105,-T"
+    assert lines[1] == "20 840 963 900,-AAAA"
+
+
+def test_merge_restatement_vcf_line(tmp_path):
+    fa = tmp_path / "r.fa"
+    seq = "ACGTTGCA" * 20
+    fa.write_text(">20\n" + "\n".join(seq[i:i + 60] for i in range(0, len(seq), 60)) + "\n")
+    (tmp_path / "r.fa.fai").write_text("20\t%d\t4\t60\t61\n" % len(seq))
+    hdr = ("msg index analysis_type tid lpos rpos center_position realigned_position was_candidate_in_window "
+           "ref_all nref_all num_reads post_prob_variant qual est_freq logZ hapfreqs indidx msq numOffAll num_indel "
+           "num_cover_forward num_cover_reverse num_unmapped_realigned var_coverage_forward var_coverage_reverse "
+           "nBQT nmmBQT mLogBQ nMMLeft nMMRight glf")
+    row = ("ok 1 dip.map 20 10 130 70 64 1 NA -GT 50 NA 321.9 NA NA NA 0 57.1 NA NA 18 24 0 8 12 NA NA NA NA NA "
+           "0/1:143.7")
+    glf = tmp_path / "a.glf.txt"
+    glf.write_text(hdr + "\n" + row + "\n")
+    n = merge_diploid.merge_output([str(glf)], str(fa), str(tmp_path / "o.vcf"))
+    assert n == 1
+    last = open(tmp_path / "o.vcf").read().splitlines()[-1].split("\t")
+    # realigned_position 64 (0-based) -> fetch 1-based pos 64 = seq[63:66]; deletion of the 2 bases after it
+    assert last[0:2] == ["20", "64"] and last[3] == seq[63:66] and last[4] == seq[63]
+    assert last[5] == "321" and last[6] == "PASS" and last[-1] == "0/1:143"
+    assert last[7].startswith("DP=50;NF=8;NR=12;NRS=18;NFS=24;HP=")
+
+
+def _truth_indels(path):
+    out = []
+    for line in open(path):
+        chrom, pos, kind, ln, alt, gt = line.split()
+        if kind in ("ins", "del"):
+            out.append((int(pos), kind, int(ln), gt))
+    return out
+
+
+def test_cpu_reference_pipeline_recovers_planted_indels(tmp_path):
+    if not run_e2e.have_binaries(("cpu",)):
+        pytest.skip("oracle/_ref/dindel_ref not built (reference sources absent)")
+    work = str(tmp_path)
+    prep = run_e2e.prepare(work, 40000, seed=3, per_file=8)
+    assert prep["n_windows"] >= 10 and len(prep["window_files"]) >= 2
+    glfs, vcf, wall, n_calls = run_e2e.run_arm("cpu", prep, work, procs=4)
+    calls = {}
+    for line in open(vcf):
+        if line.startswith("#"):
+            continue
+        d = line.split("\t")
+        if len(d[3]) != len(d[4].split(",")[0]):
+            calls[int(d[1])] = (d[3], d[4], d[9].split(":")[0])
+    truth = _truth_indels(os.path.join(work, "truth.txt"))
+    assert len(truth) >= 10
+    hit = 0
+    for pos, kind, ln, gt in truth:
+        for p in range(pos - 12, pos + 3):   # dindel left-aligns; VCF pos is the base before the event
+            if p in calls:
+                ref, alt, g = calls[p]
+                if (len(ref) - len(alt) == ln if kind == "del" else len(alt) - len(ref) == ln):
+                    hit += (g == ("1/1" if gt == "1|1" else "0/1"))
+                    break
+    assert hit >= 0.8 * len(truth), (hit, len(truth))
+
+
+def test_patched_binary_has_no_cpu_path(tmp_path):
+    """Without a CUDA device every window of the GPU-backed binary is skipped with the library's error;
+    nothing falls back to the reference's CPU loop."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CUDA device present")
+    if not run_e2e.have_binaries(("cpu", "gpu")):
+        pytest.skip("oracle/_ref binaries not built")
+    work = str(tmp_path)
+    prep = run_e2e.prepare(work, 20000, seed=5)
+    glfs, vcf, wall, n_calls = run_e2e.run_arm("gpu", prep, work, procs=1)
+    assert n_calls == 0
+    body = [l for l in open(glfs[0]).read().splitlines()[1:]]
+    assert body and all(("no_usable_CUDA_device" in l) or l.startswith("error_too_few_reads") for l in body), body[:3]
+
+
+@pytest.mark.gpu
+def test_glf_and_vcf_identical_to_cpu_reference(tmp_path):
+    if not run_e2e.have_binaries(("cpu", "gpu")):
+        pytest.skip("oracle/_ref/dindel_ref / dindel_b200 not built (reference sources absent at build time)")
+    r = subprocess.run([sys.executable, os.path.join(E2E, "run_e2e.py"), "--work", str(tmp_path), "--length", "120000",
+                        "--seed", "2", "--arms", "cpu,gpu", "--windows-per-file", "20"],
+                       capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout + r.stderr
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    assert res["glf_identical"] and res["vcf_identical"], res
+    assert res["cpu"]["vcf_calls"] >= 20 and res["cpu"]["windows_ok"] >= 40, res
