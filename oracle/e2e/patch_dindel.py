@@ -13,6 +13,7 @@ import re
 import sys
 
 src, dst = sys.argv[1], sys.argv[2]
+check = len(sys.argv) > 3 and sys.argv[3] == "--check"   # differential build, see CHECK below
 text = open(src, encoding="latin-1").read()
 
 inc = '#include "Faster.hpp"\n'
@@ -30,5 +31,36 @@ fwd = ("\t{ // dindel_b200 drop-in (INTEGRATION.md section 0)\n"
        "\t\tgpu->computeLikelihoods(haps, reads, liks, leftPos, rightPos, onHap);\n"
        "\t\treturn;\n"
        "\t}\n")
+# --check: oracle/_ref/dindel_b200_check.  After the GPU call the reference's own CPU loop runs on the same
+# window and every MLAlignment field is compared pair by pair (a differential harness on the inputs the real
+# pipeline produces: candidate haplotypes from HaplotypeDistribution, reads as they come out of the BAM);
+# one "B200CHECK" line per window on stderr, the GPU result is what the driver continues with.
+CHECK = r"""
+		{
+			static long nPairs = 0, nBad = 0;
+			long bad0 = nBad;
+			for (size_t hidx=0;hidx<haps.size();hidx++) for (size_t r=0;r<reads.size();r++) {
+				ObservationModelFBMaxErr oms(haps[hidx], reads[r], leftPos, params.obsParams);
+				MLAlignment c = oms.calcLikelihood();
+				const MLAlignment & g = liks[hidx][r];
+				bool same = c.ll==g.ll && c.llOn==g.llOn && c.llOff==g.llOff && c.offHap==g.offHap && c.offHapHMQ==g.offHapHMQ
+					&& c.firstBase==g.firstBase && c.lastBase==g.lastBase && c.numIndels==g.numIndels && c.numMismatch==g.numMismatch
+					&& c.nBQT==g.nBQT && c.nmmBQT==g.nmmBQT && c.mLogBQ==g.mLogBQ && c.nMMLeft==g.nMMLeft && c.nMMRight==g.nMMRight
+					&& c.hpos==g.hpos && c.align==g.align && c.hapIndelCovered==g.hapIndelCovered && c.hapSNPCovered==g.hapSNPCovered
+					&& c.indels.size()==g.indels.size() && c.snps.size()==g.snps.size();
+				if (same) {
+					map<int, AlignedVariant>::const_iterator a=c.indels.begin(), b=g.indels.begin();
+					for (;a!=c.indels.end();a++,b++) if (a->first!=b->first || a->second.getString()!=b->second.getString()) same=false;
+					a=c.snps.begin(); b=g.snps.begin();
+					for (;a!=c.snps.end();a++,b++) if (a->first!=b->first || a->second.getString()!=b->second.getString()) same=false;
+				}
+				nPairs++;
+				if (!same) { nBad++; cerr << "B200CHECK mismatch leftPos " << leftPos << " hap " << hidx << " read " << r << " " << bam1_qname(reads[r].getBam()) << " ll " << c.ll << " vs " << g.ll << endl; }
+			}
+			cerr << "B200CHECK window leftPos " << leftPos << " pairs " << haps.size()*reads.size() << " mismatches " << (nBad-bad0) << " total_pairs " << nPairs << " total_mismatches " << nBad << endl;
+		}
+"""
+if check:
+    fwd = fwd.replace("\t\treturn;\n", CHECK + "\t\treturn;\n")
 text = text[:m.end()] + fwd + text[m.end():]
 open(dst, "w", encoding="latin-1").write(text)
