@@ -42,7 +42,9 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--windows", type=int, default=100000, help="windows per GPU (configs[1]: 100k)")
     ap.add_argument("--cfg", type=int, default=2)
-    ap.add_argument("--no-hpos", action="store_true", help="e2e without the per-base hpos rows")
+    ap.add_argument("--no-hpos", action="store_true", help="no per-base hpos rows at all (K1 only, no K4)")
+    ap.add_argument("--hpos-d2h", action="store_true",
+                    help="e2e copies the hpos rows to the host (host-side filterHaplotypes) instead of running K4 on them")
     ap.add_argument("--cpu-windows", type=int, default=0, help="cpu_baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -265,23 +267,71 @@ def main():
     win_status = pinned_copy(lib, np.zeros(batch.n_windows, dtype=np.int32))
     on_hap = pinned_copy(lib, np.zeros(batch.n_reads, dtype=np.uint8))
     stride = (int(np.max(np.diff(batch.read_off))) + 7) & ~7
-    hpos = None if args.no_hpos else pinned_copy(lib, np.zeros((n_pairs, stride), dtype=np.int16))
+    use_k4 = not args.no_hpos and not args.hpos_d2h
+    hpos = pinned_copy(lib, np.zeros((n_pairs, stride), dtype=np.int16)) if args.hpos_d2h else None
     o = engine._BatchOut()
+    if use_k4:
+        o.flags = engine.OUT_KEEP_HPOS
+    # K4 inputs (filterHaplotypes, DInDel.cpp:1932-2100): per haplotype one *REF-like entry and, for the
+    # non-reference haplotypes, one candidate-indel entry over the middle of the haplotype (+-padCover), keyed per
+    # haplotype; strands from the read flags.  Built once (host string logic in the reference), copied every step.
+    cov = None
+    if use_k4:
+        nh_w = np.diff(batch.win_hap).astype(np.int64)
+        H = np.diff(batch.hap_off).astype(np.int64)
+        hidx = np.arange(batch.n_haps) - np.repeat(batch.win_hap[:-1], nh_w)       # hap index inside its window
+        alt = hidx > 0
+        ne_h = 1 + alt.astype(np.int64)                                             # entries per haplotype
+        e_hap = np.repeat(hidx, ne_h).astype(np.int32)
+        first = np.concatenate([[0], np.cumsum(ne_h)[:-1]])
+        e_type = np.full(int(ne_h.sum()), engine.VAR_OTHER, dtype=np.uint8)
+        e_key = np.zeros(len(e_type), dtype=np.int32)
+        e_left = np.zeros(len(e_type), dtype=np.int32)
+        e_right = np.zeros(len(e_type), dtype=np.int32)
+        ai = first[alt] + 1
+        e_type[ai] = np.where(hidx[alt] % 2 == 1, engine.VAR_INS, engine.VAR_DEL)
+        e_key[ai] = hidx[alt]
+        e_left[ai] = (H[alt] // 2 - 6).astype(np.int32)
+        e_right[ai] = (H[alt] // 2 + 6).astype(np.int32)
+        ne_w = np.add.reduceat(ne_h, batch.win_hap[:-1].astype(np.int64)) if batch.n_windows else np.zeros(0, np.int64)
+        win_entry = np.concatenate([[0], np.cumsum(ne_w)]).astype(np.int64)
+        win_key = np.concatenate([[0], np.cumsum(nh_w)]).astype(np.int64)
+        strand = ((batch.read_flags >> 1) & 1).astype(np.uint8)
+        ci, co = engine._CoverIn(), engine._CoverOut()
+        keep = [pinned_copy(lib, x) for x in (win_entry, win_key, e_hap, e_key, e_type, e_left, e_right, strand)]
+        ci.n_entries, ci.n_keys, ci.maxMismatch, ci.doFilter = len(e_type), int(win_key[-1]), 2, 0
+        (ci.win_entry, ci.win_key, ci.entry_hap, ci.entry_key, ci.entry_type, ci.entry_left, ci.entry_right,
+         ci.read_strand) = [x.ctypes.data for x in keep]
+        filt = pinned_copy(lib, np.zeros(batch.n_haps, dtype=np.uint8))
+        knf = pinned_copy(lib, np.zeros(int(win_key[-1]), dtype=np.int32))
+        knr = pinned_copy(lib, np.zeros(int(win_key[-1]), dtype=np.int32))
+        co.hap_filtered, co.key_nf, co.key_nr = filt.ctypes.data, knf.ctypes.data, knr.ctypes.data
+        cov = (ci, co, sum(x.nbytes for x in keep), filt.nbytes + knf.nbytes + knr.nbytes, knf, knr)
     o.n_pairs, o.pairs, o.win_pair = n_pairs, pairs.ctypes.data, win_pair.ctypes.data
     o.win_status, o.read_on_hap = win_status.ctypes.data, on_hap.ctypes.data
     if hpos is not None:
         o.hpos, o.hpos_stride = hpos.ctypes.data, stride
     cb = pb._c()
-    h2d = batch.input_bytes() + 2 * 8 * (batch.n_windows + 1)
-    d2h = pairs.nbytes + win_status.nbytes + on_hap.nbytes + (hpos.nbytes if hpos is not None else 0)
-    for _ in range(max(1, args.warmup - 1)):
+    h2d = batch.input_bytes() + 2 * 8 * (batch.n_windows + 1) + (cov[2] if cov else 0)
+    d2h = pairs.nbytes + win_status.nbytes + on_hap.nbytes + (hpos.nbytes if hpos is not None else 0) + (cov[3] if cov else 0)
+
+    def e2e_step():
         eng._check(lib.dindel_b200_submit(eng.h, C.byref(cb), C.byref(o)), "submit")
+        dev = eng.timing().total_ms
+        t0 = time.perf_counter()
+        if cov:
+            eng._check(lib.dindel_b200_coverage(eng.h, C.byref(cov[0]), C.byref(cov[1])), "coverage")
+        return dev, 1e3 * (time.perf_counter() - t0)
+
+    for _ in range(max(1, args.warmup - 1)):
+        e2e_step()
     barrier()
     e0 = time.perf_counter()
-    e2e_dev = 0.0
+    e2e_dev, k4_ms = 0.0, 0.0
     for _ in range(args.steps):
-        eng._check(lib.dindel_b200_submit(eng.h, C.byref(cb), C.byref(o)), "submit")
-        e2e_dev += eng.timing().total_ms
+        d, k = e2e_step()
+        e2e_dev += d
+        k4_ms += k
     barrier()
     e2e_wall = 1e3 * (time.perf_counter() - e0)
     e2e_ms = max_over_ranks(e2e_wall) / args.steps  # host wall clock around submit (includes host indexing)
@@ -300,7 +350,12 @@ def main():
             "gcups": gcups,
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": e2e_ms, "device_ms_per_step": e2e_dev / args.steps, "gcups": world * n_cells / (e2e_ms * 1e-3) / 1e9,
-                    "hpos": hpos is not None, "ll_checksum": checksum},
+                    "path": ("K1 + K4: submit (H2D, kernels, D2H of the 64-byte pair records) then dindel_b200_coverage "
+                             "(filterHaplotypes on the hpos rows where K1 left them in HBM)") if cov else
+                            ("K1, hpos rows copied to the host" if hpos is not None else "K1 only, no hpos rows"),
+                    "k4_ms_per_step": (k4_ms / args.steps) if cov else None,
+                    "k4_covering_reads": int(cov[4].sum() + cov[5].sum()) if cov else None,
+                    "hpos_d2h": hpos is not None, "ll_checksum": checksum},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "fp64-issue", "achieved": (n_cells * w_cell / (ms_per_step * 1e-3)) / 1e12,

@@ -11,6 +11,7 @@
 #include <vector>
 #include "k1_common.cuh"
 #include "k23.cuh"
+#include "k4.cuh"
 
 extern "C" size_t k1_generic_smem_per_warp(int maxS, int maxR, int bt_in_smem);
 extern "C" cudaError_t k1_generic_launch(const K1Batch *B, int grid, int warps_per_cta,
@@ -23,6 +24,8 @@ extern "C" cudaError_t k1_tiled_prepare(const K1Batch *B, cudaStream_t stream, i
 extern "C" cudaError_t k2_launch(const K2Args *a, cudaStream_t st);
 extern "C" cudaError_t k3_launch(const K3Args *a, cudaStream_t st);
 extern "C" int k3_max_haps(void);
+extern "C" size_t k4_smem_bytes(int ne, int nk, int nr, int nh);
+extern "C" cudaError_t k4_launch(const K4Args *a, int n_windows, size_t smem, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------------
 // small device kernels owned by the API layer
@@ -801,7 +804,8 @@ int dindel_b200_hpos_stride(const dindel_ctx *ctx) { return ctx && ctx->resident
 int dindel_b200_submit(dindel_ctx *ctx, const dindel_batch_in *in, dindel_batch_out *out)
 {
     if (!ctx || !out) return DINDEL_E_INVALID;
-    int rc = prepare_batch(ctx, in, out->hpos != nullptr, out->hpos ? out->hpos_stride : 0);
+    const bool keep_hpos = (out->flags & DINDEL_OUT_KEEP_HPOS) != 0; // rows stay in HBM for K4
+    int rc = prepare_batch(ctx, in, out->hpos != nullptr || keep_hpos, out->hpos ? out->hpos_stride : 0);
     if (rc != DINDEL_OK) return rc;
     rc = check_out(ctx, out);
     if (rc != DINDEL_OK) return rc;
@@ -992,6 +996,83 @@ int dindel_b200_bayes_em(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out 
     if (nv) {
         CU(cudaMemcpyAsync(out->pi, a.pi, nv * 8, cudaMemcpyDeviceToHost, st));
         CU(cudaMemcpyAsync(out->freqs, a.freqs, nv * 8, cudaMemcpyDeviceToHost, st));
+    }
+    CU(cudaStreamSynchronize(st));
+    return DINDEL_OK;
+}
+
+int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cover_out *out)
+{
+    if (!ctx || !in || !out || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "coverage needs a resident, computed batch");
+    const K1Batch &B = ctx->B;
+    if (!B.hpos) return fail(ctx, DINDEL_E_INVALID, "coverage needs the hpos rows resident (upload(want_hpos) or DINDEL_OUT_KEEP_HPOS)");
+    if (in->n_entries < 0 || in->n_keys < 0) return fail(ctx, DINDEL_E_INVALID, "n_entries / n_keys");
+    if (!in->win_entry || !in->win_key || !out->hap_filtered || (in->n_keys && (!out->key_nf || !out->key_nr)))
+        return fail(ctx, DINDEL_E_INVALID, "null array");
+    if (in->n_entries && (!in->entry_hap || !in->entry_key || !in->entry_type || !in->entry_left || !in->entry_right))
+        return fail(ctx, DINDEL_E_INVALID, "null array");
+    if (B.n_reads && !in->read_strand) return fail(ctx, DINDEL_E_INVALID, "read_strand");
+    const int nw = B.n_windows;
+    if (in->win_entry[0] != 0 || in->win_key[0] != 0 || in->win_entry[nw] != in->n_entries || in->win_key[nw] != in->n_keys)
+        return fail(ctx, DINDEL_E_INVALID, "win_entry / win_key do not span the entries / keys");
+    size_t smem = 0;
+    for (int w = 0; w < nw; w++) {
+        const long long ne = in->win_entry[w + 1] - in->win_entry[w], nk = in->win_key[w + 1] - in->win_key[w];
+        if (ne < 0 || nk < 0) return fail(ctx, DINDEL_E_INVALID, "win_entry / win_key not monotone");
+        const int nh = ctx->win_nh[w];
+        const long long np = ctx->win_pair[w + 1] - ctx->win_pair[w];
+        const int nr = nh ? (int)(np / nh) : 0;
+        int prev_h = 0;
+        for (long long e = in->win_entry[w]; e < in->win_entry[w + 1]; e++) {
+            if (in->entry_hap[e] < prev_h || in->entry_hap[e] >= nh) return fail(ctx, DINDEL_E_INVALID, "entry_hap not sorted / out of range");
+            if (in->entry_key[e] < 0 || in->entry_key[e] >= nk) return fail(ctx, DINDEL_E_INVALID, "entry_key out of range");
+            prev_h = in->entry_hap[e];
+        }
+        const size_t s = k4_smem_bytes((int)ne, (int)nk, nr, nh);
+        if (s > smem) smem = s;
+    }
+    if (smem > ctx->smem_optin) return fail(ctx, DINDEL_E_UNSUPPORTED, "window has too many (variant entries x reads) for one CTA's shared memory");
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const size_t ne = (size_t)in->n_entries, nk = (size_t)in->n_keys, nh = (size_t)B.n_haps, nr = (size_t)B.n_reads;
+    // one staging buffer: [win_entry | win_key | entry_hap | entry_key | entry_left | entry_right | entry_type | read_strand]
+    const size_t o_we = 0, o_wk = o_we + ((size_t)nw + 1) * 8, o_eh = o_wk + ((size_t)nw + 1) * 8, o_ek = o_eh + ne * 4,
+                 o_el = o_ek + ne * 4, o_er = o_el + ne * 4, o_et = o_er + ne * 4, o_rs = o_et + ((ne + 7) & ~(size_t)7),
+                 in_bytes = o_rs + ((nr + 7) & ~(size_t)7);
+    // results: [key_nf | key_nr | hap_filtered | hap_uncovered]
+    const size_t r_nf = 0, r_nr = r_nf + nk * 4, r_hf = r_nr + nk * 4, r_hu = r_hf + ((nh + 7) & ~(size_t)7),
+                 out_bytes = r_hu + ((nh + 7) & ~(size_t)7);
+    CU(ctx->d_x[0].ensure(in_bytes + 16));
+    CU(ctx->d_x[1].ensure(out_bytes + 16));
+    char *d_in = (char *)ctx->d_x[0].p, *d_out = (char *)ctx->d_x[1].p;
+    CU(cudaMemcpyAsync(d_in + o_we, in->win_entry, ((size_t)nw + 1) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_in + o_wk, in->win_key, ((size_t)nw + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (ne) {
+        CU(cudaMemcpyAsync(d_in + o_eh, in->entry_hap, ne * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_ek, in->entry_key, ne * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_el, in->entry_left, ne * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_er, in->entry_right, ne * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_et, in->entry_type, ne, cudaMemcpyHostToDevice, st));
+    }
+    if (nr) CU(cudaMemcpyAsync(d_in + o_rs, in->read_strand, nr, cudaMemcpyHostToDevice, st));
+    K4Args a;
+    a.maxMismatch = in->maxMismatch; a.doFilter = in->doFilter;
+    a.win_entry = (const long long *)(d_in + o_we); a.win_key = (const long long *)(d_in + o_wk);
+    a.entry_hap = (const int32_t *)(d_in + o_eh); a.entry_key = (const int32_t *)(d_in + o_ek);
+    a.entry_left = (const int32_t *)(d_in + o_el); a.entry_right = (const int32_t *)(d_in + o_er);
+    a.entry_type = (const uint8_t *)(d_in + o_et); a.read_strand = (const uint8_t *)(d_in + o_rs);
+    a.key_nf = (int32_t *)(d_out + r_nf); a.key_nr = (int32_t *)(d_out + r_nr);
+    a.hap_filtered = (uint8_t *)(d_out + r_hf); a.hap_uncovered = (uint8_t *)(d_out + r_hu);
+    a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.hap_off = B.hap_off; a.read_off = B.read_off;
+    a.hap_seq = B.hap_seq; a.read_seq = B.read_seq; a.pairs = B.pairs; a.hpos = B.hpos; a.hpos_stride = B.hpos_stride;
+    CU(k4_launch(&a, nw, smem, st));
+    if (nk) {
+        CU(cudaMemcpyAsync(out->key_nf, a.key_nf, nk * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(out->key_nr, a.key_nr, nk * 4, cudaMemcpyDeviceToHost, st));
+    }
+    if (nh) {
+        CU(cudaMemcpyAsync(out->hap_filtered, a.hap_filtered, nh, cudaMemcpyDeviceToHost, st));
+        if (out->hap_uncovered) CU(cudaMemcpyAsync(out->hap_uncovered, a.hap_uncovered, nh, cudaMemcpyDeviceToHost, st));
     }
     CU(cudaStreamSynchronize(st));
     return DINDEL_OK;

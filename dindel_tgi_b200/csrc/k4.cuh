@@ -1,0 +1,19 @@
+// k4.cuh — launch arguments of the haplotype-filter / variant-coverage kernel (k4_coverage.cu).
+#pragma once
+#include "k1_common.cuh"
+
+struct K4Args {
+    int maxMismatch, doFilter;
+    const long long *win_entry, *win_key;
+    const int32_t *entry_hap, *entry_key, *entry_left, *entry_right;
+    const uint8_t *entry_type, *read_strand;
+    uint8_t *hap_filtered, *hap_uncovered; // hap_uncovered may be null
+    int32_t *key_nf, *key_nr;
+    // resident batch
+    const int32_t *win_hap, *win_read;
+    const long long *win_pair, *hap_off, *read_off;
+    const uint8_t *hap_seq, *read_seq;
+    const dindel_pair_out *pairs;
+    const int16_t *hpos;
+    int hpos_stride;
+};

@@ -43,7 +43,7 @@ class _BatchIn(C.Structure):
 
 class _BatchOut(C.Structure):
     _fields_ = [("n_pairs", C.c_int64), ("pairs", C.c_void_p), ("hpos", C.c_void_p),
-                ("hpos_stride", C.c_int32), ("reserved", C.c_int32), ("win_pair", C.c_void_p),
+                ("hpos_stride", C.c_int32), ("flags", C.c_int32), ("win_pair", C.c_void_p),
                 ("win_status", C.c_void_p), ("read_on_hap", C.c_void_p)]
 
 
@@ -62,6 +62,22 @@ class _PairSumIn(C.Structure):
 class _EmIn(C.Structure):
     _fields_ = [("n_sets", C.c_int32), ("reserved", C.c_int32), ("set_window", C.c_void_p),
                 ("set_off", C.c_void_p), ("compatible", C.c_void_p), ("a0", C.c_double), ("tol", C.c_double)]
+
+
+class _CoverIn(C.Structure):
+    _fields_ = [("n_entries", C.c_int32), ("n_keys", C.c_int32), ("maxMismatch", C.c_int32), ("doFilter", C.c_int32),
+                ("win_entry", C.c_void_p), ("win_key", C.c_void_p), ("entry_hap", C.c_void_p), ("entry_key", C.c_void_p),
+                ("entry_type", C.c_void_p), ("entry_left", C.c_void_p), ("entry_right", C.c_void_p),
+                ("read_strand", C.c_void_p)]
+
+
+class _CoverOut(C.Structure):
+    _fields_ = [("hap_filtered", C.c_void_p), ("hap_uncovered", C.c_void_p), ("key_nf", C.c_void_p),
+                ("key_nr", C.c_void_p)]
+
+
+OUT_KEEP_HPOS = 1
+VAR_DEL, VAR_INS, VAR_OTHER = 0, 1, 2
 
 
 class _EmOut(C.Structure):
@@ -84,7 +100,7 @@ EXPORTS = [
     "dindel_b200_upload", "dindel_b200_run", "dindel_b200_download", "dindel_b200_sync",
     "dindel_b200_get_timing", "dindel_b200_hpos_stride", "dindel_b200_alloc_pinned",
     "dindel_b200_free_pinned", "dindel_b200_measure_fp64_peak", "dindel_b200_pair_sums",
-    "dindel_b200_bayes_em", "dindel_b200_plan_shards",
+    "dindel_b200_bayes_em", "dindel_b200_plan_shards", "dindel_b200_coverage",
 ]
 
 _lib = None
@@ -122,6 +138,7 @@ def load_library():
     lib.dindel_b200_measure_fp64_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
     lib.dindel_b200_pair_sums.argtypes = [C.c_void_p, C.POINTER(_PairSumIn), C.c_void_p]
     lib.dindel_b200_bayes_em.argtypes = [C.c_void_p, C.POINTER(_EmIn), C.POINTER(_EmOut)]
+    lib.dindel_b200_coverage.argtypes = [C.c_void_p, C.POINTER(_CoverIn), C.POINTER(_CoverOut)]
     lib.dindel_b200_plan_shards.argtypes = [C.POINTER(_BatchIn), C.c_int, C.c_void_p]
     _lib = lib
     return lib
@@ -314,11 +331,15 @@ class Engine:
         self.lib.dindel_b200_get_timing(self.h, C.byref(t))
         return t
 
-    def compute_likelihoods(self, batch, want_hpos=True):
-        """Host buffers in, host buffers out: dindel_b200_submit."""
+    def compute_likelihoods(self, batch, want_hpos=True, keep_hpos=False):
+        """Host buffers in, host buffers out: dindel_b200_submit.  keep_hpos: the hpos rows are produced and stay
+        resident in HBM for coverage() without being copied to the host (DINDEL_OUT_KEEP_HPOS)."""
         o, pairs, win_pair, win_status, on_hap, hpos = self._alloc_out(batch, want_hpos)
+        if keep_hpos:
+            o.flags = OUT_KEEP_HPOS
         cb = batch._c()
         self._check(self.lib.dindel_b200_submit(self.h, C.byref(cb), C.byref(o)), "submit")
+        self._resident, self._n_haps = (batch, want_hpos or keep_hpos), batch.n_haps
         return PairResults(pairs, win_pair, win_status, on_hap, hpos, self.timing())
 
     # resident-batch API (bench: kernel-only timing with inputs already in HBM)
@@ -361,6 +382,32 @@ class Engine:
         a.read_group = rg.ctypes.data if rg is not None else None
         self._check(self.lib.dindel_b200_pair_sums(self.h, C.byref(a), out.ctypes.data), "pair_sums")
         return [out[off[j]:off[j + 1]] for j in range(nj)]
+
+    def coverage(self, win_entries, win_nkeys, read_strand, max_mismatch=2, do_filter=False):
+        """K4 (DetInDel::filterHaplotypes, DInDel.cpp:1932-2100) over the resident batch.  win_entries: per
+        window a list of (hap, key, type, left, right) sorted by hap (map order inside a hap); win_nkeys: keys per
+        window.  Returns (hap_filtered[n_haps], hap_uncovered[n_haps], [nf arrays per window], [nr arrays])."""
+        nw = len(win_entries)
+        we = np.concatenate([[0], np.cumsum([len(e) for e in win_entries])]).astype(np.int64)
+        wk = np.concatenate([[0], np.cumsum(win_nkeys)]).astype(np.int64)
+        flat = [x for e in win_entries for x in e]
+        e = np.array(flat, dtype=np.int64).reshape(len(flat), 5) if flat else np.zeros((0, 5), dtype=np.int64)
+        eh, ek, el, er = (np.ascontiguousarray(e[:, i], dtype=np.int32) for i in (0, 1, 3, 4))
+        et = np.ascontiguousarray(e[:, 2], dtype=np.uint8)
+        rs = np.ascontiguousarray(read_strand, dtype=np.uint8)
+        batch = self._resident[0] if getattr(self, "_resident", None) else None
+        nh_tot = batch.n_haps if batch is not None else int(self._n_haps)
+        filt, unc = np.zeros(max(nh_tot, 1), dtype=np.uint8), np.zeros(max(nh_tot, 1), dtype=np.uint8)
+        nf, nr = np.zeros(max(int(wk[-1]), 1), dtype=np.int32), np.zeros(max(int(wk[-1]), 1), dtype=np.int32)
+        a, o = _CoverIn(), _CoverOut()
+        a.n_entries, a.n_keys, a.maxMismatch, a.doFilter = len(flat), int(wk[-1]), int(max_mismatch), int(bool(do_filter))
+        a.win_entry, a.win_key = we.ctypes.data, wk.ctypes.data
+        a.entry_hap, a.entry_key, a.entry_type = eh.ctypes.data, ek.ctypes.data, et.ctypes.data
+        a.entry_left, a.entry_right, a.read_strand = el.ctypes.data, er.ctypes.data, rs.ctypes.data
+        o.hap_filtered, o.hap_uncovered, o.key_nf, o.key_nr = filt.ctypes.data, unc.ctypes.data, nf.ctypes.data, nr.ctypes.data
+        self._check(self.lib.dindel_b200_coverage(self.h, C.byref(a), C.byref(o)), "coverage")
+        return (filt[:nh_tot], unc[:nh_tot], [nf[wk[w]:wk[w + 1]] for w in range(nw)],
+                [nr[wk[w]:wk[w + 1]] for w in range(nw)])
 
     def bayes_em(self, set_window, compatible, a0=0.001, tol=1e-4):
         """K3 (estimateHaplotypeFrequenciesBayesEM core).  compatible: list of uint8 arrays (nh each).

@@ -92,6 +92,10 @@ typedef struct dindel_pair_out {
     uint8_t pad[4];
 } dindel_pair_out;
 
+/* dindel_batch_out.flags: produce the hpos rows and keep them resident in HBM for
+ * dindel_b200_coverage even when out->hpos == NULL (they then never cross PCIe). */
+#define DINDEL_OUT_KEEP_HPOS 1
+
 /* Results, caller-allocated.  Pair (w, h, r) lives at win_pair[w] + r*nh(w) + h  (r-major, like
  * rl[r*nh+h] at DInDel.cpp:2129).  win_pair is filled by the library ([n_windows+1]). */
 typedef struct dindel_batch_out {
@@ -99,7 +103,7 @@ typedef struct dindel_batch_out {
     dindel_pair_out *pairs;     /* [n_pairs] */
     int16_t *hpos;              /* optional [n_pairs * hpos_stride]: MLAlignment::hpos */
     int32_t hpos_stride;        /* >= longest read when hpos != NULL */
-    int32_t reserved;
+    int32_t flags;              /* DINDEL_OUT_* */
     int64_t *win_pair;          /* [n_windows+1] */
     int32_t *win_status;        /* [n_windows] DINDEL_WIN_* (first failing pair's reason) */
     uint8_t *read_on_hap;       /* optional [n_reads]: onHap[r] (DInDel.cpp:1720) */
@@ -183,6 +187,47 @@ typedef struct dindel_em_out {
     double *freqs;   /* [set_off[n_sets]] */
 } dindel_em_out;
 int dindel_b200_bayes_em(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out *out);
+
+/* ---- K4: haplotype filter + per-variant read coverage over the RESIDENT hpos rows -------------
+ * Replaces DetInDel::filterHaplotypes (DInDel.cpp:1932-2100), the only consumer of MLAlignment::hpos
+ * in the calling pipeline: with it the hpos rows (~200 B per pair, 85 % of the D2H bytes) stay in HBM.
+ * The host lists, per haplotype and in the map order of Haplotype::indels, one ENTRY per variant
+ * (DInDel.cpp:1962): type, the read-flank interval already widened by padCover
+ * (left = getLeftFlankRead()-padCover, right = getRightFlankRead()+padCover, :1973-1974) and a KEY id
+ * naming the (position, AlignedVariant) pair the entry stands for (`PAV`, :1943), shared by the
+ * haplotypes of a window that carry the same variant.  Per entry the reads with !offHapHMQ and
+ * numIndels == 0 (:1951) are tested: covered when every position of [left, right] is spanned by the read
+ * with at most maxMismatch mismatches against the haplotype (hap 'N' exempt for deletions only,
+ * :1997-2000, :2036-2041, :2047-2060).  A haplotype's entries after its first uncovered INS/DEL are
+ * not evaluated (the `break` at :2071); filtered[h] = doFilter && an entry was uncovered (:2078-2083);
+ * per key nf / nr = distinct covering reads on the forward / reverse strand over the unfiltered
+ * haplotypes (:2089-2097).  The reference's stray read of hpos[b] at b == hpos.size() (loop bound `<=`
+ * at :1995, :2034: heap slack) is "no hit" here, and a negative code (LO/RO/INS) never hits.
+ * Needs a resident, computed batch with hpos rows (upload(want_hpos) or DINDEL_OUT_KEEP_HPOS). */
+#define DINDEL_VAR_DEL 0
+#define DINDEL_VAR_INS 1
+#define DINDEL_VAR_OTHER 2 /* SNP / *REF entries of Haplotype::indels: key exists, no coverage test */
+typedef struct dindel_cover_in {
+    int32_t n_entries;          /* over the whole batch */
+    int32_t n_keys;             /* over the whole batch */
+    int32_t maxMismatch;        /* params.obsParams.maxMismatch (--flankMaxMismatch, DInDel.cpp:3949) */
+    int32_t doFilter;           /* params.filterHaplotypes */
+    const int64_t *win_entry;   /* [n_windows+1] window -> its entries, sorted by (haplotype, map order) */
+    const int64_t *win_key;     /* [n_windows+1] window -> its keys */
+    const int32_t *entry_hap;   /* [n_entries] haplotype index inside the window */
+    const int32_t *entry_key;   /* [n_entries] key index inside the window */
+    const uint8_t *entry_type;  /* [n_entries] DINDEL_VAR_* */
+    const int32_t *entry_left;  /* [n_entries] */
+    const int32_t *entry_right; /* [n_entries] */
+    const uint8_t *read_strand; /* [n_reads] 1 = counted on the reverse strand: unmapped ? !mateIsReverse()
+                                   : isReverse() (DInDel.cpp:1987-1992) */
+} dindel_cover_in;
+typedef struct dindel_cover_out {
+    uint8_t *hap_filtered;      /* [n_haps] filtered[h] */
+    uint8_t *hap_uncovered;     /* optional [n_haps] !allCovered, whatever doFilter says */
+    int32_t *key_nf, *key_nr;   /* [n_keys] VariantCoverage (DInDel.hpp:53-66) */
+} dindel_cover_out;
+int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cover_out *out);
 
 /* pinned host memory for the caller's buffers */
 void *dindel_b200_alloc_pinned(size_t bytes);

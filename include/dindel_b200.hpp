@@ -41,6 +41,14 @@ struct ReadTraits {
 #endif
     static uint32_t start(const ReadT &r) { return uint32_t(r.posStat.first); }                      // ObservationModelFB.cpp:52
     static bool reverse(const ReadT &r) { return r.onReverseStrand; }
+#ifdef BAM_BAM_H
+    // strand a covering read is counted on (DInDel.cpp:1987-1992): unmapped ? !mateIsReverse() : isReverse()
+    static bool coverReverse(const ReadT &r)
+    {
+        const unsigned f = r.getBam()->core.flag;
+        return (f & BAM_FUNMAP) ? !(f & BAM_FMREVERSE) : (f & BAM_FREVERSE) != 0;
+    }
+#endif
 };
 
 // RAII owner of one dindel_ctx (one device).  Construct from anything with the fields of
@@ -48,7 +56,7 @@ struct ReadTraits {
 class Engine {
 public:
     template <class ObsParams>
-    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0)
+    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0), last_nh_(0), last_nr_(0)
     {
         dindel_b200_default_params(&p_);
         p_.pError = op.pError; p_.pMut = op.pMut; p_.mapQualThreshold = op.mapQualThreshold;
@@ -67,11 +75,22 @@ public:
                             std::vector<std::vector<MLA> > &liks, uint32_t leftPos, uint32_t rightPos,
                             std::vector<int> &onHap);
 
+    // Drop-in for DetInDel::filterHaplotypes(haps, reads, liks, filtered, varCoverage, doFilter)
+    // (DInDel.cpp:1932-2100) on the window computeLikelihoods was last called with: the per-base hpos rows
+    // are tested on the GPU (dindel_b200_coverage) where K1 left them; only filtered[] and the (nf, nr)
+    // counts come back.  CovMap = map<pair<int, AlignedVariant>, VariantCoverage> (any mapped type
+    // constructible from (nf, nr)).  Returns the number of filtered haplotypes (the reference prints it).
+    template <class HapT, class ReadT, class MLA, class CovMap>
+    int filterHaplotypes(const std::vector<HapT> &haps, const std::vector<ReadT> &reads,
+                         const std::vector<std::vector<MLA> > &liks, std::vector<int> &filtered,
+                         CovMap &varCoverage, bool doFilter, int maxMismatch);
+
 private:
     Engine(const Engine &);
     Engine &operator=(const Engine &);
     dindel_params p_;
     dindel_ctx *ctx_;
+    size_t last_nh_, last_nr_; // shape of the resident window (filterHaplotypes checks it is the same one)
 };
 
 // mapped types of MLA::indels and HapT::indels (C++98-friendly, the reference builds as gnu++98)
@@ -207,10 +226,12 @@ void Engine::computeLikelihoods(const std::vector<HapT> &haps, const std::vector
     int32_t status = 0;
     dindel_batch_out out;
     out.n_pairs = (int64_t)np; out.pairs = &pairs[0]; out.hpos = &hpos[0]; out.hpos_stride = stride;
-    out.reserved = 0; out.win_pair = win_pair; out.win_status = &status; out.read_on_hap = &on[0];
+    out.flags = DINDEL_OUT_KEEP_HPOS; out.win_pair = win_pair; out.win_status = &status; out.read_on_hap = &on[0];
+    last_nh_ = last_nr_ = 0;
     int rc = dindel_b200_submit(ctx_, &in, &out);
     if (rc != DINDEL_OK)
         throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx_) + ")";
+    last_nh_ = nh; last_nr_ = nr;
 
     for (size_t h = 0; h < nh; h++) {
         for (size_t r = 0; r < nr; r++) {
@@ -231,6 +252,64 @@ void Engine::computeLikelihoods(const std::vector<HapT> &haps, const std::vector
             }
         }
     }
+}
+
+template <class HapT, class ReadT, class MLA, class CovMap>
+int Engine::filterHaplotypes(const std::vector<HapT> &haps, const std::vector<ReadT> &reads,
+                             const std::vector<std::vector<MLA> > & /*liks: resident on the GPU*/,
+                             std::vector<int> &filtered, CovMap &varCoverage, bool doFilter, int maxMismatch)
+{
+    typedef ReadTraits<ReadT> RT;
+    typedef typename HapT_variant<HapT>::type AV;
+    typedef typename CovMap::key_type PAV;           // pair<int, AlignedVariant> (DInDel.cpp:1943)
+    typedef typename CovMap::mapped_type Coverage;   // VariantCoverage(nf, nr) (DInDel.hpp:53-66)
+    const size_t nh = haps.size(), nr = reads.size();
+    filtered = std::vector<int>(nh, 0);
+    varCoverage.clear();
+    if (nh == 0) return 0;
+    if (nh != last_nh_ || nr != last_nr_)
+        throw std::string("dindel_b200: filterHaplotypes called on a window other than the resident one");
+    std::map<PAV, int> keyOf; // PAV -> key index, in the map's own order (DInDel.cpp:1944)
+    std::vector<int32_t> e_hap, e_key, e_left, e_right;
+    std::vector<uint8_t> e_type, strand(nr ? nr : 1);
+    for (size_t h = 0; h < nh; h++)
+        for (typename std::map<int, AV>::const_iterator it = haps[h].indels.begin(); it != haps[h].indels.end(); ++it) {
+            const AV &av = it->second;
+            const PAV pav(it->first, av);
+            typename std::map<PAV, int>::iterator k = keyOf.find(pav);
+            if (k == keyOf.end()) k = keyOf.insert(std::make_pair(pav, (int)keyOf.size())).first;
+            e_hap.push_back((int32_t)h);
+            e_key.push_back(k->second);
+            e_type.push_back(av.getType() == AV::DEL ? DINDEL_VAR_DEL : (av.getType() == AV::INS ? DINDEL_VAR_INS : DINDEL_VAR_OTHER));
+            e_left.push_back(av.getLeftFlankRead() - p_.padCover);    // DInDel.cpp:1973
+            e_right.push_back(av.getRightFlankRead() + p_.padCover);  // DInDel.cpp:1974
+        }
+    for (size_t r = 0; r < nr; r++) strand[r] = RT::coverReverse(reads[r]) ? 1 : 0;
+    const int64_t win_entry[2] = {0, (int64_t)e_hap.size()}, win_key[2] = {0, (int64_t)keyOf.size()};
+    static const int32_t zero32 = 0;
+    static const uint8_t zero8 = 0;
+    dindel_cover_in in;
+    in.n_entries = (int32_t)e_hap.size(); in.n_keys = (int32_t)keyOf.size();
+    in.maxMismatch = maxMismatch; in.doFilter = doFilter ? 1 : 0;
+    in.win_entry = win_entry; in.win_key = win_key;
+    in.entry_hap = e_hap.empty() ? &zero32 : &e_hap[0]; in.entry_key = e_key.empty() ? &zero32 : &e_key[0];
+    in.entry_type = e_type.empty() ? &zero8 : &e_type[0];
+    in.entry_left = e_left.empty() ? &zero32 : &e_left[0]; in.entry_right = e_right.empty() ? &zero32 : &e_right[0];
+    in.read_strand = &strand[0];
+    std::vector<uint8_t> filt(nh), unc(nh);
+    std::vector<int32_t> nf(keyOf.size() ? keyOf.size() : 1), nrv(keyOf.size() ? keyOf.size() : 1);
+    dindel_cover_out out;
+    out.hap_filtered = &filt[0]; out.hap_uncovered = &unc[0]; out.key_nf = &nf[0]; out.key_nr = &nrv[0];
+    int rc = dindel_b200_coverage(ctx_, &in, &out);
+    if (rc != DINDEL_OK)
+        throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx_) + ")";
+    int numFiltered = 0;
+    for (size_t h = 0; h < nh; h++) { filtered[h] = filt[h]; numFiltered += filt[h]; }
+    // The reference creates a key when a haplotype's walk reaches the variant (DInDel.cpp:1966-1969) and
+    // consumers read varCoverage[pav] with operator[] (absent == (0,0)), so every key is materialised here.
+    for (typename std::map<PAV, int>::const_iterator k = keyOf.begin(); k != keyOf.end(); ++k)
+        varCoverage[k->first] = Coverage(nf[k->second], nrv[k->second]);
+    return numFiltered;
 }
 
 } // namespace dindel_b200

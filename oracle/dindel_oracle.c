@@ -494,3 +494,82 @@ int ora_bayes_em(const double *rl, int nr, int nh, const uint8_t *compatible, do
     free(z); free(pi); free(lpi); free(nk); free(ak);
     return iter;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * a13: DetInDel::filterHaplotypes (DInDel.cpp:1932-2100) for one window, on flat arrays.
+ * Pair (h, r) lives at r*nh+h: offHapHMQ / numIndels / hpos row (int32, hpos_stride apart).
+ * Entries = the (haplotype, variant) iterations of the loop at :1962, sorted by haplotype then map
+ * order, each naming its PAV key (:1943) and its interval left = leftFlankRead - padCover,
+ * right = rightFlankRead + padCover (:1973-1974).
+ *   selReads (:1948-1956); per DEL entry :1984-2014; per INS entry :2018-2063 (both `lenins` branches
+ *   end in "every position of [left,right] hit by this read && nmm <= maxMismatch", so lenins does not
+ *   enter); break at the first uncovered entry :2066-2071; filtered :2078-2083; per key the union over
+ *   unfiltered haplotypes, per strand :2089-2097.
+ * Two deliberate deviations from undefined behaviour in the reference (SURVEY.md 7 "hard parts"): the
+ * read of hpos[b] at b == hpos.size() (loop bound `<=`, :1995/:2034) is "no hit", and negative hpos codes
+ * (LO/RO/INS) never hit (the reference would index hap.seq with them).
+ * ------------------------------------------------------------------------------------------ */
+void ora_filter_haplotypes(int nh, int nr, const char *hap_seq, const int32_t *hap_off, const char *read_seq,
+                           const int32_t *read_off, const int32_t *hpos, int hpos_stride,
+                           const uint8_t *offHapHMQ, const int32_t *numIndels, const uint8_t *read_strand,
+                           int ne, const int32_t *entry_hap, const int32_t *entry_key, const uint8_t *entry_type,
+                           const int32_t *entry_left, const int32_t *entry_right, int nk, int maxMismatch,
+                           int doFilter, uint8_t *filtered, uint8_t *uncovered, int32_t *key_nf, int32_t *key_nr)
+{
+    /* hVarCoverage[key][h + strand*nh] as read bit maps */
+    uint8_t *cov = (uint8_t *)calloc((size_t)(nk > 0 ? nk : 1) * 2 * nh * (nr > 0 ? nr : 1), 1);
+    int h, r, e, b, k, x;
+    for (h = 0; h < nh; h++) {
+        int allCovered = 1;
+        const char *hs = hap_seq + hap_off[h];
+        const int H = hap_off[h + 1] - hap_off[h];
+        for (e = 0; e < ne; e++) {
+            int left, right, len, covered = 0;
+            uint8_t *hit;
+            if (entry_hap[e] != h) continue;
+            if (entry_type[e] != 0 && entry_type[e] != 1) continue; /* key exists, nothing to test */
+            left = entry_left[e]; right = entry_right[e]; len = right - left + 1;
+            hit = (uint8_t *)malloc(len > 0 ? len : 1);
+            for (r = 0; r < nr; r++) {
+                const size_t pi = (size_t)r * nh + h;
+                const int R = read_off[r + 1] - read_off[r];
+                const char *rs = read_seq + read_off[r];
+                int nmm = 0, csize = 0, all = 1;
+                if (offHapHMQ[pi] || numIndels[pi] != 0) continue; /* selReads */
+                for (x = 0; x < len; x++) hit[x] = 0;
+                for (b = 0; b < R; b++) { /* the reference runs to b == R: see header */
+                    const int hb = hpos[pi * hpos_stride + b];
+                    if (hb >= 0 && hb < H && hb >= left && hb <= right) {
+                        if (!hit[hb - left]) csize++;
+                        hit[hb - left] = 1;
+                        if (entry_type[e] == 0) { if (hs[hb] != 'N' && hs[hb] != rs[b]) nmm++; }
+                        else { if (hs[hb] != rs[b]) nmm++; }
+                    }
+                }
+                for (x = 0; x < len; x++) if (!hit[x]) all = 0;
+                if (entry_type[e] == 0) {
+                    if (csize >= len && nmm <= maxMismatch) { covered = 1; cov[((size_t)entry_key[e] * 2 * nh + h + (read_strand[r] ? nh : 0)) * nr + r] = 1; }
+                } else {
+                    if (nmm <= maxMismatch && all && csize >= len) { covered = 1; cov[((size_t)entry_key[e] * 2 * nh + h + (read_strand[r] ? nh : 0)) * nr + r] = 1; }
+                }
+            }
+            free(hit);
+            if (!covered) { allCovered = 0; break; }
+        }
+        if (uncovered) uncovered[h] = (uint8_t)!allCovered;
+        filtered[h] = (uint8_t)(doFilter && !allCovered);
+    }
+    for (k = 0; k < nk; k++) {
+        int nf = 0, nrv = 0;
+        for (r = 0; r < nr; r++) {
+            int f = 0, v = 0;
+            for (h = 0; h < nh; h++) if (!filtered[h]) {
+                f |= cov[((size_t)k * 2 * nh + h) * nr + r];
+                v |= cov[((size_t)k * 2 * nh + nh + h) * nr + r];
+            }
+            nf += f; nrv += v;
+        }
+        key_nf[k] = nf; key_nr[k] = nrv;
+    }
+    free(cov);
+}

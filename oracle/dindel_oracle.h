@@ -38,6 +38,12 @@ void ora_pair_sums(const double *rl, int nr, int nh, const int32_t *read_group, 
                    const double *start, double *out);
 int ora_bayes_em(const double *rl, int nr, int nh, const uint8_t *compatible, double a0, double tol,
                  double *loglik_out, double *pi_out, double *freqs_out);
+void ora_filter_haplotypes(int nh, int nr, const char *hap_seq, const int32_t *hap_off, const char *read_seq,
+                           const int32_t *read_off, const int32_t *hpos, int hpos_stride,
+                           const uint8_t *offHapHMQ, const int32_t *numIndels, const uint8_t *read_strand,
+                           int ne, const int32_t *entry_hap, const int32_t *entry_key, const uint8_t *entry_type,
+                           const int32_t *entry_left, const int32_t *entry_right, int nk, int maxMismatch,
+                           int doFilter, uint8_t *filtered, uint8_t *uncovered, int32_t *key_nf, int32_t *key_nr);
 double ora_addlogs(double a, double b);
 double ora_digamma(double x);
 

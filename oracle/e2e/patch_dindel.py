@@ -14,11 +14,13 @@ import sys
 
 src, dst = sys.argv[1], sys.argv[2]
 check = len(sys.argv) > 3 and sys.argv[3] == "--check"   # differential build, see CHECK below
+dump = len(sys.argv) > 3 and sys.argv[3] == "--dump"     # stock CPU driver + the DUMP hook below
 text = open(src, encoding="latin-1").read()
 
 inc = '#include "Faster.hpp"\n'
 assert text.count(inc) == 1
-text = text.replace(inc, inc + '#include "dindel_b200.hpp"\n')
+if not (len(sys.argv) > 3 and sys.argv[3] == "--dump"):
+    text = text.replace(inc, inc + '#include "dindel_b200.hpp"\nstatic dindel_b200::Engine *dindel_b200_gpu = 0;\n')
 
 sig = re.compile(r"\nvoid DetInDel::computeLikelihoods\(const vector<Haplotype> &haps, const vector<Read> & reads, "
                  r"vector<vector<MLAlignment> > & liks, uint32_t leftPos, uint32_t rightPos, vector<int> & onHap\)\n\{\n")
@@ -26,7 +28,7 @@ hits = list(sig.finditer(text))
 assert len(hits) == 2, len(hits)          # the first one sits inside a /* ... */ block (DInDel.cpp:1652)
 m = hits[-1]
 fwd = ("\t{ // dindel_b200 drop-in (INTEGRATION.md section 0)\n"
-       "\t\tstatic dindel_b200::Engine *gpu = 0;\n"
+       "\t\tdindel_b200::Engine *&gpu = dindel_b200_gpu;\n"
        "\t\tif (!gpu) gpu = new dindel_b200::Engine(params.obsParams, getenv(\"DINDEL_B200_DEVICE\") ? atoi(getenv(\"DINDEL_B200_DEVICE\")) : 0);\n"
        "\t\tgpu->computeLikelihoods(haps, reads, liks, leftPos, rightPos, onHap);\n"
        "\t\treturn;\n"
@@ -62,5 +64,52 @@ CHECK = r"""
 """
 if check:
     fwd = fwd.replace("\t\treturn;\n", CHECK + "\t\treturn;\n")
-text = text[:m.end()] + fwd + text[m.end():]
+if not dump:
+    text = text[:m.end()] + fwd + text[m.end():]
+    # third line of the patch: DetInDel::filterHaplotypes (DInDel.cpp:1932-2100), the only consumer of
+    # MLAlignment::hpos, forwards to the GPU where K1 left the hpos rows (K4, dindel_b200_coverage)
+    fsig = ("void DetInDel::filterHaplotypes(const vector<Haplotype> & haps, const vector<Read> & reads, const vector<vector<MLAlignment> > & liks,"
+            "  vector<int> & filtered, map<pair<int, AlignedVariant>, VariantCoverage> & varCoverage, bool doFilter)\n{\n")
+    assert text.count(fsig) == 1
+    ffwd = ("\tif (params.slower && dindel_b200_gpu && !getenv(\"DINDEL_B200_HOST_FILTER\")) { // dindel_b200 drop-in (INTEGRATION.md section 0)\n"
+            "\t\tint nf = dindel_b200_gpu->filterHaplotypes(haps, reads, liks, filtered, varCoverage, doFilter, params.obsParams.maxMismatch);\n"
+            "\t\tcout << \"Filtered \" << nf << \" haplotypes.\" << endl;\n"
+            "\t\treturn;\n"
+            "\t}\n")
+    text = text.replace(fsig, fsig + ffwd)
+
+# --dump: oracle/_ref/dindel_ref_dump = the STOCK CPU driver whose filterHaplotypes (DInDel.cpp:1932-2100)
+# appends, at its end, its inputs and outputs as text to the file named by $DINDEL_B200_DUMP_COVER.  This is
+# how tests/golden/cover_golden.json.gz is produced (tests/golden/make_cover_golden.py): golden vectors of
+# the reference's own filterHaplotypes, against which the a13 oracle restatement and the K4 kernel are pinned.
+DUMP = r"""
+	if (getenv("DINDEL_B200_DUMP_COVER")) {
+		FILE *df = fopen(getenv("DINDEL_B200_DUMP_COVER"), "a");
+		fprintf(df, "W %d %d %d %d %d\n", int(haps.size()), int(reads.size()), params.obsParams.padCover, params.obsParams.maxMismatch, int(doFilter));
+		for (size_t h=0;h<haps.size();h++) fprintf(df, "H %s\n", haps[h].seq.c_str());
+		for (size_t r=0;r<reads.size();r++) {
+			int strand = 0;
+			if (reads[r].isUnmapped()) { if (!reads[r].mateIsReverse()) strand = 1; } else { if (reads[r].isReverse()) strand = 1; }
+			fprintf(df, "R %s %d\n", reads[r].seq.seq.c_str(), strand);
+		}
+		for (size_t h=0;h<haps.size();h++) for (size_t r=0;r<reads.size();r++) {
+			fprintf(df, "P %d %d %d %d", int(h), int(r), int(liks[h][r].offHapHMQ), liks[h][r].numIndels);
+			for (size_t b=0;b<liks[h][r].hpos.size();b++) fprintf(df, " %d", liks[h][r].hpos[b]);
+			fprintf(df, "\n");
+		}
+		for (size_t h=0;h<haps.size();h++) for (map<int, AlignedVariant>::const_iterator it = haps[h].indels.begin();it!= haps[h].indels.end();it++) {
+			const AlignedVariant & av = it->second;
+			int ty = av.getType() == Variant::DEL ? 0 : (av.getType() == Variant::INS ? 1 : 2);
+			fprintf(df, "E %d %d|%d|%s %d %d %d\n", int(h), it->first, av.getStartHap(), av.getString().c_str(), ty, av.getLeftFlankRead() - params.obsParams.padCover, av.getRightFlankRead() + params.obsParams.padCover);
+		}
+		fprintf(df, "F"); for (size_t h=0;h<haps.size();h++) fprintf(df, " %d", filtered[h]); fprintf(df, "\n");
+		for (map<PAV, VariantCoverage>::const_iterator it = varCoverage.begin(); it != varCoverage.end(); it++)
+			fprintf(df, "C %d|%d|%s %d %d\n", it->first.first, it->first.second.getStartHap(), it->first.second.getString().c_str(), it->second.nf, it->second.nr);
+		fclose(df);
+	}
+"""
+if dump:
+    anchor = "\t\tvarCoverage[pav]=VariantCoverage(int(rf.size()), int(rr.size()));\n\t}\n"
+    assert text.count(anchor) == 1
+    text = text.replace(anchor, anchor + DUMP)
 open(dst, "w", encoding="latin-1").write(text)

@@ -143,13 +143,15 @@ def main():
     ap.add_argument("--procs", type=int, default=0, help="concurrent stage-3 processes (0 = host cores)")
     ap.add_argument("--gpu-procs", type=int, default=4, help="concurrent stage-3 processes sharing the GPU")
     ap.add_argument("--windows-per-file", type=int, default=1000)
+    ap.add_argument("--filter-haplotypes", action="store_true", help="pass --filterHaplotypes to stage 3 (all arms)")
     ap.add_argument("--heap-neutral", action="store_true", help="also compare with the allocator poisoning freed memory")
     a = ap.parse_args()
     arms = a.arms.split(",")
     procs = a.procs or len(os.sched_getaffinity(0))
     prep = prepare(a.work, a.length, a.seed, a.coverage, a.windows_per_file)
     res = {"length": a.length, "coverage": a.coverage, "n_candidates": prep["n_candidates"],
-           "n_windows": prep["n_windows"], "window_files": len(prep["window_files"]), "procs": procs, "gpu_procs": a.gpu_procs}
+           "n_windows": prep["n_windows"], "window_files": len(prep["window_files"]), "procs": procs, "gpu_procs": a.gpu_procs,
+           "filterHaplotypes": a.filter_haplotypes}
     verdict = True
     for tag, env in (("", None), (".hn", HEAP_NEUTRAL)):
         if env and not a.heap_neutral:
@@ -158,7 +160,8 @@ def main():
         for arm in arms:
             if arm == "check" and env:
                 continue
-            glfs, vcf, wall, n_calls = run_arm(arm, prep, a.work, procs if arm == "cpu" else a.gpu_procs, env=env, tag=tag)
+            glfs, vcf, wall, n_calls = run_arm(arm, prep, a.work, procs if arm == "cpu" else a.gpu_procs,
+                                               extra=["--filterHaplotypes"] if a.filter_haplotypes else [], env=env, tag=tag)
             ok, err = glf_stats(glfs)
             out[arm] = (glfs, vcf)
             r[arm] = {"stage3_wall_s": round(wall, 3), "vcf_calls": n_calls, "windows_ok": ok, "windows_skipped": err}

@@ -125,3 +125,29 @@ class Oracle:
     def digamma(self, x):
         self.lib.ora_digamma.restype = C.c_double
         return self.lib.ora_digamma(C.c_double(x))
+
+    # ---- a13: filterHaplotypes restatement (port only) ----
+    def filter_haplotypes(self, haps, reads, hpos, off_hap_hmq, num_indels, strand, entries, nk, max_mismatch,
+                          do_filter):
+        """One window.  haps/reads: lists of bytes; hpos: int32 [nr*nh, stride] (pair r*nh+h); off_hap_hmq /
+        num_indels: [nr*nh]; strand: [nr]; entries: list of (hap, key, type, left, right) sorted by hap.
+        -> (filtered[nh], uncovered[nh], nf[nk], nr[nk])"""
+        nh, nr = len(haps), len(reads)
+        hap_off = np.concatenate([[0], np.cumsum([len(h) for h in haps])]).astype(np.int32)
+        read_off = np.concatenate([[0], np.cumsum([len(r) for r in reads])]).astype(np.int32)
+        hs, rs = b"".join(haps) + b"\0", b"".join(reads) + b"\0"
+        hpos = np.ascontiguousarray(hpos, dtype=np.int32)
+        ohq = np.ascontiguousarray(off_hap_hmq, dtype=np.uint8)
+        ni = np.ascontiguousarray(num_indels, dtype=np.int32)
+        st = np.ascontiguousarray(strand, dtype=np.uint8)
+        ne = len(entries)
+        e = np.array(entries, dtype=np.int64).reshape(ne, 5) if ne else np.zeros((0, 5), dtype=np.int64)
+        eh, ek, el, er = (np.ascontiguousarray(e[:, i], dtype=np.int32) for i in (0, 1, 3, 4))
+        et = np.ascontiguousarray(e[:, 2], dtype=np.uint8)
+        filt, unc = np.zeros(max(nh, 1), dtype=np.uint8), np.zeros(max(nh, 1), dtype=np.uint8)
+        nf, nrv = np.zeros(max(nk, 1), dtype=np.int32), np.zeros(max(nk, 1), dtype=np.int32)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        self.lib.ora_filter_haplotypes(nh, nr, hs, vp(hap_off), rs, vp(read_off), vp(hpos), int(hpos.shape[1]) if hpos.ndim == 2 else 1,
+                                       vp(ohq), vp(ni), vp(st), ne, vp(eh), vp(ek), vp(et), vp(el), vp(er), int(nk),
+                                       int(max_mismatch), int(do_filter), vp(filt), vp(unc), vp(nf), vp(nrv))
+        return filt[:nh], unc[:nh], nf[:nk], nrv[:nk]

@@ -128,3 +128,18 @@ def test_glf_and_vcf_identical_to_cpu_reference(tmp_path):
     hn = res["heap_neutral"]
     assert hn["glf_identical"] and hn["vcf_identical"], res
     assert hn["cpu"]["vcf_calls"] >= 20 and hn["cpu"]["windows_ok"] >= 40, res
+
+
+@pytest.mark.gpu
+def test_glf_identical_with_filter_haplotypes(tmp_path):
+    """--filterHaplotypes: filtered[] from K4 (dindel_b200_coverage) now changes which haplotype pairs diploidGLF
+    considers; output still byte-identical to the stock CPU binary."""
+    if not run_e2e.have_binaries(("cpu", "gpu")):
+        pytest.skip("oracle/_ref/dindel_ref / dindel_b200 not built (reference sources absent at build time)")
+    r = subprocess.run([sys.executable, os.path.join(E2E, "run_e2e.py"), "--work", str(tmp_path), "--length", "60000",
+                        "--seed", "4", "--arms", "cpu,gpu", "--windows-per-file", "20", "--heap-neutral",
+                        "--filter-haplotypes"], capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout + r.stderr
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    hn = res["heap_neutral"]
+    assert hn["glf_identical"] and hn["vcf_identical"] and hn["cpu"]["windows_ok"] >= 20, res

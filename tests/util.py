@@ -84,3 +84,32 @@ def oracle_batch(oracle, batch, params):
 def recs_dtype():
     from oracle.pyoracle import ORA_DTYPE
     return ORA_DTYPE
+
+
+def load_cover_golden():
+    """tests/golden/cover_golden.json.gz (reference's own filterHaplotypes, make_cover_golden.py) as a list of
+    windows: dict(haps, reads, strand, hpos [nr*nh, stride] int32 (r-major), ohq, ni, entries [(h, key id, type,
+    left, right)], keys [str], nk, maxMismatch, doFilter, filtered, cov {key str: (nf, nr)})."""
+    import gzip
+    import json
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cover_golden.json.gz")
+    out = []
+    for w in json.load(gzip.open(path, "rt")):
+        nh, nr = w["nh"], w["nr"]
+        stride = max(len(r) for r in w["reads"])
+        hpos = np.full((nr * nh, stride), -32768, dtype=np.int32)
+        ohq, ni = np.zeros(nr * nh, dtype=np.uint8), np.zeros(nr * nh, dtype=np.int32)
+        for p in w["pairs"]:
+            h, r = p[0], p[1]
+            ohq[r * nh + h], ni[r * nh + h] = p[2], p[3]
+            hpos[r * nh + h, :len(p) - 4] = p[4:]
+        keys, entries = [], []
+        for h, key, ty, left, right in w["entries"]:   # already sorted by hap, map order inside a hap
+            if key not in keys:
+                keys.append(key)
+            entries.append((h, keys.index(key), ty, left, right))
+        out.append(dict(haps=[s.encode() for s in w["haps"]], reads=[s.encode() for s in w["reads"]],
+                        strand=np.array(w["strand"], dtype=np.uint8), hpos=hpos, ohq=ohq, ni=ni, entries=entries,
+                        keys=keys, nk=len(keys), maxMismatch=w["maxMismatch"], doFilter=w["doFilter"],
+                        filtered=np.array(w["filtered"], dtype=np.uint8), cov={k: (a, b) for k, a, b in w["cov"]}))
+    return out
