@@ -31,6 +31,9 @@
 #ifndef K1_TILED_CRO_MAXC
 #define K1_TILED_CRO_MAXC 5
 #endif
+#ifndef K1_LEFT_TREE
+#define K1_LEFT_TREE 1
+#endif
 #define FULLMASK 0xffffffffu
 
 // call f(integral_constant<int, cro>) for the run-time value cro in [0, C)
@@ -282,6 +285,35 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
                     double best[C], a1[C];
                     uint32_t code[C], bit1[C];
                     // jumps y = 1..J from column x-y (cpp:1784-1795)
+#if K1_LEFT_TREE
+                    // "take iff v >= best" over y = 1..J picks the LAST y attaining the maximum; the same winner
+                    // comes out of any reduction tree whose nodes prefer the later operand on ties, so the
+                    // candidates are reduced pairwise (depth 1 + J/2 instead of J dependent compare-selects).
+#pragma unroll
+                    for (int y = 1; y <= J; y += 2) {
+#pragma unroll
+                        for (int c = 0; c < C; c++) {
+                            const double va = (y == 1) ? ((WO[J + c - 1] + lpn[c]) + WP[J + c - 1]) + lpn[c]
+                                                       : ((WO[J + c - y] + lpD[c][(y >= 2) ? y - 2 : 0]) + WP[J + c - y]) + lpn[c];
+                            double pm = va;
+                            uint32_t pc = (uint32_t)(y - 1);
+                            if (y + 1 <= J) {
+                                const double vb = ((WO[J + c - (y + 1)] + lpD[c][y - 1]) + WP[J + c - (y + 1)]) + lpn[c];
+                                const bool pb = (vb >= va);
+                                pm = pb ? vb : va;
+                                pc = pb ? (uint32_t)y : (uint32_t)(y - 1);
+                            }
+                            if (y == 1) {
+                                best[c] = pm;
+                                code[c] = pc;
+                            } else {
+                                const bool p = (pm >= best[c]);
+                                best[c] = p ? pm : best[c];
+                                code[c] = p ? pc : code[c];
+                            }
+                        }
+                    }
+#else
 #pragma unroll
                     for (int c = 0; c < C; c++) {
                         best[c] = ((WO[J + c - 1] + lpn[c]) + WP[J + c - 1]) + lpn[c];
@@ -297,6 +329,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
                             code[c] = p ? (uint32_t)(y - 1) : code[c];
                         }
                     }
+#endif
                     // from plane-1 x-1 (cpp:1807-1811)
 #pragma unroll
                     for (int c = 0; c < C; c++) {
