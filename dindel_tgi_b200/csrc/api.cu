@@ -189,7 +189,7 @@ struct dindel_ctx {
     HostBuf win_pair, win_unit; // [n_windows+1] prefix sums (pinned: uploaded by async copies)
     std::vector<int> win_nh;
     dindel_timing timing;
-    int force_generic = 0, force_chunks = 0, force_lanes = 0;
+    int force_generic = 0, force_chunks = 0, force_lanes = 0, force_bt_global = -1;
     Range all;                 // the whole resident batch (resident API)
 };
 
@@ -353,6 +353,8 @@ int dindel_b200_create(const dindel_params *p, int device, dindel_ctx **out)
     ctx->force_chunks = fc ? atoi(fc) : 0;
     const char *fl = getenv("DINDEL_B200_LANES");
     ctx->force_lanes = fl ? atoi(fl) : 0;
+    const char *fb = getenv("DINDEL_B200_BT_GLOBAL"); // generic kernel: 1 / 0 forces the back-pointer plan
+    ctx->force_bt_global = fb ? atoi(fb) : -1;
     memset(&ctx->timing, 0, sizeof(ctx->timing));
     *out = ctx;
     return DINDEL_OK;
@@ -666,21 +668,32 @@ static int k1_range(dindel_ctx *ctx, const Range &g, Lane &ln, int *launches)
             *launches += n;
         } else {
             // generic kernel: pick the shared-memory plan
+            // Two plans: back-pointers (one byte per state column and row) in shared memory, or in a per-warp
+            // slot of global memory (L2 resident; written once per row, read once per row by the back-trace).
+            // The rows themselves always live in shared memory.  Long reads x long haplotypes (configs[3]:
+            // 250 x 322 -> 80 KB of back-pointers per pair) leave room for 2 warps per SM under the first plan;
+            // the kernel is latency bound, so the plan with more resident warps per SM wins (forceable for tests).
             const size_t budget = ctx->smem_optin;
-            int bt_in_smem = 1, warps = 4;
-            size_t pw = k1_generic_smem_per_warp(b.max_S, b.max_R, 1);
-            while (warps > 1 && pw * warps > budget) warps >>= 1;
-            if (pw * warps > budget) {
-                bt_in_smem = 0;
-                warps = 4;
-                pw = k1_generic_smem_per_warp(b.max_S, b.max_R, 0);
-                while (warps > 1 && pw * warps > budget) warps >>= 1;
-                if (pw * warps > budget) return fail(ctx, DINDEL_E_UNSUPPORTED, "shape exceeds shared memory");
+            int bt_in_smem = 1, warps = 4, ctas_per_sm = 1;
+            size_t pw = 0;
+            int best_res = 0;
+            for (int plan = 1; plan >= 0; plan--) {
+                int wp = 4;
+                const size_t p = k1_generic_smem_per_warp(b.max_S, b.max_R, plan);
+                while (wp > 1 && p * wp > budget) wp >>= 1;
+                if (p * wp > budget) continue;
+                int cps = (int)((size_t)(228 * 1024 - 1024) / (p * wp + 1024));
+                if (cps < 1) cps = 1;
+                if (cps * wp > 32) cps = 32 / wp;
+                const int res = cps * wp;
+                const bool forced = ctx->force_bt_global >= 0 && plan == (ctx->force_bt_global ? 0 : 1);
+                if (forced || (ctx->force_bt_global < 0 && (best_res == 0 || res >= 2 * best_res))) {
+                    bt_in_smem = plan; warps = wp; ctas_per_sm = cps; pw = p; best_res = res;
+                    if (forced) break;
+                }
             }
+            if (best_res == 0) return fail(ctx, DINDEL_E_UNSUPPORTED, "shape exceeds shared memory");
             size_t smem = pw * warps;
-            int ctas_per_sm = (int)((size_t)(228 * 1024 - 1024) / (smem + 1024));
-            if (ctas_per_sm < 1) ctas_per_sm = 1;
-            if (ctas_per_sm * warps > 32) ctas_per_sm = 32 / warps;
             int grid = ctx->num_sms * ctas_per_sm;
             long long need = (g.u1 - g.u0 + warps - 1) / warps;
             if (grid > need) grid = (int)need;
