@@ -8,8 +8,10 @@ process N shards ("weak" scaling, no data-path collective: windows are independe
 
   value : pairs/s with the batch already resident in HBM (dindel_b200_upload once, then
           dindel_b200_run per step), device time from CUDA events on the library's stream.
-  e2e   : the same through dindel_b200_submit with pinned HOST buffers: H2D of every input array,
-          kernels, D2H of the pair records (+ hpos) inside the timed region, every step.
+  e2e   : the same through the C ABI with pinned HOST buffers, every step: dindel_b200_submit (H2D of every
+          input array, kernels, D2H of the 64-byte pair records) followed by dindel_b200_coverage (K4 =
+          filterHaplotypes on the hpos rows where K1 left them in HBM; H2D of the variant entries, D2H of
+          filtered[] and the coverage counts).  --hpos-d2h copies the hpos rows to the host instead.
   roofline : K1 is bound by the FP64 add/compare issue rate, not HBM: achieved =
           cells/s x W_cell (5J+10 FP64 pipe ops per cell), peak = DADD rate measured on this GPU.
   cpu_baseline / --impl reference : the reference's own ObservationModelFBMaxErr (oracle/_ref,
@@ -338,6 +340,27 @@ def main():
     e2e_val = world * n_pairs / (e2e_ms * 1e-3)
     checksum = float(pairs["ll"].sum())
 
+    # ---- K2 / K3 over the resident likelihood matrix (reported beside the step, not part of it) ----
+    infer = None
+    if world == 1:
+        nh_w = np.diff(batch.win_hap).astype(np.int64)
+        jw = np.arange(batch.n_windows, dtype=np.int32)
+        starts = [np.zeros(int(n * (n + 1) // 2)) for n in nh_w]
+        eng.pair_sums(jw[:8], starts[:8])                           # warm-up
+        t0 = time.perf_counter()
+        sums = eng.pair_sums(jw, starts)                            # diploidGLF core, one job per window
+        k2_ms = 1e3 * (time.perf_counter() - t0)
+        infer = {"k2_pair_sums_ms": k2_ms, "k2_windows_per_s": batch.n_windows / (k2_ms * 1e-3),
+                 "k2_frac_of_k1_step": k2_ms / ms_per_step, "k2_checksum": float(sum(float(x.sum()) for x in sums[:1000]))}
+        if args.cfg == 3:
+            comp = [np.ones(int(n), dtype=np.uint8) for n in nh_w]
+            eng.bayes_em(jw[:2], comp[:2])
+            t0 = time.perf_counter()
+            ll, it, _, _ = eng.bayes_em(jw, comp)                   # Bayes EM core, one active-variant set per window
+            k3_ms = 1e3 * (time.perf_counter() - t0)
+            infer.update({"k3_bayes_em_ms": k3_ms, "k3_sets_per_s": batch.n_windows / (k3_ms * 1e-3),
+                          "k3_frac_of_k1_step": k3_ms / ms_per_step, "k3_mean_iters": float(np.mean(it))})
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -360,10 +383,15 @@ def main():
             "clocks": clocks,
             "roofline": {"bound": "fp64-issue", "achieved": (n_cells * w_cell / (ms_per_step * 1e-3)) / 1e12,
                          "peak": fp64_peak / 1e12, "unit": "TOP/s",
-                         "frac": (n_cells * w_cell / (ms_per_step * 1e-3)) / fp64_peak, "traffic": None,
+                         "frac": (n_cells * w_cell / (ms_per_step * 1e-3)) / fp64_peak,
+                         # dram read+write of k1_tiled_kernel<4,6> from one `ncu --set full` capture (profiles/
+                         # r1_k1_tiled_v4_k4.md: 302 MB for 8.9 G cells, hpos rows included), scaled to this step's cells
+                         "traffic": int(n_cells * (301.8e6 / 8.9e9)) if args.cfg == 2 and not args.no_hpos else None,
                          "w_cell": w_cell, "peak_source": "measured here: dindel_b200_measure_fp64_peak (register-resident DADD chains)",
                          "hbm_gbs": (h2d + d2h) / (ms_per_step * 1e-3) / 1e9},
         }
+        if infer:
+            line["inference_kernels"] = infer
         if world == 1 and not args.no_cpu_baseline:
             cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
             nwin = args.cpu_windows or max(8, int(100 * cores))

@@ -254,6 +254,186 @@ void Engine::computeLikelihoods(const std::vector<HapT> &haps, const std::vector
     }
 }
 
+
+// The throughput binding: the caller's window loop split into prepare -> add() ->
+// one flush() per batch -> result() / filterResult() per window.  One dindel_b200_submit (pipelined H2D /
+// kernels / D2H) and one dindel_b200_coverage serve every window added since the last clear(); results are
+// what Engine::computeLikelihoods / Engine::filterHaplotypes return window by window (same code expands them).
+template <class HapT, class ReadT>
+class WindowBatch {
+    typedef ReadTraits<ReadT> RT;
+    typedef typename HapT_variant<HapT>::type AV;
+    typedef std::pair<int, AV> PAV;
+public:
+    // fullAlignments = false: the per-base hpos rows stay on the GPU (DINDEL_OUT_KEEP_HPOS); result() then fills the
+    // scalar MLAlignment fields and the hapIndelCovered / hapSNPCovered maps but leaves hpos / align / indels / snps
+    // empty (nothing in the calling pipeline reads them once filterResult() replaces filterHaplotypes).
+    explicit WindowBatch(Engine &e, int maxMismatch = 2, bool doFilter = false, bool fullAlignments = true)
+        : eng_(e), maxMismatch_(maxMismatch), doFilter_(doFilter), flushed_(false), full_(fullAlignments) { clear(); }
+    void clear()
+    {
+        hap_start_.clear(); win_hap_.assign(1, 0); win_read_.assign(1, 0); hap_off_.assign(1, 0); read_off_.assign(1, 0);
+        hap_seq_.clear(); read_seq_.clear(); qual_.clear(); mapq_.clear(); flags_.clear(); strand_.clear(); start_.clear();
+        win_entry_.assign(1, 0); win_key_.assign(1, 0); e_hap_.clear(); e_key_.clear(); e_left_.clear(); e_right_.clear();
+        e_type_.clear(); keys_.clear(); maxR_ = 0; flushed_ = false;
+    }
+    size_t size() const { return hap_start_.size(); }
+    // copies what the engine needs of one window (DetInDel::computeLikelihoods' arguments + the variant entries of
+    // DetInDel::filterHaplotypes, DInDel.cpp:1962-1974); returns the window's index in the batch
+    int add(const std::vector<HapT> &haps, const std::vector<ReadT> &reads, uint32_t leftPos)
+    {
+        flushed_ = false;
+        const int pad = eng_.params().padCover;
+        std::map<PAV, int> keyOf;
+        std::vector<PAV> keys;
+        for (size_t h = 0; h < haps.size(); h++) {
+            hap_seq_ += haps[h].seq; hap_off_.push_back((int64_t)hap_seq_.size());
+            for (typename std::map<int, AV>::const_iterator it = haps[h].indels.begin(); it != haps[h].indels.end(); ++it) {
+                const AV &av = it->second;
+                const PAV pav(it->first, av);
+                typename std::map<PAV, int>::iterator k = keyOf.find(pav);
+                if (k == keyOf.end()) { k = keyOf.insert(std::make_pair(pav, (int)keys.size())).first; keys.push_back(pav); }
+                e_hap_.push_back((int32_t)h); e_key_.push_back(k->second);
+                e_type_.push_back(av.getType() == AV::DEL ? DINDEL_VAR_DEL : (av.getType() == AV::INS ? DINDEL_VAR_INS : DINDEL_VAR_OTHER));
+                e_left_.push_back(av.getLeftFlankRead() - pad); e_right_.push_back(av.getRightFlankRead() + pad);
+            }
+        }
+        for (size_t r = 0; r < reads.size(); r++) {
+            const std::string &sq = RT::seq(reads[r]);
+            const uint8_t *ph = RT::phred(reads[r]);
+            read_seq_ += sq; read_off_.push_back((int64_t)read_seq_.size());
+            qual_.insert(qual_.end(), ph, ph + sq.size());
+            mapq_.push_back(RT::mapq(reads[r])); start_.push_back(RT::start(reads[r]));
+            flags_.push_back((uint8_t)((RT::unmapped(reads[r]) ? DINDEL_READ_UNMAPPED : 0) | (RT::reverse(reads[r]) ? DINDEL_READ_REVERSE : 0)));
+            strand_.push_back(RT::coverReverse(reads[r]) ? 1 : 0);
+            if (sq.size() > maxR_) maxR_ = sq.size();
+        }
+        hap_start_.push_back(leftPos);
+        win_hap_.push_back((int32_t)(hap_off_.size() - 1)); win_read_.push_back((int32_t)(read_off_.size() - 1));
+        win_entry_.push_back((int64_t)e_hap_.size()); win_key_.push_back(win_key_.back() + (int64_t)keys.size());
+        keys_.push_back(keys);
+        return (int)hap_start_.size() - 1;
+    }
+    void flush();
+    template <class MLA>
+    void result(int w, const std::vector<HapT> &haps, const std::vector<ReadT> &reads,
+                std::vector<std::vector<MLA> > &liks, std::vector<int> &onHap) const;
+    template <class CovMap>
+    int filterResult(int w, std::vector<int> &filtered, CovMap &varCoverage) const;
+private:
+    Engine &eng_;
+    int maxMismatch_;
+    bool doFilter_, flushed_, full_;
+    size_t maxR_;
+    int stride_;
+    std::vector<uint32_t> hap_start_, start_;
+    std::vector<int32_t> win_hap_, win_read_, e_hap_, e_key_, e_left_, e_right_, status_, nf_, nr_;
+    std::vector<int64_t> hap_off_, read_off_, win_entry_, win_key_, win_pair_;
+    std::string hap_seq_, read_seq_;
+    std::vector<uint8_t> qual_, mapq_, flags_, strand_, e_type_, on_, filt_;
+    std::vector<std::vector<PAV> > keys_;
+    std::vector<dindel_pair_out> pairs_;
+    std::vector<int16_t> hpos_;
+};
+
+
+template <class HapT, class ReadT>
+void WindowBatch<HapT, ReadT>::flush()
+{
+    const size_t nw = size();
+    if (nw == 0) { flushed_ = true; return; }
+    static const uint8_t none8 = 0;
+    static const uint32_t none32 = 0;
+    static const int32_t zero32 = 0;
+    dindel_batch_in in;
+    in.n_windows = (int32_t)nw; in.n_haps = win_hap_.back(); in.n_reads = win_read_.back(); in.reserved = 0;
+    in.hap_start = &hap_start_[0]; in.win_hap = &win_hap_[0]; in.win_read = &win_read_[0];
+    in.hap_off = &hap_off_[0]; in.hap_seq = hap_seq_.data(); in.read_off = &read_off_[0]; in.read_seq = read_seq_.data();
+    in.read_qual = qual_.empty() ? &none8 : &qual_[0]; in.read_mapq = mapq_.empty() ? &none8 : &mapq_[0];
+    in.read_start = start_.empty() ? &none32 : &start_[0]; in.read_flags = flags_.empty() ? &none8 : &flags_[0];
+    const int64_t np = dindel_b200_count_pairs(&in);
+    stride_ = (int)((maxR_ + 7) & ~(size_t)7); if (stride_ < 8) stride_ = 8;
+    pairs_.resize((size_t)(np ? np : 1));
+    if (full_) hpos_.resize((size_t)(np ? np : 1) * (size_t)stride_);
+    win_pair_.assign(nw + 1, 0); status_.assign(nw, 0); on_.assign(in.n_reads ? in.n_reads : 1, 0);
+    dindel_batch_out out;
+    out.n_pairs = np; out.pairs = &pairs_[0]; out.hpos = full_ ? &hpos_[0] : 0; out.hpos_stride = full_ ? stride_ : 0;
+    out.flags = DINDEL_OUT_KEEP_HPOS; out.win_pair = &win_pair_[0]; out.win_status = &status_[0]; out.read_on_hap = &on_[0];
+    int rc = dindel_b200_submit(eng_.ctx(), &in, &out);
+    if (rc != DINDEL_OK)
+        throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(eng_.ctx()) + ")";
+    // K4 over the rows K1 left in HBM
+    dindel_cover_in ci;
+    ci.n_entries = (int32_t)e_hap_.size(); ci.n_keys = (int32_t)win_key_.back(); ci.maxMismatch = maxMismatch_; ci.doFilter = doFilter_ ? 1 : 0;
+    ci.win_entry = &win_entry_[0]; ci.win_key = &win_key_[0];
+    ci.entry_hap = e_hap_.empty() ? &zero32 : &e_hap_[0]; ci.entry_key = e_key_.empty() ? &zero32 : &e_key_[0];
+    ci.entry_type = e_type_.empty() ? &none8 : &e_type_[0];
+    ci.entry_left = e_left_.empty() ? &zero32 : &e_left_[0]; ci.entry_right = e_right_.empty() ? &zero32 : &e_right_[0];
+    ci.read_strand = strand_.empty() ? &none8 : &strand_[0];
+    filt_.assign(in.n_haps ? in.n_haps : 1, 0);
+    nf_.assign(ci.n_keys ? ci.n_keys : 1, 0); nr_.assign(ci.n_keys ? ci.n_keys : 1, 0);
+    dindel_cover_out co;
+    co.hap_filtered = &filt_[0]; co.hap_uncovered = 0; co.key_nf = &nf_[0]; co.key_nr = &nr_[0];
+    rc = dindel_b200_coverage(eng_.ctx(), &ci, &co);
+    if (rc != DINDEL_OK)
+        throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(eng_.ctx()) + ")";
+    flushed_ = true;
+}
+
+// DetInDel::computeLikelihoods' results for window w, with its guards (see Engine::computeLikelihoods).
+template <class HapT, class ReadT>
+template <class MLA>
+void WindowBatch<HapT, ReadT>::result(int w, const std::vector<HapT> &haps, const std::vector<ReadT> &reads,
+                                      std::vector<std::vector<MLA> > &liks, std::vector<int> &onHap) const
+{
+    if (!flushed_ || w < 0 || (size_t)w >= size()) throw std::string("dindel_b200: result() before flush() / bad window");
+    const size_t nh = haps.size(), nr = reads.size();
+    if ((size_t)(win_hap_[w + 1] - win_hap_[w]) != nh || (size_t)(win_read_[w + 1] - win_read_[w]) != nr)
+        throw std::string("dindel_b200: result() called with another window's haplotypes / reads");
+    onHap = std::vector<int>(nr, 0);
+    liks = std::vector<std::vector<MLA> >(nh, std::vector<MLA>(nr));
+    const int pad = eng_.params().padCover;
+    for (size_t h = 0; h < nh; h++)
+        for (size_t r = 0; r < nr; r++) {
+            const size_t i = (size_t)win_pair_[w] + r * nh + h;
+            const dindel_pair_out &rec = pairs_[i];
+            MLA &ml = liks[h][r];
+            if (rec.status == DINDEL_WIN_HAPSIZE) throw std::string("hapSize error.");
+            if (full_) {
+                expandAlignment(rec, &hpos_[i * (size_t)stride_], haps[h], RT::seq(reads[r]), pad, ml);
+            } else {
+                ml.ll = rec.ll; ml.llOn = rec.llOn; ml.llOff = rec.llOff; ml.offHap = rec.offHap != 0; ml.offHapHMQ = rec.offHapHMQ != 0;
+                ml.firstBase = rec.firstBase; ml.lastBase = rec.lastBase; ml.nBQT = rec.nBQT; ml.nmmBQT = rec.nmmBQT;
+                ml.mLogBQ = rec.mLogBQ; ml.nMMRight = rec.nMMRight; ml.nMMLeft = rec.nMMLeft;
+                ml.numIndels = rec.numIndels; ml.numMismatch = rec.numMismatch;
+                for (typename std::map<int, AV>::const_iterator it = haps[h].indels.begin(); it != haps[h].indels.end(); ++it)
+                    ml.hapIndelCovered[it->first] = it->second.isCovered(pad, ml.firstBase, ml.lastBase);
+                for (typename std::map<int, AV>::const_iterator it = haps[h].snps.begin(); it != haps[h].snps.end(); ++it)
+                    ml.hapSNPCovered[it->first] = it->second.isCovered(pad, ml.firstBase, ml.lastBase);
+            }
+            if (!ml.offHapHMQ) onHap[r] = 1;
+            if (rec.status == DINDEL_WIN_LL_POSITIVE) { std::cerr << "Likelihood>0" << std::endl; exit(1); }
+            if (rec.status == DINDEL_WIN_NAN) { std::cout << "NAN/Inf error" << std::endl; throw std::string("Nan detected"); }
+        }
+}
+
+// DetInDel::filterHaplotypes' results for window w (computed by K4 during flush()).
+template <class HapT, class ReadT>
+template <class CovMap>
+int WindowBatch<HapT, ReadT>::filterResult(int w, std::vector<int> &filtered, CovMap &varCoverage) const
+{
+    typedef typename CovMap::mapped_type Coverage;
+    if (!flushed_ || w < 0 || (size_t)w >= size()) throw std::string("dindel_b200: filterResult() before flush() / bad window");
+    const size_t nh = (size_t)(win_hap_[w + 1] - win_hap_[w]);
+    filtered = std::vector<int>(nh, 0);
+    varCoverage.clear();
+    int n = 0;
+    for (size_t h = 0; h < nh; h++) { filtered[h] = filt_[win_hap_[w] + h]; n += filtered[h]; }
+    for (size_t k = 0; k < keys_[w].size(); k++)
+        varCoverage[keys_[w][k]] = Coverage(nf_[win_key_[w] + k], nr_[win_key_[w] + k]);
+    return n;
+}
+
 template <class HapT, class ReadT, class MLA, class CovMap>
 int Engine::filterHaplotypes(const std::vector<HapT> &haps, const std::vector<ReadT> &reads,
                              const std::vector<std::vector<MLA> > & /*liks: resident on the GPU*/,

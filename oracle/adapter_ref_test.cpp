@@ -89,6 +89,32 @@ static bool same_avmap(const std::map<int, AlignedVariant> &a, const std::map<in
 }
 static bool same_bits(double a, double b) { return memcmp(&a, &b, sizeof(double)) == 0; }
 
+/* stand-in for VariantCoverage (DInDel.hpp:53-66; DInDel.hpp itself drags in the whole driver) */
+struct Cov {
+    int nf, nr;
+    Cov() : nf(0), nr(0) {}
+    Cov(int f, int r) : nf(f), nr(r) {}
+    bool operator==(const Cov &o) const { return nf == o.nf && nr == o.nr; }
+};
+typedef std::map<std::pair<int, AlignedVariant>, Cov> CovMap;
+static bool same_cov(const CovMap &a, const CovMap &b)
+{
+    if (a.size() != b.size()) return false;
+    CovMap::const_iterator i = a.begin(), j = b.begin();
+    for (; i != a.end(); ++i, ++j)
+        if (i->first.first != j->first.first || !same_av(i->first.second, j->first.second) || !(i->second == j->second)) return false;
+    return true;
+}
+static bool same_mla(const MLAlignment &a, const MLAlignment &b)
+{
+    return same_bits(a.ll, b.ll) && same_bits(a.llOn, b.llOn) && same_bits(a.llOff, b.llOff) && same_bits(a.mLogBQ, b.mLogBQ) &&
+           a.offHap == b.offHap && a.offHapHMQ == b.offHapHMQ && a.firstBase == b.firstBase && a.lastBase == b.lastBase &&
+           a.numIndels == b.numIndels && a.numMismatch == b.numMismatch && a.nBQT == b.nBQT && a.nmmBQT == b.nmmBQT &&
+           a.nMMLeft == b.nMMLeft && a.nMMRight == b.nMMRight && a.hpos == b.hpos && a.align == b.align &&
+           same_avmap(a.indels, b.indels) && same_avmap(a.snps, b.snps) && a.hapIndelCovered == b.hapIndelCovered &&
+           a.hapSNPCovered == b.hapSNPCovered;
+}
+
 #define CHECK(cond, what)                                                                              \
     do {                                                                                               \
         if (!(cond)) {                                                                                 \
@@ -109,7 +135,14 @@ int main(int argc, char **argv)
         fprintf(stderr, "no engine: %s\n", s.c_str());
         return 2;
     }
-    long n_pairs = 0, n_ind = 0, n_snp = 0, n_cov = 0;
+    long n_pairs = 0, n_ind = 0, n_snp = 0, n_cov = 0, n_filt = 0, n_covreads = 0;
+    /* kept for the batch check below: every window's inputs and its one-window results */
+    std::vector<std::vector<Haplotype> > allHaps;
+    std::vector<std::vector<Read> > allReads;
+    std::vector<uint32_t> allLeft;
+    std::vector<std::vector<std::vector<MLAlignment> > > allLiks;
+    std::vector<std::vector<int> > allOn, allFiltered;
+    std::vector<CovMap> allCov;
     for (int w = 0; w < n_windows; w++) {
         const uint32_t leftPos = 100000u + 1000u * (uint32_t)w;
         const int H = rndint(100, 130), nh = rndint(2, 6), nr = rndint(8, 30);
@@ -193,7 +226,43 @@ int main(int argc, char **argv)
             }
         std::cout.rdbuf(old);
         if (onHap != refOn) { fprintf(stderr, "MISMATCH window %d: onHap\n", w); return 1; }
+        /* filterHaplotypes on the resident window (K4) */
+        std::vector<int> filtered;
+        CovMap cov;
+        gpu->filterHaplotypes(haps, reads, liks, filtered, cov, true, op.maxMismatch);
+        allHaps.push_back(haps); allReads.push_back(reads); allLeft.push_back(leftPos);
+        allLiks.push_back(liks); allOn.push_back(onHap); allFiltered.push_back(filtered); allCov.push_back(cov);
     }
+    /* the throughput binding: all windows in ONE submit + ONE coverage call (dindel_b200::WindowBatch) must give
+     * exactly what the window-at-a-time calls gave */
+    for (int full = 1; full >= 0; full--) {
+        dindel_b200::WindowBatch<Haplotype, Read> wb(*gpu, op.maxMismatch, true, full != 0);
+        for (int w = 0; w < n_windows; w++)
+            if (wb.add(allHaps[w], allReads[w], allLeft[w]) != w) { fprintf(stderr, "MISMATCH batch: window index\n"); return 1; }
+        wb.flush();
+        for (int w = 0; w < n_windows; w++) {
+            std::vector<std::vector<MLAlignment> > liks;
+            std::vector<int> onHap, filtered;
+            CovMap cov;
+            wb.result(w, allHaps[w], allReads[w], liks, onHap);
+            wb.filterResult(w, filtered, cov);
+            if (onHap != allOn[w] || filtered != allFiltered[w] || !same_cov(cov, allCov[w])) { fprintf(stderr, "MISMATCH batch window %d: onHap / filtered / coverage\n", w); return 1; }
+            for (size_t h = 0; h < liks.size(); h++)
+                for (size_t r = 0; r < liks[h].size(); r++) {
+                    const MLAlignment &a = liks[h][r], &b = allLiks[w][h][r];
+                    const bool ok = full ? same_mla(a, b)
+                                         : (same_bits(a.ll, b.ll) && a.offHapHMQ == b.offHapHMQ && a.numIndels == b.numIndels && a.firstBase == b.firstBase &&
+                                            a.lastBase == b.lastBase && a.hapIndelCovered == b.hapIndelCovered && a.hapSNPCovered == b.hapSNPCovered &&
+                                            a.nBQT == b.nBQT && same_bits(a.mLogBQ, b.mLogBQ) && a.hpos.empty());
+                    if (!ok) { fprintf(stderr, "MISMATCH batch (full %d) window %d hap %d read %d\n", full, w, (int)h, (int)r); return 1; }
+                }
+            if (full) {
+                for (size_t h = 0; h < filtered.size(); h++) n_filt += filtered[h];
+                for (CovMap::const_iterator it = cov.begin(); it != cov.end(); ++it) n_covreads += it->second.nf + it->second.nr;
+            }
+        }
+    }
+    if (n_covreads == 0) { fprintf(stderr, "MISMATCH: no covering reads counted at all\n"); return 1; }
     /* error behaviour: a haplotype shorter than maxLengthDel throws "hapSize error." like the reference
      * constructor (ObservationModelFB.cpp:47) */
     {
@@ -212,7 +281,8 @@ int main(int argc, char **argv)
         }
     }
     delete gpu;
-    printf("adapter_ref_test ok: %ld pairs identical to the reference class (%ld indel events, %ld snps, %ld covered hap indels)\n",
-           n_pairs, n_ind, n_snp, n_cov);
+    printf("adapter_ref_test ok: %ld pairs identical to the reference class (%ld indel events, %ld snps, %ld covered hap indels); "
+           "batched submit == window-at-a-time (%ld filtered haplotypes, %ld covering reads)\n",
+           n_pairs, n_ind, n_snp, n_cov, n_filt, n_covreads);
     return 0;
 }
