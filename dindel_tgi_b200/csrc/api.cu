@@ -17,9 +17,12 @@ extern "C" size_t k1_generic_smem_per_warp(int maxS, int maxR, int bt_in_smem);
 extern "C" cudaError_t k1_generic_launch(const K1Batch *B, int grid, int warps_per_cta,
                                          int bt_in_smem, size_t smem_bytes, cudaStream_t stream);
 extern "C" int k1_tiled_supported(int maxS, int maxR, int J);
+extern "C" void k1_tiled_class_table(int J, int32_t out[6]);
+extern "C" size_t k1_tiled_bt_slot_bytes(int maxR, int J);
+extern "C" size_t k1_tiled_bt_slots(int num_sms);
 extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream_t stream,
-                                       int *launches, unsigned class_mask);
-extern "C" unsigned k1_tiled_class_of(int S);
+                                       int *launches, unsigned class_mask, int J);
+extern "C" unsigned k1_tiled_class_of(int S, int J);
 extern "C" cudaError_t k1_tiled_prepare(const K1Batch *B, cudaStream_t stream, int *launches);
 extern "C" cudaError_t k2_launch(const K2Args *a, cudaStream_t st);
 extern "C" cudaError_t k3_launch(const K3Args *a, cudaStream_t st);
@@ -538,6 +541,7 @@ static int prepare_batch(dindel_ctx *ctx, const dindel_batch_in *in, int want_hp
     B.luts = (const K1Luts *)ctx->d_luts.p;
     B.max_R = maxR > 0 ? maxR : 1;
     B.max_S = maxH + 2;
+    k1_tiled_class_table(ctx->luts.numT - 1, B.class_c);
     memset(&ctx->timing, 0, sizeof(ctx->timing));
     ctx->timing.n_pairs = n_pairs;
     long long cells = 0;
@@ -574,7 +578,7 @@ static void scan_range(dindel_ctx *ctx, const dindel_batch_in *in, int w0, int w
     g.u0 = ctx->win_unit[w0]; g.u1 = ctx->win_unit[w1];
     g.class_mask = 0;
     for (int h = g.h0; h < g.h1; h++) {
-        unsigned cls = k1_tiled_class_of((int)(in->hap_off[h + 1] - in->hap_off[h]) + 2);
+        unsigned cls = k1_tiled_class_of((int)(in->hap_off[h + 1] - in->hap_off[h]) + 2, ctx->luts.numT - 1);
         if (cls < 32) g.class_mask |= 1u << cls;
     }
     const unsigned char *hs = (const unsigned char *)in->hap_seq, *rs = (const unsigned char *)in->read_seq;
@@ -664,7 +668,13 @@ static int k1_range(dindel_ctx *ctx, const Range &g, Lane &ln, int *launches)
     if (g.u1 > g.u0) {
         if (g.use_tiled) {
             int n = 0;
-            CU(k1_tiled_launch(&b, ctx->num_sms, st, &n, g.class_mask));
+            const int J = ctx->luts.numT - 1;
+            b.bt_slot_bytes = (long long)k1_tiled_bt_slot_bytes(b.max_R, J);
+            if (b.bt_slot_bytes) { // J > 7: back-pointer rows live in global memory, one slot per resident warp
+                CU(ln.d_bt.ensure((size_t)b.bt_slot_bytes * k1_tiled_bt_slots(ctx->num_sms)));
+                b.bt_scratch = (uint8_t *)ln.d_bt.p;
+            }
+            CU(k1_tiled_launch(&b, ctx->num_sms, st, &n, g.class_mask, J));
             *launches += n;
         } else {
             // generic kernel: pick the shared-memory plan

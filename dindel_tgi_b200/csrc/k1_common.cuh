@@ -17,8 +17,8 @@
 #ifndef K1_READ_CHUNK
 #define K1_READ_CHUNK 4 // reads per work unit (window, hap, chunk): small units keep launch tails short
 #endif
-#define K1_TILED_SLOTS 8    // RO slots per shape class (columns per lane <= 8)
-#define K1_TILED_BUCKETS 48 // 6 shape classes x 8 slots
+#define K1_TILED_SLOTS 16   // RO slots per shape class (columns per lane <= 16)
+#define K1_TILED_BUCKETS 96 // 6 shape classes x 16 slots
 
 struct K1Luts {
     // ObservationModelFB.cpp:232-234 by base phred (Read.hpp:143-148 conversion included)
@@ -61,8 +61,10 @@ struct K1Batch {
     uint2 *units;
     unsigned *bucket_start;      // [K1_TILED_BUCKETS + 1]
     unsigned *bucket_work;       // [2 * K1_TILED_BUCKETS] counts, then fill cursors
+    int32_t class_c[6];          // tiled kernel: state columns per lane of each shape class (depends on J), 0 = unused
     const K1Luts *luts;
-    uint8_t *bt_scratch;         // generic kernel: per-warp back-pointer slots when smem is short
+    uint8_t *bt_scratch;         // per-warp back-pointer slots in global memory (generic kernel when smem is
+                                 // short; tiled kernel for J > 7, where a pair's rows are too large for smem)
     long long bt_slot_bytes;
     int32_t max_R, max_S;
 };

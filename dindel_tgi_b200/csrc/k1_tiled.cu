@@ -34,6 +34,7 @@
 #ifndef K1_LEFT_TREE
 #define K1_LEFT_TREE 1
 #endif
+#define K1_TILED_BTG_MAX_CTAS 2 // resident CTAs per SM of the classes that keep back-pointers in global memory
 #define FULLMASK 0xffffffffu
 
 // call f(integral_constant<int, cro>) for the run-time value cro in [0, C)
@@ -52,9 +53,9 @@ struct TiledCfg {
     static constexpr int U16 = NIB ? (C + 3) / 4 : (C + 1) / 2; // 16-bit back-pointer units per lane-row
 };
 
-__host__ __device__ inline size_t tiled_smem_per_warp(int C, int U16, int maxR)
+__host__ __device__ inline size_t tiled_smem_per_warp(int C, int U16, int maxR, bool bt_global = false)
 {
-    size_t b = (size_t)maxR * U16 * 64   // back-pointers
+    size_t b = (bt_global ? 0 : (size_t)maxR * U16 * 64) // back-pointers
                + (size_t)maxR * 16       // eq / uq
                + (size_t)2 * 32 * C * 8  // alpha[bMid]+obs[bMid]
                + (size_t)maxR * 2        // map state
@@ -144,8 +145,10 @@ __device__ __forceinline__ void scan_first_wins(const double (&v0)[C], const dou
     }
 }
 
-template <int C, int J>
-__global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_kernel(K1Batch B, int cls)
+// MINB: resident CTAs per SM the register budget is set for; BTG: back-pointer rows in a per-warp slot of
+// global memory (L2 resident) instead of shared memory (long reads x wide classes: 250 x 352 columns = 96 KB).
+template <int C, int J, int MINB, bool BTG>
+__global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Batch B, int cls)
 {
     using Cfg = TiledCfg<C, J>;
     constexpr int U16 = Cfg::U16;
@@ -160,9 +163,10 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
         s_hp_lpn[i] = L->hp_lpn[i];
     }
     __syncthreads();
-    unsigned char *base = smem_raw + tiled_smem_per_warp(C, U16, maxR) * wib;
-    uint16_t *sm_bt = reinterpret_cast<uint16_t *>(base);
-    double *sm_eq = reinterpret_cast<double *>(base + (size_t)maxR * U16 * 64);
+    unsigned char *base = smem_raw + tiled_smem_per_warp(C, U16, maxR, BTG) * wib;
+    uint16_t *sm_bt = BTG ? reinterpret_cast<uint16_t *>(B.bt_scratch + ((long long)blockIdx.x * K1_TILED_WPC + wib) * B.bt_slot_bytes)
+                          : reinterpret_cast<uint16_t *>(base);
+    double *sm_eq = reinterpret_cast<double *>(base + (BTG ? 0 : (size_t)maxR * U16 * 64));
     double *sm_uq = sm_eq + maxR;
     double *sm_ao = sm_uq + maxR; // [2][32*C]
     int16_t *sm_ms = reinterpret_cast<int16_t *>(sm_ao + 2 * 32 * C);
@@ -607,15 +611,22 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, K1_TILED_MINB) k1_tiled_ker
 // ------------------------------------------------------------------------------------------
 // host side: shape classes and launches
 // ------------------------------------------------------------------------------------------
-static const int kClassC[] = {2, 3, 4, 5, 6, 8};
-static const int kNumClass = 6;
-__constant__ int d_kClassC[6] = {2, 3, 4, 5, 6, 8};
+// Shape classes = state columns per lane.  J = 6 (CLI default maxLengthIndel 5): six classes up to S = 256.
+// J = 11 (maxLengthDel 10, configs[3]): three wide classes up to S = 352, back-pointers in global memory.
+static const int kClassC6[6] = {2, 3, 4, 5, 6, 8};
+static const int kClassC11[6] = {8, 10, 11, 0, 0, 0};
+static const int *class_table(int J) { return J == 6 ? kClassC6 : (J == 11 ? kClassC11 : nullptr); }
+extern "C" void k1_tiled_class_table(int J, int32_t out[6])
+{
+    const int *t = class_table(J);
+    for (int i = 0; i < 6; i++) out[i] = t ? t[i] : 0;
+}
 
-__device__ __forceinline__ int tiled_class_of_dev(int S)
+__device__ __forceinline__ int tiled_class_of_dev(const K1Batch &B, int S)
 {
 #pragma unroll
     for (int i = 0; i < 6; i++)
-        if (S <= 32 * d_kClassC[i]) return i;
+        if (B.class_c[i] > 0 && S <= 32 * B.class_c[i]) return i;
     return -1;
 }
 
@@ -632,9 +643,9 @@ __global__ void k1_tiled_units(K1Batch B, int pass)
     if (nchunk == 0) return;
     for (int h = 0; h < nh; h++) {
         const int H = (int)(B.hap_off[h0 + h + 1] - B.hap_off[h0 + h]);
-        const int cls = tiled_class_of_dev(H + 2);
+        const int cls = tiled_class_of_dev(B, H + 2);
         if (cls < 0) continue;
-        const int bkt = cls * K1_TILED_SLOTS + (H + 1) % d_kClassC[cls];
+        const int bkt = cls * K1_TILED_SLOTS + (H + 1) % B.class_c[cls];
         if (pass == 0) {
             atomicAdd(&B.bucket_work[bkt], nchunk);
         } else {
@@ -670,59 +681,80 @@ extern "C" cudaError_t k1_tiled_prepare(const K1Batch *B, cudaStream_t st, int *
     return cudaGetLastError();
 }
 
-template <int C, int J>
+template <int C, int J, int MINB, bool BTG>
 static cudaError_t launch_one(const K1Batch *B, int num_sms, int cls, cudaStream_t st)
 {
     constexpr int U16 = TiledCfg<C, J>::U16;
     const int warps = K1_TILED_WPC;
-    const size_t smem = tiled_smem_per_warp(C, U16, B->max_R) * warps;
-    cudaError_t e = cudaFuncSetAttribute(k1_tiled_kernel<C, J>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t smem = tiled_smem_per_warp(C, U16, B->max_R, BTG) * warps;
+    cudaError_t e = cudaFuncSetAttribute(k1_tiled_kernel<C, J, MINB, BTG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_tiled_kernel<C, J>, warps * 32, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_tiled_kernel<C, J, MINB, BTG>, warps * 32, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) return cudaErrorInvalidConfiguration;
+    if (BTG && per_sm > K1_TILED_BTG_MAX_CTAS) per_sm = K1_TILED_BTG_MAX_CTAS; // scratch slots are sized for this
     long long grid = (long long)num_sms * per_sm;
     long long need = (B->unit_end - B->unit_begin + warps - 1) / warps;
     if (grid > need) grid = need;
     if (grid < 1) grid = 1;
-    k1_tiled_kernel<C, J><<<(int)grid, warps * 32, smem, st>>>(*B, cls);
+    k1_tiled_kernel<C, J, MINB, BTG><<<(int)grid, warps * 32, smem, st>>>(*B, cls);
     return cudaGetLastError();
 }
 
+// global back-pointer scratch the J > 7 classes need: one slot per resident warp of a full grid
+extern "C" size_t k1_tiled_bt_slot_bytes(int maxR, int J)
+{
+    if (J <= 7) return 0;
+    const int *t = class_table(J);
+    int C = 0;
+    for (int i = 0; t && i < 6; i++) if (t[i] > C) C = t[i];
+    return (((size_t)maxR + 1) * ((C + 1) / 2) * 64 + 255) & ~(size_t)255;
+}
+extern "C" size_t k1_tiled_bt_slots(int num_sms) { return (size_t)num_sms * K1_TILED_BTG_MAX_CTAS * K1_TILED_WPC; }
 
 extern "C" int k1_tiled_supported(int maxS, int maxR, int J)
 {
-    if (J != 6) return 0;
-    if (maxS > 32 * kClassC[kNumClass - 1]) return 0;
-    // back-pointers of the largest class must fit one CTA of 4 warps in shared memory
-    int C = kClassC[kNumClass - 1];
-    for (int i = 0; i < kNumClass; i++)
-        if (maxS <= 32 * kClassC[i]) { C = kClassC[i]; break; }
-    int U16 = (C + 3) / 4;
-    return tiled_smem_per_warp(C, U16, maxR) * K1_TILED_WPC <= 200 * 1024;
+    const int *t = class_table(J);
+    if (!t) return 0;
+    int C = 0;
+    for (int i = 0; i < 6; i++)
+        if (t[i] > 0 && maxS <= 32 * t[i]) { C = t[i]; break; }
+    if (C == 0) return 0;
+    if (J > 7) return tiled_smem_per_warp(C, (C + 1) / 2, maxR, true) * K1_TILED_WPC <= 100 * 1024;
+    // back-pointers of the largest class present must fit one CTA of 4 warps in shared memory
+    return tiled_smem_per_warp(C, (C + 3) / 4, maxR) * K1_TILED_WPC <= 200 * 1024;
 }
 
 // One launch per shape class present (class = state columns per lane).  `class_mask` bit i set
 // when some haplotype of the batch falls in class i.
 extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream_t st, int *launches,
-                                       unsigned class_mask)
+                                       unsigned class_mask, int J)
 {
     int n = 0;
     cudaError_t e = cudaSuccess;
-    for (int i = 0; i < kNumClass && e == cudaSuccess; i++) {
-        if (!(class_mask & (1u << i))) continue;
+    const int *t = class_table(J);
+    for (int i = 0; t && i < 6 && e == cudaSuccess; i++) {
+        if (!(class_mask & (1u << i)) || t[i] == 0) continue;
         if (n == 0) {
             e = cudaMemsetAsync(B->counter, 0, 8 * sizeof(unsigned long long), st);
             if (e != cudaSuccess) break;
         }
-        switch (kClassC[i]) {
-        case 2: e = launch_one<2, 6>(B, num_sms, i, st); break;
-        case 3: e = launch_one<3, 6>(B, num_sms, i, st); break;
-        case 4: e = launch_one<4, 6>(B, num_sms, i, st); break;
-        case 5: e = launch_one<5, 6>(B, num_sms, i, st); break;
-        case 6: e = launch_one<6, 6>(B, num_sms, i, st); break;
-        case 8: e = launch_one<8, 6>(B, num_sms, i, st); break;
+        if (J == 6) {
+            switch (t[i]) {
+            case 2: e = launch_one<2, 6, K1_TILED_MINB, false>(B, num_sms, i, st); break;
+            case 3: e = launch_one<3, 6, K1_TILED_MINB, false>(B, num_sms, i, st); break;
+            case 4: e = launch_one<4, 6, K1_TILED_MINB, false>(B, num_sms, i, st); break;
+            case 5: e = launch_one<5, 6, K1_TILED_MINB, false>(B, num_sms, i, st); break;
+            case 6: e = launch_one<6, 6, K1_TILED_MINB, false>(B, num_sms, i, st); break;
+            case 8: e = launch_one<8, 6, K1_TILED_MINB, false>(B, num_sms, i, st); break;
+            }
+        } else {
+            switch (t[i]) {
+            case 8: e = launch_one<8, 11, 2, true>(B, num_sms, i, st); break;
+            case 10: e = launch_one<10, 11, 2, true>(B, num_sms, i, st); break;
+            case 11: e = launch_one<11, 11, 2, true>(B, num_sms, i, st); break;
+            }
         }
         n++;
     }
@@ -730,9 +762,10 @@ extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream
     return e;
 }
 
-extern "C" unsigned k1_tiled_class_of(int S)
+extern "C" unsigned k1_tiled_class_of(int S, int J)
 {
-    for (int i = 0; i < kNumClass; i++)
-        if (S <= 32 * kClassC[i]) return (unsigned)i;
+    const int *t = class_table(J);
+    for (int i = 0; t && i < 6; i++)
+        if (t[i] > 0 && S <= 32 * t[i]) return (unsigned)i;
     return 0xffffffffu;
 }
