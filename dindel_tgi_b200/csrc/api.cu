@@ -185,7 +185,9 @@ struct dindel_ctx {
     std::string err;
     DevBuf d_luts, d_hap_start, d_win_hap, d_win_read, d_win_pair, d_win_unit, d_hap_off,
         d_hap_seq, d_hap_hp, d_read_off, d_read_seq, d_read_qual, d_read_mapq, d_read_start,
-        d_read_flags, d_pairs, d_hpos, d_win_status, d_on_hap, d_x[8];
+        d_read_flags, d_pairs, d_hpos, d_win_status, d_on_hap, d_x[8],
+        d_read_ins_mode, d_read_ins_anchor, d_read_lib, d_lib_off, d_lib_logp, d_lib_log95;
+    int n_libs = 0;
     // resident batch
     bool resident = false, ran = false;
     K1Batch B;
@@ -231,13 +233,15 @@ static double hp_error(int hpLen) // ReadIndelErrorModel.hpp:28-50
     return pbe;
 }
 static void bmid_prior(const dindel_params &p, double lInsgNoIns, double mapQual, double lo[2],
-                       double on[2]) // ObservationModelFB.cpp:268-305, pinsert == 0
+                       double on[2], double *l1m, double lins[2]) // ObservationModelFB.cpp:268-305, pinsert == 0
 {
     double mq = 1.0 - mapQual;
     if (-10.0 * log10(mq) > p.mapQualThreshold) mq = pow(10.0, -p.mapQualThreshold / 10.0);
     double pOff = mq;
+    *l1m = log((1.0 - pOff));
     for (int i = 0; i < 2; i++) {
         double lIns = (i == 1) ? lInsgNoIns : log(1.0 - exp(lInsgNoIns));
+        lins[i] = lIns;
         lo[i] = log(pOff) + lIns + 0.0;
         on[i] = 0.0 + log((1.0 - pOff)) + lIns;
     }
@@ -262,11 +266,11 @@ static void build_luts(const dindel_params &p, K1Luts &L)
     L.lNoInsgNoIns = log(1 - p.pError);
     for (int ph = 0; ph < 256; ph++) {
         double lo[2], on[2];
-        bmid_prior(p, lInsgNoIns, phred_to_prob(ph), lo, on);
+        bmid_prior(p, lInsgNoIns, phred_to_prob(ph), lo, on, &L.prior1m[ph], L.priorIns);
         L.priorLO[0][ph] = lo[0]; L.priorLO[1][ph] = lo[1];
         L.priorOn[0][ph] = on[0]; L.priorOn[1][ph] = on[1];
     }
-    bmid_prior(p, lInsgNoIns, 1.0 - 1e-10, L.priorLO_H, L.priorOn_H); // :1093
+    bmid_prior(p, lInsgNoIns, 1.0 - 1e-10, L.priorLO_H, L.priorOn_H, &L.prior1m_H, L.priorIns); // :1093
     L.hp_lpe[0] = log(1e-5);                          // :1678-1679
     L.hp_lpn[0] = log(1 - 1e-5);
     for (int len = 1; len < K1_HP_LUT; len++) {
@@ -371,7 +375,8 @@ int dindel_b200_destroy(dindel_ctx *ctx)
     DevBuf *bufs[] = {&ctx->d_luts, &ctx->d_hap_start, &ctx->d_win_hap, &ctx->d_win_read,
                       &ctx->d_win_pair, &ctx->d_win_unit, &ctx->d_hap_off, &ctx->d_hap_seq, &ctx->d_hap_hp,
                       &ctx->d_read_off, &ctx->d_read_seq, &ctx->d_read_qual, &ctx->d_read_mapq,
-                      &ctx->d_read_start, &ctx->d_read_flags, &ctx->d_pairs, &ctx->d_hpos,
+                      &ctx->d_read_start, &ctx->d_read_flags, &ctx->d_pairs, &ctx->d_hpos, &ctx->d_read_ins_mode,
+                      &ctx->d_read_ins_anchor, &ctx->d_read_lib, &ctx->d_lib_off, &ctx->d_lib_logp, &ctx->d_lib_log95,
                       &ctx->d_win_status, &ctx->d_on_hap};
     for (DevBuf *b : bufs) b->release();
     for (int i = 0; i < 8; i++) ctx->d_x[i].release();
@@ -412,6 +417,29 @@ static int validate(const dindel_batch_in *in)
     if (in->n_reads && in->read_off[in->n_reads] > 0 && (!in->read_seq || !in->read_qual))
         return DINDEL_E_INVALID;
     if (in->n_reads && (!in->read_mapq || !in->read_start || !in->read_flags)) return DINDEL_E_INVALID;
+    return DINDEL_OK;
+}
+
+int dindel_b200_set_libraries(dindel_ctx *ctx, int n_libs, const int64_t *lib_off, const double *probs,
+                              const double *ninetyfifth_pct_prob)
+{
+    if (!ctx || n_libs < 0 || (n_libs > 0 && (!lib_off || !probs || !ninetyfifth_pct_prob))) return fail(ctx, DINDEL_E_INVALID, "set_libraries");
+    for (int l = 0; l < n_libs; l++)
+        if (lib_off[l + 1] <= lib_off[l] || lib_off[0] != 0) return fail(ctx, DINDEL_E_INVALID, "lib_off (every library needs >= 1 entry)");
+    CU(cudaSetDevice(ctx->device));
+    ctx->resident = false;
+    ctx->n_libs = n_libs;
+    if (n_libs == 0) return DINDEL_OK;
+    const size_t n = (size_t)lib_off[n_libs];
+    std::vector<double> lp(n), l95((size_t)n_libs);
+    std::vector<long long> off((size_t)n_libs + 1);
+    for (size_t i = 0; i < n; i++) lp[i] = log(probs[i]);                       // cpp:285,287: log(getProb(.))
+    for (int l = 0; l < n_libs; l++) l95[l] = log(ninetyfifth_pct_prob[l]);     // cpp:289
+    for (int l = 0; l <= n_libs; l++) off[l] = lib_off[l];
+    CU(ctx->d_lib_off.ensure(off.size() * 8)); CU(ctx->d_lib_logp.ensure(n * 8)); CU(ctx->d_lib_log95.ensure(l95.size() * 8));
+    CU(cudaMemcpy(ctx->d_lib_off.p, off.data(), off.size() * 8, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(ctx->d_lib_logp.p, lp.data(), n * 8, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(ctx->d_lib_log95.p, l95.data(), l95.size() * 8, cudaMemcpyHostToDevice));
     return DINDEL_OK;
 }
 
@@ -512,6 +540,18 @@ static int prepare_batch(dindel_ctx *ctx, const dindel_batch_in *in, int want_hp
     CU(ctx->d_read_mapq.ensure((size_t)nr + 16));
     CU(ctx->d_read_start.ensure((size_t)nr * 4 + 16));
     CU(ctx->d_read_flags.ensure((size_t)nr + 16));
+    const bool has_ins = in->read_ins_mode != nullptr;
+    if (has_ins) {
+        if (!in->read_ins_anchor || !in->read_lib) return fail(ctx, DINDEL_E_INVALID, "read_ins_mode without read_ins_anchor / read_lib");
+        for (int r = 0; r < nr; r++) {
+            if (in->read_ins_mode[r] > DINDEL_INS_MATE_FORWARD) return fail(ctx, DINDEL_E_INVALID, "read_ins_mode");
+            if (in->read_ins_mode[r] != DINDEL_INS_NONE && (in->read_lib[r] < 0 || in->read_lib[r] >= ctx->n_libs))
+                return fail(ctx, DINDEL_E_INVALID, "read_lib out of range (call dindel_b200_set_libraries first)");
+        }
+        CU(ctx->d_read_ins_mode.ensure((size_t)nr + 16));
+        CU(ctx->d_read_ins_anchor.ensure((size_t)nr * 4 + 16));
+        CU(ctx->d_read_lib.ensure((size_t)nr * 4 + 16));
+    }
     CU(ctx->d_hap_hp.ensure((size_t)hap_bytes + 2 * (size_t)nh + 16));
     CU(ctx->d_pairs.ensure((size_t)n_pairs * sizeof(dindel_pair_out) + 64));
     CU(ctx->d_win_status.ensure((size_t)nw * 4 + 16));
@@ -536,6 +576,14 @@ static int prepare_batch(dindel_ctx *ctx, const dindel_batch_in *in, int want_hp
     B.read_mapq = (const uint8_t *)ctx->d_read_mapq.p;
     B.read_flags = (const uint8_t *)ctx->d_read_flags.p;
     B.read_start = (const uint32_t *)ctx->d_read_start.p;
+    if (has_ins) {
+        B.read_ins_mode = (const uint8_t *)ctx->d_read_ins_mode.p;
+        B.read_ins_anchor = (const int32_t *)ctx->d_read_ins_anchor.p;
+        B.read_lib = (const int32_t *)ctx->d_read_lib.p;
+        B.lib_off = (const long long *)ctx->d_lib_off.p;
+        B.lib_logp = (const double *)ctx->d_lib_logp.p;
+        B.lib_log95 = (const double *)ctx->d_lib_log95.p;
+    }
     B.pairs = (dindel_pair_out *)ctx->d_pairs.p;
     B.hpos = want_hpos ? (int16_t *)ctx->d_hpos.p : nullptr;
     B.luts = (const K1Luts *)ctx->d_luts.p;
@@ -615,6 +663,11 @@ static int copy_in_range(dindel_ctx *ctx, const dindel_batch_in *in, const Range
     UPR(d_read_mapq, in->read_mapq, g.r0, nrr, 1);
     UPR(d_read_start, in->read_start, g.r0, nrr, 4);
     UPR(d_read_flags, in->read_flags, g.r0, nrr, 1);
+    if (in->read_ins_mode) {
+        UPR(d_read_ins_mode, in->read_ins_mode, g.r0, nrr, 1);
+        UPR(d_read_ins_anchor, in->read_ins_anchor, g.r0, nrr, 4);
+        UPR(d_read_lib, in->read_lib, g.r0, nrr, 4);
+    }
 #undef UPR
     return DINDEL_OK;
 }

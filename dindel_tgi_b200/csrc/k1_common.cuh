@@ -31,6 +31,9 @@ struct K1Luts {
     double priorLO[2][256], priorOn[2][256];
     // the artificial high-mapping-quality prior (mapQual = 1-1e-10, cpp:1093): [plane]
     double priorLO_H[2], priorOn_H[2];
+    // the same prior in parts, for reads with an insert-size term pinsert[x] (cpp:283-303):
+    // prior[x] = (pinsert[x] + prior1m) + priorIns[plane]; prior[LO] = priorLO + pinsert[0]
+    double prior1m[256], prior1m_H, priorIns[2];
     // setupTransitionProbs (cpp:1678-1703) by run-length code; code 0 = the 1e-5 default
     double hp_lpe[K1_HP_LUT], hp_lpn[K1_HP_LUT];
     // cpp:1643-1667
@@ -53,6 +56,12 @@ struct K1Batch {
     const long long *read_off;
     const uint8_t *read_seq, *read_qual, *read_mapq, *read_flags;
     const uint32_t *read_start;
+    // insert-size prior (all null when no read has one): per read mode / anchor / library, per library the
+    // log-probabilities by insert size (lib_off[l] .. lib_off[l+1]) and log(95th-percentile probability)
+    const uint8_t *read_ins_mode;
+    const int32_t *read_ins_anchor, *read_lib;
+    const long long *lib_off;
+    const double *lib_logp, *lib_log95;
     dindel_pair_out *pairs;
     int16_t *hpos;
     unsigned long long *counter; // work-queue heads (generic kernel: [0]; tiled kernel: one per class)
@@ -68,6 +77,18 @@ struct K1Batch {
     long long bt_slot_bytes;
     int32_t max_R, max_S;
 };
+
+// pinsert[x] of computeBMidPrior (cpp:283-290) for hap column x in [1, H]; plain int arithmetic like the reference
+// (its hapStart member is an int, ObservationModelFB.hpp:112), Library::getProb's clamp (Library.hpp:61-66).
+__device__ __forceinline__ double k1_pinsert(const double *logp, int maxins, int mode, int anchor, int hapStart,
+                                             int x, int R, int bMid)
+{
+    int d = (mode == DINDEL_INS_MATE_REVERSE) ? (hapStart + x - bMid - anchor) : (hapStart + x + R - bMid - anchor);
+    d = d < 0 ? -d : d;
+    if (d < 0) d = -d;
+    if (d >= maxins) d = maxins - 1;
+    return logp[d];
+}
 
 // ObservationModelFB.cpp:35-102 (Init): anchor base of one pair.
 __device__ __forceinline__ int k1_bmid(uint32_t hapStart, int H, int R, uint32_t mReadStart,

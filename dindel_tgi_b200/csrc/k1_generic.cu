@@ -271,17 +271,37 @@ __global__ void __launch_bounds__(128) k1_generic_kernel(K1Batch B, int bt_in_sm
             int msR = 0, msH = 0;
             if (lane == 0) {
                 const double *Bm = sm.P[cur];
+                // insert-size prior of this read (cpp:279-293; only with --libFile)
+                const int insMode = B.read_ins_mode ? (int)B.read_ins_mode[r] : DINDEL_INS_NONE;
+                int insAnchor = 0, insMax = 1;
+                const double *insLogp = nullptr;
+                double ins0 = 0.0;
+                if (insMode != DINDEL_INS_NONE) {
+                    const int lib = B.read_lib[r];
+                    insAnchor = B.read_ins_anchor[r];
+                    insLogp = B.lib_logp + B.lib_off[lib];
+                    insMax = (int)(B.lib_off[lib + 1] - B.lib_off[lib]);
+                    ins0 = B.lib_log95[lib];
+                }
                 for (int s = 0; s < 2 * S; s++) {
                     int pl = s >= S;
                     int x = pl ? s - S : s;
                     double t = sm.ao[s] + Bm[s];
                     double pr = (x == 0) ? L->priorLO[pl][mapq] : (x == RO) ? -100.0 : L->priorOn[pl][mapq];
+                    double prH = (x == 0) ? L->priorLO_H[pl] : (x == RO) ? -100.0 : L->priorOn_H[pl];
+                    if (insMode != DINDEL_INS_NONE && x != RO) {
+                        if (x == 0) { pr = pr + ins0; prH = prH + ins0; } // cpp:298
+                        else {                                            // cpp:301
+                            const double pin = k1_pinsert(insLogp, insMax, insMode, insAnchor, (int)hapStart, x, R, bMid);
+                            pr = (pin + L->prior1m[mapq]) + L->priorIns[pl];
+                            prH = (pin + L->prior1m_H) + L->priorIns[pl];
+                        }
+                    }
                     double v = t + pr;
                     if (v > ll + 1e-10) { ll = v; msR = s; }
                     if (x == 0) { if (v > llOff) llOff = v; }
                     else if (x != RO) { if (v > llOn) llOn = v; }
-                    pr = (x == 0) ? L->priorLO_H[pl] : (x == RO) ? -100.0 : L->priorOn_H[pl];
-                    v = t + pr;
+                    v = t + prH;
                     if (v > llH + 1e-10) { llH = v; msH = s; }
                 }
             }

@@ -564,16 +564,39 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                 const double pOn0 = L->priorOn[0][mapq], pOn1 = L->priorOn[1][mapq];
                 const double hLO0 = L->priorLO_H[0], hLO1 = L->priorLO_H[1];
                 const double hOn0 = L->priorOn_H[0], hOn1 = L->priorOn_H[1];
+                // insert-size prior of this read (cpp:279-293): warp-uniform, rare (only with --libFile)
+                const int insMode = B.read_ins_mode ? (int)B.read_ins_mode[r] : DINDEL_INS_NONE;
+                int insAnchor = 0, insMax = 1;
+                const double *insLogp = nullptr;
+                double ins0 = 0.0;
+                if (insMode != DINDEL_INS_NONE) {
+                    const int lib = B.read_lib[r];
+                    insAnchor = B.read_ins_anchor[r];
+                    insLogp = B.lib_logp + B.lib_off[lib];
+                    insMax = (int)(B.lib_off[lib + 1] - B.lib_off[lib]);
+                    ins0 = B.lib_log95[lib];
+                }
 #pragma unroll
                 for (int c = 0; c < C; c++) {
                     const int x = c0 + c;
                     const double t0 = sm_ao[x] + P0[c];
                     const double t1v = sm_ao[32 * C + x] + P1[c];
                     const bool lo = (x == 0), ro = (x == RO), pad = (x > RO);
-                    vR0[c] = pad ? K1_NEG_INF : t0 + (lo ? pLO0 : ro ? -100.0 : pOn0);
-                    vR1[c] = pad ? K1_NEG_INF : t1v + (lo ? pLO1 : ro ? -100.0 : pOn1);
-                    vH0[c] = pad ? K1_NEG_INF : t0 + (lo ? hLO0 : ro ? -100.0 : hOn0);
-                    vH1[c] = pad ? K1_NEG_INF : t1v + (lo ? hLO1 : ro ? -100.0 : hOn1);
+                    double qR0 = lo ? pLO0 : pOn0, qR1 = lo ? pLO1 : pOn1, qH0 = lo ? hLO0 : hOn0, qH1 = lo ? hLO1 : hOn1;
+                    if (insMode != DINDEL_INS_NONE && !ro && !pad) {
+                        if (lo) { // (log(pOff) + logpIns) + pinsert[0]  (cpp:298)
+                            qR0 = pLO0 + ins0; qR1 = pLO1 + ins0; qH0 = hLO0 + ins0; qH1 = hLO1 + ins0;
+                        } else {  // (pinsert[x] + log(1 - pOff)) + logpIns  (cpp:301)
+                            const double pin = k1_pinsert(insLogp, insMax, insMode, insAnchor, (int)hapStart, x, R, bMid);
+                            const double aR = pin + L->prior1m[mapq], aH = pin + L->prior1m_H;
+                            qR0 = aR + L->priorIns[0]; qR1 = aR + L->priorIns[1];
+                            qH0 = aH + L->priorIns[0]; qH1 = aH + L->priorIns[1];
+                        }
+                    }
+                    vR0[c] = pad ? K1_NEG_INF : t0 + (ro ? -100.0 : qR0);
+                    vR1[c] = pad ? K1_NEG_INF : t1v + (ro ? -100.0 : qR1);
+                    vH0[c] = pad ? K1_NEG_INF : t0 + (ro ? -100.0 : qH0);
+                    vH1[c] = pad ? K1_NEG_INF : t1v + (ro ? -100.0 : qH1);
                     if (x >= 1 && x <= H) {
                         onMax = (vR0[c] > onMax) ? vR0[c] : onMax;
                         onMax = (vR1[c] > onMax) ? vR1[c] : onMax;

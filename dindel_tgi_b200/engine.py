@@ -38,7 +38,8 @@ class _BatchIn(C.Structure):
                 ("hap_start", C.c_void_p), ("win_hap", C.c_void_p), ("win_read", C.c_void_p),
                 ("hap_off", C.c_void_p), ("hap_seq", C.c_void_p), ("read_off", C.c_void_p),
                 ("read_seq", C.c_void_p), ("read_qual", C.c_void_p), ("read_mapq", C.c_void_p),
-                ("read_start", C.c_void_p), ("read_flags", C.c_void_p)]
+                ("read_start", C.c_void_p), ("read_flags", C.c_void_p),
+                ("read_ins_mode", C.c_void_p), ("read_ins_anchor", C.c_void_p), ("read_lib", C.c_void_p)]
 
 
 class _BatchOut(C.Structure):
@@ -100,7 +101,7 @@ EXPORTS = [
     "dindel_b200_upload", "dindel_b200_run", "dindel_b200_download", "dindel_b200_sync",
     "dindel_b200_get_timing", "dindel_b200_hpos_stride", "dindel_b200_alloc_pinned",
     "dindel_b200_free_pinned", "dindel_b200_measure_fp64_peak", "dindel_b200_pair_sums",
-    "dindel_b200_bayes_em", "dindel_b200_plan_shards", "dindel_b200_coverage",
+    "dindel_b200_bayes_em", "dindel_b200_plan_shards", "dindel_b200_coverage", "dindel_b200_set_libraries",
 ]
 
 _lib = None
@@ -139,6 +140,7 @@ def load_library():
     lib.dindel_b200_pair_sums.argtypes = [C.c_void_p, C.POINTER(_PairSumIn), C.c_void_p]
     lib.dindel_b200_bayes_em.argtypes = [C.c_void_p, C.POINTER(_EmIn), C.POINTER(_EmOut)]
     lib.dindel_b200_coverage.argtypes = [C.c_void_p, C.POINTER(_CoverIn), C.POINTER(_CoverOut)]
+    lib.dindel_b200_set_libraries.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.dindel_b200_plan_shards.argtypes = [C.POINTER(_BatchIn), C.c_int, C.c_void_p]
     _lib = lib
     return lib
@@ -216,12 +218,17 @@ class Batch:
                                       self.hap_seq, self.read_off, self.read_seq, self.read_qual,
                                       self.read_mapq, self.read_start, self.read_flags))
 
-    def _c(self):
+    def _c(self, ins=None):
+        """ins: optional (read_ins_mode u8, read_ins_anchor i32, read_lib i32) arrays (insert-size prior)."""
         b = _BatchIn()
         b.n_windows, b.n_haps, b.n_reads = self.n_windows, self.n_haps, self.n_reads
         for n in ("hap_start", "win_hap", "win_read", "hap_off", "hap_seq", "read_off", "read_seq",
                   "read_qual", "read_mapq", "read_start", "read_flags"):
             setattr(b, n, getattr(self, n).ctypes.data)
+        if ins is not None:
+            self._ins = (np.ascontiguousarray(ins[0], dtype=np.uint8), np.ascontiguousarray(ins[1], dtype=np.int32),
+                         np.ascontiguousarray(ins[2], dtype=np.int32))
+            b.read_ins_mode, b.read_ins_anchor, b.read_lib = (a.ctypes.data for a in self._ins)
         return b
 
     def window(self, w):
@@ -331,13 +338,22 @@ class Engine:
         self.lib.dindel_b200_get_timing(self.h, C.byref(t))
         return t
 
-    def compute_likelihoods(self, batch, want_hpos=True, keep_hpos=False):
+    def set_libraries(self, probs, p95):
+        """probs: list of Library::probs arrays; p95: list of getNinetyFifthPctProb() (dindel_b200_set_libraries)."""
+        off = np.concatenate([[0], np.cumsum([len(p) for p in probs])]).astype(np.int64)
+        flat = np.ascontiguousarray(np.concatenate(probs) if probs else np.zeros(0), dtype=np.float64)
+        p95 = np.ascontiguousarray(p95, dtype=np.float64)
+        self._check(self.lib.dindel_b200_set_libraries(self.h, len(probs), off.ctypes.data_as(C.c_void_p),
+                                                       flat.ctypes.data_as(C.c_void_p), p95.ctypes.data_as(C.c_void_p)),
+                    "set_libraries")
+
+    def compute_likelihoods(self, batch, want_hpos=True, keep_hpos=False, ins=None):
         """Host buffers in, host buffers out: dindel_b200_submit.  keep_hpos: the hpos rows are produced and stay
         resident in HBM for coverage() without being copied to the host (DINDEL_OUT_KEEP_HPOS)."""
         o, pairs, win_pair, win_status, on_hap, hpos = self._alloc_out(batch, want_hpos)
         if keep_hpos:
             o.flags = OUT_KEEP_HPOS
-        cb = batch._c()
+        cb = batch._c(ins)
         self._check(self.lib.dindel_b200_submit(self.h, C.byref(cb), C.byref(o)), "submit")
         self._resident, self._n_haps = (batch, want_hpos or keep_hpos), batch.n_haps
         return PairResults(pairs, win_pair, win_status, on_hap, hpos, self.timing())

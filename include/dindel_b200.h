@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define DINDEL_B200_ABI_VERSION 1
+#define DINDEL_B200_ABI_VERSION 2
 
 /* error codes (batch-fatal) */
 #define DINDEL_OK 0
@@ -74,7 +74,20 @@ typedef struct dindel_batch_in {
     const uint8_t *read_mapq;   /* [n_reads] phred mapping quality (bam core.qual) */
     const uint32_t *read_start; /* [n_reads] uint32_t(read.posStat.first) (cpp:52) */
     const uint8_t *read_flags;  /* [n_reads] DINDEL_READ_* */
+    /* Insert-size prior of computeBMidPrior (ObservationModelFB.cpp:279-293), used when the pipeline runs with
+     * --libFile (params.mapUnmappedReads, DInDel.cpp:4268-4272).  All three NULL = no read has one.  Per read:
+     *   read_ins_mode   DINDEL_INS_NONE unless mapUnmappedReads && read.isPaired() && !mateIsUnmapped() &&
+     *                   mateLen != -1 && core.tid == core.mtid (cpp:279,283); then DINDEL_INS_MATE_REVERSE when
+     *                   mateIsReverse() (cpp:284-285) else DINDEL_INS_MATE_FORWARD (cpp:286-287)
+     *   read_ins_anchor int(matePos + mateLen) for MATE_REVERSE, int(matePos) for MATE_FORWARD
+     *   read_lib        index of the read's Library among those given to dindel_b200_set_libraries */
+    const uint8_t *read_ins_mode;
+    const int32_t *read_ins_anchor;
+    const int32_t *read_lib;
 } dindel_batch_in;
+#define DINDEL_INS_NONE 0
+#define DINDEL_INS_MATE_REVERSE 1
+#define DINDEL_INS_MATE_FORWARD 2
 
 /* Flat image of one MLAlignment (MLAlignment.hpp:50-70), 64 bytes.  The AlignedVariant maps
  * (indels/snps/hapIndelCovered/hapSNPCovered) are pure functions of hpos / firstBase / lastBase
@@ -127,6 +140,13 @@ const char *dindel_b200_last_error(const dindel_ctx *ctx);
 /* one context = one device + one stream; use from one host thread at a time */
 int dindel_b200_create(const dindel_params *p, int device, dindel_ctx **out);
 int dindel_b200_destroy(dindel_ctx *ctx);
+
+/* Insert-size libraries (Library.hpp:31-129): library l holds Library::probs (normalised, floored at 1e-10,
+ * maxins = lib_off[l+1]-lib_off[l] entries; getProb clamps |x| to maxins-1, Library.hpp:61-66) and its
+ * getNinetyFifthPctProb().  The library takes log() of them with the host libm, as cpp:285-289 does per call.
+ * Replaces the set given before; needed only when some read has read_ins_mode != DINDEL_INS_NONE. */
+int dindel_b200_set_libraries(dindel_ctx *ctx, int n_libs, const int64_t *lib_off, const double *probs,
+                              const double *ninetyfifth_pct_prob);
 
 int64_t dindel_b200_count_pairs(const dindel_batch_in *in);
 int64_t dindel_b200_count_cells(const dindel_batch_in *in);

@@ -42,6 +42,20 @@ struct ReadTraits {
     static uint32_t start(const ReadT &r) { return uint32_t(r.posStat.first); }                      // ObservationModelFB.cpp:52
     static bool reverse(const ReadT &r) { return r.onReverseStrand; }
 #ifdef BAM_BAM_H
+    // insert-size prior of computeBMidPrior (ObservationModelFB.cpp:279-293): which formula applies to this read
+    // (the caller ANDs it with params.mapUnmappedReads), its anchor coordinate, and its Library (Read.hpp:258)
+    static int insertMode(const ReadT &r)
+    {
+        const bam1_t *b = r.getBam();
+        if (!(b->core.flag & BAM_FPAIRED) || (b->core.flag & BAM_FMUNMAP) || r.mateLen == -1 || b->core.tid != b->core.mtid)
+            return DINDEL_INS_NONE;
+        return (b->core.flag & BAM_FMREVERSE) ? DINDEL_INS_MATE_REVERSE : DINDEL_INS_MATE_FORWARD;
+    }
+    static int32_t insertAnchor(const ReadT &r, int mode)
+    {
+        return mode == DINDEL_INS_MATE_REVERSE ? int(r.matePos + r.mateLen) : int(r.matePos);
+    }
+    static __typeof__(&((const ReadT *)0)->getLibrary()) library(const ReadT &r) { return &r.getLibrary(); }
     // strand a covering read is counted on (DInDel.cpp:1987-1992): unmapped ? !mateIsReverse() : isReverse()
     static bool coverReverse(const ReadT &r)
     {
@@ -56,19 +70,39 @@ struct ReadTraits {
 class Engine {
 public:
     template <class ObsParams>
-    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0), last_nh_(0), last_nr_(0)
+    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0), last_nh_(0), last_nr_(0), mapUnmapped_(false), libOff_(1, 0)
     {
         dindel_b200_default_params(&p_);
         p_.pError = op.pError; p_.pMut = op.pMut; p_.mapQualThreshold = op.mapQualThreshold;
         p_.pFirstgLO = op.pFirstgLO; p_.checkBaseQualThreshold = op.checkBaseQualThreshold;
         p_.maxLengthDel = op.maxLengthDel; p_.padCover = op.padCover; p_.bMid = op.bMid;
         p_.forceReadOnHaplotype = op.forceReadOnHaplotype ? 1 : 0;
+        mapUnmapped_ = op.mapUnmappedReads ? true : false; // set by --libFile (DInDel.cpp:4268-4272)
         int rc = dindel_b200_create(&p_, device, &ctx_);
         if (rc != DINDEL_OK) throw std::string("dindel_b200: ") + dindel_b200_strerror(rc);
     }
     ~Engine() { if (ctx_) dindel_b200_destroy(ctx_); }
     dindel_ctx *ctx() const { return ctx_; }
     const dindel_params &params() const { return p_; }
+    bool mapUnmappedReads() const { return mapUnmapped_; }
+    void setMapUnmappedReads(bool v) { mapUnmapped_ = v; } // the reference flips it after construction (DInDel.cpp:4270)
+
+    // Index of an insert-size library (Library.hpp:31-129) among those uploaded to the GPU; a library seen for the
+    // first time is read out through its public interface and all of them are re-sent (dindel_b200_set_libraries).
+    template <class LibT>
+    int libraryIndex(const LibT *lib)
+    {
+        std::map<const void *, int>::const_iterator it = libIndex_.find((const void *)lib);
+        if (it != libIndex_.end()) return it->second;
+        const int idx = (int)libP95_.size(), maxins = lib->getMaxInsertSize();
+        for (int d = 0; d < maxins; d++) libProbs_.push_back(lib->getProb(d));
+        libOff_.push_back((int64_t)libProbs_.size());
+        libP95_.push_back(lib->getNinetyFifthPctProb());
+        libIndex_[(const void *)lib] = idx;
+        int rc = dindel_b200_set_libraries(ctx_, (int)libP95_.size(), &libOff_[0], &libProbs_[0], &libP95_[0]);
+        if (rc != DINDEL_OK) throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx_) + ")";
+        return idx;
+    }
 
     template <class HapT, class ReadT, class MLA>
     void computeLikelihoods(const std::vector<HapT> &haps, const std::vector<ReadT> &reads,
@@ -91,6 +125,10 @@ private:
     dindel_params p_;
     dindel_ctx *ctx_;
     size_t last_nh_, last_nr_; // shape of the resident window (filterHaplotypes checks it is the same one)
+    bool mapUnmapped_;
+    std::map<const void *, int> libIndex_;
+    std::vector<int64_t> libOff_;
+    std::vector<double> libProbs_, libP95_;
 };
 
 // mapped types of MLA::indels and HapT::indels (C++98-friendly, the reference builds as gnu++98)
@@ -192,8 +230,10 @@ void Engine::computeLikelihoods(const std::vector<HapT> &haps, const std::vector
     if (nh == 0 || nr == 0) return;
     std::vector<int64_t> hap_off(1, 0), read_off(1, 0);
     std::string hap_seq, read_seq;
-    std::vector<uint8_t> qual, mapq, flags;
+    std::vector<uint8_t> qual, mapq, flags, insMode;
     std::vector<uint32_t> start;
+    std::vector<int32_t> insAnchor, insLib;
+    bool anyIns = false;
     size_t maxR = 0;
     for (size_t h = 0; h < nh; h++) { hap_seq += haps[h].seq; hap_off.push_back((int64_t)hap_seq.size()); }
     for (size_t r = 0; r < nr; r++) {
@@ -206,6 +246,11 @@ void Engine::computeLikelihoods(const std::vector<HapT> &haps, const std::vector
         flags.push_back((uint8_t)((RT::unmapped(reads[r]) ? DINDEL_READ_UNMAPPED : 0) |
                                   (RT::reverse(reads[r]) ? DINDEL_READ_REVERSE : 0)));
         if (sq.size() > maxR) maxR = sq.size();
+        const int mode = mapUnmapped_ ? RT::insertMode(reads[r]) : DINDEL_INS_NONE;                   // cpp:279,283
+        insMode.push_back((uint8_t)mode);
+        insAnchor.push_back(mode != DINDEL_INS_NONE ? RT::insertAnchor(reads[r], mode) : 0);
+        insLib.push_back(mode != DINDEL_INS_NONE ? libraryIndex(RT::library(reads[r])) : 0);
+        anyIns = anyIns || mode != DINDEL_INS_NONE;
     }
     int32_t win_hap[2] = {0, (int32_t)nh}, win_read[2] = {0, (int32_t)nr};
     static const uint8_t none = 0;
@@ -216,6 +261,7 @@ void Engine::computeLikelihoods(const std::vector<HapT> &haps, const std::vector
     in.read_off = &read_off[0]; in.read_seq = read_seq.data();
     in.read_qual = qual.empty() ? &none : &qual[0];
     in.read_mapq = &mapq[0]; in.read_start = &start[0]; in.read_flags = &flags[0];
+    in.read_ins_mode = anyIns ? &insMode[0] : 0; in.read_ins_anchor = anyIns ? &insAnchor[0] : 0; in.read_lib = anyIns ? &insLib[0] : 0;
 
     const size_t np = nh * nr;
     const int stride = (int)((maxR + 7) & ~(size_t)7) > 0 ? (int)((maxR + 7) & ~(size_t)7) : 8;
@@ -276,6 +322,7 @@ public:
         hap_seq_.clear(); read_seq_.clear(); qual_.clear(); mapq_.clear(); flags_.clear(); strand_.clear(); start_.clear();
         win_entry_.assign(1, 0); win_key_.assign(1, 0); e_hap_.clear(); e_key_.clear(); e_left_.clear(); e_right_.clear();
         e_type_.clear(); keys_.clear(); maxR_ = 0; flushed_ = false;
+        insMode_.clear(); insAnchor_.clear(); insLib_.clear(); anyIns_ = false;
     }
     size_t size() const { return hap_start_.size(); }
     // copies what the engine needs of one window (DetInDel::computeLikelihoods' arguments + the variant entries of
@@ -307,6 +354,11 @@ public:
             flags_.push_back((uint8_t)((RT::unmapped(reads[r]) ? DINDEL_READ_UNMAPPED : 0) | (RT::reverse(reads[r]) ? DINDEL_READ_REVERSE : 0)));
             strand_.push_back(RT::coverReverse(reads[r]) ? 1 : 0);
             if (sq.size() > maxR_) maxR_ = sq.size();
+            const int mode = eng_.mapUnmappedReads() ? RT::insertMode(reads[r]) : DINDEL_INS_NONE;
+            insMode_.push_back((uint8_t)mode);
+            insAnchor_.push_back(mode != DINDEL_INS_NONE ? RT::insertAnchor(reads[r], mode) : 0);
+            insLib_.push_back(mode != DINDEL_INS_NONE ? eng_.libraryIndex(RT::library(reads[r])) : 0);
+            anyIns_ = anyIns_ || mode != DINDEL_INS_NONE;
         }
         hap_start_.push_back(leftPos);
         win_hap_.push_back((int32_t)(hap_off_.size() - 1)); win_read_.push_back((int32_t)(read_off_.size() - 1));
@@ -323,8 +375,10 @@ public:
 private:
     Engine &eng_;
     int maxMismatch_;
-    bool doFilter_, flushed_, full_;
+    bool doFilter_, flushed_, full_, anyIns_;
     size_t maxR_;
+    std::vector<uint8_t> insMode_;
+    std::vector<int32_t> insAnchor_, insLib_;
     int stride_;
     std::vector<uint32_t> hap_start_, start_;
     std::vector<int32_t> win_hap_, win_read_, e_hap_, e_key_, e_left_, e_right_, status_, nf_, nr_;
@@ -351,6 +405,7 @@ void WindowBatch<HapT, ReadT>::flush()
     in.hap_off = &hap_off_[0]; in.hap_seq = hap_seq_.data(); in.read_off = &read_off_[0]; in.read_seq = read_seq_.data();
     in.read_qual = qual_.empty() ? &none8 : &qual_[0]; in.read_mapq = mapq_.empty() ? &none8 : &mapq_[0];
     in.read_start = start_.empty() ? &none32 : &start_[0]; in.read_flags = flags_.empty() ? &none8 : &flags_[0];
+    in.read_ins_mode = anyIns_ ? &insMode_[0] : 0; in.read_ins_anchor = anyIns_ ? &insAnchor_[0] : 0; in.read_lib = anyIns_ ? &insLib_[0] : 0;
     const int64_t np = dindel_b200_count_pairs(&in);
     stride_ = (int)((maxR_ + 7) & ~(size_t)7); if (stride_ < 8) stride_ = 8;
     pairs_.resize((size_t)(np ? np : 1));

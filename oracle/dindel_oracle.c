@@ -169,18 +169,40 @@ static void step_inc(const hmm_t *m, double *B, const double *P, const double *O
 }
 
 /* ObservationModelFB.cpp:268-305 with pinsert == 0 (no --libFile). */
-static void bmid_prior(const hmm_t *m, double *prior, double mapQual, double mapQualThreshold)
+/* Insert-size term of one read (ObservationModelFB.cpp:279-293): mode 0 = none; 1 = mate on the reverse strand,
+ * anchor = int(matePos + mateLen); 2 = mate forward, anchor = int(matePos).  probs = Library::probs (maxins
+ * entries), p95 = getNinetyFifthPctProb(). */
+typedef struct {
+    int mode, anchor, maxins;
+    const double *probs;
+    double p95;
+} ins_t;
+
+/* ObservationModelFB.cpp:268-305. */
+static void bmid_prior(const hmm_t *m, double *prior, double mapQual, double mapQualThreshold, const ins_t *ins,
+                       int hapStart, int bMid)
 {
-    int S = m->S, H = m->H, RO = m->RO, i, x;
+    int S = m->S, H = m->H, RO = m->RO, R = m->R, i, x;
     double mq = 1.0 - mapQual, pOff;
+    double *pinsert = (double *)calloc((size_t)S, sizeof(double));
     if (-10.0 * log10(mq) > mapQualThreshold) mq = pow(10.0, -mapQualThreshold / 10.0);
     pOff = mq;
+    if (ins && ins->mode != 0) { /* :283-290; Library::getProb clamps (Library.hpp:61-66) */
+        for (x = 1; x < H + 1; x++) {
+            int d = (ins->mode == 1) ? abs(hapStart + x - bMid - ins->anchor) : abs(hapStart + x + R - bMid - ins->anchor);
+            if (d < 0) d = -d;
+            if (d >= ins->maxins) d = ins->maxins - 1;
+            pinsert[x] = log(ins->probs[d]);
+        }
+        pinsert[0] = log(ins->p95);
+    }
     for (i = 0; i < 2; i++) {
         double lIns = (i == 1) ? m->lInsgNoIns : log(1.0 - exp(m->lInsgNoIns));
-        prior[i * S + 0] = log(pOff) + lIns + 0.0;
+        prior[i * S + 0] = log(pOff) + lIns + pinsert[0];
         prior[i * S + RO] = -100.0;
-        for (x = 1; x < H + 1; x++) prior[i * S + x] = 0.0 + log((1.0 - pOff)) + lIns;
+        for (x = 1; x < H + 1; x++) prior[i * S + x] = pinsert[x] + log((1.0 - pOff)) + lIns;
     }
+    free(pinsert);
 }
 
 /* ObservationModelFB.cpp:35-102: the anchor base. */
@@ -209,9 +231,9 @@ static int compute_bmid(int H, int R, double posStatFirst, int unmapped, uint32_
     return bMid;
 }
 
-int ora_pair(const char *hap, int H, const char *read, int R, const double *qual, double mapQual,
-             double posStatFirst, int unmapped, uint32_t hapStart, const ora_params *p,
-             ora_pair_out *out, int32_t *hpos_out, int32_t *mapState_out)
+static int pair_core(const char *hap, int H, const char *read, int R, const double *qual, double mapQual,
+                     double posStatFirst, int unmapped, uint32_t hapStart, const ora_params *p,
+                     ora_pair_out *out, int32_t *hpos_out, int32_t *mapState_out, const ins_t *ins)
 {
     hmm_t m;
     int S = H + 2, W = 2 * S, RO = H + 1, b, x, s, bMid;
@@ -272,8 +294,8 @@ int ora_pair(const char *hap, int H, const char *read, int R, const double *qual
                      *o = obs + (size_t)bMid * W;
         double ll = -HUGE_VAL, llHMQ = -HUGE_VAL, off = -HUGE_VAL, on = -HUGE_VAL;
         int msR = 0;
-        bmid_prior(&m, priorR, mapQual, p->mapQualThreshold);
-        bmid_prior(&m, priorH, 1.0 - 1e-10, p->mapQualThreshold);
+        bmid_prior(&m, priorR, mapQual, p->mapQualThreshold, ins, (int)hapStart, bMid);
+        bmid_prior(&m, priorH, 1.0 - 1e-10, p->mapQualThreshold, ins, (int)hapStart, bMid);
         for (s = 0; s < W; s++) {
             double v = a[s] + o[s] + be[s] + priorR[s];
             if (v > ll + 1e-10) { ll = v; msR = s; }
@@ -342,6 +364,24 @@ int ora_pair(const char *hap, int H, const char *read, int R, const double *qual
     free(m.lpe); free(m.lpn); free(obs); free(alpha); free(beta); free(btf); free(btb); free(ms);
     free(priorR); free(priorH);
     return 0;
+}
+
+int ora_pair(const char *hap, int H, const char *read, int R, const double *qual, double mapQual,
+             double posStatFirst, int unmapped, uint32_t hapStart, const ora_params *p,
+             ora_pair_out *out, int32_t *hpos, int32_t *mapState)
+{
+    return pair_core(hap, H, read, R, qual, mapQual, posStatFirst, unmapped, hapStart, p, out, hpos, mapState, 0);
+}
+
+/* The same with the insert-size prior of a paired read under --libFile (params.mapUnmappedReads). */
+int ora_pair_ins(const char *hap, int H, const char *read, int R, const double *qual, double mapQual,
+                 double posStatFirst, int unmapped, uint32_t hapStart, const ora_params *p,
+                 ora_pair_out *out, int32_t *hpos, int32_t *mapState, int ins_mode, int ins_anchor,
+                 const double *lib_probs, int maxins, double p95)
+{
+    ins_t ins;
+    ins.mode = ins_mode; ins.anchor = ins_anchor; ins.maxins = maxins; ins.probs = lib_probs; ins.p95 = p95;
+    return pair_core(hap, H, read, R, qual, mapQual, posStatFirst, unmapped, hapStart, p, out, hpos, mapState, &ins);
 }
 
 /* The double loop of DetInDel::computeLikelihoods (DInDel.cpp:1715-1737) over flat buffers;

@@ -29,6 +29,11 @@ int ora_pair(const char *hap, int H, const char *read, int R, const double *qual
              double posStatFirst, int unmapped, uint32_t hapStart, const ora_params *p,
              ora_pair_out *out, int32_t *hpos, int32_t *mapState);
 
+int ora_pair_ins(const char *hap, int H, const char *read, int R, const double *qual, double mapQual,
+                 double posStatFirst, int unmapped, uint32_t hapStart, const ora_params *p,
+                 ora_pair_out *out, int32_t *hpos, int32_t *mapState, int ins_mode, int ins_anchor,
+                 const double *lib_probs, int maxins, double p95);
+
 int ora_window(const char *hap_seq, const int32_t *hap_off, int nh, const char *read_seq,
                const uint8_t *read_qual, const int32_t *read_off, const uint8_t *mapq,
                const uint32_t *mReadStart, const uint8_t *flags, int nr, uint32_t hapStart,

@@ -67,7 +67,7 @@ def prepare(work, length, seed, coverage=30.0, per_file=1000, min_count=2):
     make_windows.select_candidates(s1 + ".variants.txt", sel, min_count)
     files = make_windows.split_and_merge(sel, os.path.join(work, "win"), 20, per_file)
     n_win = sum(1 for f in files for _ in open(f))
-    return {"ref": ref, "bam": bam, "window_files": files, "n_windows": n_win,
+    return {"ref": ref, "bam": bam, "window_files": files, "n_windows": n_win, "libraries": s1 + ".libraries.txt",
             "n_candidates": sum(1 for _ in open(sel))}
 
 
@@ -144,6 +144,8 @@ def main():
     ap.add_argument("--gpu-procs", type=int, default=4, help="concurrent stage-3 processes sharing the GPU")
     ap.add_argument("--windows-per-file", type=int, default=1000)
     ap.add_argument("--filter-haplotypes", action="store_true", help="pass --filterHaplotypes to stage 3 (all arms)")
+    ap.add_argument("--lib-file", action="store_true", help="pass --libFile <stage-1 libraries> to stage 3 (all arms): "
+                    "insert-size prior + mate rescue of unmapped reads, as in the README pipeline")
     ap.add_argument("--heap-neutral", action="store_true", help="also compare with the allocator poisoning freed memory")
     a = ap.parse_args()
     arms = a.arms.split(",")
@@ -151,7 +153,7 @@ def main():
     prep = prepare(a.work, a.length, a.seed, a.coverage, a.windows_per_file)
     res = {"length": a.length, "coverage": a.coverage, "n_candidates": prep["n_candidates"],
            "n_windows": prep["n_windows"], "window_files": len(prep["window_files"]), "procs": procs, "gpu_procs": a.gpu_procs,
-           "filterHaplotypes": a.filter_haplotypes}
+           "filterHaplotypes": a.filter_haplotypes, "libFile": a.lib_file}
     verdict = True
     for tag, env in (("", None), (".hn", HEAP_NEUTRAL)):
         if env and not a.heap_neutral:
@@ -161,7 +163,8 @@ def main():
             if arm == "check" and env:
                 continue
             glfs, vcf, wall, n_calls = run_arm(arm, prep, a.work, procs if arm == "cpu" else a.gpu_procs,
-                                               extra=["--filterHaplotypes"] if a.filter_haplotypes else [], env=env, tag=tag)
+                                               extra=(["--filterHaplotypes"] if a.filter_haplotypes else []) +
+                                               (["--libFile", prep["libraries"]] if a.lib_file else []), env=env, tag=tag)
             ok, err = glf_stats(glfs)
             out[arm] = (glfs, vcf)
             r[arm] = {"stage3_wall_s": round(wall, 3), "vcf_calls": n_calls, "windows_ok": ok, "windows_skipped": err}

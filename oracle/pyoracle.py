@@ -75,6 +75,37 @@ class Oracle:
                    ms.ctypes.data_as(C.c_void_p))
         return out[0], hpos[:R], ms[:R]
 
+    def library(self, counts):
+        """reference only: Library(counts) -> (probs[maxins], p95)   (Library.hpp:31-129)"""
+        counts = np.ascontiguousarray(counts, dtype=np.float64)
+        probs = np.zeros(len(counts), dtype=np.float64)
+        p95 = C.c_double()
+        n = self.lib.ref_library(counts.ctypes.data_as(C.c_void_p), len(counts), probs.ctypes.data_as(C.c_void_p), C.byref(p95))
+        return probs[:n].copy(), p95.value
+
+    def pair_ins(self, hap, read, qual, map_qual, pos_stat_first, unmapped, hap_start, params, ins_mode, ins_anchor,
+                 probs=None, p95=None, counts=None):
+        """pair() with the insert-size prior (ObservationModelFB.cpp:279-293).  The port takes the library's probs
+        and p95; the reference builds its own Library from the raw histogram `counts`."""
+        hap, read = bytes(hap), bytes(read)
+        R = len(read)
+        q = np.ascontiguousarray(qual, dtype=np.float64)
+        out = np.zeros(1, dtype=ORA_DTYPE)
+        hpos = np.zeros(max(R, 1), dtype=np.int32)
+        ms = np.zeros(max(R, 1), dtype=np.int32)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        if self.kind == "port":
+            pr = np.ascontiguousarray(probs, dtype=np.float64)
+            self.lib.ora_pair_ins(hap, len(hap), read, R, vp(q), C.c_double(map_qual), C.c_double(pos_stat_first),
+                                  int(unmapped), C.c_uint32(hap_start & 0xffffffff), C.byref(params), vp(out), vp(hpos),
+                                  vp(ms), int(ins_mode), int(ins_anchor), vp(pr), len(pr), C.c_double(p95))
+        else:
+            cn = np.ascontiguousarray(counts, dtype=np.float64)
+            self.lib.ref_pair_ins(hap, len(hap), read, R, vp(q), C.c_double(map_qual), C.c_double(pos_stat_first),
+                                  int(unmapped), C.c_uint32(hap_start & 0xffffffff), C.byref(params), vp(out), vp(hpos),
+                                  vp(ms), int(ins_mode), int(ins_anchor), vp(cn), len(cn))
+        return out[0], hpos[:R], ms[:R]
+
     def window(self, batch, w, params, want_hpos=True):
         """All pairs of window w of an engine.Batch -> (records r-major [nr*nh], hpos [nr*nh, stride])."""
         h0, h1 = int(batch.win_hap[w]), int(batch.win_hap[w + 1])

@@ -12,6 +12,7 @@
  * Mirrors the loop of DetInDel::computeLikelihoods (DInDel.cpp:1707-1739) in ref_window().
  */
 #include <stdint.h>
+#include <stdio.h>
 #include <string.h>
 #include <string>
 #include <vector>
@@ -112,6 +113,69 @@ int ref_pair(const char *hap, int H, const char *read, int R, const double *qual
     std::streambuf *old = std::cout.rdbuf();
     std::ostringstream sink;
     std::cout.rdbuf(sink.rdbuf());
+    int rc = 0;
+    try {
+        Probe om(h, r, hapStart, op);
+        MLAlignment ml = om.calcLikelihood();
+        flatten(ml, om.getBMid(), out, hpos, R);
+        if (mapState) {
+            std::vector<int> ms = om.getMapState();
+            for (int b = 0; b < R; b++) mapState[b] = ms[b];
+        }
+    } catch (std::string &s) {
+        memset(out, 0, sizeof(*out));
+        out->status = 1;
+        rc = 1;
+    }
+    std::cout.rdbuf(old);
+    return rc;
+}
+
+/* Library(counts) as LibraryCollection::addFromFile builds it (Library.hpp:31-129): exports what the product is
+ * given through dindel_b200_set_libraries: probs[0..maxins), and the 95th-percentile probability.  Returns maxins. */
+int ref_library(const double *counts, int n, double *probs_out, double *p95_out)
+{
+    std::streambuf *old = std::cout.rdbuf();
+    std::ostringstream sink;
+    std::cout.rdbuf(sink.rdbuf());
+    Library lib(std::vector<double>(counts, counts + n));
+    std::cout.rdbuf(old);
+    const int maxins = lib.getMaxInsertSize();
+    for (int d = 0; d < maxins; d++) probs_out[d] = lib.getProb(d);
+    *p95_out = lib.getNinetyFifthPctProb();
+    return maxins;
+}
+
+/* One pair with the insert-size prior active (ObservationModelFB.cpp:279-293): a paired read whose mate is mapped
+ * on the same target, params.mapUnmappedReads set as `--libFile` does (DInDel.cpp:4268-4272).  ins_mode 1 = mate on
+ * the reverse strand (anchor = matePos + mateLen), 2 = forward (anchor = matePos), 0 = paired but mate unmapped. */
+int ref_pair_ins(const char *hap, int H, const char *read, int R, const double *qual, double mapQual,
+                 double posStatFirst, int unmapped, uint32_t hapStart, const ref_params *p,
+                 ref_pair_out *out, int32_t *hpos, int32_t *mapState, int ins_mode, int ins_anchor,
+                 const double *counts, int n_counts)
+{
+    ObservationModelParameters op;
+    fill_params(p, op);
+    op.mapUnmappedReads = true;
+    std::streambuf *old = std::cout.rdbuf();
+    std::ostringstream sink;
+    std::cout.rdbuf(sink.rdbuf());
+    Library lib(std::vector<double>(counts, counts + n_counts));
+    Haplotype h;
+    h.seq.assign(hap, H);
+    Read r;
+    make_read(r, read, R, qual, mapQual, posStatFirst, unmapped);
+    r.bam->core.flag |= BAM_FPAIRED;
+    r.bam->core.tid = 0; r.bam->core.mtid = 0;
+    r.library = &lib;
+    if (ins_mode == 0) {
+        r.bam->core.flag |= BAM_FMUNMAP;
+    } else if (ins_mode == 1) {
+        r.bam->core.flag |= BAM_FMREVERSE;
+        r.mateLen = 100; r.matePos = ins_anchor - 100;
+    } else {
+        r.mateLen = 100; r.matePos = ins_anchor;
+    }
     int rc = 0;
     try {
         Probe om(h, r, hapStart, op);

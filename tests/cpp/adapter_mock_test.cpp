@@ -46,12 +46,17 @@ template <> struct ReadTraits<MockRead> {
     static bool unmapped(const MockRead &r) { return r.unmapped; }
     static uint32_t start(const MockRead &r) { return r.start; }
     static bool reverse(const MockRead &r) { return r.reverse; }
+    static bool coverReverse(const MockRead &r) { return r.reverse; }
+    static int insertMode(const MockRead &) { return DINDEL_INS_NONE; }
+    static int32_t insertAnchor(const MockRead &, int) { return 0; }
+    struct NoLib { int getMaxInsertSize() const { return 1; } double getProb(int) const { return 1.0; } double getNinetyFifthPctProb() const { return 1.0; } };
+    static const NoLib *library(const MockRead &) { return 0; }
 };
 }
 struct Params { // ObservationModel.hpp:28-99, CLI values (DInDel.cpp:4122-4157)
     double pError, pMut, mapQualThreshold, pFirstgLO, checkBaseQualThreshold;
     int maxLengthDel, padCover, bMid;
-    bool forceReadOnHaplotype;
+    bool forceReadOnHaplotype, mapUnmappedReads;
 };
 
 static MockRead mk(const std::string &s, uint32_t start)
@@ -64,7 +69,7 @@ static MockRead mk(const std::string &s, uint32_t start)
 
 int main()
 {
-    Params p = {5e-4, 1e-5, 100.0, 0.01, 0.95, 5, 2, -1, false};
+    Params p = {5e-4, 1e-5, 100.0, 0.01, 0.95, 5, 2, -1, false, false};
     dindel_b200::Engine *eng = 0;
     try {
         eng = new dindel_b200::Engine(p, 0);

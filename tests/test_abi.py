@@ -26,13 +26,13 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(engine.EXPORTS) == names
-    assert lib.dindel_b200_abi_version() == 1
+    assert lib.dindel_b200_abi_version() == 2
 
 
 def test_struct_layouts_match_header():
     assert C.sizeof(engine.Params) == 56
     assert engine.PAIR_DTYPE.itemsize == 64
-    assert C.sizeof(engine._BatchIn) == 16 + 11 * 8
+    assert C.sizeof(engine._BatchIn) == 16 + 14 * 8
     assert C.sizeof(engine._BatchOut) == 8 + 8 + 8 + 8 + 8 + 8 + 8
     assert C.sizeof(engine.Timing) == 5 * 4 + 2 * 4 + 4 + 16  # 4 bytes padding before the int64s
 

@@ -143,3 +143,21 @@ def test_glf_identical_with_filter_haplotypes(tmp_path):
     res = json.loads(r.stdout.strip().splitlines()[-1])
     hn = res["heap_neutral"]
     assert hn["glf_identical"] and hn["vcf_identical"] and hn["cpu"]["windows_ok"] >= 20, res
+
+
+@pytest.mark.gpu
+def test_glf_identical_with_lib_file(tmp_path):
+    """--libFile (the README pipeline): insert-size prior in computeBMidPrior (ObservationModelFB.cpp:279-293) for every
+    paired read + mate rescue of unmapped reads on the host; the GPU arm gets the libraries through
+    dindel_b200_set_libraries.  Every pipeline pair equals the reference class's, glf and VCF byte-identical."""
+    if not run_e2e.have_binaries(("cpu", "gpu", "check")):
+        pytest.skip("oracle/_ref binaries not built (reference sources absent at build time)")
+    r = subprocess.run([sys.executable, os.path.join(E2E, "run_e2e.py"), "--work", str(tmp_path), "--length", "60000",
+                        "--seed", "6", "--arms", "cpu,gpu,check", "--windows-per-file", "20", "--heap-neutral",
+                        "--lib-file"], capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout + r.stderr
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    chk = res["default"]["check"]
+    assert chk["pair_mismatches"] == 0 and chk["pairs_compared"] >= 5000, res
+    hn = res["heap_neutral"]
+    assert hn["glf_identical"] and hn["vcf_identical"] and hn["cpu"]["windows_ok"] >= 20, res
