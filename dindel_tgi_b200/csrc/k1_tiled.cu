@@ -34,7 +34,10 @@
 #ifndef K1_LEFT_TREE
 #define K1_LEFT_TREE 1
 #endif
-#define K1_TILED_BTG_MAX_CTAS 2 // resident CTAs per SM of the classes that keep back-pointers in global memory
+#ifndef K1_TILED_J11_MINB
+#define K1_TILED_J11_MINB 2
+#endif
+#define K1_TILED_BTG_MAX_CTAS K1_TILED_J11_MINB // resident CTAs per SM of the classes that keep back-pointers in global memory
 #define FULLMASK 0xffffffffu
 
 // call f(integral_constant<int, cro>) for the run-time value cro in [0, C)
@@ -774,9 +777,9 @@ extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream
             }
         } else {
             switch (t[i]) {
-            case 8: e = launch_one<8, 11, 2, true>(B, num_sms, i, st); break;
-            case 10: e = launch_one<10, 11, 2, true>(B, num_sms, i, st); break;
-            case 11: e = launch_one<11, 11, 2, true>(B, num_sms, i, st); break;
+            case 8: e = launch_one<8, 11, K1_TILED_J11_MINB, true>(B, num_sms, i, st); break;
+            case 10: e = launch_one<10, 11, K1_TILED_J11_MINB, true>(B, num_sms, i, st); break;
+            case 11: e = launch_one<11, 11, K1_TILED_J11_MINB, true>(B, num_sms, i, st); break;
             }
         }
         n++;

@@ -71,12 +71,12 @@ def prepare(work, length, seed, coverage=30.0, per_file=1000, min_count=2):
             "n_candidates": sum(1 for _ in open(sel))}
 
 
-def run_arm(arm, prep, work, procs, extra=(), env=None, tag=""):
+def run_arm(arm, prep, work, procs, extra=(), env=None, tag="", mode="--doDiploid"):
     """stage 3 + 4 for one arm.  Returns (glf paths, vcf path, wall seconds of stage 3, VCF calls)."""
     def one(k_f):
         k, wf = k_f
         out = os.path.join(work, "%s%s.%d" % (arm, tag, k))
-        sh([BIN[arm], "--analysis", "indels", "--doDiploid", "--bamFile", prep["bam"], "--ref", prep["ref"],
+        sh([BIN[arm], "--analysis", "indels", mode, "--bamFile", prep["bam"], "--ref", prep["ref"],
             "--varFile", wf, "--outputFile", out] + list(extra), out + ".log", env)
         return out + ".glf.txt"
     t0 = time.perf_counter()
@@ -84,7 +84,11 @@ def run_arm(arm, prep, work, procs, extra=(), env=None, tag=""):
         glfs = list(ex.map(one, enumerate(prep["window_files"], 1)))
     wall = time.perf_counter() - t0
     vcf = os.path.join(work, arm + tag + ".vcf")
-    n_calls = merge_diploid.merge_output(glfs, prep["ref"], vcf)
+    if mode == "--doDiploid":
+        n_calls = merge_diploid.merge_output(glfs, prep["ref"], vcf)
+    else:
+        open(vcf, "w").close()
+        n_calls = 0
     return glfs, vcf, wall, n_calls
 
 
@@ -144,6 +148,8 @@ def main():
     ap.add_argument("--gpu-procs", type=int, default=4, help="concurrent stage-3 processes sharing the GPU")
     ap.add_argument("--windows-per-file", type=int, default=1000)
     ap.add_argument("--filter-haplotypes", action="store_true", help="pass --filterHaplotypes to stage 3 (all arms)")
+    ap.add_argument("--pooled", action="store_true", help="--doPooled instead of --doDiploid (Bayes EM path, configs[2]); "
+                    "glf compared, no VCF (mergeOutputPooled.py is not restated)")
     ap.add_argument("--lib-file", action="store_true", help="pass --libFile <stage-1 libraries> to stage 3 (all arms): "
                     "insert-size prior + mate rescue of unmapped reads, as in the README pipeline")
     ap.add_argument("--heap-neutral", action="store_true", help="also compare with the allocator poisoning freed memory")
@@ -153,7 +159,7 @@ def main():
     prep = prepare(a.work, a.length, a.seed, a.coverage, a.windows_per_file)
     res = {"length": a.length, "coverage": a.coverage, "n_candidates": prep["n_candidates"],
            "n_windows": prep["n_windows"], "window_files": len(prep["window_files"]), "procs": procs, "gpu_procs": a.gpu_procs,
-           "filterHaplotypes": a.filter_haplotypes, "libFile": a.lib_file}
+           "filterHaplotypes": a.filter_haplotypes, "libFile": a.lib_file, "pooled": a.pooled}
     verdict = True
     for tag, env in (("", None), (".hn", HEAP_NEUTRAL)):
         if env and not a.heap_neutral:
@@ -164,7 +170,8 @@ def main():
                 continue
             glfs, vcf, wall, n_calls = run_arm(arm, prep, a.work, procs if arm == "cpu" else a.gpu_procs,
                                                extra=(["--filterHaplotypes"] if a.filter_haplotypes else []) +
-                                               (["--libFile", prep["libraries"]] if a.lib_file else []), env=env, tag=tag)
+                                               (["--libFile", prep["libraries"]] if a.lib_file else []), env=env, tag=tag,
+                                               mode="--doPooled" if a.pooled else "--doDiploid")
             ok, err = glf_stats(glfs)
             out[arm] = (glfs, vcf)
             r[arm] = {"stage3_wall_s": round(wall, 3), "vcf_calls": n_calls, "windows_ok": ok, "windows_skipped": err}

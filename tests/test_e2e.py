@@ -161,3 +161,18 @@ def test_glf_identical_with_lib_file(tmp_path):
     assert chk["pair_mismatches"] == 0 and chk["pairs_compared"] >= 5000, res
     hn = res["heap_neutral"]
     assert hn["glf_identical"] and hn["vcf_identical"] and hn["cpu"]["windows_ok"] >= 20, res
+
+
+@pytest.mark.gpu
+def test_glf_identical_pooled(tmp_path):
+    """--doPooled (estimateHaplotypeFrequenciesBayesEM, the path of configs[2]): K1 and K4 feed the reference's own EM;
+    glf byte-identical to the stock CPU binary (both arms use the same digamma shim)."""
+    if not run_e2e.have_binaries(("cpu", "gpu")):
+        pytest.skip("oracle/_ref binaries not built (reference sources absent at build time)")
+    r = subprocess.run([sys.executable, os.path.join(E2E, "run_e2e.py"), "--work", str(tmp_path), "--length", "50000",
+                        "--seed", "8", "--arms", "cpu,gpu", "--windows-per-file", "20", "--heap-neutral", "--pooled"],
+                       capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout + r.stderr
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    hn = res["heap_neutral"]
+    assert hn["glf_identical"] and hn["cpu"]["windows_ok"] >= 15, res
