@@ -9,6 +9,7 @@
 #include <string.h>
 #include <string>
 #include <vector>
+#include <chrono>
 #include "k1_common.cuh"
 #include "k23.cuh"
 #include "k4.cuh"
@@ -195,7 +196,18 @@ struct dindel_ctx {
     std::vector<int> win_nh;
     dindel_timing timing;
     int force_generic = 0, force_chunks = 0, force_lanes = 0, force_bt_global = -1;
+    // DINDEL_B200_TRACE=1: cumulative host wall time inside submit / coverage, printed every 50 submits (stderr)
+    int trace = 0;
+    long n_submit = 0, n_cover = 0;
+    double t_submit = 0.0, t_cover = 0.0, t_create = 0.0;
     Range all;                 // the whole resident batch (resident API)
+};
+
+struct TraceTimer {
+    double *acc;
+    std::chrono::steady_clock::time_point t0;
+    explicit TraceTimer(double *a) : acc(a), t0(std::chrono::steady_clock::now()) {}
+    ~TraceTimer() { if (acc) *acc += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
 };
 
 static int fail(dindel_ctx *c, int code, const std::string &msg)
@@ -325,6 +337,7 @@ int dindel_b200_create(const dindel_params *p, int device, dindel_ctx **out)
         cudaGetLastError();
         return DINDEL_E_NO_DEVICE;
     }
+    const std::chrono::steady_clock::time_point t_create0 = std::chrono::steady_clock::now();
     dindel_ctx *ctx = new dindel_ctx();
     ctx->device = device;
     ctx->params = *p;
@@ -363,6 +376,8 @@ int dindel_b200_create(const dindel_params *p, int device, dindel_ctx **out)
     const char *fb = getenv("DINDEL_B200_BT_GLOBAL"); // generic kernel: 1 / 0 forces the back-pointer plan
     ctx->force_bt_global = fb ? atoi(fb) : -1;
     memset(&ctx->timing, 0, sizeof(ctx->timing));
+    ctx->trace = getenv("DINDEL_B200_TRACE") != nullptr;
+    ctx->t_create = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_create0).count();
     *out = ctx;
     return DINDEL_OK;
 }
@@ -880,6 +895,10 @@ int dindel_b200_hpos_stride(const dindel_ctx *ctx) { return ctx && ctx->resident
 int dindel_b200_submit(dindel_ctx *ctx, const dindel_batch_in *in, dindel_batch_out *out)
 {
     if (!ctx || !out) return DINDEL_E_INVALID;
+    TraceTimer tt(ctx->trace ? &ctx->t_submit : nullptr);
+    if (ctx->trace && ++ctx->n_submit % 50 == 0)
+        fprintf(stderr, "dindel_b200 trace: %ld submits %.3f s, %ld coverage calls %.3f s, create %.3f s\n", ctx->n_submit,
+                ctx->t_submit, ctx->n_cover, ctx->t_cover, ctx->t_create);
     const bool keep_hpos = (out->flags & DINDEL_OUT_KEEP_HPOS) != 0; // rows stay in HBM for K4
     int rc = prepare_batch(ctx, in, out->hpos != nullptr || keep_hpos, out->hpos ? out->hpos_stride : 0);
     if (rc != DINDEL_OK) return rc;
@@ -1080,6 +1099,8 @@ int dindel_b200_bayes_em(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out 
 int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cover_out *out)
 {
     if (!ctx || !in || !out || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "coverage needs a resident, computed batch");
+    TraceTimer tt(ctx->trace ? &ctx->t_cover : nullptr);
+    ctx->n_cover++;
     const K1Batch &B = ctx->B;
     if (!B.hpos) return fail(ctx, DINDEL_E_INVALID, "coverage needs the hpos rows resident (upload(want_hpos) or DINDEL_OUT_KEEP_HPOS)");
     if (in->n_entries < 0 || in->n_keys < 0) return fail(ctx, DINDEL_E_INVALID, "n_entries / n_keys");
