@@ -237,6 +237,15 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def sum_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # shards differ per rank (seeded by rank): the job's units are the sum over ranks, not world x rank 0's
+    tot_pairs, tot_cells = sum_over_ranks(float(n_pairs)), sum_over_ranks(float(n_cells))
     fp64_peak = eng.measure_fp64_peak()
 
     # ---- resident-input throughput (value) ----
@@ -257,8 +266,8 @@ def main():
     clocks = sampler.stop()
     dev_ms = max_over_ranks(float(np.sum(k1_ms)))
     ms_per_step = dev_ms / args.steps
-    value = world * n_pairs / (ms_per_step * 1e-3)
-    gcups = world * n_cells / (ms_per_step * 1e-3) / 1e9
+    value = tot_pairs / (ms_per_step * 1e-3)
+    gcups = tot_cells / (ms_per_step * 1e-3) / 1e9
 
     # ---- end to end through dindel_b200_submit with pinned host buffers ----
     names = ("hap_start", "win_hap", "win_read", "hap_off", "hap_seq", "read_off", "read_seq", "read_qual",
@@ -337,7 +346,7 @@ def main():
     barrier()
     e2e_wall = 1e3 * (time.perf_counter() - e0)
     e2e_ms = max_over_ranks(e2e_wall) / args.steps  # host wall clock around submit (includes host indexing)
-    e2e_val = world * n_pairs / (e2e_ms * 1e-3)
+    e2e_val = tot_pairs / (e2e_ms * 1e-3)
     checksum = float(pairs["ll"].sum())
 
     # ---- K2 / K3 over the resident likelihood matrix (reported beside the step, not part of it) ----
@@ -372,7 +381,7 @@ def main():
                        "gen_s": round(gen_s, 1), "wall_ms_per_step": wall_ms / args.steps},
             "gcups": gcups,
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": e2e_ms, "device_ms_per_step": e2e_dev / args.steps, "gcups": world * n_cells / (e2e_ms * 1e-3) / 1e9,
+                    "ms_per_step": e2e_ms, "device_ms_per_step": e2e_dev / args.steps, "gcups": tot_cells / (e2e_ms * 1e-3) / 1e9,
                     "path": ("K1 + K4: submit (H2D, kernels, D2H of the 64-byte pair records) then dindel_b200_coverage "
                              "(filterHaplotypes on the hpos rows where K1 left them in HBM)") if cov else
                             ("K1, hpos rows copied to the host" if hpos is not None else "K1 only, no hpos rows"),
@@ -381,9 +390,9 @@ def main():
                     "hpos_d2h": hpos is not None, "ll_checksum": checksum},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "fp64-issue", "achieved": (n_cells * w_cell / (ms_per_step * 1e-3)) / 1e12,
+            "roofline": {"bound": "fp64-issue", "achieved": (tot_cells / world * w_cell / (ms_per_step * 1e-3)) / 1e12,
                          "peak": fp64_peak / 1e12, "unit": "TOP/s",
-                         "frac": (n_cells * w_cell / (ms_per_step * 1e-3)) / fp64_peak,
+                         "frac": (tot_cells / world * w_cell / (ms_per_step * 1e-3)) / fp64_peak,
                          # dram read+write of k1_tiled_kernel<4,6> from one `ncu --set full` capture (profiles/
                          # r1_k1_tiled_v4_k4.md: 302 MB for 8.9 G cells, hpos rows included), scaled to this step's cells
                          "traffic": int(n_cells * (301.8e6 / 8.9e9)) if args.cfg == 2 and not args.no_hpos else None,
