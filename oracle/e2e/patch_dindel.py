@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """oracle/e2e/patch_dindel.py — TEST INFRASTRUCTURE ONLY.
 
-Applies INTEGRATION.md's two-line patch to the reference's driver at BUILD time:
+Applies INTEGRATION.md's three-line patch to the reference's driver at BUILD time:
     python oracle/e2e/patch_dindel.py /root/reference/DInDel.cpp oracle/_ref/DInDel_b200.cpp
 The output (git-ignored, under oracle/_ref/) is DInDel.cpp with (1) `#include "dindel_b200.hpp"` after
 its own includes and (2) the body of DetInDel::computeLikelihoods (DInDel.cpp:1707-1739) preceded by a

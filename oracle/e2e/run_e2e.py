@@ -5,7 +5,7 @@ End-to-end check of BASELINE.json configs[0] (`dindel --analysis indels --doDipl
 chr20 BAM, 30x 100-bp reads, ~120-bp windows from makeWindows): the reference's own pipeline is run
 twice over the same window files,
   arm "cpu": oracle/_ref/dindel_ref   (stock reference binary)
-  arm "gpu": oracle/_ref/dindel_b200  (same sources + INTEGRATION.md's two-line patch: K1 on the B200)
+  arm "gpu": oracle/_ref/dindel_b200  (same sources + INTEGRATION.md's three-line patch: K1 on the B200)
 and the `.glf.txt` files and the merged VCFs are compared byte for byte.
 
   stage 1  dindel_ref --analysis getCIGARindels          (README.md pipeline; GetCandidates.cpp:387)

@@ -5,7 +5,7 @@ synthetic chr20 FASTA + 30x BAM -> `--analysis getCIGARindels` -> windows -> `--
   * CPU: the window scripts' restatements (oracle/e2e/make_windows.py, merge_diploid.py), and the stock
     reference binary (oracle/_ref/dindel_ref, built where /root/reference exists) recovering the planted
     indels from the synthetic BAM -- this pins the fixture generator and the harness.
-  * GPU: the reference binary with INTEGRATION.md's two-line patch (oracle/_ref/dindel_b200: K1 runs on
+  * GPU: the reference binary with INTEGRATION.md's three-line patch (oracle/_ref/dindel_b200: K1 and K4 run on
     the B200 through include/dindel_b200.hpp) produces `.glf.txt` files and a VCF that are byte-identical
     to the stock CPU binary's (north star: "final VCF indel calls and genotypes must be bit-exact").
 """
