@@ -182,6 +182,8 @@ struct dindel_ctx {
     cudaStream_t stream = nullptr, s_in = nullptr, s_out = nullptr;
     Lane lane[DINDEL_NUM_LANES];
     cudaEvent_t ev[6];
+    cudaEvent_t ev_k[2];          // around the kernel of the last pair_sums / bayes_em / coverage call
+    float last_kernel_ms = 0.f;
     std::vector<cudaEvent_t> evpool; // per-chunk events of a pipelined submit
     std::string err;
     DevBuf d_luts, d_hap_start, d_win_hap, d_win_read, d_win_pair, d_win_unit, d_hap_off,
@@ -351,6 +353,7 @@ int dindel_b200_create(const dindel_params *p, int device, dindel_ctx **out)
     for (int i = 1; i < DINDEL_NUM_LANES && e == cudaSuccess; i++)
         e = cudaStreamCreateWithFlags(&ctx->lane[i].st, cudaStreamNonBlocking);
     for (int i = 0; i < 6 && e == cudaSuccess; i++) e = cudaEventCreate(&ctx->ev[i]);
+    for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaEventCreate(&ctx->ev_k[i]);
     if (e != cudaSuccess) {
         delete ctx;
         return DINDEL_E_CUDA;
@@ -401,6 +404,7 @@ int dindel_b200_destroy(dindel_ctx *ctx)
         if (i > 0 && ln.st) cudaStreamDestroy(ln.st);
     }
     for (int i = 0; i < 6; i++) cudaEventDestroy(ctx->ev[i]);
+    for (int i = 0; i < 2; i++) cudaEventDestroy(ctx->ev_k[i]);
     for (cudaEvent_t e : ctx->evpool) cudaEventDestroy(e);
     ctx->win_pair.release();
     ctx->win_unit.release();
@@ -886,6 +890,8 @@ int dindel_b200_download(dindel_ctx *ctx, dindel_batch_out *out)
     return DINDEL_OK;
 }
 
+float dindel_b200_last_kernel_ms(const dindel_ctx *ctx) { return ctx ? ctx->last_kernel_ms : 0.f; }
+
 int dindel_b200_hpos_stride(const dindel_ctx *ctx) { return ctx && ctx->resident ? ctx->B.hpos_stride : 0; }
 
 // computeLikelihoods for a whole batch, host buffers in and out, as a pipeline over chunks of
@@ -1048,9 +1054,12 @@ int dindel_b200_pair_sums(dindel_ctx *ctx, const dindel_pairsum_in *in, double *
     a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.pairs = B.pairs;
     volatile double half = 0.5;
     a.log_half = log(half); // DInDel.cpp:3091 log(0.5), host libm
+    CU(cudaEventRecord(ctx->ev_k[0], st));
     CU(k2_launch(&a, st));
+    CU(cudaEventRecord(ctx->ev_k[1], st));
     if (nv) CU(cudaMemcpyAsync(out, a.out, nv * 8, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev_k[0], ctx->ev_k[1]);
     return DINDEL_OK;
 }
 
@@ -1085,7 +1094,9 @@ int dindel_b200_bayes_em(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out 
     a.loglik = (double *)ctx->d_x[3].p; a.iters = (int32_t *)ctx->d_x[4].p;
     a.pi = (double *)ctx->d_x[5].p; a.freqs = (double *)ctx->d_x[6].p;
     a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.pairs = B.pairs;
+    CU(cudaEventRecord(ctx->ev_k[0], st));
     CU(k3_launch(&a, st));
+    CU(cudaEventRecord(ctx->ev_k[1], st));
     CU(cudaMemcpyAsync(out->loglik, a.loglik, ns * 8, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(out->iters, a.iters, ns * 4, cudaMemcpyDeviceToHost, st));
     if (nv) {
@@ -1093,6 +1104,7 @@ int dindel_b200_bayes_em(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out 
         CU(cudaMemcpyAsync(out->freqs, a.freqs, nv * 8, cudaMemcpyDeviceToHost, st));
     }
     CU(cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev_k[0], ctx->ev_k[1]);
     return DINDEL_OK;
 }
 
@@ -1162,7 +1174,9 @@ int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cove
     a.hap_filtered = (uint8_t *)(d_out + r_hf); a.hap_uncovered = (uint8_t *)(d_out + r_hu);
     a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.hap_off = B.hap_off; a.read_off = B.read_off;
     a.hap_seq = B.hap_seq; a.read_seq = B.read_seq; a.pairs = B.pairs; a.hpos = B.hpos; a.hpos_stride = B.hpos_stride;
+    CU(cudaEventRecord(ctx->ev_k[0], st));
     CU(k4_launch(&a, nw, smem, st));
+    CU(cudaEventRecord(ctx->ev_k[1], st));
     if (nk) {
         CU(cudaMemcpyAsync(out->key_nf, a.key_nf, nk * 4, cudaMemcpyDeviceToHost, st));
         CU(cudaMemcpyAsync(out->key_nr, a.key_nr, nk * 4, cudaMemcpyDeviceToHost, st));
@@ -1172,6 +1186,7 @@ int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cove
         if (out->hap_uncovered) CU(cudaMemcpyAsync(out->hap_uncovered, a.hap_uncovered, nh, cudaMemcpyDeviceToHost, st));
     }
     CU(cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev_k[0], ctx->ev_k[1]);
     return DINDEL_OK;
 }
 

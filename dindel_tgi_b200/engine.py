@@ -10,6 +10,7 @@ Host-side mirror of the reference interface (same names and argument meaning):
   Params                             ~  ObservationModelParameters    (ObservationModel.hpp:28-99)
 """
 import ctypes as C
+import time
 import os
 
 import numpy as np
@@ -102,6 +103,7 @@ EXPORTS = [
     "dindel_b200_get_timing", "dindel_b200_hpos_stride", "dindel_b200_alloc_pinned",
     "dindel_b200_free_pinned", "dindel_b200_measure_fp64_peak", "dindel_b200_pair_sums",
     "dindel_b200_bayes_em", "dindel_b200_plan_shards", "dindel_b200_coverage", "dindel_b200_set_libraries",
+    "dindel_b200_last_kernel_ms",
 ]
 
 _lib = None
@@ -132,6 +134,8 @@ def load_library():
     lib.dindel_b200_sync.argtypes = [C.c_void_p]
     lib.dindel_b200_download.argtypes = [C.c_void_p, C.POINTER(_BatchOut)]
     lib.dindel_b200_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
+    lib.dindel_b200_last_kernel_ms.argtypes = [C.c_void_p]
+    lib.dindel_b200_last_kernel_ms.restype = C.c_float
     lib.dindel_b200_hpos_stride.argtypes = [C.c_void_p]
     lib.dindel_b200_alloc_pinned.restype = C.c_void_p
     lib.dindel_b200_alloc_pinned.argtypes = [C.c_size_t]
@@ -396,7 +400,10 @@ class Engine:
         a = _PairSumIn()
         a.n_jobs, a.job_window, a.job_group, a.job_off, a.start = nj, jw.ctypes.data, jg.ctypes.data, off.ctypes.data, st.ctypes.data
         a.read_group = rg.ctypes.data if rg is not None else None
+        t0 = time.perf_counter()
         self._check(self.lib.dindel_b200_pair_sums(self.h, C.byref(a), out.ctypes.data), "pair_sums")
+        self.last_call_ms = 1e3 * (time.perf_counter() - t0)  # the C call alone (H2D, kernel, D2H), no Python packing
+        self.last_kernel_ms = float(self.lib.dindel_b200_last_kernel_ms(self.h))
         return [out[off[j]:off[j + 1]] for j in range(nj)]
 
     def coverage(self, win_entries, win_nkeys, read_strand, max_mismatch=2, do_filter=False):
@@ -437,5 +444,8 @@ class Engine:
         a, o = _EmIn(), _EmOut()
         a.n_sets, a.set_window, a.set_off, a.compatible, a.a0, a.tol = ns, sw.ctypes.data, off.ctypes.data, comp.ctypes.data, a0, tol
         o.loglik, o.iters, o.pi, o.freqs = ll.ctypes.data, it.ctypes.data, pi.ctypes.data, fr.ctypes.data
+        t0 = time.perf_counter()
         self._check(self.lib.dindel_b200_bayes_em(self.h, C.byref(a), C.byref(o)), "bayes_em")
+        self.last_call_ms = 1e3 * (time.perf_counter() - t0)
+        self.last_kernel_ms = float(self.lib.dindel_b200_last_kernel_ms(self.h))
         return ll, it, [pi[off[j]:off[j + 1]] for j in range(ns)], [fr[off[j]:off[j + 1]] for j in range(ns)]

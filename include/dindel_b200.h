@@ -6,9 +6,11 @@
  *     ObservationModelFBMaxErr(hap, read, leftPos, obsParams).calcLikelihood()
  *     (ObservationModelFB.hpp:160,133; ObservationModelFB.cpp:1068)         -> dindel_b200_submit
  *   - the pair-marginalisation core of DetInDel::diploidGLF (DInDel.cpp:3085-3113,3349-3390)
- *                                                                            -> dindel_b200_diploid
+ *                                                                            -> dindel_b200_pair_sums
  *   - the variational-Bayes EM core of DetInDel::estimateHaplotypeFrequenciesBayesEM
  *     (DInDel.cpp:2431-2543)                                                 -> dindel_b200_bayes_em
+ *   - DetInDel::filterHaplotypes (DInDel.cpp:1932-2100), the consumer of MLAlignment::hpos
+ *                                                                            -> dindel_b200_coverage
  * Plain C, POD only, caller-owned buffers, no exceptions: every entry returns 0 or a negative
  * DINDEL_E_* code (dindel_b200_strerror).  There is NO CPU fallback: without a CUDA device every
  * compute entry fails with DINDEL_E_NO_DEVICE.
@@ -168,6 +170,8 @@ int dindel_b200_download(dindel_ctx *ctx, dindel_batch_out *out);
 int dindel_b200_sync(dindel_ctx *ctx);                        /* wait for run(); updates timing */
 int dindel_b200_get_timing(const dindel_ctx *ctx, dindel_timing *t);
 int dindel_b200_hpos_stride(const dindel_ctx *ctx);           /* stride of the resident hpos rows */
+/* device time (CUDA events) of the kernel of the last pair_sums / bayes_em / coverage call, ms */
+float dindel_b200_last_kernel_ms(const dindel_ctx *ctx);
 
 /* ---- K2: haplotype-pair sums over the RESIDENT likelihood matrix (after run/submit) ----------
  * Replaces the inner loops of DetInDel::diploidGLF (DInDel.cpp:3085-3113: start = 0;

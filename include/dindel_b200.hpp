@@ -24,6 +24,9 @@
 #include <iostream>
 #include <map>
 #include <string>
+#include <time.h>
+#include <cstdlib>
+#include <cstdio>
 #include <vector>
 #include "dindel_b200.h"
 
@@ -70,7 +73,7 @@ struct ReadTraits {
 class Engine {
 public:
     template <class ObsParams>
-    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0), last_nh_(0), last_nr_(0), mapUnmapped_(false), libOff_(1, 0)
+    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0), last_nh_(0), last_nr_(0), t_cl_(0.0), t_fh_(0.0), n_cl_(0), mapUnmapped_(false), libOff_(1, 0)
     {
         dindel_b200_default_params(&p_);
         p_.pError = op.pError; p_.pMut = op.pMut; p_.mapQualThreshold = op.mapQualThreshold;
@@ -125,6 +128,15 @@ private:
     dindel_params p_;
     dindel_ctx *ctx_;
     size_t last_nh_, last_nr_; // shape of the resident window (filterHaplotypes checks it is the same one)
+    // DINDEL_B200_TRACE: wall time inside the adapter's two entries (packing + C call + re-expansion), stderr
+    double t_cl_, t_fh_;
+    long n_cl_;
+    static double now() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec; }
+    struct Tick {
+        double *acc; double t0;
+        explicit Tick(double *a) : acc(a), t0(now()) {}
+        ~Tick() { *acc += now() - t0; }
+    };
     bool mapUnmapped_;
     std::map<const void *, int> libIndex_;
     std::vector<int64_t> libOff_;
@@ -224,6 +236,9 @@ void Engine::computeLikelihoods(const std::vector<HapT> &haps, const std::vector
                                 std::vector<int> &onHap)
 {
     typedef ReadTraits<ReadT> RT;
+    Tick tick(&t_cl_);
+    if (++n_cl_ % 50 == 0 && getenv("DINDEL_B200_TRACE"))
+        fprintf(stderr, "dindel_b200 adapter trace: %ld windows, computeLikelihoods %.3f s, filterHaplotypes %.3f s\n", n_cl_, t_cl_, t_fh_);
     const size_t nh = haps.size(), nr = reads.size();
     onHap = std::vector<int>(nr, 0);
     liks = std::vector<std::vector<MLA> >(nh, std::vector<MLA>(nr));
@@ -498,6 +513,7 @@ int Engine::filterHaplotypes(const std::vector<HapT> &haps, const std::vector<Re
     typedef typename HapT_variant<HapT>::type AV;
     typedef typename CovMap::key_type PAV;           // pair<int, AlignedVariant> (DInDel.cpp:1943)
     typedef typename CovMap::mapped_type Coverage;   // VariantCoverage(nf, nr) (DInDel.hpp:53-66)
+    Tick tick(&t_fh_);
     const size_t nh = haps.size(), nr = reads.size();
     filtered = std::vector<int>(nh, 0);
     varCoverage.clear();
