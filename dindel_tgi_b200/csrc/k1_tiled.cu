@@ -35,7 +35,10 @@
 #define K1_LEFT_TREE 1
 #endif
 #ifndef K1_TILED_J11_MINB
-#define K1_TILED_J11_MINB 2
+#define K1_TILED_J11_MINB 3
+#endif
+#ifndef K1_TILED_TBL_MINC
+#define K1_TILED_TBL_MINC 4 // J = 6 classes wider than this also take the shared-memory jump tables
 #endif
 #define K1_TILED_BTG_MAX_CTAS K1_TILED_J11_MINB // resident CTAs per SM of the classes that keep back-pointers in global memory
 #define FULLMASK 0xffffffffu
@@ -155,8 +158,14 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
 {
     using Cfg = TiledCfg<C, J>;
     constexpr int U16 = Cfg::U16;
+    // TBL (J > 7): the per-column jump tables lp(x, y) do not fit the register file next to the row windows
+    // (C*(2J-1) doubles); they are kept once per CTA in shared memory, indexed by the homopolymer code of the
+    // column that owns the entry, and the "-inf outside the haplotype" entries become -inf halo columns instead.
+    constexpr bool TBL = (J > 7) || (C > K1_TILED_TBL_MINC);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double s_hp_lpe[K1_HP_LUT], s_hp_lpn[K1_HP_LUT];
+    __shared__ double s_tl[TBL ? K1_HP_LUT * (J - 1) : 1]; // [code][y-2] = logProbError + (y-1)*lInsgIns (cpp:1791)
+    __shared__ double s_tr[TBL ? K1_HP_LUT * J : 1];       // [code][y-1] = lp(y) + logProbNoError    (cpp:1732-1735)
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
     const K1Luts *__restrict__ L = B.luts;
@@ -164,6 +173,18 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
     for (int i = threadIdx.x; i < K1_HP_LUT; i += blockDim.x) {
         s_hp_lpe[i] = L->hp_lpe[i];
         s_hp_lpn[i] = L->hp_lpn[i];
+    }
+    if constexpr (TBL) {
+        for (int i = threadIdx.x; i < K1_HP_LUT * (J - 1); i += blockDim.x) {
+            const int code = i / (J - 1), y = i % (J - 1) + 2;
+            s_tl[i] = L->hp_lpe[code] + (double)(y - 1) * L->lInsgIns;
+        }
+        for (int i = threadIdx.x; i < K1_HP_LUT * J; i += blockDim.x) {
+            const int code = i / J, y = i % J + 1;
+            const double lpn_s = L->hp_lpn[code], lpe_s = L->hp_lpe[code];
+            const double lp = (y == 1) ? lpn_s : (lpe_s + (double)(y - 1) * L->lInsgIns);
+            s_tr[i] = lp + lpn_s;
+        }
     }
     __syncthreads();
     unsigned char *base = smem_raw + tiled_smem_per_warp(C, U16, maxR, BTG) * wib;
@@ -251,22 +272,31 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
             // candidate chains advanced in lock step (y outer, c inner) so that the chains of the C
             // cells interleave in the instruction stream.
             {
-                double lpn[C], lpe[C], lpD[C][J - 1];
+                double lpn[C], lpe[C], lpD[TBL ? 1 : C][TBL ? 1 : J - 1];
+                int offL[TBL ? C : 1];
 #pragma unroll
                 for (int c = 0; c < C; c++) {
                     const int x = c0 + c;
                     const int code = hp[x <= RO ? x : RO];
                     lpe[c] = s_hp_lpe[code];
                     lpn[c] = s_hp_lpn[code];
+                    if constexpr (TBL) {
+                        offL[c] = code * (J - 1);
+                    } else {
 #pragma unroll
-                    for (int y = 2; y <= J; y++) // cpp:1791; a source left of LO can never win -> -inf
-                        lpD[c][y - 2] = pin_d((x - y >= 0) ? lpe[c] + (double)(y - 1) * lInsgIns : K1_NEG_INF);
+                        for (int y = 2; y <= J; y++) // cpp:1791; a source left of LO can never win -> -inf
+                            lpD[c][y - 2] = pin_d((x - y >= 0) ? lpe[c] + (double)(y - 1) * lInsgIns : K1_NEG_INF);
+                    }
                     P0[c] = 0.0; // alpha[0] = 0 (cpp:335-338)
                     P1[c] = 0.0;
                 }
                 // lpe of the column left of this lane's first (RO's "from S+H" candidate, cpp:1805)
                 const double lpeLm1 = s_hp_lpe[hp[(c0 >= 1 && c0 - 1 <= RO) ? c0 - 1 : 0]];
 
+                auto LPD = [&](int c, int k) -> double {
+                    if constexpr (TBL) return s_tl[offL[c] + k];
+                    else return lpD[c][k];
+                };
                 auto left_rows = [&](auto cro_tag) {
                 constexpr int CRO = decltype(cro_tag)::value;
                 for (int b = 1; b <= bMid; b++) {
@@ -286,6 +316,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                         const int ci = d * C - j;
                         WP[J - j] = shfl_up_d(WP[J + ci], d);
                         WO[J - j] = shfl_up_d(WO[J + ci], d);
+                        if constexpr (TBL) WP[J - j] = (lane < d) ? K1_NEG_INF : WP[J - j]; // column c0-j < 0
                     }
                     t1w[0] = shfl_up_d(t1w[C], 1); // lane 0: only LO would use it (overridden)
 
@@ -301,11 +332,11 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
 #pragma unroll
                         for (int c = 0; c < C; c++) {
                             const double va = (y == 1) ? ((WO[J + c - 1] + lpn[c]) + WP[J + c - 1]) + lpn[c]
-                                                       : ((WO[J + c - y] + lpD[c][(y >= 2) ? y - 2 : 0]) + WP[J + c - y]) + lpn[c];
+                                                       : ((WO[J + c - y] + LPD(c, (y >= 2) ? y - 2 : 0)) + WP[J + c - y]) + lpn[c];
                             double pm = va;
                             uint32_t pc = (uint32_t)(y - 1);
                             if (y + 1 <= J) {
-                                const double vb = ((WO[J + c - (y + 1)] + lpD[c][y - 1]) + WP[J + c - (y + 1)]) + lpn[c];
+                                const double vb = ((WO[J + c - (y + 1)] + LPD(c, y - 1)) + WP[J + c - (y + 1)]) + lpn[c];
                                 const bool pb = (vb >= va);
                                 pm = pb ? vb : va;
                                 pc = pb ? (uint32_t)y : (uint32_t)(y - 1);
@@ -330,7 +361,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                     for (int y = 2; y <= J; y++) {
 #pragma unroll
                         for (int c = 0; c < C; c++) {
-                            const double v = ((WO[J + c - y] + lpD[c][y - 2]) + WP[J + c - y]) + lpn[c];
+                            const double v = ((WO[J + c - y] + LPD(c, y - 2)) + WP[J + c - y]) + lpn[c];
                             const bool p = (v >= best[c]);
                             best[c] = p ? v : best[c];
                             code[c] = p ? (uint32_t)(y - 1) : code[c];
@@ -425,24 +456,37 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
             // Window W*[k] over columns c0 .. c0+C-1+J (own at k = c, the J columns to the right
             // from the neighbour lanes).
             {
-                double cI[C][J], lpeN[C];
+                double cI[TBL ? 1 : C][TBL ? 1 : J], lpeN[C];
+                int offR[TBL ? C + J : 1]; // [k]: table row of column c0+k (clamped to RO), k = 1 .. C+J-1
+                if constexpr (TBL) {
+#pragma unroll
+                    for (int k = 1; k < C + J; k++) offR[k] = (int)hp[(c0 + k <= RO) ? c0 + k : RO] * J;
+                }
 #pragma unroll
                 for (int c = 0; c < C; c++) {
                     const int x = c0 + c;
+                    if constexpr (TBL) {
+                        lpeN[c] = s_hp_lpe[hp[(x + 1 <= RO) ? x + 1 : RO]]; // logProbError[x+1] (cpp:1748)
+                    } else {
 #pragma unroll
-                    for (int y = 1; y <= J; y++) {
-                        const int nx = (x + y <= RO) ? x + y : RO; // cpp:1728-1729
-                        const int code = hp[nx];
-                        const double lpn_s = s_hp_lpn[code], lpe_s = s_hp_lpe[code];
-                        const double lp = (y == 1) ? lpn_s : (lpe_s + (double)(y - 1) * lInsgIns); // cpp:1732
-                        cI[c][y - 1] = pin_d((x + y <= RO) ? lp + lpn_s : K1_NEG_INF); // duplicates of RO never win
-                        if (y == 1) lpeN[c] = lpe_s; // logProbError[x+1] (cpp:1748)
+                        for (int y = 1; y <= J; y++) {
+                            const int nx = (x + y <= RO) ? x + y : RO; // cpp:1728-1729
+                            const int code = hp[nx];
+                            const double lpn_s = s_hp_lpn[code], lpe_s = s_hp_lpe[code];
+                            const double lp = (y == 1) ? lpn_s : (lpe_s + (double)(y - 1) * lInsgIns); // cpp:1732
+                            cI[c][y - 1] = pin_d((x + y <= RO) ? lp + lpn_s : K1_NEG_INF); // duplicates of RO never win
+                            if (y == 1) lpeN[c] = lpe_s; // logProbError[x+1] (cpp:1748)
+                        }
                     }
                     P0[c] = (x <= RO) ? 0.0 : K1_NEG_INF; // beta[R-1] = 0; columns beyond RO never win
                     P1[c] = (x <= RO) ? 0.0 : K1_NEG_INF;
                 }
                 const double lpnRO = s_hp_lpn[hp[RO]];
 
+                auto CI = [&](int c, int k) -> double { // k = y-1; target column x+y = c0 + c + k + 1
+                    if constexpr (TBL) return s_tr[offR[c + k + 1] + k];
+                    else return cI[c][k];
+                };
                 auto right_rows = [&](auto cro_tag) {
                 constexpr int CRO = decltype(cro_tag)::value;
                 for (int b = R - 1; b > bMid; b--) {
@@ -462,6 +506,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                         const int ci = (C - 1 + j) % C;
                         WP[C - 1 + j] = shfl_down_d(WP[ci], d);
                         WO[C - 1 + j] = shfl_down_d(WO[ci], d);
+                        if constexpr (TBL) WP[C - 1 + j] = (lane + d > 31) ? K1_NEG_INF : WP[C - 1 + j]; // beyond lane 31
                     }
                     uw[C] = shfl_down_d(uw[0], 1); // lane 31: column is RO or padding (overridden)
 
@@ -470,14 +515,14 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                     // jumps y = 1..J to column x+y (cpp:1724-1737)
 #pragma unroll
                     for (int c = 0; c < C; c++) {
-                        best[c] = (cI[c][0] + WP[c + 1]) + WO[c + 1];
+                        best[c] = (CI(c, 0) + WP[c + 1]) + WO[c + 1];
                         code[c] = 0;
                     }
 #pragma unroll
                     for (int y = 2; y <= J; y++) {
 #pragma unroll
                         for (int c = 0; c < C; c++) {
-                            const double v = (cI[c][y - 1] + WP[c + y]) + WO[c + y];
+                            const double v = (CI(c, y - 1) + WP[c + y]) + WO[c + y];
                             const bool p = (v > best[c] + K1_EPS);
                             best[c] = p ? v : best[c];
                             code[c] = p ? (uint32_t)(y - 1) : code[c];
