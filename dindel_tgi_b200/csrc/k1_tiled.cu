@@ -153,7 +153,9 @@ __device__ __forceinline__ void scan_first_wins(const double (&v0)[C], const dou
 
 // MINB: resident CTAs per SM the register budget is set for; BTG: back-pointer rows in a per-warp slot of
 // global memory (L2 resident) instead of shared memory (long reads x wide classes: 250 x 352 columns = 96 KB).
-template <int C, int J, int MINB, bool BTG>
+// INS: some read of the batch carries an insert-size prior (--libFile); kept out of the common instantiation
+// (its presence in the meeting row costs the row loops 4 % through register allocation).
+template <int C, int J, int MINB, bool BTG, bool INS>
 __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Batch B, int cls)
 {
     using Cfg = TiledCfg<C, J>;
@@ -613,16 +615,18 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                 const double hLO0 = L->priorLO_H[0], hLO1 = L->priorLO_H[1];
                 const double hOn0 = L->priorOn_H[0], hOn1 = L->priorOn_H[1];
                 // insert-size prior of this read (cpp:279-293): warp-uniform, rare (only with --libFile)
-                const int insMode = B.read_ins_mode ? (int)B.read_ins_mode[r] : DINDEL_INS_NONE;
-                int insAnchor = 0, insMax = 1;
+                int insMode = DINDEL_INS_NONE, insAnchor = 0, insMax = 1;
                 const double *insLogp = nullptr;
                 double ins0 = 0.0;
-                if (insMode != DINDEL_INS_NONE) {
-                    const int lib = B.read_lib[r];
-                    insAnchor = B.read_ins_anchor[r];
-                    insLogp = B.lib_logp + B.lib_off[lib];
-                    insMax = (int)(B.lib_off[lib + 1] - B.lib_off[lib]);
-                    ins0 = B.lib_log95[lib];
+                if constexpr (INS) {
+                    insMode = (int)B.read_ins_mode[r];
+                    if (insMode != DINDEL_INS_NONE) {
+                        const int lib = B.read_lib[r];
+                        insAnchor = B.read_ins_anchor[r];
+                        insLogp = B.lib_logp + B.lib_off[lib];
+                        insMax = (int)(B.lib_off[lib + 1] - B.lib_off[lib]);
+                        ins0 = B.lib_log95[lib];
+                    }
                 }
 #pragma unroll
                 for (int c = 0; c < C; c++) {
@@ -631,7 +635,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                     const double t1v = sm_ao[32 * C + x] + P1[c];
                     const bool lo = (x == 0), ro = (x == RO), pad = (x > RO);
                     double qR0 = lo ? pLO0 : pOn0, qR1 = lo ? pLO1 : pOn1, qH0 = lo ? hLO0 : hOn0, qH1 = lo ? hLO1 : hOn1;
-                    if (insMode != DINDEL_INS_NONE && !ro && !pad) {
+                    if (INS && insMode != DINDEL_INS_NONE && !ro && !pad) {
                         if (lo) { // (log(pOff) + logpIns) + pinsert[0]  (cpp:298)
                             qR0 = pLO0 + ins0; qR1 = pLO1 + ins0; qH0 = hLO0 + ins0; qH1 = hLO1 + ins0;
                         } else {  // (pinsert[x] + log(1 - pOff)) + logpIns  (cpp:301)
@@ -752,16 +756,26 @@ extern "C" cudaError_t k1_tiled_prepare(const K1Batch *B, cudaStream_t st, int *
     return cudaGetLastError();
 }
 
+template <int C, int J, int MINB, bool BTG, bool INS>
+static cudaError_t launch_one_ins(const K1Batch *B, int num_sms, int cls, cudaStream_t st);
+
 template <int C, int J, int MINB, bool BTG>
 static cudaError_t launch_one(const K1Batch *B, int num_sms, int cls, cudaStream_t st)
+{
+    return B->read_ins_mode ? launch_one_ins<C, J, MINB, BTG, true>(B, num_sms, cls, st)
+                            : launch_one_ins<C, J, MINB, BTG, false>(B, num_sms, cls, st);
+}
+
+template <int C, int J, int MINB, bool BTG, bool INS>
+static cudaError_t launch_one_ins(const K1Batch *B, int num_sms, int cls, cudaStream_t st)
 {
     constexpr int U16 = TiledCfg<C, J>::U16;
     const int warps = K1_TILED_WPC;
     const size_t smem = tiled_smem_per_warp(C, U16, B->max_R, BTG) * warps;
-    cudaError_t e = cudaFuncSetAttribute(k1_tiled_kernel<C, J, MINB, BTG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k1_tiled_kernel<C, J, MINB, BTG, INS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_tiled_kernel<C, J, MINB, BTG>, warps * 32, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_tiled_kernel<C, J, MINB, BTG, INS>, warps * 32, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) return cudaErrorInvalidConfiguration;
     if (BTG && per_sm > K1_TILED_BTG_MAX_CTAS) per_sm = K1_TILED_BTG_MAX_CTAS; // scratch slots are sized for this
@@ -769,7 +783,7 @@ static cudaError_t launch_one(const K1Batch *B, int num_sms, int cls, cudaStream
     long long need = (B->unit_end - B->unit_begin + warps - 1) / warps;
     if (grid > need) grid = need;
     if (grid < 1) grid = 1;
-    k1_tiled_kernel<C, J, MINB, BTG><<<(int)grid, warps * 32, smem, st>>>(*B, cls);
+    k1_tiled_kernel<C, J, MINB, BTG, INS><<<(int)grid, warps * 32, smem, st>>>(*B, cls);
     return cudaGetLastError();
 }
 
