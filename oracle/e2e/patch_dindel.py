@@ -108,8 +108,32 @@ DUMP = r"""
 		fclose(df);
 	}
 """
+# --dump, second hook: the two call sites of DetInDel::getCIGAR (DInDel.cpp:511 pooled / :610 diploid, the
+# --outputRealignedBAM option) append, per read, the inputs of the haplotype choice (:502-509, :597-606) and of
+# getCIGAR (:728-882: the read's hpos, the haplotype's hap.ml.hpos, refSeqPos) and the resulting CIGAR to the file
+# named by $DINDEL_B200_DUMP_CIGAR: golden vectors for the a-next row "realigned-BAM CIGARs" (K5,
+# tests/golden/make_cigar_golden.py).
+DUMP_CIG = r"""
+						if (getenv("DINDEL_B200_DUMP_CIGAR")) {
+							FILE *df = fopen(getenv("DINDEL_B200_DUMP_CIGAR"), "a");
+							const int hx = HX;
+							fprintf(df, "G MODE %d %d %d %d %d %d %d", H1, H2, int(haps.size()), int(onHap[r]), hx, refSeqPos, cigars[r].refPos);
+							fprintf(df, " L"); for (size_t h=0;h<haps.size();h++) fprintf(df, " %.17g", liks[h][r].ll);
+							fprintf(df, " N"); for (size_t h=0;h<haps.size();h++) fprintf(df, " %d", haps[h].countIndels());
+							fprintf(df, " P"); for (size_t b=0;b<liks[hx][r].hpos.size();b++) fprintf(df, " %d", liks[hx][r].hpos[b]);
+							fprintf(df, " M"); for (size_t b=0;b<haps[hx].ml.hpos.size();b++) fprintf(df, " %d", haps[hx].ml.hpos[b]);
+							fprintf(df, " C"); for (size_t c=0;c<cigars[r].size();c++) fprintf(df, " %d %d", cigars[r][c].first, cigars[r][c].second);
+							fprintf(df, "\n");
+							fclose(df);
+						}
+"""
 if dump:
     anchor = "\t\tvarCoverage[pav]=VariantCoverage(int(rf.size()), int(rr.size()));\n\t}\n"
     assert text.count(anchor) == 1
     text = text.replace(anchor, anchor + DUMP)
+    a1 = "\t\t\t\t\t\tcigars[r]=getCIGAR(haps[hidx], reads[r], liks[hidx][r], refSeqPos);\n"
+    a2 = "\t\t\t\t\t\tcigars[r]=getCIGAR(haps[hmax], reads[r], liks[hmax][r], refSeqPos);\n"
+    assert text.count(a1) == 1 and text.count(a2) == 1
+    text = text.replace(a1, a1 + DUMP_CIG.replace("HX", "hidx").replace("MODE", "B").replace("H1", "-1").replace("H2", "-1"))
+    text = text.replace(a2, a2 + DUMP_CIG.replace("HX", "hmax").replace("MODE", "D").replace("H1", "hpl.h1").replace("H2", "hpl.h2"))
 open(dst, "w", encoding="latin-1").write(text)
