@@ -13,6 +13,7 @@
 #include "k1_common.cuh"
 #include "k23.cuh"
 #include "k4.cuh"
+#include "k5.cuh"
 
 extern "C" size_t k1_generic_smem_per_warp(int maxS, int maxR, int bt_in_smem);
 extern "C" cudaError_t k1_generic_launch(const K1Batch *B, int grid, int warps_per_cta,
@@ -30,6 +31,9 @@ extern "C" cudaError_t k3_launch(const K3Args *a, cudaStream_t st);
 extern "C" int k3_max_haps(void);
 extern "C" size_t k4_smem_bytes(int ne, int nk, int nr, int nh);
 extern "C" cudaError_t k4_launch(const K4Args *a, int n_windows, size_t smem, cudaStream_t st);
+extern "C" size_t k5_smem_bytes(int pitch);
+extern "C" int k5_pitch(int max_R);
+extern "C" cudaError_t k5_launch(const K5Args *a, int n_sms, size_t smem, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------------
 // small device kernels owned by the API layer
@@ -191,6 +195,7 @@ struct dindel_ctx {
         d_read_flags, d_pairs, d_hpos, d_win_status, d_on_hap, d_x[8],
         d_read_ins_mode, d_read_ins_anchor, d_read_lib, d_lib_off, d_lib_logp, d_lib_log95;
     int n_libs = 0;
+    long long hap_bases = 0;   // hap_off[n_haps] of the resident batch
     // resident batch
     bool resident = false, ran = false;
     K1Batch B;
@@ -552,6 +557,7 @@ static int prepare_batch(dindel_ctx *ctx, const dindel_batch_in *in, int want_hp
     CU(ctx->d_win_pair.ensure(((size_t)nw + 1) * 8 + 16));
     CU(ctx->d_win_unit.ensure(((size_t)nw + 1) * 8 + 16));
     CU(ctx->d_hap_off.ensure(((size_t)nh + 1) * 8 + 16));
+    ctx->hap_bases = hap_bytes;
     CU(ctx->d_hap_seq.ensure((size_t)hap_bytes + 16));
     CU(ctx->d_read_off.ensure(((size_t)nr + 1) * 8 + 16));
     CU(ctx->d_read_seq.ensure((size_t)read_bytes + 16));
@@ -1185,6 +1191,63 @@ int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cove
         CU(cudaMemcpyAsync(out->hap_filtered, a.hap_filtered, nh, cudaMemcpyDeviceToHost, st));
         if (out->hap_uncovered) CU(cudaMemcpyAsync(out->hap_uncovered, a.hap_uncovered, nh, cudaMemcpyDeviceToHost, st));
     }
+    CU(cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev_k[0], ctx->ev_k[1]);
+    return DINDEL_OK;
+}
+
+int dindel_b200_cigars(dindel_ctx *ctx, const dindel_cigar_in *in, dindel_cigar_out *out)
+{
+    if (!ctx || !in || !out || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "cigars needs a resident, computed batch");
+    const K1Batch &B = ctx->B;
+    if (!B.hpos) return fail(ctx, DINDEL_E_INVALID, "cigars needs the hpos rows resident (upload(want_hpos) or DINDEL_OUT_KEEP_HPOS)");
+    if (in->mode != DINDEL_CIGAR_PAIR && in->mode != DINDEL_CIGAR_BEST) return fail(ctx, DINDEL_E_INVALID, "mode");
+    if (in->cigar_cap < 1) return fail(ctx, DINDEL_E_INVALID, "cigar_cap");
+    const size_t nw = (size_t)B.n_windows, nh = (size_t)B.n_haps, nr = (size_t)B.n_reads, cap = (size_t)in->cigar_cap;
+    const size_t nb = (size_t)ctx->hap_bases;
+    if (!in->win_ref_start || (nb && !in->hap_ref_pos)) return fail(ctx, DINDEL_E_INVALID, "null array");
+    if (in->mode == DINDEL_CIGAR_PAIR && (!in->win_h1 || !in->win_h2 || (nh && !in->hap_n_indels)))
+        return fail(ctx, DINDEL_E_INVALID, "PAIR mode needs win_h1 / win_h2 / hap_n_indels");
+    if (nr && (!out->read_hap || !out->read_ref_pos || !out->read_n_ops || !out->ops)) return fail(ctx, DINDEL_E_INVALID, "null array");
+    if (!nr) return DINDEL_OK;
+    const int pitch = k5_pitch(B.max_R);
+    const size_t smem = k5_smem_bytes(pitch);
+    if (smem > ctx->smem_optin) return fail(ctx, DINDEL_E_UNSUPPORTED, "reads too long for one CTA's shared memory");
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const bool pairm = in->mode == DINDEL_CIGAR_PAIR;
+    // staging: [win_h1 | win_h2 | win_ref_start | hap_n_indels | hap_ref_pos]; results: [read_hap | read_ref_pos | read_n_ops | ops]
+    const size_t o_h1 = 0, o_h2 = o_h1 + nw * 4, o_rs = o_h2 + nw * 4, o_ni = o_rs + nw * 4, o_rp = o_ni + nh * 4,
+                 in_bytes = o_rp + nb * 4;
+    const size_t r_h = 0, r_p = r_h + nr * 4, r_n = r_p + nr * 4, r_o = r_n + nr * 4, out_bytes = r_o + nr * cap * 4;
+    CU(ctx->d_x[0].ensure(in_bytes + 16));
+    CU(ctx->d_x[1].ensure(out_bytes + 16));
+    char *d_in = (char *)ctx->d_x[0].p, *d_out = (char *)ctx->d_x[1].p;
+    if (pairm) {
+        CU(cudaMemcpyAsync(d_in + o_h1, in->win_h1, nw * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_h2, in->win_h2, nw * 4, cudaMemcpyHostToDevice, st));
+        if (nh) CU(cudaMemcpyAsync(d_in + o_ni, in->hap_n_indels, nh * 4, cudaMemcpyHostToDevice, st));
+    }
+    CU(cudaMemcpyAsync(d_in + o_rs, in->win_ref_start, nw * 4, cudaMemcpyHostToDevice, st));
+    if (nb) CU(cudaMemcpyAsync(d_in + o_rp, in->hap_ref_pos, nb * 4, cudaMemcpyHostToDevice, st));
+    K5Args a;
+    a.mode = in->mode; a.cap = in->cigar_cap; a.pitch = pitch;
+    a.win_h1 = (const int32_t *)(d_in + o_h1); a.win_h2 = (const int32_t *)(d_in + o_h2);
+    a.win_ref_start = (const int32_t *)(d_in + o_rs); a.hap_n_indels = (const int32_t *)(d_in + o_ni);
+    a.hap_ref_pos = (const int32_t *)(d_in + o_rp);
+    a.read_hap = (int32_t *)(d_out + r_h); a.read_ref_pos = (int32_t *)(d_out + r_p); a.read_n_ops = (int32_t *)(d_out + r_n);
+    a.ops = (uint32_t *)(d_out + r_o);
+    a.n_windows = B.n_windows; a.n_reads = B.n_reads;
+    a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.hap_off = B.hap_off; a.read_off = B.read_off;
+    a.pairs = B.pairs; a.on_hap = (const uint8_t *)ctx->d_on_hap.p; a.hpos = B.hpos; a.hpos_stride = B.hpos_stride;
+    CU(cudaMemsetAsync(a.ops, 0, nr * cap * 4, st));
+    CU(cudaEventRecord(ctx->ev_k[0], st));
+    CU(k5_launch(&a, ctx->num_sms, smem, st));
+    CU(cudaEventRecord(ctx->ev_k[1], st));
+    CU(cudaMemcpyAsync(out->read_hap, a.read_hap, nr * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out->read_ref_pos, a.read_ref_pos, nr * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out->read_n_ops, a.read_n_ops, nr * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out->ops, a.ops, nr * cap * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev_k[0], ctx->ev_k[1]);
     return DINDEL_OK;

@@ -78,6 +78,16 @@ class _CoverOut(C.Structure):
                 ("key_nr", C.c_void_p)]
 
 
+class _CigarIn(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("cigar_cap", C.c_int32), ("win_h1", C.c_void_p), ("win_h2", C.c_void_p),
+                ("win_ref_start", C.c_void_p), ("hap_n_indels", C.c_void_p), ("hap_ref_pos", C.c_void_p)]
+
+
+class _CigarOut(C.Structure):
+    _fields_ = [("read_hap", C.c_void_p), ("read_ref_pos", C.c_void_p), ("read_n_ops", C.c_void_p), ("ops", C.c_void_p)]
+
+
+CIGAR_PAIR, CIGAR_BEST = 0, 1
 OUT_KEEP_HPOS = 1
 VAR_DEL, VAR_INS, VAR_OTHER = 0, 1, 2
 
@@ -103,7 +113,7 @@ EXPORTS = [
     "dindel_b200_get_timing", "dindel_b200_hpos_stride", "dindel_b200_alloc_pinned",
     "dindel_b200_free_pinned", "dindel_b200_measure_fp64_peak", "dindel_b200_pair_sums",
     "dindel_b200_bayes_em", "dindel_b200_plan_shards", "dindel_b200_coverage", "dindel_b200_set_libraries",
-    "dindel_b200_last_kernel_ms",
+    "dindel_b200_last_kernel_ms", "dindel_b200_cigars",
 ]
 
 _lib = None
@@ -431,6 +441,27 @@ class Engine:
         self._check(self.lib.dindel_b200_coverage(self.h, C.byref(a), C.byref(o)), "coverage")
         return (filt[:nh_tot], unc[:nh_tot], [nf[wk[w]:wk[w + 1]] for w in range(nw)],
                 [nr[wk[w]:wk[w + 1]] for w in range(nw)])
+
+    def cigars(self, mode, win_ref_start, hap_ref_pos, win_h1=None, win_h2=None, hap_n_indels=None, cigar_cap=16):
+        """K5 (the haplotype choice of DInDel.cpp:503-509 / :597-606 + DetInDel::getCIGAR, DInDel.cpp:728-882) over
+        the resident batch.  hap_ref_pos: flat int32 laid out like hap_seq.  Returns (read_hap[n_reads],
+        read_ref_pos[n_reads], read_n_ops[n_reads], ops[n_reads, cigar_cap]) with ops = len << 4 | op."""
+        batch = self._resident[0] if getattr(self, "_resident", None) else None
+        nr = batch.n_reads if batch is not None else int(self._n_reads)
+        i32 = lambda x: None if x is None else np.ascontiguousarray(x, dtype=np.int32)
+        rs, rp, h1, h2, ni = i32(win_ref_start), i32(hap_ref_pos), i32(win_h1), i32(win_h2), i32(hap_n_indels)
+        ptr = lambda x: None if x is None else x.ctypes.data
+        rh, rr, rn = (np.zeros(max(nr, 1), dtype=np.int32) for _ in range(3))
+        ops = np.zeros((max(nr, 1), int(cigar_cap)), dtype=np.uint32)
+        a, o = _CigarIn(), _CigarOut()
+        a.mode, a.cigar_cap = int(mode), int(cigar_cap)
+        a.win_h1, a.win_h2, a.win_ref_start, a.hap_n_indels, a.hap_ref_pos = ptr(h1), ptr(h2), ptr(rs), ptr(ni), ptr(rp)
+        o.read_hap, o.read_ref_pos, o.read_n_ops, o.ops = rh.ctypes.data, rr.ctypes.data, rn.ctypes.data, ops.ctypes.data
+        t0 = time.perf_counter()
+        self._check(self.lib.dindel_b200_cigars(self.h, C.byref(a), C.byref(o)), "cigars")
+        self.last_call_ms = 1e3 * (time.perf_counter() - t0)
+        self.last_kernel_ms = float(self.lib.dindel_b200_last_kernel_ms(self.h))
+        return rh[:nr], rr[:nr], rn[:nr], ops[:nr]
 
     def bayes_em(self, set_window, compatible, a0=0.001, tol=1e-4):
         """K3 (estimateHaplotypeFrequenciesBayesEM core).  compatible: list of uint8 arrays (nh each).

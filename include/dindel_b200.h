@@ -11,6 +11,8 @@
  *     (DInDel.cpp:2431-2543)                                                 -> dindel_b200_bayes_em
  *   - DetInDel::filterHaplotypes (DInDel.cpp:1932-2100), the consumer of MLAlignment::hpos
  *                                                                            -> dindel_b200_coverage
+ *   - the realigned-read CIGARs of --outputRealignedBAM: DetInDel::getCIGAR (DInDel.cpp:728-882) and the
+ *     haplotype choice at its call sites (:503-509, :597-606)                -> dindel_b200_cigars
  * Plain C, POD only, caller-owned buffers, no exceptions: every entry returns 0 or a negative
  * DINDEL_E_* code (dindel_b200_strerror).  There is NO CPU fallback: without a CUDA device every
  * compute entry fails with DINDEL_E_NO_DEVICE.
@@ -22,7 +24,7 @@
 extern "C" {
 #endif
 
-#define DINDEL_B200_ABI_VERSION 2
+#define DINDEL_B200_ABI_VERSION 3
 
 /* error codes (batch-fatal) */
 #define DINDEL_OK 0
@@ -117,7 +119,7 @@ typedef struct dindel_batch_out {
     int64_t n_pairs;            /* capacity of pairs[] (>= dindel_b200_count_pairs) */
     dindel_pair_out *pairs;     /* [n_pairs] */
     int16_t *hpos;              /* optional [n_pairs * hpos_stride]: MLAlignment::hpos */
-    int32_t hpos_stride;        /* >= longest read when hpos != NULL */
+    int32_t hpos_stride;        /* >= longest read when hpos != NULL; row entries past a read's length are unspecified */
     int32_t flags;              /* DINDEL_OUT_* */
     int64_t *win_pair;          /* [n_windows+1] */
     int32_t *win_status;        /* [n_windows] DINDEL_WIN_* (first failing pair's reason) */
@@ -252,6 +254,46 @@ typedef struct dindel_cover_out {
     int32_t *key_nf, *key_nr;   /* [n_keys] VariantCoverage (DInDel.hpp:53-66) */
 } dindel_cover_out;
 int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cover_out *out);
+
+/* ---- K5: realigned-read CIGARs over the RESIDENT hpos rows (--outputRealignedBAM) --------------
+ * Replaces the per-read loops at the two call sites of DetInDel::getCIGAR (DInDel.cpp:500-513 pooled,
+ * :596-611 diploid) and getCIGAR itself (DInDel.cpp:728-882): with it the realigned-BAM option needs no hpos
+ * row on the host either; 4 * (3 + cigar_cap) bytes per READ come back instead of 2 * R bytes per PAIR.
+ * Per read r of window w:
+ *   1. the haplotype it is realigned to.  DINDEL_CIGAR_PAIR (diploid, :597-606): the better of the window's MAP
+ *      pair (win_h1[w], win_h2[w]) (getMaxHap, host); |ll1 - ll2| < 1e-8 -> h1 if hap_n_indels[h1] <
+ *      hap_n_indels[h2] (Haplotype::countIndels, Haplotype.hpp:254-261) else h2.  DINDEL_CIGAR_BEST (pooled,
+ *      :503-509): the first strict arg-max of ll over the window's haplotypes; reads with !onHap[r] are skipped
+ *      (read_n_ops = 0, :502).  A window with win_h1[w] < 0 is skipped in PAIR mode (read_n_ops = 0).
+ *   2. npos[b] = hap_ref_pos[hpos[b]] for hpos[b] >= 0, else hpos[b] (:745-747): hap_ref_pos is hap.ml.hpos, the
+ *      haplotype's own alignment to the reference segment (ObservationModelSeqAn.hpp:170-233; >= 0 or a
+ *      DINDEL_HPOS_* code), laid out like hap_seq (hap_off).
+ *   3. the CIGAR state machine of :776-873, literally (soft clips either side of the first / last base with
+ *      npos >= 0; M / I / D runs; the reference's silent no-op cases stay no-ops).
+ * Results per read: read_hap (index inside the window), read_ref_pos (CIGAR::refPos = win_ref_start[w] + npos of
+ * the first aligned base, :798; -1 for a wholly clipped read, where the reference leaves it unset), read_n_ops
+ * (number of operations; the first min(n, cigar_cap) are stored; negative = the reference's throw:
+ * -1..-4 "Error(n)!", -5 "How is this possible? (1)"), ops[r * cigar_cap + k] = len << 4 | op (BAM encoding,
+ * what writeRealignedBAMFile stores at :695).  The reference's scan for the last aligned base (:779) runs off
+ * the front of the vector when no base is aligned; that case is the whole-read soft clip of :782-786 here.
+ * Needs a resident, computed batch with hpos rows (upload(want_hpos) or DINDEL_OUT_KEEP_HPOS). */
+#define DINDEL_CIGAR_PAIR 0
+#define DINDEL_CIGAR_BEST 1
+typedef struct dindel_cigar_in {
+    int32_t mode;                  /* DINDEL_CIGAR_* */
+    int32_t cigar_cap;             /* operations per read the ops rows hold (>= 1) */
+    const int32_t *win_h1, *win_h2;    /* [n_windows] PAIR mode only */
+    const int32_t *win_ref_start;  /* [n_windows] refSeqPos (= leftPos, DInDel.cpp:401) */
+    const int32_t *hap_n_indels;   /* [n_haps] PAIR mode only */
+    const int32_t *hap_ref_pos;    /* [hap_off[n_haps]] */
+} dindel_cigar_in;
+typedef struct dindel_cigar_out {
+    int32_t *read_hap;      /* [n_reads] */
+    int32_t *read_ref_pos;  /* [n_reads] */
+    int32_t *read_n_ops;    /* [n_reads] */
+    uint32_t *ops;          /* [n_reads * cigar_cap] */
+} dindel_cigar_out;
+int dindel_b200_cigars(dindel_ctx *ctx, const dindel_cigar_in *in, dindel_cigar_out *out);
 
 /* pinned host memory for the caller's buffers */
 void *dindel_b200_alloc_pinned(size_t bytes);

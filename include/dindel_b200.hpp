@@ -122,6 +122,17 @@ public:
                          const std::vector<std::vector<MLA> > &liks, std::vector<int> &filtered,
                          CovMap &varCoverage, bool doFilter, int maxMismatch);
 
+    // Drop-in for the per-read loops around DetInDel::getCIGAR of --outputRealignedBAM (DInDel.cpp:500-513 pooled:
+    // pass h1 < 0; :596-611 diploid: pass the MAP pair hpl.h1 / hpl.h2 of getMaxHap) on the window
+    // computeLikelihoods was last called with: the haplotype choice and getCIGAR (DInDel.cpp:728-882) run on the
+    // GPU over the resident ll / hpos rows (K5, dindel_b200_cigars); CigarT = DetInDel::CIGAR (a
+    // vector<pair<int,int> > of (BAM op, length) with an int refPos, DInDel.hpp:168-173).  Reads the pooled loop
+    // skips (!onHap[r]) get an empty CIGAR; refPos of a wholly clipped read (unset by the reference) is -1.
+    // The reference's throws ("Error(n)!", "How is this possible? (1)") are thrown as the same strings.
+    template <class HapT, class CigarT>
+    void realignedCigars(const std::vector<HapT> &haps, size_t nReads, int refSeqPos, int h1, int h2,
+                         std::vector<CigarT> &cigars);
+
 private:
     Engine(const Engine &);
     Engine &operator=(const Engine &);
@@ -561,6 +572,48 @@ int Engine::filterHaplotypes(const std::vector<HapT> &haps, const std::vector<Re
     for (typename std::map<PAV, int>::const_iterator k = keyOf.begin(); k != keyOf.end(); ++k)
         varCoverage[k->first] = Coverage(nf[k->second], nrv[k->second]);
     return numFiltered;
+}
+
+template <class HapT, class CigarT>
+void Engine::realignedCigars(const std::vector<HapT> &haps, size_t nReads, int refSeqPos, int h1, int h2,
+                             std::vector<CigarT> &cigars)
+{
+    const size_t nh = haps.size(), nr = nReads;
+    cigars.assign(nr, CigarT());
+    if (nh == 0 || nr == 0) return;
+    if (nh != last_nh_ || nr != last_nr_)
+        throw std::string("dindel_b200: realignedCigars called on a window other than the resident one");
+    std::vector<int32_t> refpos, nind(nh);
+    for (size_t h = 0; h < nh; h++) {
+        if (haps[h].ml.hpos.size() != haps[h].seq.size()) throw std::string("Haplotype has not been aligned!"); // DInDel.cpp:730
+        refpos.insert(refpos.end(), haps[h].ml.hpos.begin(), haps[h].ml.hpos.end());
+        nind[h] = haps[h].countIndels();
+    }
+    static const int32_t zero32 = 0;
+    const int cap = 32;
+    const int32_t wh1 = h1, wh2 = h2, wstart = refSeqPos;
+    dindel_cigar_in in;
+    in.mode = h1 < 0 ? DINDEL_CIGAR_BEST : DINDEL_CIGAR_PAIR; in.cigar_cap = cap;
+    in.win_h1 = &wh1; in.win_h2 = &wh2; in.win_ref_start = &wstart;
+    in.hap_n_indels = &nind[0]; in.hap_ref_pos = refpos.empty() ? &zero32 : &refpos[0];
+    std::vector<int32_t> rh(nr), rp(nr), rn(nr);
+    std::vector<uint32_t> ops(nr * (size_t)cap);
+    dindel_cigar_out out;
+    out.read_hap = &rh[0]; out.read_ref_pos = &rp[0]; out.read_n_ops = &rn[0]; out.ops = &ops[0];
+    int rc = dindel_b200_cigars(ctx_, &in, &out);
+    if (rc != DINDEL_OK)
+        throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx_) + ")";
+    for (size_t r = 0; r < nr; r++) {
+        if (rn[r] == -5) throw std::string("How is this possible? (1)");                 // DInDel.cpp:827
+        if (rn[r] < 0) { char msg[32]; snprintf(msg, sizeof msg, "Error(%d)!", -rn[r]); throw std::string(msg); }
+        if (rn[r] > cap) throw std::string("dindel_b200: realigned CIGAR with more than 32 operations");
+        CigarT &c = cigars[r];
+        for (int k = 0; k < rn[r]; k++) {
+            const uint32_t x = ops[r * cap + k];
+            c.push_back(typename CigarT::value_type((int)(x & 15u), (int)(x >> 4)));
+        }
+        c.refPos = rp[r];
+    }
 }
 
 } // namespace dindel_b200

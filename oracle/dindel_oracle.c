@@ -613,3 +613,84 @@ void ora_filter_haplotypes(int nh, int nr, const char *hap_seq, const int32_t *h
     }
     free(cov);
 }
+
+/* ---- realigned-BAM CIGARs (--outputRealignedBAM) --------------------------------------------
+ * ora_choose_hap: which haplotype a read is realigned to.
+ *   mode 0 (diploid, DInDel.cpp:597-606): the better of the MAP pair (h1, h2); |ll1-ll2| < 1e-8 -> h1 when it has
+ *           strictly fewer INS/DEL variants (Haplotype::countIndels, Haplotype.hpp:254-261), else h2.
+ *   mode 1 (pooled, DInDel.cpp:503-509): first strict arg-max of ll over all haplotypes, hidx = 0 to start with.
+ * ll[h] is the read's likelihood on haplotype h (liks[h][r].ll). */
+int ora_choose_hap(int mode, int nh, const double *ll, const int32_t *n_indels, int h1, int h2)
+{
+    if (mode == 0) {
+        if (fabs(ll[h1] - ll[h2]) < 1e-8) return n_indels[h1] < n_indels[h2] ? h1 : h2;
+        return ll[h1] > ll[h2] ? h1 : h2;
+    }
+    double llmax = -HUGE_VAL;
+    int hidx = 0;
+    for (int h = 0; h < nh; h++)
+        if (ll[h] > llmax) { llmax = ll[h]; hidx = h; }
+    return hidx;
+}
+
+/* ora_get_cigar: DetInDel::getCIGAR (DInDel.cpp:728-882).  hpos[R] = the read's MLAlignment::hpos on the chosen
+ * haplotype, hml[H] = that haplotype's own alignment to the reference segment (hap.ml.hpos,
+ * ObservationModelSeqAn.hpp:170-233: >= 0, or INS / LO / RO).  ops[] receives (op, len) pairs in BAM numbering
+ * (M 0, I 1, D 2, S 4), at most cap of them are stored; returns the number of operations, or -(n) for the
+ * reference's `throw string("Error(n)!")` (n = 1..4) and -5 for "How is this possible? (1)".  *refPos = CIGAR::refPos
+ * (left unset by the reference for a wholly clipped read: reported as -1 here).
+ * The reference's scan for the last aligned base (`while (npos[b]<0) b--`, :779) runs off the front of the vector
+ * when no base is aligned; that case is "lastbonh < 0" here. */
+int ora_get_cigar(int R, const int32_t *hpos, int H, const int32_t *hml, int refSeqStart, int32_t *refPos,
+                  int32_t *ops, int cap)
+{
+    enum { M = 0, I = 1, D = 2, S = 4, INS = -1 };
+    int n = 0;
+#define PUSH(op, len) do { if (n < cap) { ops[2 * n] = (op); ops[2 * n + 1] = (len); } n++; } while (0)
+#define NPOS(b) (hpos[b] >= 0 ? (hpos[b] < H ? hml[hpos[b]] : -5) : hpos[b])   /* :745-747 */
+    *refPos = -1;
+    int b = R - 1;
+    while (b >= 0 && NPOS(b) < 0) b--;
+    const int lastbonh = b;
+    if (lastbonh < 0) { PUSH(S, R); return n; }                                  /* :782-786 */
+    b = 0;
+    while (NPOS(b) < 0) b++;
+    if (b > 0) PUSH(S, b);
+    int prevponr = NPOS(b);
+    *refPos = refSeqStart + prevponr;
+    int curr = M, len = 1;
+    while (b < lastbonh) {                                                       /* :806-862 */
+        const int chp = NPOS(b), nhp = NPOS(b + 1);
+        if (nhp == INS) {
+            if (chp == INS) {
+                if (curr != I) return -1;
+                len++;
+            } else if (chp >= 0) {
+                if (curr != M) return -2;
+                PUSH(M, len);
+                len = 1; curr = I; prevponr = chp;
+            } else return -5;
+        } else if (chp >= 0 && nhp >= 0 && nhp - chp == 1) {
+            if (curr != M) return -3;
+            len++; prevponr = nhp;
+        } else if (chp >= 0 && nhp >= 0 && nhp - chp > 1) {
+            if (curr != M) return -4;
+            PUSH(M, len);
+            PUSH(D, nhp - chp - 1);
+            curr = M; len = 1; prevponr = nhp;
+        } else if (chp == INS && nhp - prevponr == 1) {
+            PUSH(I, len);
+            curr = M; len = 1; prevponr = nhp;
+        } else if (chp == INS && nhp - prevponr > 1) {
+            PUSH(I, len);
+            PUSH(D, nhp - prevponr - 1);
+            curr = M; len = 1; prevponr = nhp;
+        }
+        b++;
+    }
+    PUSH(curr, len);
+    if (R - 1 - lastbonh > 0) PUSH(S, R - 1 - lastbonh);
+#undef PUSH
+#undef NPOS
+    return n;
+}

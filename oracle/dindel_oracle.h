@@ -49,6 +49,9 @@ void ora_filter_haplotypes(int nh, int nr, const char *hap_seq, const int32_t *h
                            int ne, const int32_t *entry_hap, const int32_t *entry_key, const uint8_t *entry_type,
                            const int32_t *entry_left, const int32_t *entry_right, int nk, int maxMismatch,
                            int doFilter, uint8_t *filtered, uint8_t *uncovered, int32_t *key_nf, int32_t *key_nr);
+int ora_choose_hap(int mode, int nh, const double *ll, const int32_t *n_indels, int h1, int h2);
+int ora_get_cigar(int R, const int32_t *hpos, int H, const int32_t *hml, int refSeqStart, int32_t *refPos,
+                  int32_t *ops, int cap);
 double ora_addlogs(double a, double b);
 double ora_digamma(double x);
 

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """oracle/e2e/patch_dindel.py — TEST INFRASTRUCTURE ONLY.
 
-Applies INTEGRATION.md's three-line patch to the reference's driver at BUILD time:
+Applies INTEGRATION.md's four-line patch to the reference's driver at BUILD time:
     python oracle/e2e/patch_dindel.py /root/reference/DInDel.cpp oracle/_ref/DInDel_b200.cpp
 The output (git-ignored, under oracle/_ref/) is DInDel.cpp with (1) `#include "dindel_b200.hpp"` after
 its own includes and (2) the body of DetInDel::computeLikelihoods (DInDel.cpp:1707-1739) preceded by a
@@ -77,6 +77,21 @@ if not dump:
             "\t\treturn;\n"
             "\t}\n")
     text = text.replace(fsig, fsig + ffwd)
+    # fourth line of the patch: the per-read loops around DetInDel::getCIGAR (--outputRealignedBAM, DInDel.cpp:500-513
+    # pooled / :596-611 diploid) take the CIGARs K5 (dindel_b200_cigars) derived on the GPU from the resident ll / hpos
+    # rows; $DINDEL_B200_HOST_CIGAR keeps the reference's own loop (used to compare the two inside one binary)
+    decl = "\t\t\t\tvector < CIGAR > cigars(reads.size());\n"
+    assert text.count(decl) == 2
+    gcall = ("\t\t\t\tvector < CIGAR > gpuCigars; // dindel_b200 drop-in (INTEGRATION.md section 0)\n"
+             "\t\t\t\tif (dindel_b200_gpu && !getenv(\"DINDEL_B200_HOST_CIGAR\")) dindel_b200_gpu->realignedCigars(haps, reads.size(), refSeqPos, H1, H2, gpuCigars);\n")
+    i1 = text.index(decl)
+    text = text[:i1] + decl + gcall.replace("H1", "-1").replace("H2", "-1") + text[i1 + len(decl):]
+    i2 = text.index(decl, i1 + len(decl))
+    text = text[:i2] + decl + gcall.replace("H1", "hpl.h1").replace("H2", "hpl.h2") + text[i2 + len(decl):]
+    for hx in ("hidx", "hmax"):
+        call = "\t\t\t\t\t\tcigars[r]=getCIGAR(haps[%s], reads[r], liks[%s][r], refSeqPos);\n" % (hx, hx)
+        assert text.count(call) == 1
+        text = text.replace(call, "\t\t\t\t\t\tif (!gpuCigars.empty()) cigars[r]=gpuCigars[r]; else\n" + call)
 
 # --dump: oracle/_ref/dindel_ref_dump = the STOCK CPU driver whose filterHaplotypes (DInDel.cpp:1932-2100)
 # appends, at its end, its inputs and outputs as text to the file named by $DINDEL_B200_DUMP_COVER.  This is

@@ -137,6 +137,64 @@ def diff_lines(a_files, b_files, limit=5):
     return len(out), out[:limit]
 
 
+def bam_records(path):
+    """Alignment records of a BAM file (SAM/BAM spec 4.2): list of (core fields, cigar, rest-of-record bytes)."""
+    import gzip
+    import struct
+    d = gzip.open(path, "rb").read()          # BGZF = concatenated gzip members
+    assert d[:4] == b"BAM\1", path
+    l_text, = struct.unpack_from("<i", d, 4)
+    o = 8 + l_text
+    n_ref, = struct.unpack_from("<i", d, o)
+    o += 4
+    for _ in range(n_ref):
+        l_name, = struct.unpack_from("<i", d, o)
+        o += 4 + l_name + 4
+    recs = []
+    while o < len(d):
+        bs, = struct.unpack_from("<i", d, o)
+        ref_id, pos, l_name, mapq, bin_, n_cig, flag, l_seq, nref, npos, tlen = struct.unpack_from("<iiBBHHHiiii", d, o + 4)
+        q = o + 36
+        name = d[q:q + l_name]
+        cig = struct.unpack_from("<%dI" % n_cig, d, q + l_name)
+        rest = d[q + l_name + 4 * n_cig:o + 4 + bs]
+        recs.append({"name": name, "ref": ref_id, "pos": pos, "mapq": mapq, "flag": flag, "l_seq": l_seq, "nref": nref,
+                     "npos": npos, "tlen": tlen, "cigar": cig, "rest": rest})
+        o += 4 + bs
+    return recs
+
+
+def compare_realigned_bams(work, arm_a, arm_b, tag):
+    """The per-window realigned BAMs (<out>.ra.<index>_<tid>_<left>_<right>.bam, DInDel.cpp:517-519 / :615-619) of two
+    arms, record by record.  pos / isize of a wholly soft-clipped read are not compared: the reference never sets
+    CIGAR::refPos for it (DInDel.cpp:782-786), so its own value is whatever the stack held."""
+    import glob
+    fa = sorted(glob.glob(os.path.join(work, "%s%s.*.ra.*.bam" % (arm_a, tag))))
+    n_rec = n_bad = n_changed = 0
+    first = None
+    for f in fa:
+        g = os.path.join(work, arm_b + os.path.basename(f)[len(arm_a):])
+        if not os.path.exists(g):
+            n_bad += 1
+            first = first or "missing " + g
+            continue
+        ra, rb = bam_records(f), bam_records(g)
+        if len(ra) != len(rb):
+            n_bad += 1
+            first = first or "record count " + f
+            continue
+        for x, y in zip(ra, rb):
+            n_rec += 1
+            clipped = len(x["cigar"]) == 1 and x["cigar"][0] == (x["l_seq"] << 4 | 4)
+            keys = [k for k in x if not (clipped and k in ("pos", "tlen"))]
+            n_changed += any(c & 15 in (1, 2, 4) for c in x["cigar"])
+            if any(x[k] != y[k] for k in keys):
+                n_bad += 1
+                first = first or "%s %s: %s vs %s" % (os.path.basename(f), x["name"], {k: x[k] for k in keys if k != "rest"},
+                                                      {k: y[k] for k in keys if k != "rest"})
+    return {"files": len(fa), "records": n_rec, "records_with_indel_or_clip": n_changed, "mismatches": n_bad, "first": first}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--work", required=True)
@@ -152,6 +210,8 @@ def main():
                     "glf compared, no VCF (mergeOutputPooled.py is not restated)")
     ap.add_argument("--lib-file", action="store_true", help="pass --libFile <stage-1 libraries> to stage 3 (all arms): "
                     "insert-size prior + mate rescue of unmapped reads, as in the README pipeline")
+    ap.add_argument("--realigned-bam", action="store_true", help="pass --outputRealignedBAM to stage 3 (all arms) and "
+                    "compare the per-window realigned BAMs (the gpu arm's CIGARs come from K5, dindel_b200_cigars)")
     ap.add_argument("--heap-neutral", action="store_true", help="also compare with the allocator poisoning freed memory")
     a = ap.parse_args()
     arms = a.arms.split(",")
@@ -170,7 +230,8 @@ def main():
                 continue
             glfs, vcf, wall, n_calls = run_arm(arm, prep, a.work, procs if arm == "cpu" else a.gpu_procs,
                                                extra=(["--filterHaplotypes"] if a.filter_haplotypes else []) +
-                                               (["--libFile", prep["libraries"]] if a.lib_file else []), env=env, tag=tag,
+                                               (["--libFile", prep["libraries"]] if a.lib_file else []) +
+                                               (["--outputRealignedBAM"] if a.realigned_bam else []), env=env, tag=tag,
                                                mode="--doPooled" if a.pooled else "--doDiploid")
             ok, err = glf_stats(glfs)
             out[arm] = (glfs, vcf)
@@ -182,6 +243,9 @@ def main():
             n, first = diff_lines(out["cpu"][0], out["gpu"][0])
             r["glf_identical"], r["glf_diff_lines"], r["glf_diff_first"] = n == 0, n, first
             r["vcf_identical"] = open(out["cpu"][1], "rb").read() == open(out["gpu"][1], "rb").read()
+            if a.realigned_bam:
+                r["realigned_bam"] = compare_realigned_bams(a.work, "cpu", "gpu", tag)
+                verdict = verdict and r["realigned_bam"]["mismatches"] == 0 and r["realigned_bam"]["records"] > 0
         res["heap_neutral" if env else "default"] = r
     # the verdict: identical output with the stray read neutralised when asked for, else as run
     last = res.get("heap_neutral", res["default"])

@@ -182,3 +182,21 @@ class Oracle:
                                        vp(ohq), vp(ni), vp(st), ne, vp(eh), vp(ek), vp(et), vp(el), vp(er), int(nk),
                                        int(max_mismatch), int(do_filter), vp(filt), vp(unc), vp(nf), vp(nrv))
         return filt[:nh], unc[:nh], nf[:nk], nrv[:nk]
+
+    def choose_hap(self, mode, ll, n_indels, h1=-1, h2=-1):
+        """Haplotype a read is realigned to (DInDel.cpp:597-606 mode 0 / :503-509 mode 1)."""
+        ll = np.ascontiguousarray(ll, dtype=np.float64)
+        ni = np.ascontiguousarray(n_indels, dtype=np.int32)
+        return int(self.lib.ora_choose_hap(int(mode), len(ll), ll.ctypes.data_as(C.c_void_p), ni.ctypes.data_as(C.c_void_p),
+                                           int(h1), int(h2)))
+
+    def get_cigar(self, hpos, hml, ref_start, cap=64):
+        """DetInDel::getCIGAR (DInDel.cpp:728-882) -> (n_ops or -error, refPos, [(op, len), ...])."""
+        hpos = np.ascontiguousarray(hpos, dtype=np.int32)
+        hml = np.ascontiguousarray(hml, dtype=np.int32)
+        ops = np.zeros(2 * cap, dtype=np.int32)
+        ref_pos = C.c_int32(0)
+        n = int(self.lib.ora_get_cigar(len(hpos), hpos.ctypes.data_as(C.c_void_p), len(hml), hml.ctypes.data_as(C.c_void_p),
+                                       int(ref_start), C.byref(ref_pos), ops.ctypes.data_as(C.c_void_p), cap))
+        k = max(0, min(n, cap))
+        return n, int(ref_pos.value), [(int(ops[2 * i]), int(ops[2 * i + 1])) for i in range(k)]

@@ -16,10 +16,14 @@ struct MockAV { // Variant.hpp:78-175: the members this path touches
     MockAV(const std::string &s, int sh, int eh, int sr, int er) : str(s), startHap(sh), endHap(eh), startRead(sr), endRead(er) {}
     bool isCovered(int pad, int firstBase, int lastBase) const { return firstBase + pad <= startRead && lastBase - pad >= endRead; }
 };
-struct MockHap { // Haplotype.hpp:40-70
+struct MockHapML { std::vector<int> hpos; };
+struct MockHap { // Haplotype.hpp:40-70, countIndels :254-261, ml = its alignment to the reference segment
     std::string seq;
     std::map<int, MockAV> indels, snps;
+    MockHapML ml;
+    int countIndels() const { return (int)indels.size(); }
 };
+struct MockCigar : public std::vector<std::pair<int, int> > { int refPos; }; // DInDel.hpp:168-173
 struct MockRead {
     std::string seq;
     std::vector<uint8_t> phred;
@@ -124,6 +128,24 @@ int main()
         CHECK(m.snps.size() == 1 && m.snps.begin()->first == 50 && m.numMismatch == 1 && m.nmmBQT == 1);
         CHECK(m.snps.begin()->second.str[0] == ref[50] && m.snps.begin()->second.str.substr(1, 2) == "=>");
         CHECK(m.align[50] == snp[20]);
+    }
+    { // realigned-read CIGARs of the resident window (K5): diploid pair (0, 1), then the pooled choice
+        std::vector<MockCigar> cig;
+        std::string err;
+        try { eng->realignedCigars(haps, reads.size(), 7000, 0, 1, cig); } catch (std::string &s) { err = s; }
+        CHECK(err == "Haplotype has not been aligned!");
+        for (int b = 0; b < (int)haps[0].seq.size(); b++) haps[0].ml.hpos.push_back(b);
+        for (int b = 0; b < (int)haps[1].seq.size(); b++) haps[1].ml.hpos.push_back(b < 50 ? b : b + 3);
+        for (int pooled = 0; pooled < 2; pooled++) {
+            eng->realignedCigars(haps, reads.size(), 7000, pooled ? -1 : 0, pooled ? -1 : 1, cig);
+            CHECK(cig.size() == 4);
+            CHECK(cig[0].size() == 1 && cig[0][0] == std::make_pair(0, 60) && cig[0].refPos == 7010);
+            CHECK(cig[1].size() == 3 && cig[1][0] == std::make_pair(0, 30) && cig[1][1] == std::make_pair(2, 3) &&
+                  cig[1][2] == std::make_pair(0, 30) && cig[1].refPos == 7020);
+            CHECK(cig[2].size() == 3 && cig[2][0].first == 0 && cig[2][1] == std::make_pair(1, 2) && cig[2][2].first == 0 &&
+                  cig[2][0].second + cig[2][2].second == 60 && cig[2].refPos == 7015);
+            CHECK(cig[3].size() == 1 && cig[3][0] == std::make_pair(0, 50) && cig[3].refPos == 7030);
+        }
     }
     { // a haplotype shorter than maxLengthDel: "hapSize error." (ObservationModelFB.cpp:47)
         std::vector<MockHap> bad(2);

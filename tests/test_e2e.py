@@ -176,3 +176,22 @@ def test_glf_identical_pooled(tmp_path):
     res = json.loads(r.stdout.strip().splitlines()[-1])
     hn = res["heap_neutral"]
     assert hn["glf_identical"] and hn["cpu"]["windows_ok"] >= 15, res
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pooled", [False, True])
+def test_realigned_bams_identical(tmp_path, pooled):
+    """--outputRealignedBAM: the per-window realigned BAMs of the GPU-backed binary (CIGARs and positions from K5,
+    dindel_b200_cigars, the fourth patch line) equal the stock CPU binary's record by record, --doDiploid (haplotype
+    choice among the MAP pair, DInDel.cpp:597-606) and --doPooled (best haplotype, :503-509); glf identical too."""
+    if not run_e2e.have_binaries(("cpu", "gpu")):
+        pytest.skip("oracle/_ref binaries not built (reference sources absent at build time)")
+    r = subprocess.run([sys.executable, os.path.join(E2E, "run_e2e.py"), "--work", str(tmp_path), "--length", "40000",
+                        "--seed", "12", "--arms", "cpu,gpu", "--windows-per-file", "20", "--realigned-bam"] +
+                       (["--pooled"] if pooled else []), capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout + r.stderr
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    d = res["default"]
+    rb = d["realigned_bam"]
+    assert rb["mismatches"] == 0 and rb["files"] >= 10 and rb["records"] >= 1000 and rb["records_with_indel_or_clip"] >= 50, res
+    assert d["glf_identical"], res

@@ -113,3 +113,13 @@ def load_cover_golden():
                         keys=keys, nk=len(keys), maxMismatch=w["maxMismatch"], doFilter=w["doFilter"],
                         filtered=np.array(w["filtered"], dtype=np.uint8), cov={k: (a, b) for k, a, b in w["cov"]}))
     return out
+
+
+def load_cigar_golden():
+    """tests/golden/cigar_golden.json.gz (the reference's own getCIGAR call sites, make_cigar_golden.py): list of
+    per-read dicts mode ('D' diploid / 'B' pooled), h1, h2, nh, onHap, hmax, refStart, refPos, ll[nh], nInd[nh],
+    hpos[R], hml[H], cigar [op, len, op, len, ...]."""
+    import gzip
+    import json
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cigar_golden.json.gz")
+    return json.load(gzip.open(path, "rt"))
