@@ -360,6 +360,15 @@ def main():
         k2_ms = eng.last_call_ms                                    # wall time of the C call (H2D + kernel + D2H)
         infer = {"k2_pair_sums_ms": k2_ms, "k2_kernel_ms": eng.last_kernel_ms, "k2_windows_per_s": batch.n_windows / (k2_ms * 1e-3),
                  "k2_frac_of_k1_step": k2_ms / ms_per_step, "k2_checksum": float(sum(float(x.sum()) for x in sums[:1000]))}
+        if cov:   # K5 over the hpos rows the e2e step left resident: realigned-read CIGARs, diploid choice among (0, nh-1)
+            hml = (np.arange(len(batch.hap_seq), dtype=np.int64) - np.repeat(batch.hap_off[:-1], np.diff(batch.hap_off))).astype(np.int32)
+            k5a = (engine.CIGAR_PAIR, np.zeros(batch.n_windows, np.int32), hml, np.zeros(batch.n_windows, np.int32),
+                   (nh_w - 1).astype(np.int32), np.zeros(batch.n_haps, np.int32))
+            eng.cigars(*k5a, cigar_cap=16, n_reads=batch.n_reads)   # warm-up (buffers grow once)
+            _, _, k5n, _ = eng.cigars(*k5a, cigar_cap=16, n_reads=batch.n_reads)
+            infer.update({"k5_cigars_ms": eng.last_call_ms, "k5_kernel_ms": eng.last_kernel_ms,
+                          "k5_reads_per_s": batch.n_reads / (eng.last_call_ms * 1e-3), "k5_frac_of_k1_step": eng.last_call_ms / ms_per_step,
+                          "k5_ops_checksum": int(k5n.sum())})
         if args.cfg == 3:
             comp = [np.ones(int(n), dtype=np.uint8) for n in nh_w]
             eng.bayes_em(jw, comp)                                  # warm-up at full size

@@ -442,12 +442,13 @@ class Engine:
         return (filt[:nh_tot], unc[:nh_tot], [nf[wk[w]:wk[w + 1]] for w in range(nw)],
                 [nr[wk[w]:wk[w + 1]] for w in range(nw)])
 
-    def cigars(self, mode, win_ref_start, hap_ref_pos, win_h1=None, win_h2=None, hap_n_indels=None, cigar_cap=16):
+    def cigars(self, mode, win_ref_start, hap_ref_pos, win_h1=None, win_h2=None, hap_n_indels=None, cigar_cap=16,
+               n_reads=None):
         """K5 (the haplotype choice of DInDel.cpp:503-509 / :597-606 + DetInDel::getCIGAR, DInDel.cpp:728-882) over
         the resident batch.  hap_ref_pos: flat int32 laid out like hap_seq.  Returns (read_hap[n_reads],
         read_ref_pos[n_reads], read_n_ops[n_reads], ops[n_reads, cigar_cap]) with ops = len << 4 | op."""
         batch = self._resident[0] if getattr(self, "_resident", None) else None
-        nr = batch.n_reads if batch is not None else int(self._n_reads)
+        nr = int(n_reads) if n_reads is not None else (batch.n_reads if batch is not None else int(self._n_reads))
         i32 = lambda x: None if x is None else np.ascontiguousarray(x, dtype=np.int32)
         rs, rp, h1, h2, ni = i32(win_ref_start), i32(hap_ref_pos), i32(win_h1), i32(win_h2), i32(hap_n_indels)
         ptr = lambda x: None if x is None else x.ctypes.data

@@ -398,6 +398,13 @@ public:
                 std::vector<std::vector<MLA> > &liks, std::vector<int> &onHap) const;
     template <class CovMap>
     int filterResult(int w, std::vector<int> &filtered, CovMap &varCoverage) const;
+    // Realigned-read CIGARs of EVERY window of the flushed batch in one K5 call (see Engine::realignedCigars).
+    // allHaps[w] = the haplotypes window w was added with (their ml.hpos / countIndels() are read here: the
+    // haplotype-to-reference alignment is not part of add()); refSeqPos[w]; h1[w] / h2[w] = the MAP pair of window w
+    // (getMaxHap), h1[w] < 0 skips the window; pooled = the choice of DInDel.cpp:503-509 instead (h1 / h2 unused).
+    template <class CigarT>
+    void cigars(const std::vector<std::vector<HapT> > &allHaps, const std::vector<int> &refSeqPos, bool pooled,
+                const std::vector<int> &h1, const std::vector<int> &h2, std::vector<std::vector<CigarT> > &out) const;
 private:
     Engine &eng_;
     int maxMismatch_;
@@ -572,6 +579,60 @@ int Engine::filterHaplotypes(const std::vector<HapT> &haps, const std::vector<Re
     for (typename std::map<PAV, int>::const_iterator k = keyOf.begin(); k != keyOf.end(); ++k)
         varCoverage[k->first] = Coverage(nf[k->second], nrv[k->second]);
     return numFiltered;
+}
+
+template <class HapT, class ReadT>
+template <class CigarT>
+void WindowBatch<HapT, ReadT>::cigars(const std::vector<std::vector<HapT> > &allHaps, const std::vector<int> &refSeqPos,
+                                      bool pooled, const std::vector<int> &h1, const std::vector<int> &h2,
+                                      std::vector<std::vector<CigarT> > &out) const
+{
+    const size_t nw = size();
+    if (!flushed_) throw std::string("dindel_b200: cigars() before flush()");
+    if (allHaps.size() != nw || refSeqPos.size() != nw || (!pooled && (h1.size() != nw || h2.size() != nw)))
+        throw std::string("dindel_b200: cigars(): one entry per window expected");
+    out.assign(nw, std::vector<CigarT>());
+    const size_t nr = nw ? (size_t)win_read_.back() : 0;
+    if (nr == 0) return;
+    std::vector<int32_t> refpos, nind, wh1(nw, -1), wh2(nw, -1), wstart(nw);
+    for (size_t w = 0; w < nw; w++) {
+        if (allHaps[w].size() != (size_t)(win_hap_[w + 1] - win_hap_[w])) throw std::string("dindel_b200: cigars(): haplotypes of another window");
+        for (size_t h = 0; h < allHaps[w].size(); h++) {
+            const HapT &hp = allHaps[w][h];
+            if (hp.ml.hpos.size() != hp.seq.size()) throw std::string("Haplotype has not been aligned!"); // DInDel.cpp:730
+            refpos.insert(refpos.end(), hp.ml.hpos.begin(), hp.ml.hpos.end());
+            nind.push_back(hp.countIndels());
+        }
+        wstart[w] = refSeqPos[w];
+        if (!pooled) { wh1[w] = h1[w]; wh2[w] = h2[w]; }
+    }
+    static const int32_t zero32 = 0;
+    const int cap = 32;
+    dindel_cigar_in in;
+    in.mode = pooled ? DINDEL_CIGAR_BEST : DINDEL_CIGAR_PAIR; in.cigar_cap = cap;
+    in.win_h1 = &wh1[0]; in.win_h2 = &wh2[0]; in.win_ref_start = &wstart[0];
+    in.hap_n_indels = nind.empty() ? &zero32 : &nind[0]; in.hap_ref_pos = refpos.empty() ? &zero32 : &refpos[0];
+    std::vector<int32_t> rh(nr), rp(nr), rn(nr);
+    std::vector<uint32_t> ops(nr * (size_t)cap);
+    dindel_cigar_out co;
+    co.read_hap = &rh[0]; co.read_ref_pos = &rp[0]; co.read_n_ops = &rn[0]; co.ops = &ops[0];
+    int rc = dindel_b200_cigars(eng_.ctx(), &in, &co);
+    if (rc != DINDEL_OK)
+        throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(eng_.ctx()) + ")";
+    for (size_t w = 0; w < nw; w++) {
+        out[w].assign((size_t)(win_read_[w + 1] - win_read_[w]), CigarT());
+        for (size_t r = (size_t)win_read_[w]; r < (size_t)win_read_[w + 1]; r++) {
+            if (rn[r] == -5) throw std::string("How is this possible? (1)");
+            if (rn[r] < 0) { char msg[32]; snprintf(msg, sizeof msg, "Error(%d)!", -rn[r]); throw std::string(msg); }
+            if (rn[r] > cap) throw std::string("dindel_b200: realigned CIGAR with more than 32 operations");
+            CigarT &c = out[w][r - (size_t)win_read_[w]];
+            for (int k = 0; k < rn[r]; k++) {
+                const uint32_t x = ops[r * cap + k];
+                c.push_back(typename CigarT::value_type((int)(x & 15u), (int)(x >> 4)));
+            }
+            c.refPos = rp[r];
+        }
+    }
 }
 
 template <class HapT, class CigarT>

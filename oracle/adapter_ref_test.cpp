@@ -19,6 +19,14 @@
 #include <vector>
 #include "ObservationModelFB.hpp" /* the reference's: pulls Haplotype.hpp, Read.hpp, MLAlignment.hpp, bam.h */
 #include "dindel_b200.hpp"
+extern "C" {
+#include "dindel_oracle.h" /* ora_choose_hap / ora_get_cigar: the restatement pinned on the reference's golden CIGARs */
+}
+struct RefCigar : public std::vector<std::pair<int, int> > { int refPos; }; /* DetInDel::CIGAR, DInDel.hpp:168-173 */
+static bool same_cigar(const RefCigar &a, const RefCigar &b)
+{
+    return (const std::vector<std::pair<int, int> > &)a == (const std::vector<std::pair<int, int> > &)b && a.refPos == b.refPos;
+}
 
 static uint64_t rng_state = 0x9E3779B97F4A7C15ULL;
 static uint32_t rnd()
@@ -143,12 +151,16 @@ int main(int argc, char **argv)
     std::vector<std::vector<std::vector<MLAlignment> > > allLiks;
     std::vector<std::vector<int> > allOn, allFiltered;
     std::vector<CovMap> allCov;
+    std::vector<std::vector<RefCigar> > allCigD, allCigP;
+    std::vector<int> allH1, allH2, allRefPos;
+    long n_cig = 0, n_cig_ops = 0;
     for (int w = 0; w < n_windows; w++) {
         const uint32_t leftPos = 100000u + 1000u * (uint32_t)w;
         const int H = rndint(100, 130), nh = rndint(2, 6), nr = rndint(8, 30);
         const std::string ref = rndseq(H);
         std::vector<Haplotype> haps(nh);
         haps[0].seq = ref;
+        for (int b = 0; b < H; b++) haps[0].ml.hpos.push_back(b);
         for (int h = 1; h < nh; h++) {
             std::string s = ref;
             const int p = rndint(H / 3, 2 * H / 3), len = rndint(1, 5);
@@ -156,6 +168,10 @@ int main(int argc, char **argv)
             if (rnd() & 1) { var = std::string("-") + s.substr(p, len); s.erase(p, len); }
             else { std::string ins = rndseq(len); var = std::string("+") + ins; s.insert(p, ins); }
             haps[h].seq = s;
+            /* what alignHaplotypes leaves in hap.ml.hpos (ObservationModelSeqAn.hpp:170-233): the haplotype's own
+             * alignment to the reference segment, known here by construction */
+            for (int b = 0; b < (int)s.size(); b++)
+                haps[h].ml.hpos.push_back(var[0] == '-' ? (b < p ? b : b + len) : (b < p ? b : (b < p + len ? MLAlignment::INS : b - len)));
             /* what alignHaplotypes leaves in hap.indels / hap.snps (DInDel.cpp:1477-1482): variants with
              * their position on this haplotype; only isCovered() reads them on this path */
             haps[h].indels[p] = AlignedVariant(var, p, p + len - 1, p, p + (var[0] == '-' ? 0 : len - 1));
@@ -230,6 +246,29 @@ int main(int argc, char **argv)
         std::vector<int> filtered;
         CovMap cov;
         gpu->filterHaplotypes(haps, reads, liks, filtered, cov, true, op.maxMismatch);
+        /* realigned-read CIGARs of the resident window (K5) against the restatement run on the REFERENCE's liks */
+        std::vector<RefCigar> cigD, cigP;
+        const int ch1 = (int)(rnd() % nh), ch2 = (int)(rnd() % nh);
+        gpu->realignedCigars(haps, reads.size(), (int)leftPos, ch1, ch2, cigD);
+        gpu->realignedCigars(haps, reads.size(), (int)leftPos, -1, -1, cigP);
+        for (int mode = 0; mode < 2; mode++)
+            for (size_t r = 0; r < reads.size(); r++) {
+                const RefCigar &got = mode ? cigP[r] : cigD[r];
+                if (mode && !onHap[r]) { if (!got.empty()) { fprintf(stderr, "MISMATCH window %d read %d: CIGAR for a read off all haplotypes\n", w, (int)r); return 1; } continue; }
+                std::vector<double> ll(nh);
+                std::vector<int32_t> ni(nh);
+                for (int h = 0; h < nh; h++) { ll[h] = liks[h][r].ll; ni[h] = haps[h].countIndels(); }
+                const int hx = ora_choose_hap(mode, nh, &ll[0], &ni[0], ch1, ch2);
+                std::vector<int32_t> hp(liks[hx][r].hpos.begin(), liks[hx][r].hpos.end()), hm(haps[hx].ml.hpos.begin(), haps[hx].ml.hpos.end());
+                int32_t refPos = 0, ops[64];
+                const int n = ora_get_cigar((int)hp.size(), &hp[0], (int)hm.size(), &hm[0], (int)leftPos, &refPos, ops, 32);
+                RefCigar want;
+                for (int k = 0; k < n; k++) want.push_back(std::make_pair((int)ops[2 * k], (int)ops[2 * k + 1]));
+                want.refPos = refPos;
+                if (n < 1 || !same_cigar(got, want)) { fprintf(stderr, "MISMATCH window %d read %d mode %d: CIGAR (%d ops vs %d, refPos %d vs %d)\n", w, (int)r, mode, (int)got.size(), n, got.refPos, refPos); return 1; }
+                n_cig++; n_cig_ops += n;
+            }
+        allCigD.push_back(cigD); allCigP.push_back(cigP); allH1.push_back(ch1); allH2.push_back(ch2); allRefPos.push_back((int)leftPos);
         allHaps.push_back(haps); allReads.push_back(reads); allLeft.push_back(leftPos);
         allLiks.push_back(liks); allOn.push_back(onHap); allFiltered.push_back(filtered); allCov.push_back(cov);
     }
@@ -240,6 +279,14 @@ int main(int argc, char **argv)
         for (int w = 0; w < n_windows; w++)
             if (wb.add(allHaps[w], allReads[w], allLeft[w]) != w) { fprintf(stderr, "MISMATCH batch: window index\n"); return 1; }
         wb.flush();
+        { /* every window's CIGARs in one K5 call == the window-at-a-time calls (also when the hpos rows never left the GPU) */
+            std::vector<std::vector<RefCigar> > bD, bP;
+            wb.cigars(allHaps, allRefPos, false, allH1, allH2, bD);
+            wb.cigars(allHaps, allRefPos, true, allH1, allH2, bP);
+            for (int w = 0; w < n_windows; w++)
+                for (size_t r = 0; r < allReads[w].size(); r++)
+                    if (!same_cigar(bD[w][r], allCigD[w][r]) || !same_cigar(bP[w][r], allCigP[w][r])) { fprintf(stderr, "MISMATCH batch (full %d) window %d read %d: CIGAR\n", full, w, (int)r); return 1; }
+        }
         for (int w = 0; w < n_windows; w++) {
             std::vector<std::vector<MLAlignment> > liks;
             std::vector<int> onHap, filtered;
@@ -282,7 +329,8 @@ int main(int argc, char **argv)
     }
     delete gpu;
     printf("adapter_ref_test ok: %ld pairs identical to the reference class (%ld indel events, %ld snps, %ld covered hap indels); "
-           "batched submit == window-at-a-time (%ld filtered haplotypes, %ld covering reads)\n",
-           n_pairs, n_ind, n_snp, n_cov, n_filt, n_covreads);
+           "batched submit == window-at-a-time (%ld filtered haplotypes, %ld covering reads); %ld realigned-read CIGARs (%ld operations) "
+           "identical to getCIGAR's restatement on the reference's alignments, batched == window-at-a-time\n",
+           n_pairs, n_ind, n_snp, n_cov, n_filt, n_covreads, n_cig, n_cig_ops);
     return 0;
 }
