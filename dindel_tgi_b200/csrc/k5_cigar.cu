@@ -2,12 +2,14 @@
 //
 // Replaces, per read, the haplotype choice at the two call sites of DetInDel::getCIGAR (DInDel.cpp:503-509 pooled,
 // :597-606 diploid) and getCIGAR itself (DInDel.cpp:728-882).  One warp works on 32 consecutive reads:
-//   stage   for each of its reads in turn the 32 lanes pick the haplotype (two ll loads, or a strict first-arg-max
-//           scan over the window's ll row), stream that pair's hpos row out of HBM (coalesced int16 loads), map every
-//           base through the haplotype's own reference alignment hap_ref_pos (npos[b], :745-747; the gather hits L1 /
-//           L2, a haplotype's row is shared by all reads of the window) and park npos in the warp's shared-memory
-//           tile; one ballot pass finds the first and the last base with npos >= 0 (:778-796);
-//   walk    lane i then runs the reference's sequential CIGAR state machine (:806-862) on read i out of shared memory
+//   choose  lane i resolves read i: its window, its row of pair records and the haplotype (two ll loads, or a strict
+//           first-arg-max scan over the row): the 32 chains of dependent loads run side by side;
+//   stage   for each of the 32 reads in turn the warp streams the chosen pair's hpos row out of HBM (coalesced int16
+//           loads, the next read's row in flight meanwhile), maps every base through the haplotype's own reference
+//           alignment hap_ref_pos (npos[b], :745-747; the gather hits L1 / L2, a haplotype's row is shared by all reads
+//           of the window) and parks npos in the warp's shared-memory tile;
+//   walk    lane i finds the first and the last base with npos >= 0 (:778-796) and runs the reference's sequential
+//           CIGAR state machine (:806-862) on read i out of shared memory
 //           (row pitch = an odd number of 32-bit words: the 32 lanes hit 32 different banks), writing BAM-encoded operations.
 // Integer / byte work, HBM-bound on the hpos rows of the chosen pairs (2R bytes per read in, 4 * (3 + cap) out);
 // no floating point beyond the ll comparison, no tensor cores.
@@ -30,6 +32,16 @@ __device__ __forceinline__ int k5_find_window(const int32_t *win_read, int nw, i
     return lo;
 }
 
+// first 128 bases of a read's hpos row: 4 independent coalesced int16 loads per lane (-5 = past the read / no row)
+__device__ __forceinline__ void k5_load_row(const int16_t *hp, int R, int lane, int x[4])
+{
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int b = 32 * k + lane;
+        x[k] = (hp && b < R) ? (int)hp[b] : -5;
+    }
+}
+
 __global__ void __launch_bounds__(K5_WARPS * 32) k5_cigar_kernel(K5Args a)
 {
     extern __shared__ int32_t k5_sm[];
@@ -38,17 +50,19 @@ __global__ void __launch_bounds__(K5_WARPS * 32) k5_cigar_kernel(K5Args a)
     const int ngroups = (a.n_reads + 31) >> 5;
     for (int g = blockIdx.x * K5_WARPS + warp; g < ngroups; g += gridDim.x * K5_WARPS) {
         const int r_base = g << 5;
-        // per-lane state of "its" read (lane i <-> read r_base + i), filled while that read is staged
-        int my_R = 0, my_first = 0, my_last = -1, my_hap = -1, my_ref0 = 0, my_skip = 1;
-        int w = k5_find_window(a.win_read, a.n_windows, r_base);
-        for (int i = 0; i < 32; i++) {
-            const int r = r_base + i;
-            if (r >= a.n_reads) break;
+        const int r = r_base + lane;
+        // ---- choose: lane i resolves read r_base + i (window, pair row, haplotype): 32 dependent-load chains at once ----
+        int my_R = 0, my_hap = -1, my_ref0 = 0, my_H = 0;
+        const int16_t *my_hp = nullptr;
+        const int32_t *my_ref = nullptr;
+        int w = k5_find_window(a.win_read, a.n_windows, r_base);   // same address in every lane: one search per warp
+        if (r < a.n_reads) {
             while (r >= a.win_read[w + 1]) w++;
             const int h0 = a.win_hap[w], nh = a.win_hap[w + 1] - h0;
-            const int R = (int)(a.read_off[r + 1] - a.read_off[r]);
-            const dindel_pair_out *row = a.pairs + a.win_pair[w] + (long long)(r - a.win_read[w]) * nh;
-            // ---- which haplotype (warp-uniform) ----
+            my_R = (int)(a.read_off[r + 1] - a.read_off[r]);
+            my_ref0 = a.win_ref_start[w];
+            const long long p0 = a.win_pair[w] + (long long)(r - a.win_read[w]) * nh;
+            const dindel_pair_out *row = a.pairs + p0;
             int hx = -1;
             if (a.mode == DINDEL_CIGAR_PAIR) {
                 const int h1 = a.win_h1[w], h2 = a.win_h2[w];
@@ -58,51 +72,64 @@ __global__ void __launch_bounds__(K5_WARPS * 32) k5_cigar_kernel(K5Args a)
                     else hx = l1 > l2 ? h1 : h2;                                                                  // :601-605
                 }
             } else if (a.on_hap[r]) {                                                                             // :502
-                // first strict maximum (:505-508): largest value, lowest index among equals; NaN never wins
-                double best = -HUGE_VAL; int bh = 0;
-                for (int hb = 0; hb < nh; hb += 32) {
-                    const int h = hb + lane;
-                    double v = h < nh ? row[h].ll : -HUGE_VAL;
-                    int vh = h < nh ? h : 0x7fffffff;
-                    if (!(v > -HUGE_VAL)) { v = -HUGE_VAL; vh = 0x7fffffff; }
-                    for (int o = 16; o; o >>= 1) {
-                        const double ov = __shfl_xor_sync(FULLMASK, v, o);
-                        const int oh = __shfl_xor_sync(FULLMASK, vh, o);
-                        if (ov > v || (ov == v && oh < vh)) { v = ov; vh = oh; }
-                    }
-                    if (v > best) { best = v; bh = vh; }
+                double best = -HUGE_VAL;                                                                          // :503-508
+                hx = 0;
+                for (int h = 0; h < nh; h++) {
+                    const double v = row[h].ll;
+                    if (v > best) { best = v; hx = h; }
                 }
-                hx = bh;
+                if (nh <= 0) hx = -1;
             }
-            // ---- stage npos of (r, hx) ----
-            int first = R, last = -1;
             if (hx >= 0) {
-                const int16_t *hp = a.hpos + (size_t)(a.win_pair[w] + (long long)(r - a.win_read[w]) * nh + hx) * a.hpos_stride;
                 const long long ho = a.hap_off[h0 + hx];
-                const int H = (int)(a.hap_off[h0 + hx + 1] - ho);
-                const int32_t *ref = a.hap_ref_pos + ho;
-                for (int b0 = 0; b0 < R; b0 += 32) {
-                    const int b = b0 + lane;
-                    int np = -5;
-                    if (b < R) {
-                        const int x = hp[b];
-                        np = x >= 0 ? (x < H ? ref[x] : -5) : x;
-                        tile[i * a.pitch + b] = np;
-                    }
-                    const unsigned on = __ballot_sync(FULLMASK, b < R && np >= 0);
-                    if (on) {
-                        if (first == R) first = b0 + __ffs(on) - 1;
-                        last = b0 + 31 - __clz(on);
-                    }
-                }
+                my_H = (int)(a.hap_off[h0 + hx + 1] - ho);
+                my_ref = a.hap_ref_pos + ho;
+                my_hp = a.hpos + (size_t)(p0 + hx) * a.hpos_stride;
+                my_hap = hx;
             }
-            if (lane == i) {
-                my_R = R; my_first = first; my_last = last; my_hap = hx; my_skip = hx < 0; my_ref0 = a.win_ref_start[w];
+        }
+        // ---- stage: the warp streams read i's hpos row (coalesced), maps it through the haplotype's reference alignment
+        //      (npos[b], :745-747) and parks it in row i of its tile; read i + 1's row is in flight while read i is mapped ----
+        int xn[4];
+        {
+            const int16_t *hp0 = (const int16_t *)__shfl_sync(FULLMASK, (unsigned long long)my_hp, 0);
+            k5_load_row(hp0, __shfl_sync(FULLMASK, my_R, 0), lane, xn);
+        }
+        for (int i = 0; i < 32; i++) {
+            const int16_t *hp = (const int16_t *)__shfl_sync(FULLMASK, (unsigned long long)my_hp, i);
+            const int32_t *ref = (const int32_t *)__shfl_sync(FULLMASK, (unsigned long long)my_ref, i);
+            const int R = __shfl_sync(FULLMASK, my_R, i), H = __shfl_sync(FULLMASK, my_H, i);
+            int x[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) x[k] = xn[k];
+            if (i < 31) {
+                const int16_t *hpn = (const int16_t *)__shfl_sync(FULLMASK, (unsigned long long)my_hp, i + 1);
+                k5_load_row(hpn, __shfl_sync(FULLMASK, my_R, i + 1), lane, xn);
+            }
+            if (!hp) continue;                                   // warp-uniform: skipped read / past the batch
+            int32_t *trow = tile + i * a.pitch;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int b = 32 * k + lane;
+                if (b < R) trow[b] = x[k] >= 0 ? (x[k] < H ? ref[x[k]] : -5) : x[k];
+            }
+            for (int b = 128 + lane; b < R; b += 32) {           // reads longer than 128 bases
+                const int xb = hp[b];
+                trow[b] = xb >= 0 ? (xb < H ? ref[xb] : -5) : xb;
             }
         }
         __syncwarp();
+        // first / last base on the haplotype and on the reference (:778-796), by the lane that owns the read
+        const int my_skip = my_hap < 0;
+        int my_first = my_R, my_last = -1;
+        if (!my_skip) {
+            const int32_t *np = tile + lane * a.pitch;
+            int b = my_R - 1;
+            while (b >= 0 && np[b] < 0) b--;
+            my_last = b;
+            if (b >= 0) { b = 0; while (np[b] < 0) b++; my_first = b; }
+        }
         // ---- walk: lane i owns read r_base + i ----
-        const int r = r_base + lane;
         if (r < a.n_reads) {
             int n = 0, ref_pos = -1;
             uint32_t *ops = a.ops + (size_t)r * a.cap;
