@@ -68,6 +68,32 @@ struct ReadTraits {
 #endif
 };
 
+namespace detail {
+// dindel_b200_cigars with 6 operation slots per read (36 bytes per read back over PCIe; nearly every realigned read is
+// M, S M, M S, M I M or M D M), run again with the exact capacity in the rare batch where a read needs more.
+inline int run_cigars(dindel_ctx *ctx, dindel_cigar_in &in, size_t nr, std::vector<int32_t> &rh, std::vector<int32_t> &rp,
+                      std::vector<int32_t> &rn, std::vector<uint32_t> &ops)
+{
+    int cap = 6;
+    if (getenv("DINDEL_B200_CIGAR_CAP") && atoi(getenv("DINDEL_B200_CIGAR_CAP")) > 0) cap = atoi(getenv("DINDEL_B200_CIGAR_CAP")); // tests: force the second pass
+    rh.resize(nr); rp.resize(nr); rn.resize(nr);
+    for (int pass = 0; pass < 2; pass++) {
+        ops.assign(nr * (size_t)cap, 0u);
+        in.cigar_cap = cap;
+        dindel_cigar_out out;
+        out.read_hap = &rh[0]; out.read_ref_pos = &rp[0]; out.read_n_ops = &rn[0]; out.ops = &ops[0];
+        int rc = dindel_b200_cigars(ctx, &in, &out);
+        if (rc != DINDEL_OK)
+            throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx) + ")";
+        int need = 0;
+        for (size_t r = 0; r < nr; r++) if (rn[r] > need) need = rn[r];
+        if (need <= cap) break;
+        cap = need;
+    }
+    return cap;
+}
+} // namespace detail
+
 // RAII owner of one dindel_ctx (one device).  Construct from anything with the fields of
 // ObservationModelParameters (ObservationModel.hpp:28-99) that the path reads.
 class Engine {
@@ -607,25 +633,19 @@ void WindowBatch<HapT, ReadT>::cigars(const std::vector<std::vector<HapT> > &all
         if (!pooled) { wh1[w] = h1[w]; wh2[w] = h2[w]; }
     }
     static const int32_t zero32 = 0;
-    const int cap = 32;
     dindel_cigar_in in;
-    in.mode = pooled ? DINDEL_CIGAR_BEST : DINDEL_CIGAR_PAIR; in.cigar_cap = cap;
+    in.mode = pooled ? DINDEL_CIGAR_BEST : DINDEL_CIGAR_PAIR;
     in.win_h1 = &wh1[0]; in.win_h2 = &wh2[0]; in.win_ref_start = &wstart[0];
     in.hap_n_indels = nind.empty() ? &zero32 : &nind[0]; in.hap_ref_pos = refpos.empty() ? &zero32 : &refpos[0];
-    std::vector<int32_t> rh(nr), rp(nr), rn(nr);
-    std::vector<uint32_t> ops(nr * (size_t)cap);
-    dindel_cigar_out co;
-    co.read_hap = &rh[0]; co.read_ref_pos = &rp[0]; co.read_n_ops = &rn[0]; co.ops = &ops[0];
-    int rc = dindel_b200_cigars(eng_.ctx(), &in, &co);
-    if (rc != DINDEL_OK)
-        throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(eng_.ctx()) + ")";
+    std::vector<int32_t> rh, rp, rn;
+    std::vector<uint32_t> ops;
+    const int cap = detail::run_cigars(eng_.ctx(), in, nr, rh, rp, rn, ops);
     for (size_t w = 0; w < nw; w++) {
         out[w].assign((size_t)(win_read_[w + 1] - win_read_[w]), CigarT());
         for (size_t r = (size_t)win_read_[w]; r < (size_t)win_read_[w + 1]; r++) {
             if (rn[r] == -5) throw std::string("How is this possible? (1)");
             if (rn[r] < 0) { char msg[32]; snprintf(msg, sizeof msg, "Error(%d)!", -rn[r]); throw std::string(msg); }
-            if (rn[r] > cap) throw std::string("dindel_b200: realigned CIGAR with more than 32 operations");
-            CigarT &c = out[w][r - (size_t)win_read_[w]];
+                CigarT &c = out[w][r - (size_t)win_read_[w]];
             for (int k = 0; k < rn[r]; k++) {
                 const uint32_t x = ops[r * cap + k];
                 c.push_back(typename CigarT::value_type((int)(x & 15u), (int)(x >> 4)));
@@ -651,23 +671,17 @@ void Engine::realignedCigars(const std::vector<HapT> &haps, size_t nReads, int r
         nind[h] = haps[h].countIndels();
     }
     static const int32_t zero32 = 0;
-    const int cap = 32;
     const int32_t wh1 = h1, wh2 = h2, wstart = refSeqPos;
     dindel_cigar_in in;
-    in.mode = h1 < 0 ? DINDEL_CIGAR_BEST : DINDEL_CIGAR_PAIR; in.cigar_cap = cap;
+    in.mode = h1 < 0 ? DINDEL_CIGAR_BEST : DINDEL_CIGAR_PAIR;
     in.win_h1 = &wh1; in.win_h2 = &wh2; in.win_ref_start = &wstart;
     in.hap_n_indels = &nind[0]; in.hap_ref_pos = refpos.empty() ? &zero32 : &refpos[0];
-    std::vector<int32_t> rh(nr), rp(nr), rn(nr);
-    std::vector<uint32_t> ops(nr * (size_t)cap);
-    dindel_cigar_out out;
-    out.read_hap = &rh[0]; out.read_ref_pos = &rp[0]; out.read_n_ops = &rn[0]; out.ops = &ops[0];
-    int rc = dindel_b200_cigars(ctx_, &in, &out);
-    if (rc != DINDEL_OK)
-        throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx_) + ")";
+    std::vector<int32_t> rh, rp, rn;
+    std::vector<uint32_t> ops;
+    const int cap = detail::run_cigars(ctx_, in, nr, rh, rp, rn, ops);
     for (size_t r = 0; r < nr; r++) {
         if (rn[r] == -5) throw std::string("How is this possible? (1)");                 // DInDel.cpp:827
         if (rn[r] < 0) { char msg[32]; snprintf(msg, sizeof msg, "Error(%d)!", -rn[r]); throw std::string(msg); }
-        if (rn[r] > cap) throw std::string("dindel_b200: realigned CIGAR with more than 32 operations");
         CigarT &c = cigars[r];
         for (int k = 0; k < rn[r]; k++) {
             const uint32_t x = ops[r * cap + k];

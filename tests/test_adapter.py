@@ -44,6 +44,9 @@ def test_adapter_mock_types_on_gpu(tmp_path):
     exe = _build(tmp_path, "gnu++98")
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "adapter_mock_test ok" in r.stdout, r.stdout + r.stderr
+    # one operation slot per read to start with: every CIGAR longer than that goes through the adapter's second pass
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300, env=dict(os.environ, DINDEL_B200_CIGAR_CAP="1"))
+    assert r.returncode == 0 and "adapter_mock_test ok" in r.stdout, r.stdout + r.stderr
 
 
 @pytest.mark.gpu
@@ -51,4 +54,6 @@ def test_adapter_with_reference_types_matches_reference_class():
     if not os.path.exists(REF_TEST):
         pytest.skip("oracle/_ref/adapter_ref_test not built (reference sources absent at build time)")
     r = subprocess.run([REF_TEST, "40"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "adapter_ref_test ok" in r.stdout, r.stdout + r.stderr
+    r = subprocess.run([REF_TEST, "12"], capture_output=True, text=True, timeout=600, env=dict(os.environ, DINDEL_B200_CIGAR_CAP="2"))
     assert r.returncode == 0 and "adapter_ref_test ok" in r.stdout, r.stdout + r.stderr

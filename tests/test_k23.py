@@ -119,3 +119,16 @@ def test_gpu_bayes_em(port_oracle):
         assert np.allclose(pi[j], wpi, rtol=RTOL, atol=0)
         assert np.allclose(fr[j], wfr, rtol=1e-8, atol=1e-300)
     e.close()
+
+
+def test_oracle_digamma_against_cephes(port_oracle):
+    """boost::math::digamma (DInDel.cpp:2466, 2472) is third party and absent here, so `ora_digamma` cannot be pinned
+    against it; it is cross-checked against an independent published implementation instead (Cephes psi through
+    scipy.special.digamma) over the arguments the EM can produce (a0 = 0.001 up to nk + a0 for 10^5 reads): absolute
+    error below 1e-14 * max(1, |psi|), i.e. the two agree to the last digits everywhere, the root at 1.4616 included."""
+    from scipy.special import digamma
+    xs = np.concatenate([np.logspace(-3, 5, 4000), np.arange(1, 2000) + 0.001, [1.4616321449683623, 0.001, 1.0, 2.0]])
+    got = np.array([port_oracle.digamma(float(x)) for x in xs])
+    want = digamma(xs)
+    assert (np.abs(got - want) <= 1e-14 * np.maximum(1.0, np.abs(want))).all()
+    assert abs(port_oracle.digamma(1.0) + 0.5772156649015329) < 1e-15      # -gamma
