@@ -443,17 +443,24 @@ class Engine:
                 [nr[wk[w]:wk[w + 1]] for w in range(nw)])
 
     def cigars(self, mode, win_ref_start, hap_ref_pos, win_h1=None, win_h2=None, hap_n_indels=None, cigar_cap=16,
-               n_reads=None):
+               n_reads=None, out=None):
         """K5 (the haplotype choice of DInDel.cpp:503-509 / :597-606 + DetInDel::getCIGAR, DInDel.cpp:728-882) over
         the resident batch.  hap_ref_pos: flat int32 laid out like hap_seq.  Returns (read_hap[n_reads],
-        read_ref_pos[n_reads], read_n_ops[n_reads], ops[n_reads, cigar_cap]) with ops = len << 4 | op."""
+        read_ref_pos[n_reads], read_n_ops[n_reads], ops[n_reads, cigar_cap]) with ops = len << 4 | op.
+        out: optional caller-owned (read_hap, read_ref_pos, read_n_ops, ops) arrays of those shapes (e.g. pinned)."""
         batch = self._resident[0] if getattr(self, "_resident", None) else None
         nr = int(n_reads) if n_reads is not None else (batch.n_reads if batch is not None else int(self._n_reads))
         i32 = lambda x: None if x is None else np.ascontiguousarray(x, dtype=np.int32)
         rs, rp, h1, h2, ni = i32(win_ref_start), i32(hap_ref_pos), i32(win_h1), i32(win_h2), i32(hap_n_indels)
         ptr = lambda x: None if x is None else x.ctypes.data
-        rh, rr, rn = (np.zeros(max(nr, 1), dtype=np.int32) for _ in range(3))
-        ops = np.zeros((max(nr, 1), int(cigar_cap)), dtype=np.uint32)
+        if out is not None:
+            rh, rr, rn, ops = out
+            if any(x.dtype != np.int32 or x.size < max(nr, 1) or not x.flags.c_contiguous for x in (rh, rr, rn)) \
+                    or ops.dtype != np.uint32 or ops.size < max(nr, 1) * int(cigar_cap) or not ops.flags.c_contiguous:
+                raise ValueError("cigars: out arrays must be contiguous int32[n_reads] x3 and uint32[n_reads, cigar_cap]")
+        else:
+            rh, rr, rn = (np.zeros(max(nr, 1), dtype=np.int32) for _ in range(3))
+            ops = np.zeros((max(nr, 1), int(cigar_cap)), dtype=np.uint32)
         a, o = _CigarIn(), _CigarOut()
         a.mode, a.cigar_cap = int(mode), int(cigar_cap)
         a.win_h1, a.win_h2, a.win_ref_start, a.hap_n_indels, a.hap_ref_pos = ptr(h1), ptr(h2), ptr(rs), ptr(ni), ptr(rp)
