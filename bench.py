@@ -172,7 +172,7 @@ def run_reference(args, rank, world):
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_name(args):
@@ -195,8 +195,30 @@ def pinned_copy(lib, arr):
     return out
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """stdout carries the ONE JSON line and nothing else: everything any library writes to fd 1 from here on
+    (NCCL's version banner under torchrun, for one) goes to stderr; emit() writes to the original stdout."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
     args = parse()
+    claim_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -367,6 +389,7 @@ def main():
             # called the way the adapter calls it (include/dindel_b200.hpp): 6 operation slots per read in pinned
             # buffers, one exact-capacity second pass only if some read needs more
             cap = 6
+            k5a = (k5a[0],) + tuple(pinned_copy(lib, x) for x in k5a[1:])
             k5o = [pinned_copy(lib, np.zeros(batch.n_reads, np.int32)) for _ in range(3)] + \
                   [pinned_copy(lib, np.zeros((batch.n_reads, cap), np.uint32))]
             eng.cigars(*k5a, cigar_cap=cap, n_reads=batch.n_reads, out=k5o)   # warm-up (buffers grow once)
@@ -427,7 +450,7 @@ def main():
                                     "sample": "first %d windows of the workload (%d pairs, %.1f s wall, one process per core)" % (
                                         r["windows"], r["pairs"], r["wall_s"]),
                                     "gcups": r["cells"] / r["wall_s"] / 1e9}
-        print(json.dumps(line), flush=True)
+        emit(line)
     eng.close()
     if dist is not None:
         dist.destroy_process_group()

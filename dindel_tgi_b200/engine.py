@@ -456,7 +456,8 @@ class Engine:
         if out is not None:
             rh, rr, rn, ops = out
             if any(x.dtype != np.int32 or x.size < max(nr, 1) or not x.flags.c_contiguous for x in (rh, rr, rn)) \
-                    or ops.dtype != np.uint32 or ops.size < max(nr, 1) * int(cigar_cap) or not ops.flags.c_contiguous:
+                    or ops.dtype != np.uint32 or ops.ndim != 2 or ops.shape[1] != int(cigar_cap) or ops.shape[0] < max(nr, 1) \
+                    or not ops.flags.c_contiguous:
                 raise ValueError("cigars: out arrays must be contiguous int32[n_reads] x3 and uint32[n_reads, cigar_cap]")
         else:
             rh, rr, rn = (np.zeros(max(nr, 1), dtype=np.int32) for _ in range(3))
