@@ -389,7 +389,6 @@ def main():
             # called the way the adapter calls it (include/dindel_b200.hpp): 6 operation slots per read in pinned
             # buffers, one exact-capacity second pass only if some read needs more
             cap = 6
-            k5a = (k5a[0],) + tuple(pinned_copy(lib, x) for x in k5a[1:])
             k5o = [pinned_copy(lib, np.zeros(batch.n_reads, np.int32)) for _ in range(3)] + \
                   [pinned_copy(lib, np.zeros((batch.n_reads, cap), np.uint32))]
             eng.cigars(*k5a, cigar_cap=cap, n_reads=batch.n_reads, out=k5o)   # warm-up (buffers grow once)

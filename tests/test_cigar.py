@@ -164,25 +164,6 @@ def test_k5_full_size_invariants(engine_cli):
     assert ((rh == h1[win_of_read]) | (rh == h2[win_of_read])).all()
     aligned = rp >= 0
     assert aligned.mean() > 0.5 and (rp[aligned] >= 103).all()
-    # the adapter's call shape (include/dindel_b200.hpp): 6 slots per read into caller-owned pinned buffers
-    import ctypes as C
-    lib, nr, keep = engine_cli.lib, batch.n_reads, []
-    def pinned(shape, dt):
-        n = int(np.prod(shape)) * np.dtype(dt).itemsize
-        p = lib.dindel_b200_alloc_pinned(n)
-        assert p
-        keep.append(p)
-        return np.frombuffer((C.c_uint8 * n).from_address(p), dtype=dt).reshape(shape)
-    out = [pinned((nr,), np.int32) for _ in range(3)] + [pinned((nr, 6), np.uint32)]
-    rh6, rp6, rn6, ops6 = engine_cli.cigars(engine.CIGAR_PAIR, np.full(batch.n_windows, 100, np.int32), hml, h1, h2,
-                                            np.zeros(batch.n_haps, np.int32), cigar_cap=6, out=out)
-    assert (rh6 == rh).all() and (rp6 == rp).all() and (rn6 == rn).all() and (ops6 == ops[:, :6]).all()
-    with pytest.raises(ValueError):
-        engine_cli.cigars(engine.CIGAR_PAIR, np.full(batch.n_windows, 100, np.int32), hml, h1, h2,
-                          np.zeros(batch.n_haps, np.int32), cigar_cap=16, out=out)
-    del out, rh6, rp6, rn6, ops6
-    for p in keep:
-        lib.dindel_b200_free_pinned(C.c_void_p(p))
 
 
 @pytest.mark.gpu
