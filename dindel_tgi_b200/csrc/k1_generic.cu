@@ -92,7 +92,9 @@ __global__ void __launch_bounds__(128) k1_generic_kernel(K1Batch B, int bt_in_sm
         if (lane == 0) unit = B.unit_begin + (long long)atomicAdd(B.counter, 1ULL);
         unit = __shfl_sync(0xffffffffu, unit, 0);
         if (unit >= B.unit_end) break;
-        const int w = k1_find_window(B.win_unit, B.n_windows, unit);
+        // search only this launch's window range: in a pipelined submit the CSR arrays of later chunks are
+        // not uploaded yet when this chunk's kernel runs
+        const int w = B.w_begin + k1_find_window(B.win_unit + B.w_begin, B.w_end - B.w_begin, unit);
         const int h0 = B.win_hap[w], nh = B.win_hap[w + 1] - h0;
         const int r0 = B.win_read[w], nr = B.win_read[w + 1] - r0;
         const int nchunk = (nr + K1_READ_CHUNK - 1) / K1_READ_CHUNK;

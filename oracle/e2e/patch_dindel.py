@@ -142,7 +142,51 @@ DUMP_CIG = r"""
 							fclose(df);
 						}
 """
+# --dump, third hook: the numeric cores of DetInDel::diploidGLF (DInDel.cpp:3085-3120, :3240-3266, :3349-3390) and of
+# DetInDel::estimateHaplotypeFrequenciesBayesEM (:2431-2545, :2683-2694) append their inputs (the rl matrix, priors,
+# filtered[], compatible[]) and their intermediate results (per-pair sums, arg-max pairs, qual / genoqual, per-position
+# genotype likelihoods; per active-variant set: iterations, loglik, pi, freqs; logz; pooled genotype likelihoods) to the
+# file named by $DINDEL_B200_DUMP_INFER, doubles as %.17g.  Golden vectors of the reference's own arithmetic for K2 / K3
+# (tests/golden/make_infer_golden.py -> tests/golden/infer_golden.json.gz).
+def DF(body):
+    return ('if (getenv("DINDEL_B200_DUMP_INFER")) { FILE *df = fopen(getenv("DINDEL_B200_DUMP_INFER"), "a"); '
+            + body + ' fclose(df); }\n')
+DUMP_INF = [
+    # diploidGLF: rl matrix + filtered (after the rl loop, DInDel.cpp:2962)
+    ("\t// get all variants\n", "before", 1, 0,
+     DF('fprintf(df, "DW %d %d\\n", int(nh), int(nr)); fprintf(df, "RL"); for (size_t i=0;i<nh*nr;i++) fprintf(df, " %.17g", rl[i]); '
+        'fprintf(df, "\\nFILT"); for (size_t h=0;h<nh;h++) fprintf(df, " %d", filtered[h]); fprintf(df, "\\n");')),
+    ("\t\tpairs_posterior[h1*nh+h2] = ll + prior[h1*nh+h2];\n", "after", 1, 0,
+     DF('fprintf(df, "PP %d %d %.17g %.17g %d %d\\n", int(h1), int(h2), ll, prior[h1*nh+h2], hap_num_candidate_indels[h1], hap_num_candidate_indels[h2]);')),
+    ("\tif (max_indel_pair[0]==-1 || max_indel_pair[1]==-1) throw string(\"Could not find indel allele\");\t\n", "before", 1, 0,
+     DF('fprintf(df, "MAP %d %d %d %d %.17g %.17g %.17g\\n", max_indel_pair[0], max_indel_pair[1], max_noindel_pair[0], max_noindel_pair[1], max_ll_indel, max_ll_noindel, qual);')),
+    ("\t\t\tgenoqual = - 10.0*( max_ll_altgeno - addLogs(max_ll_indel, max_ll_altgeno) )/log(10.0);\n", "after", 1, 0,
+     DF('fprintf(df, "GQ %d %.17g %.17g\\n", it->first, max_ll_altgeno, genoqual);')),
+    ("\t\t\tIGIt igit = genLiks.find(genotype);\n", "before", 1, 0,
+     DF('fprintf(df, "SL %d %d %d %d %d %.17g %.17g\\n", pos, int(h1), int(h2), v1, v2, pr, ll);')),
+    ("\t\t//cout << \"hx1: \" << hx1 << \" hx2: \" << hx2 << \" postprob: \" << maxll << endl;\n", "after", 1, 0,
+     DF('fprintf(df, "SM %d %d %d %.17g", pos, hx1, hx2, maxll); for (IGIt g=genLiks.begin();g!=genLiks.end();g++) fprintf(df, " %d/%d:%.17g", *(g->first.begin()), *(g->first.rbegin()), g->second); fprintf(df, "\\n");')),
+    # estimateHaplotypeFrequenciesBayesEM: rl matrix (filled at :2125-2139), then per set, then logz, then pooled genotype sums
+    ("\tcout << \"ALWAYS CALLING ::filterHaplotypes\" << endl;\n", "before", 1, 0,
+     DF('fprintf(df, "EW %d %d %.17g %.17g\\n", int(nh), int(nr), params.bayesa0, params.EMtol); fprintf(df, "RL"); for (size_t i=0;i<nh*nr;i++) fprintf(df, " %.17g", rl[i]); '
+        'fprintf(df, "\\nPOOL"); for (size_t r=0;r<nr;r++) fprintf(df, " %d", reads[r].poolID); fprintf(df, "\\n");')),
+    ("\t\tlogliks[th]=loglik;\n", "after", 1, 0,
+     DF('fprintf(df, "SET %d %d %d %.17g %.17g C", th, numah, iter, loglik, logprior); for (size_t h=0;h<nh;h++) fprintf(df, " %d", compatible[h]); '
+        'fprintf(df, " PI"); for (size_t h=0;h<nh;h++) fprintf(df, " %.17g", pi[h]); fprintf(df, " E %.17g\\n", eOld);')),
+    ("\tfor (int a=0;a<nav;a++) {\n\t\tpost[a]=exp(logliks[a]+logpriors[a]-logz);\n", "before", 1, 0,
+     DF('fprintf(df, "LOGZ %.17g FR", logz); for (size_t i=0;i<size_t(nav)*nh;i++) fprintf(df, " %.17g", freqs[i]); fprintf(df, "\\n");')),
+    ("\t\tlogp-=logz;\n", "after", 1, 0,
+     DF('fprintf(df, "VAR %d %.17g %.17g HF", idx, logp, freq); for (size_t h=0;h<nh;h++) fprintf(df, " %.17g", hapFreqs[h]); fprintf(df, " HV"); for (size_t h=0;h<nh;h++) fprintf(df, " %d", hapHasVar[h*nv+idx]); fprintf(df, "\\n");')),
+    ("\t\t\t\t\tlik[genotype]=addLogs(lik[genotype],ll);\n", "before", 1, 0,
+     DF('fprintf(df, "PG %d %d %d %d %.17g %.17g\\n", idx, int(b), int(h1), int(h2), pr, ll);')),
+]
 if dump:
+    for anchor, where, count, which, code in DUMP_INF:
+        assert text.count(anchor) == count, (anchor, text.count(anchor))
+        i = -1
+        for _ in range(which + 1):
+            i = text.index(anchor, i + 1)
+        text = text[:i] + (code + anchor if where == "before" else anchor + code) + text[i + len(anchor):]
     anchor = "\t\tvarCoverage[pav]=VariantCoverage(int(rf.size()), int(rr.size()));\n\t}\n"
     assert text.count(anchor) == 1
     text = text.replace(anchor, anchor + DUMP)

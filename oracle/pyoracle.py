@@ -153,6 +153,10 @@ class Oracle:
         it = self.lib.ora_bayes_em(vp(rl), nr, nh, vp(comp), C.c_double(a0), C.c_double(tol), C.byref(ll), vp(pi), vp(fr))
         return ll.value, it, pi, fr
 
+    def addlogs(self, a, b):
+        self.lib.ora_addlogs.restype = C.c_double
+        return self.lib.ora_addlogs(C.c_double(a), C.c_double(b))
+
     def digamma(self, x):
         self.lib.ora_digamma.restype = C.c_double
         return self.lib.ora_digamma(C.c_double(x))
