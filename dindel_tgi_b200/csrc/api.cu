@@ -10,6 +10,10 @@
 #include <string>
 #include <vector>
 #include <chrono>
+#include <thread>
+#include <mutex>
+#include <condition_variable>
+#include <nvtx3/nvToolsExt.h>
 #include "k1_common.cuh"
 #include "k23.cuh"
 #include "k4.cuh"
@@ -26,8 +30,8 @@ extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream
                                        int *launches, unsigned class_mask, int J);
 extern "C" unsigned k1_tiled_class_of(int S, int J);
 extern "C" cudaError_t k1_tiled_prepare(const K1Batch *B, cudaStream_t stream, int *launches);
-extern "C" cudaError_t k2_launch(const K2Args *a, cudaStream_t st);
-extern "C" cudaError_t k3_launch(const K3Args *a, cudaStream_t st);
+extern "C" cudaError_t k2_launch(const K2Args *a, int max_npairs, cudaStream_t st);
+extern "C" cudaError_t k3_launch(const K3Args *a, int max_nh, int max_nr, size_t smem_optin, cudaStream_t st);
 extern "C" int k3_max_haps(void);
 extern "C" size_t k4_smem_bytes(int ne, int nk, int nr, int nh);
 extern "C" cudaError_t k4_launch(const K4Args *a, int n_windows, size_t smem, cudaStream_t st);
@@ -146,7 +150,7 @@ struct HostBuf {
             if (p) cudaFreeHost(p);
             p = nullptr; cap = 0;
             size_t want = n + n / 8 + 16;
-            if (cudaHostAlloc((void **)&p, want * sizeof(long long), cudaHostAllocDefault) != cudaSuccess) {
+            if (cudaHostAlloc((void **)&p, want * sizeof(long long), cudaHostAllocPortable) != cudaSuccess) {
                 cudaGetLastError();
                 return false;
             }
@@ -169,8 +173,9 @@ struct Lane {
     DevBuf d_counter, d_units, d_buckets, d_bt;
 };
 #define DINDEL_NUM_LANES 2
+#define DINDEL_EV_PER_CHUNK 6 // h2d begin / end, kernels begin / end, d2h begin / end
 
-// A contiguous window range of the resident batch with its slices of every CSR array.
+// A contiguous window range of the batch with its slices of every CSR array.
 struct Range {
     int w0, w1, h0, h1, r0, r1;
     long long hb0, hb1, rb0, rb1, p0, p1, u0, u1;
@@ -195,19 +200,28 @@ struct dindel_ctx {
         d_read_flags, d_pairs, d_hpos, d_win_status, d_on_hap, d_x[8],
         d_read_ins_mode, d_read_ins_anchor, d_read_lib, d_lib_off, d_lib_logp, d_lib_log95;
     int n_libs = 0;
-    long long hap_bases = 0;   // hap_off[n_haps] of the resident batch
-    // resident batch
+    // The RESIDENT RANGE: windows [base.w0, base.w1) of the indexed host batch live in the device buffers above, each
+    // buffer holding only the range's slice.  Every pointer in B (and the three below) is REBASED, i.e. moved back
+    // by the slice's first index, so that the kernels keep using the batch's absolute window / haplotype / read /
+    // pair indices unchanged whichever range is resident (a whole batch is the range [0, n_windows): offset 0).
     bool resident = false, ran = false;
+    Range base;                // first indices of the resident range (what the buffers' element 0 stands for)
     K1Batch B;
+    int32_t *p_win_status = nullptr; // rebased like B.*
+    uint8_t *p_on_hap = nullptr, *p_hap_hp = nullptr;
+    // index of the whole host batch (index_batch): prefix sums over all its windows
+    int idx_windows = 0;
+    long long hap_bases_total = 0;
     HostBuf win_pair, win_unit; // [n_windows+1] prefix sums (pinned: uploaded by async copies)
     std::vector<int> win_nh;
     dindel_timing timing;
+    size_t mem_budget = (size_t)48 << 30; // bytes of device memory one resident range may take ($DINDEL_B200_MEM_BUDGET)
     int force_generic = 0, force_chunks = 0, force_lanes = 0, force_bt_global = -1;
     // DINDEL_B200_TRACE=1: cumulative host wall time inside submit / coverage, printed every 50 submits (stderr)
     int trace = 0;
     long n_submit = 0, n_cover = 0;
     double t_submit = 0.0, t_cover = 0.0, t_create = 0.0;
-    Range all;                 // the whole resident batch (resident API)
+    Range all;                 // the resident range with its kernel choice (resident API)
 };
 
 struct TraceTimer {
@@ -215,6 +229,12 @@ struct TraceTimer {
     std::chrono::steady_clock::time_point t0;
     explicit TraceTimer(double *a) : acc(a), t0(std::chrono::steady_clock::now()) {}
     ~TraceTimer() { if (acc) *acc += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
+};
+
+// NVTX ranges (pack / H2D / K1 / K4 / D2H): visible in nsys / ncu timelines, no-ops otherwise
+struct Nvtx {
+    explicit Nvtx(const char *name) { nvtxRangePushA(name); }
+    ~Nvtx() { nvtxRangePop(); }
 };
 
 static int fail(dindel_ctx *c, int code, const std::string &msg)
@@ -381,6 +401,8 @@ int dindel_b200_create(const dindel_params *p, int device, dindel_ctx **out)
     ctx->force_chunks = fc ? atoi(fc) : 0;
     const char *fl = getenv("DINDEL_B200_LANES");
     ctx->force_lanes = fl ? atoi(fl) : 0;
+    const char *mb = getenv("DINDEL_B200_MEM_BUDGET"); // bytes of device memory per resident range (tests: force several ranges)
+    if (mb && atoll(mb) > 0) ctx->mem_budget = (size_t)atoll(mb);
     const char *fb = getenv("DINDEL_B200_BT_GLOBAL"); // generic kernel: 1 / 0 forces the back-pointer plan
     ctx->force_bt_global = fb ? atoi(fb) : -1;
     memset(&ctx->timing, 0, sizeof(ctx->timing));
@@ -514,16 +536,17 @@ int dindel_b200_plan_shards(const dindel_batch_in *in, int n_shards, int32_t *fi
 }
 
 // ------------------------------------------------------------------------------------------
-// batch plumbing: host indexing + device allocation (prepare_batch), then per window range:
-// host scan (which kernel), H2D of the range's slices, prep kernels, K1 + summary, D2H.
+// batch plumbing: host index of the whole batch (index_batch), then per RESIDENT RANGE of windows:
+// device allocation + pointer rebasing (prepare_range) and, per pipeline chunk inside the range,
+// host scan (which kernel), H2D of the chunk's slices, prep kernels, K1 + summary, D2H.
 // ------------------------------------------------------------------------------------------
-static int prepare_batch(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos, int hstride_req)
+static int index_batch(dindel_ctx *ctx, const dindel_batch_in *in, bool validated)
 {
-    if (validate(in) != DINDEL_OK) return fail(ctx, DINDEL_E_INVALID, "inconsistent batch");
+    if (!validated && validate(in) != DINDEL_OK) return fail(ctx, DINDEL_E_INVALID, "inconsistent batch");
     CU(cudaSetDevice(ctx->device));
     ctx->resident = false;
     ctx->ran = false;
-    const int nw = in->n_windows, nh = in->n_haps, nr = in->n_reads;
+    const int nw = in->n_windows;
     if (!ctx->win_pair.assign((size_t)nw + 1) || !ctx->win_unit.assign((size_t)nw + 1))
         return fail(ctx, DINDEL_E_NOMEM, "pinned host index arrays");
     ctx->win_nh.assign((size_t)nw, 0);
@@ -533,96 +556,146 @@ static int prepare_batch(dindel_ctx *ctx, const dindel_batch_in *in, int want_hp
         ctx->win_pair[w + 1] = ctx->win_pair[w] + a * b;
         ctx->win_unit[w + 1] = ctx->win_unit[w] + a * ((b + K1_READ_CHUNK - 1) / K1_READ_CHUNK);
     }
+    ctx->idx_windows = nw;
+    ctx->hap_bases_total = in->n_haps ? in->hap_off[in->n_haps] : 0;
+    return DINDEL_OK;
+}
+
+static long long range_cells(const dindel_batch_in *in, int w0, int w1)
+{
+    long long cells = 0;
+    for (int w = w0; w < w1; w++) {
+        int h0 = in->win_hap[w], h1 = in->win_hap[w + 1], r0 = in->win_read[w], r1 = in->win_read[w + 1];
+        cells += ((in->hap_off[h1] - in->hap_off[h0]) + 2LL * (h1 - h0)) * (in->read_off[r1] - in->read_off[r0]);
+    }
+    return cells;
+}
+
+// cost-balanced contiguous split of windows [w0, w1) into n parts (dindel_b200_plan_shards on a sub-range)
+static void plan_range(const dindel_batch_in *in, int w0, int w1, int n, int32_t *first)
+{
+    const int nw = w1 - w0;
+    std::vector<long long> pre((size_t)nw + 1, 0);
+    for (int i = 0; i < nw; i++) {
+        const int w = w0 + i;
+        int h0 = in->win_hap[w], h1 = in->win_hap[w + 1], r0 = in->win_read[w], r1 = in->win_read[w + 1];
+        long long cols = (in->hap_off[h1] - in->hap_off[h0]) + 2LL * (h1 - h0);
+        long long rows = in->read_off[r1] - in->read_off[r0];
+        pre[i + 1] = pre[i] + cols * rows + 1; // +1: empty windows still cost a slot
+    }
+    first[0] = w0;
+    int i = 0;
+    for (int k = 1; k < n; k++) {
+        // first boundary whose prefix reaches k/n of the total (rounded to the nearer side)
+        const long long target = (long long)(((__int128)pre[nw] * k) / n);
+        while (i < nw && pre[i + 1] <= target) i++;
+        if (i < nw && target - pre[i] > pre[i + 1] - target) i++;
+        first[k] = w0 + i;
+    }
+    first[n] = w1;
+}
+
+// Makes windows [w0, w1) of the indexed batch the resident range: device buffers sized for the range's slices,
+// every pointer the kernels use moved back by the slice's first index.
+static int prepare_range(dindel_ctx *ctx, const dindel_batch_in *in, int w0, int w1, int want_hpos, int hstride_req)
+{
+    ctx->resident = false;
+    ctx->ran = false;
+    Range &b = ctx->base;
+    memset(&b, 0, sizeof(b));
+    b.w0 = w0; b.w1 = w1;
+    b.h0 = in->win_hap[w0]; b.h1 = in->win_hap[w1];
+    b.r0 = in->win_read[w0]; b.r1 = in->win_read[w1];
+    b.hb0 = in->n_haps ? in->hap_off[b.h0] : 0; b.hb1 = in->n_haps ? in->hap_off[b.h1] : 0;
+    b.rb0 = in->n_reads ? in->read_off[b.r0] : 0; b.rb1 = in->n_reads ? in->read_off[b.r1] : 0;
+    b.p0 = ctx->win_pair[w0]; b.p1 = ctx->win_pair[w1];
+    b.u0 = ctx->win_unit[w0]; b.u1 = ctx->win_unit[w1];
+    const size_t nw = (size_t)(w1 - w0), nh = (size_t)(b.h1 - b.h0), nr = (size_t)(b.r1 - b.r0);
     int maxH = 0, maxR = 0;
-    for (int h = 0; h < nh; h++) {
+    for (int h = b.h0; h < b.h1; h++) {
         long long l = in->hap_off[h + 1] - in->hap_off[h];
         if (l > 32000) return fail(ctx, DINDEL_E_UNSUPPORTED, "haplotype longer than 32000");
         if (l > maxH) maxH = (int)l;
     }
-    for (int r = 0; r < nr; r++) {
+    for (int r = b.r0; r < b.r1; r++) {
         long long l = in->read_off[r + 1] - in->read_off[r];
         if (l > 32000) return fail(ctx, DINDEL_E_UNSUPPORTED, "read longer than 32000");
         if (l > maxR) maxR = (int)l;
     }
-    const long long n_pairs = ctx->win_pair[nw], n_units = ctx->win_unit[nw];
-    const long long hap_bytes = nh ? in->hap_off[nh] : 0, read_bytes = nr ? in->read_off[nr] : 0;
+    const long long n_pairs = b.p1 - b.p0, n_units = b.u1 - b.u0;
+    const long long hap_bytes = b.hb1 - b.hb0, read_bytes = b.rb1 - b.rb0;
     int hstride = 0;
     if (want_hpos) {
         hstride = hstride_req > 0 ? hstride_req : ((maxR + 7) & ~7);
         if (hstride < maxR) return fail(ctx, DINDEL_E_INVALID, "hpos_stride shorter than the longest read");
     }
-    CU(ctx->d_hap_start.ensure((size_t)nw * 4 + 16));
-    CU(ctx->d_win_hap.ensure(((size_t)nw + 1) * 4 + 16));
-    CU(ctx->d_win_read.ensure(((size_t)nw + 1) * 4 + 16));
-    CU(ctx->d_win_pair.ensure(((size_t)nw + 1) * 8 + 16));
-    CU(ctx->d_win_unit.ensure(((size_t)nw + 1) * 8 + 16));
-    CU(ctx->d_hap_off.ensure(((size_t)nh + 1) * 8 + 16));
-    ctx->hap_bases = hap_bytes;
+    CU(ctx->d_hap_start.ensure(nw * 4 + 16));
+    CU(ctx->d_win_hap.ensure((nw + 1) * 4 + 16));
+    CU(ctx->d_win_read.ensure((nw + 1) * 4 + 16));
+    CU(ctx->d_win_pair.ensure((nw + 1) * 8 + 16));
+    CU(ctx->d_win_unit.ensure((nw + 1) * 8 + 16));
+    CU(ctx->d_hap_off.ensure((nh + 1) * 8 + 16));
     CU(ctx->d_hap_seq.ensure((size_t)hap_bytes + 16));
-    CU(ctx->d_read_off.ensure(((size_t)nr + 1) * 8 + 16));
+    CU(ctx->d_read_off.ensure((nr + 1) * 8 + 16));
     CU(ctx->d_read_seq.ensure((size_t)read_bytes + 16));
     CU(ctx->d_read_qual.ensure((size_t)read_bytes + 16));
-    CU(ctx->d_read_mapq.ensure((size_t)nr + 16));
-    CU(ctx->d_read_start.ensure((size_t)nr * 4 + 16));
-    CU(ctx->d_read_flags.ensure((size_t)nr + 16));
+    CU(ctx->d_read_mapq.ensure(nr + 16));
+    CU(ctx->d_read_start.ensure(nr * 4 + 16));
+    CU(ctx->d_read_flags.ensure(nr + 16));
     const bool has_ins = in->read_ins_mode != nullptr;
     if (has_ins) {
         if (!in->read_ins_anchor || !in->read_lib) return fail(ctx, DINDEL_E_INVALID, "read_ins_mode without read_ins_anchor / read_lib");
-        for (int r = 0; r < nr; r++) {
+        for (int r = b.r0; r < b.r1; r++) {
             if (in->read_ins_mode[r] > DINDEL_INS_MATE_FORWARD) return fail(ctx, DINDEL_E_INVALID, "read_ins_mode");
             if (in->read_ins_mode[r] != DINDEL_INS_NONE && (in->read_lib[r] < 0 || in->read_lib[r] >= ctx->n_libs))
                 return fail(ctx, DINDEL_E_INVALID, "read_lib out of range (call dindel_b200_set_libraries first)");
         }
-        CU(ctx->d_read_ins_mode.ensure((size_t)nr + 16));
-        CU(ctx->d_read_ins_anchor.ensure((size_t)nr * 4 + 16));
-        CU(ctx->d_read_lib.ensure((size_t)nr * 4 + 16));
+        CU(ctx->d_read_ins_mode.ensure(nr + 16));
+        CU(ctx->d_read_ins_anchor.ensure(nr * 4 + 16));
+        CU(ctx->d_read_lib.ensure(nr * 4 + 16));
     }
-    CU(ctx->d_hap_hp.ensure((size_t)hap_bytes + 2 * (size_t)nh + 16));
+    CU(ctx->d_hap_hp.ensure((size_t)hap_bytes + 2 * nh + 16));
     CU(ctx->d_pairs.ensure((size_t)n_pairs * sizeof(dindel_pair_out) + 64));
-    CU(ctx->d_win_status.ensure((size_t)nw * 4 + 16));
-    CU(ctx->d_on_hap.ensure((size_t)nr + 16));
+    CU(ctx->d_win_status.ensure(nw * 4 + 16));
+    CU(ctx->d_on_hap.ensure(nr + 16));
     if (want_hpos) CU(ctx->d_hpos.ensure((size_t)n_pairs * hstride * 2 + 16));
 
     K1Batch &B = ctx->B;
     memset(&B, 0, sizeof(B));
-    B.n_windows = nw; B.n_haps = nh; B.n_reads = nr; B.hpos_stride = hstride;
+    B.n_windows = in->n_windows; B.n_haps = in->n_haps; B.n_reads = in->n_reads; B.hpos_stride = hstride;
     B.n_units = n_units; B.n_pairs = n_pairs;
-    B.hap_start = (const uint32_t *)ctx->d_hap_start.p;
-    B.win_hap = (const int32_t *)ctx->d_win_hap.p;
-    B.win_read = (const int32_t *)ctx->d_win_read.p;
-    B.win_pair = (const long long *)ctx->d_win_pair.p;
-    B.win_unit = (const long long *)ctx->d_win_unit.p;
-    B.hap_off = (const long long *)ctx->d_hap_off.p;
-    B.hap_seq = (const uint8_t *)ctx->d_hap_seq.p;
-    B.hap_hp = (const uint8_t *)ctx->d_hap_hp.p;
-    B.read_off = (const long long *)ctx->d_read_off.p;
-    B.read_seq = (const uint8_t *)ctx->d_read_seq.p;
-    B.read_qual = (const uint8_t *)ctx->d_read_qual.p;
-    B.read_mapq = (const uint8_t *)ctx->d_read_mapq.p;
-    B.read_flags = (const uint8_t *)ctx->d_read_flags.p;
-    B.read_start = (const uint32_t *)ctx->d_read_start.p;
+    B.w_begin = w0; B.w_end = w1; B.unit_begin = b.u0; B.unit_end = b.u1;
+    B.hap_start = (const uint32_t *)ctx->d_hap_start.p - b.w0;
+    B.win_hap = (const int32_t *)ctx->d_win_hap.p - b.w0;
+    B.win_read = (const int32_t *)ctx->d_win_read.p - b.w0;
+    B.win_pair = (const long long *)ctx->d_win_pair.p - b.w0;
+    B.win_unit = (const long long *)ctx->d_win_unit.p - b.w0;
+    B.hap_off = (const long long *)ctx->d_hap_off.p - b.h0;
+    B.hap_seq = (const uint8_t *)ctx->d_hap_seq.p - b.hb0;
+    ctx->p_hap_hp = (uint8_t *)ctx->d_hap_hp.p - (b.hb0 + 2LL * b.h0); // column base of hap h = hap_off[h] + 2*h
+    B.hap_hp = ctx->p_hap_hp;
+    B.read_off = (const long long *)ctx->d_read_off.p - b.r0;
+    B.read_seq = (const uint8_t *)ctx->d_read_seq.p - b.rb0;
+    B.read_qual = (const uint8_t *)ctx->d_read_qual.p - b.rb0;
+    B.read_mapq = (const uint8_t *)ctx->d_read_mapq.p - b.r0;
+    B.read_flags = (const uint8_t *)ctx->d_read_flags.p - b.r0;
+    B.read_start = (const uint32_t *)ctx->d_read_start.p - b.r0;
     if (has_ins) {
-        B.read_ins_mode = (const uint8_t *)ctx->d_read_ins_mode.p;
-        B.read_ins_anchor = (const int32_t *)ctx->d_read_ins_anchor.p;
-        B.read_lib = (const int32_t *)ctx->d_read_lib.p;
+        B.read_ins_mode = (const uint8_t *)ctx->d_read_ins_mode.p - b.r0;
+        B.read_ins_anchor = (const int32_t *)ctx->d_read_ins_anchor.p - b.r0;
+        B.read_lib = (const int32_t *)ctx->d_read_lib.p - b.r0;
         B.lib_off = (const long long *)ctx->d_lib_off.p;
         B.lib_logp = (const double *)ctx->d_lib_logp.p;
         B.lib_log95 = (const double *)ctx->d_lib_log95.p;
     }
-    B.pairs = (dindel_pair_out *)ctx->d_pairs.p;
-    B.hpos = want_hpos ? (int16_t *)ctx->d_hpos.p : nullptr;
+    B.pairs = (dindel_pair_out *)ctx->d_pairs.p - b.p0;
+    B.hpos = want_hpos ? (int16_t *)ctx->d_hpos.p - b.p0 * hstride : nullptr;
+    ctx->p_win_status = (int32_t *)ctx->d_win_status.p - b.w0;
+    ctx->p_on_hap = (uint8_t *)ctx->d_on_hap.p - b.r0;
     B.luts = (const K1Luts *)ctx->d_luts.p;
     B.max_R = maxR > 0 ? maxR : 1;
     B.max_S = maxH + 2;
     k1_tiled_class_table(ctx->luts.numT - 1, B.class_c);
-    memset(&ctx->timing, 0, sizeof(ctx->timing));
-    ctx->timing.n_pairs = n_pairs;
-    long long cells = 0;
-    for (int w = 0; w < nw; w++) {
-        int h0 = in->win_hap[w], h1 = in->win_hap[w + 1], r0 = in->win_read[w], r1 = in->win_read[w + 1];
-        cells += ((in->hap_off[h1] - in->hap_off[h0]) + 2LL * (h1 - h0)) * (in->read_off[r1] - in->read_off[r0]);
-    }
-    ctx->timing.n_cells = cells;
     return DINDEL_OK;
 }
 
@@ -666,38 +739,40 @@ static void scan_range(dindel_ctx *ctx, const dindel_batch_in *in, int w0, int w
 
 static int copy_in_range(dindel_ctx *ctx, const dindel_batch_in *in, const Range &g, cudaStream_t st)
 {
-#define UPR(buf, src, first, count, esz)                                                        \
+    const Range &b = ctx->base;
+    // element `first` of the host array lands at element (first - base) of the range's device slice
+#define UPR(buf, src, first, base, count, esz)                                                  \
     do {                                                                                        \
         if ((count) > 0)                                                                        \
-            CU(cudaMemcpyAsync((char *)ctx->buf.p + (size_t)(first) * (esz),                    \
+            CU(cudaMemcpyAsync((char *)ctx->buf.p + (size_t)((first) - (base)) * (esz),         \
                                (const char *)(src) + (size_t)(first) * (esz),                   \
                                (size_t)(count) * (esz), cudaMemcpyHostToDevice, st));           \
     } while (0)
     const int nwr = g.w1 - g.w0, nhr = g.h1 - g.h0, nrr = g.r1 - g.r0;
     if (nwr <= 0) return DINDEL_OK;
-    UPR(d_hap_start, in->hap_start, g.w0, nwr, 4);
-    UPR(d_win_hap, in->win_hap, g.w0, nwr + 1, 4);
-    UPR(d_win_read, in->win_read, g.w0, nwr + 1, 4);
-    UPR(d_win_pair, ctx->win_pair.data(), g.w0, nwr + 1, 8);
-    UPR(d_win_unit, ctx->win_unit.data(), g.w0, nwr + 1, 8);
-    UPR(d_hap_off, in->hap_off, g.h0, nhr + 1, 8);
-    UPR(d_hap_seq, in->hap_seq, g.hb0, g.hb1 - g.hb0, 1);
-    UPR(d_read_off, in->read_off, g.r0, nrr + 1, 8);
-    UPR(d_read_seq, in->read_seq, g.rb0, g.rb1 - g.rb0, 1);
-    UPR(d_read_qual, in->read_qual, g.rb0, g.rb1 - g.rb0, 1);
-    UPR(d_read_mapq, in->read_mapq, g.r0, nrr, 1);
-    UPR(d_read_start, in->read_start, g.r0, nrr, 4);
-    UPR(d_read_flags, in->read_flags, g.r0, nrr, 1);
+    UPR(d_hap_start, in->hap_start, g.w0, b.w0, nwr, 4);
+    UPR(d_win_hap, in->win_hap, g.w0, b.w0, nwr + 1, 4);
+    UPR(d_win_read, in->win_read, g.w0, b.w0, nwr + 1, 4);
+    UPR(d_win_pair, ctx->win_pair.data(), g.w0, b.w0, nwr + 1, 8);
+    UPR(d_win_unit, ctx->win_unit.data(), g.w0, b.w0, nwr + 1, 8);
+    UPR(d_hap_off, in->hap_off, g.h0, b.h0, nhr + 1, 8);
+    UPR(d_hap_seq, in->hap_seq, g.hb0, b.hb0, g.hb1 - g.hb0, 1);
+    UPR(d_read_off, in->read_off, g.r0, b.r0, nrr + 1, 8);
+    UPR(d_read_seq, in->read_seq, g.rb0, b.rb0, g.rb1 - g.rb0, 1);
+    UPR(d_read_qual, in->read_qual, g.rb0, b.rb0, g.rb1 - g.rb0, 1);
+    UPR(d_read_mapq, in->read_mapq, g.r0, b.r0, nrr, 1);
+    UPR(d_read_start, in->read_start, g.r0, b.r0, nrr, 4);
+    UPR(d_read_flags, in->read_flags, g.r0, b.r0, nrr, 1);
     if (in->read_ins_mode) {
-        UPR(d_read_ins_mode, in->read_ins_mode, g.r0, nrr, 1);
-        UPR(d_read_ins_anchor, in->read_ins_anchor, g.r0, nrr, 4);
-        UPR(d_read_lib, in->read_lib, g.r0, nrr, 4);
+        UPR(d_read_ins_mode, in->read_ins_mode, g.r0, b.r0, nrr, 1);
+        UPR(d_read_ins_anchor, in->read_ins_anchor, g.r0, b.r0, nrr, 4);
+        UPR(d_read_lib, in->read_lib, g.r0, b.r0, nrr, 4);
     }
 #undef UPR
     return DINDEL_OK;
 }
 
-// K1Batch of one range on one lane (work-queue state of that lane).
+// K1Batch of one chunk on one lane (work-queue state of that lane).
 static K1Batch range_batch(dindel_ctx *ctx, const Range &g, Lane &ln)
 {
     K1Batch b = ctx->B;
@@ -710,22 +785,21 @@ static K1Batch range_batch(dindel_ctx *ctx, const Range &g, Lane &ln)
     return b;
 }
 
-// lane buffers large enough for any range of up to max_units work units
+// lane buffers large enough for any chunk of up to max_units work units
 static int ensure_lane(dindel_ctx *ctx, Lane &ln, long long max_units)
 {
     CU(ln.d_units.ensure((size_t)max_units * sizeof(uint2) + 16));
     return DINDEL_OK;
 }
 
-// prep kernels of a range: homopolymer codes per hap column (K0) and, for the tiled kernel, the
+// prep kernels of a chunk: homopolymer codes per hap column (K0) and, for the tiled kernel, the
 // bucketed work-unit lists
 static int prep_range(dindel_ctx *ctx, const Range &g, Lane &ln, int *launches)
 {
     cudaStream_t st = ln.st;
     const int nhr = g.h1 - g.h0;
     if (nhr > 0) {
-        k0_hap_tables<<<(nhr + 127) / 128, 128, 0, st>>>(g.h0, g.h1, ctx->B.hap_off, ctx->B.hap_seq,
-                                                         (uint8_t *)ctx->d_hap_hp.p);
+        k0_hap_tables<<<(nhr + 127) / 128, 128, 0, st>>>(g.h0, g.h1, ctx->B.hap_off, ctx->B.hap_seq, ctx->p_hap_hp);
         CU(cudaGetLastError());
         (*launches)++;
     }
@@ -738,7 +812,7 @@ static int prep_range(dindel_ctx *ctx, const Range &g, Lane &ln, int *launches)
     return DINDEL_OK;
 }
 
-// K1 over a range + per-window status / onHap
+// K1 over a chunk + per-window status / onHap
 static int k1_range(dindel_ctx *ctx, const Range &g, Lane &ln, int *launches)
 {
     cudaStream_t st = ln.st;
@@ -787,7 +861,7 @@ static int k1_range(dindel_ctx *ctx, const Range &g, Lane &ln, int *launches)
             if (grid > need) grid = (int)need;
             if (!bt_in_smem) {
                 b.bt_slot_bytes = (((long long)b.max_S * b.max_R) + 255) & ~255LL;
-                // allocated at full-grid size up front, so a later range never reallocates it
+                // allocated at full-grid size up front, so a later chunk never reallocates it
                 CU(ln.d_bt.ensure((size_t)b.bt_slot_bytes * ctx->num_sms * ctas_per_sm * warps));
                 b.bt_scratch = (uint8_t *)ln.d_bt.p;
             }
@@ -799,8 +873,7 @@ static int k1_range(dindel_ctx *ctx, const Range &g, Lane &ln, int *launches)
     if (g.w1 > g.w0) {
         int threads = 128, wpb = threads / 32;
         k1_window_summary<<<(g.w1 - g.w0 + wpb - 1) / wpb, threads, 0, st>>>(
-            g.w0, g.w1, b.win_hap, b.win_read, b.win_pair, b.pairs, (int32_t *)ctx->d_win_status.p,
-            (uint8_t *)ctx->d_on_hap.p);
+            g.w0, g.w1, b.win_hap, b.win_read, b.win_pair, b.pairs, ctx->p_win_status, ctx->p_on_hap);
         CU(cudaGetLastError());
         (*launches)++;
     }
@@ -811,37 +884,54 @@ static int copy_out_range(dindel_ctx *ctx, dindel_batch_out *out, const Range &g
 {
     const K1Batch &B = ctx->B;
     const long long np = g.p1 - g.p0;
-    if (np > 0)
+    if (out->pairs && np > 0)
         CU(cudaMemcpyAsync(out->pairs + g.p0, B.pairs + g.p0, (size_t)np * sizeof(dindel_pair_out),
                            cudaMemcpyDeviceToHost, st));
     if (out->hpos && np > 0)
         CU(cudaMemcpyAsync(out->hpos + g.p0 * B.hpos_stride, B.hpos + g.p0 * B.hpos_stride,
                            (size_t)np * B.hpos_stride * 2, cudaMemcpyDeviceToHost, st));
     if (out->win_status && g.w1 > g.w0)
-        CU(cudaMemcpyAsync(out->win_status + g.w0, (int32_t *)ctx->d_win_status.p + g.w0,
+        CU(cudaMemcpyAsync(out->win_status + g.w0, ctx->p_win_status + g.w0,
                            (size_t)(g.w1 - g.w0) * 4, cudaMemcpyDeviceToHost, st));
     if (out->read_on_hap && g.r1 > g.r0)
-        CU(cudaMemcpyAsync(out->read_on_hap + g.r0, (uint8_t *)ctx->d_on_hap.p + g.r0, (size_t)(g.r1 - g.r0),
+        CU(cudaMemcpyAsync(out->read_on_hap + g.r0, ctx->p_on_hap + g.r0, (size_t)(g.r1 - g.r0),
                            cudaMemcpyDeviceToHost, st));
     return DINDEL_OK;
 }
 
-static int check_out(dindel_ctx *ctx, dindel_batch_out *out)
+static int check_out(dindel_ctx *ctx, const dindel_batch_out *out, bool pairs_required)
 {
-    const K1Batch &B = ctx->B;
     if (!out) return fail(ctx, DINDEL_E_INVALID, "null out");
-    if (out->n_pairs < B.n_pairs || (B.n_pairs > 0 && !out->pairs))
-        return fail(ctx, DINDEL_E_INVALID, "pairs[] too small");
-    if (out->hpos && (!B.hpos || out->hpos_stride != B.hpos_stride))
-        return fail(ctx, DINDEL_E_INVALID, "hpos requested but batch uploaded without it (or stride mismatch)");
+    const long long total = ctx->win_pair[(size_t)ctx->idx_windows];
+    if (pairs_required && total > 0 && !out->pairs) return fail(ctx, DINDEL_E_INVALID, "pairs[] is NULL");
+    if (out->pairs && out->n_pairs < total) return fail(ctx, DINDEL_E_INVALID, "pairs[] too small");
+    if (out->hpos && out->hpos_stride <= 0) return fail(ctx, DINDEL_E_INVALID, "hpos without hpos_stride");
     return DINDEL_OK;
+}
+
+// every stream of the context idle (error paths: nothing may still touch the caller's buffers or ours)
+static void drain(dindel_ctx *ctx)
+{
+    cudaStreamSynchronize(ctx->s_in);
+    cudaStreamSynchronize(ctx->s_out);
+    for (int i = 0; i < DINDEL_NUM_LANES; i++) cudaStreamSynchronize(ctx->lane[i].st);
+    cudaGetLastError();
+    ctx->resident = false;
+    ctx->ran = false;
 }
 
 int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos)
 {
     if (!ctx) return DINDEL_E_INVALID;
-    int rc = prepare_batch(ctx, in, want_hpos, 0);
+    int rc = index_batch(ctx, in, false);
     if (rc != DINDEL_OK) return rc;
+    memset(&ctx->timing, 0, sizeof(ctx->timing));
+    ctx->timing.n_ranges = 1; ctx->timing.n_chunks = 1;
+    if (in->n_windows == 0) return fail(ctx, DINDEL_E_INVALID, "empty batch");
+    rc = prepare_range(ctx, in, 0, in->n_windows, want_hpos, 0);
+    if (rc != DINDEL_OK) return rc;
+    ctx->timing.n_pairs = ctx->B.n_pairs;
+    ctx->timing.n_cells = range_cells(in, 0, in->n_windows);
     Lane &ln = ctx->lane[0];
     cudaStream_t st = ln.st;
     scan_range(ctx, in, 0, in->n_windows, ctx->all);
@@ -849,13 +939,15 @@ int dindel_b200_upload(dindel_ctx *ctx, const dindel_batch_in *in, int want_hpos
     if (rc != DINDEL_OK) return rc;
     CU(cudaEventRecord(ctx->ev[0], st));
     rc = copy_in_range(ctx, in, ctx->all, st);
-    if (rc != DINDEL_OK) return rc;
+    if (rc != DINDEL_OK) { drain(ctx); return rc; }
     CU(cudaEventRecord(ctx->ev[1], st));
     int pl = 0;
     rc = prep_range(ctx, ctx->all, ln, &pl);
-    if (rc != DINDEL_OK) return rc;
+    if (rc != DINDEL_OK) { drain(ctx); return rc; }
     ctx->timing.prep_launches = pl;
     CU(cudaEventRecord(ctx->ev[2], st));
+    // the caller may free or reuse its input arrays as soon as upload returns
+    CU(cudaStreamSynchronize(st));
     ctx->resident = true;
     return DINDEL_OK;
 }
@@ -868,7 +960,7 @@ int dindel_b200_run(dindel_ctx *ctx)
     CU(cudaEventRecord(ctx->ev[3], ln.st));
     int launches = 0;
     int rc = k1_range(ctx, ctx->all, ln, &launches);
-    if (rc != DINDEL_OK) return rc;
+    if (rc != DINDEL_OK) { drain(ctx); return rc; }
     CU(cudaEventRecord(ctx->ev[4], ln.st));
     ctx->timing.k1_launches = launches;
     ctx->ran = true;
@@ -878,21 +970,25 @@ int dindel_b200_run(dindel_ctx *ctx)
 int dindel_b200_download(dindel_ctx *ctx, dindel_batch_out *out)
 {
     if (!ctx || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "nothing to download");
-    int rc = check_out(ctx, out);
+    if (ctx->base.w0 != 0 || ctx->base.w1 != ctx->idx_windows)
+        return fail(ctx, DINDEL_E_INVALID, "download needs the whole batch resident (it was streamed in ranges)");
+    int rc = check_out(ctx, out, true);
     if (rc != DINDEL_OK) return rc;
+    if (out->hpos && (!ctx->B.hpos || out->hpos_stride != ctx->B.hpos_stride))
+        return fail(ctx, DINDEL_E_INVALID, "hpos requested but batch uploaded without it (or stride mismatch)");
     CU(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     rc = copy_out_range(ctx, out, ctx->all, st);
-    if (rc != DINDEL_OK) return rc;
+    if (rc != DINDEL_OK) { drain(ctx); return rc; }
     CU(cudaEventRecord(ctx->ev[5], st));
     CU(cudaStreamSynchronize(st));
-    if (out->win_pair) memcpy(out->win_pair, ctx->win_pair.data(), ((size_t)ctx->B.n_windows + 1) * 8);
+    if (out->win_pair) memcpy(out->win_pair, ctx->win_pair.data(), ((size_t)ctx->idx_windows + 1) * 8);
     dindel_timing &t = ctx->timing;
     cudaEventElapsedTime(&t.h2d_ms, ctx->ev[0], ctx->ev[1]);
     cudaEventElapsedTime(&t.prep_ms, ctx->ev[1], ctx->ev[2]);
     cudaEventElapsedTime(&t.k1_ms, ctx->ev[3], ctx->ev[4]);
     cudaEventElapsedTime(&t.d2h_ms, ctx->ev[4], ctx->ev[5]);
-    cudaEventElapsedTime(&t.total_ms, ctx->ev[0], ctx->ev[5]);
+    t.total_ms = t.h2d_ms + t.prep_ms + t.k1_ms + t.d2h_ms;
     return DINDEL_OK;
 }
 
@@ -900,31 +996,35 @@ float dindel_b200_last_kernel_ms(const dindel_ctx *ctx) { return ctx ? ctx->last
 
 int dindel_b200_hpos_stride(const dindel_ctx *ctx) { return ctx && ctx->resident ? ctx->B.hpos_stride : 0; }
 
-// computeLikelihoods for a whole batch, host buffers in and out, as a pipeline over chunks of
-// windows (cost-balanced contiguous ranges): chunk c+1's H2D copies (stream s_in) run under
-// chunk c's kernels (compute lanes, alternating) and chunk c-1's D2H copies (stream s_out).
-// With pinned host buffers (dindel_b200_alloc_pinned) the copies are truly asynchronous.
-int dindel_b200_submit(dindel_ctx *ctx, const dindel_batch_in *in, dindel_batch_out *out)
+// forward: the stages on the resident range
+static int coverage_resident(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cover_out *out);
+static int sums_resident(dindel_ctx *ctx, const dindel_job *job, const std::vector<long long> &sum_off);
+static int em_resident(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out *out, bool need_all);
+
+// One resident range [a, b) of the batch through the chunked pipeline: chunk c+1's H2D copies (stream s_in) run
+// under chunk c's kernels (compute lanes, alternating) and chunk c-1's D2H copies (stream s_out).  With pinned
+// host buffers (dindel_b200_alloc_pinned) the copies are truly asynchronous.  Then the optional stages of the job
+// on the range's resident results.
+static int run_range(dindel_ctx *ctx, const dindel_job *job, int a, int b, int want_hpos, int hstride,
+                     const std::vector<long long> &sum_off, bool whole_batch)
 {
-    if (!ctx || !out) return DINDEL_E_INVALID;
-    TraceTimer tt(ctx->trace ? &ctx->t_submit : nullptr);
-    if (ctx->trace && ++ctx->n_submit % 50 == 0)
-        fprintf(stderr, "dindel_b200 trace: %ld submits %.3f s, %ld coverage calls %.3f s, create %.3f s\n", ctx->n_submit,
-                ctx->t_submit, ctx->n_cover, ctx->t_cover, ctx->t_create);
-    const bool keep_hpos = (out->flags & DINDEL_OUT_KEEP_HPOS) != 0; // rows stay in HBM for K4
-    int rc = prepare_batch(ctx, in, out->hpos != nullptr || keep_hpos, out->hpos ? out->hpos_stride : 0);
-    if (rc != DINDEL_OK) return rc;
-    rc = check_out(ctx, out);
-    if (rc != DINDEL_OK) return rc;
-    const int nw = in->n_windows;
+    const dindel_batch_in *in = job->in;
+    dindel_batch_out *out = job->out;
+    int rc;
+    {
+        Nvtx nv("dindel_b200:index+alloc");
+        rc = prepare_range(ctx, in, a, b, want_hpos, hstride);
+        if (rc != DINDEL_OK) return rc;
+    }
+    if (out->hpos && out->hpos_stride != ctx->B.hpos_stride) return fail(ctx, DINDEL_E_INVALID, "hpos_stride mismatch");
+    const long long cells = range_cells(in, a, b);
     // chunk plan: about 8e9 cells (~30 ms of K1) per chunk, at most 64 chunks
-    int n_chunks = ctx->force_chunks > 0 ? ctx->force_chunks : (int)(ctx->timing.n_cells / 8000000000LL);
+    int n_chunks = ctx->force_chunks > 0 ? ctx->force_chunks : (int)(cells / 8000000000LL);
     if (n_chunks > 64) n_chunks = 64;
-    if (n_chunks > nw) n_chunks = nw;
+    if (n_chunks > b - a) n_chunks = b - a;
     if (n_chunks < 1) n_chunks = 1;
     std::vector<int32_t> bounds((size_t)n_chunks + 1, 0);
-    if (dindel_b200_plan_shards(in, n_chunks, bounds.data()) != DINDEL_OK)
-        return fail(ctx, DINDEL_E_INVALID, "chunk plan");
+    plan_range(in, a, b, n_chunks, bounds.data());
     long long max_units = 0;
     for (int c = 0; c < n_chunks; c++) {
         long long u = ctx->win_unit[bounds[c + 1]] - ctx->win_unit[bounds[c]];
@@ -933,54 +1033,83 @@ int dindel_b200_submit(dindel_ctx *ctx, const dindel_batch_in *in, dindel_batch_
     int n_lanes = n_chunks > 1 ? DINDEL_NUM_LANES : 1;
     if (ctx->force_lanes >= 1 && ctx->force_lanes < n_lanes) n_lanes = ctx->force_lanes;
     for (int i = 0; i < n_lanes; i++) {
-        rc = ensure_lane(ctx, ctx->lane[i], max_units);
+        rc = ensure_lane(ctx, ctx->lane[i], whole_batch && i == 0 ? ctx->B.n_units : max_units);
         if (rc != DINDEL_OK) return rc;
     }
-    while ((int)ctx->evpool.size() < 4 * n_chunks) {
+    while ((int)ctx->evpool.size() < DINDEL_EV_PER_CHUNK * n_chunks) {
         cudaEvent_t e;
         CU(cudaEventCreate(&e));
         ctx->evpool.push_back(e);
     }
     cudaStream_t s_in = n_chunks > 1 ? ctx->s_in : ctx->stream;
     cudaStream_t s_out = n_chunks > 1 ? ctx->s_out : ctx->stream;
-    CU(cudaEventRecord(ctx->ev[0], s_in));
     int launches = 0, prep_launches = 0;
     std::vector<Range> rg((size_t)n_chunks);
-    for (int c = 0; c < n_chunks; c++) {
-        Range &g = rg[c];
-        Lane &ln = ctx->lane[c % n_lanes];
-        cudaEvent_t e_in = ctx->evpool[4 * c], e_k0 = ctx->evpool[4 * c + 1], e_k1 = ctx->evpool[4 * c + 2];
-        scan_range(ctx, in, bounds[c], bounds[c + 1], g); // host work, overlaps the GPU's earlier chunks
-        rc = copy_in_range(ctx, in, g, s_in);
-        if (rc != DINDEL_OK) return rc;
-        CU(cudaEventRecord(e_in, s_in));
-        CU(cudaStreamWaitEvent(ln.st, e_in, 0));
-        CU(cudaEventRecord(e_k0, ln.st));
-        rc = prep_range(ctx, g, ln, &prep_launches);
-        if (rc == DINDEL_OK) rc = k1_range(ctx, g, ln, &launches);
-        if (rc != DINDEL_OK) return rc;
-        CU(cudaEventRecord(e_k1, ln.st));
-        CU(cudaStreamWaitEvent(s_out, e_k1, 0));
-        rc = copy_out_range(ctx, out, g, s_out);
-        if (rc != DINDEL_OK) return rc;
+    rc = DINDEL_OK;
+    {
+        Nvtx nv("dindel_b200:pipeline(H2D|K1|D2H)");
+        cudaError_t ce = cudaEventRecord(ctx->ev[0], s_in);
+        for (int c = 0; c < n_chunks && rc == DINDEL_OK && ce == cudaSuccess; c++) {
+            Range &g = rg[c];
+            Lane &ln = ctx->lane[c % n_lanes];
+            cudaEvent_t *E = &ctx->evpool[(size_t)DINDEL_EV_PER_CHUNK * c];
+            {
+                Nvtx nv2("dindel_b200:scan");
+                scan_range(ctx, in, bounds[c], bounds[c + 1], g); // host work, overlaps the GPU's earlier chunks
+            }
+            ce = cudaEventRecord(E[0], s_in);
+            if (ce == cudaSuccess) rc = copy_in_range(ctx, in, g, s_in);
+            if (rc != DINDEL_OK) break;
+            if (ce == cudaSuccess) ce = cudaEventRecord(E[1], s_in);
+            if (ce == cudaSuccess) ce = cudaStreamWaitEvent(ln.st, E[1], 0);
+            if (ce == cudaSuccess) ce = cudaEventRecord(E[2], ln.st);
+            if (ce != cudaSuccess) break;
+            rc = prep_range(ctx, g, ln, &prep_launches);
+            if (rc == DINDEL_OK) rc = k1_range(ctx, g, ln, &launches);
+            if (rc != DINDEL_OK) break;
+            ce = cudaEventRecord(E[3], ln.st);
+            if (ce == cudaSuccess) ce = cudaStreamWaitEvent(s_out, E[3], 0);
+            if (ce == cudaSuccess) ce = cudaEventRecord(E[4], s_out);
+            if (ce != cudaSuccess) break;
+            rc = copy_out_range(ctx, out, g, s_out);
+            if (rc != DINDEL_OK) break;
+            ce = cudaEventRecord(E[5], s_out);
+        }
+        if (rc == DINDEL_OK && ce == cudaSuccess) ce = cudaEventRecord(ctx->ev[5], s_out);
+        if (rc == DINDEL_OK && ce != cudaSuccess)
+            rc = fail(ctx, DINDEL_E_CUDA, std::string("pipeline: ") + cudaGetErrorString(ce));
+        // Whatever happened, nothing may be in flight when we return: the copies reference the caller's buffers
+        // and the next range (or the caller) reuses ours.
+        cudaError_t se = cudaStreamSynchronize(s_out);
+        for (int i = 0; i < n_lanes; i++) { cudaError_t x = cudaStreamSynchronize(ctx->lane[i].st); if (se == cudaSuccess) se = x; }
+        { cudaError_t x = cudaStreamSynchronize(s_in); if (se == cudaSuccess) se = x; }
+        if (rc == DINDEL_OK && se != cudaSuccess) rc = fail(ctx, DINDEL_E_CUDA, std::string("pipeline sync: ") + cudaGetErrorString(se));
+        if (rc != DINDEL_OK) { drain(ctx); return rc; }
     }
-    CU(cudaEventRecord(ctx->ev[5], s_out));
-    CU(cudaStreamSynchronize(s_out));
-    for (int i = 0; i < n_lanes; i++) CU(cudaStreamSynchronize(ctx->lane[i].st));
-    CU(cudaStreamSynchronize(s_in));
-    if (out->win_pair) memcpy(out->win_pair, ctx->win_pair.data(), ((size_t)nw + 1) * 8);
     dindel_timing &t = ctx->timing;
-    t.k1_ms = 0.f;
-    for (int c = 0; c < n_chunks; c++) {
-        float ms = 0.f;
-        cudaEventElapsedTime(&ms, ctx->evpool[4 * c + 1], ctx->evpool[4 * c + 2]);
-        t.k1_ms += ms; // sum of the chunks' kernel spans (spans of the two lanes overlap)
+    {
+        float first_k = 1e30f, last_k = 0.f;
+        for (int c = 0; c < n_chunks; c++) {
+            cudaEvent_t *E = &ctx->evpool[(size_t)DINDEL_EV_PER_CHUNK * c];
+            float ms = 0.f, k0 = 0.f, k1 = 0.f;
+            cudaEventElapsedTime(&ms, E[0], E[1]); t.h2d_ms += ms;
+            cudaEventElapsedTime(&ms, E[4], E[5]); t.d2h_ms += ms;
+            cudaEventElapsedTime(&k0, ctx->ev[0], E[2]);
+            cudaEventElapsedTime(&k1, ctx->ev[0], E[3]);
+            if (k0 < first_k) first_k = k0;
+            if (k1 > last_k) last_k = k1;
+        }
+        t.k1_ms += last_k - first_k; // span from the first kernel's start to the last kernel's end (lanes overlap)
+        float tot = 0.f;
+        cudaEventElapsedTime(&tot, ctx->ev[0], ctx->ev[5]);
+        t.total_ms += tot;
     }
-    cudaEventElapsedTime(&t.total_ms, ctx->ev[0], ctx->ev[5]);
-    t.h2d_ms = t.prep_ms = t.d2h_ms = 0.f; // overlapped: not separable in a pipelined submit
-    t.k1_launches = launches;
-    t.prep_launches = prep_launches;
-    // the batch stays resident for K2 / K3 and for run()/download()
+    t.k1_launches += launches;
+    t.prep_launches += prep_launches;
+    t.n_chunks += n_chunks;
+    t.n_pairs += ctx->B.n_pairs;
+    t.n_cells += cells;
+    // the range is resident for the stages below (and, when it is the whole batch, for K2..K5 and run()/download())
     ctx->all = rg[0];
     for (int c = 1; c < n_chunks; c++) {
         ctx->all.use_tiled = ctx->all.use_tiled && rg[c].use_tiled;
@@ -992,17 +1121,154 @@ int dindel_b200_submit(dindel_ctx *ctx, const dindel_batch_in *in, dindel_batch_
         ctx->all.p1 = z.p1; ctx->all.u1 = z.u1;
         if (ctx->all.u1 - ctx->all.u0 >= 0xffffffffLL) ctx->all.use_tiled = false;
     }
-    rc = ensure_lane(ctx, ctx->lane[0], ctx->B.n_units);
-    if (rc != DINDEL_OK) return rc;
-    if (n_chunks > 1 && ctx->all.use_tiled) { // run() on the whole batch needs whole-batch unit lists
+    if (whole_batch && n_chunks > 1 && ctx->all.use_tiled) { // run() on the whole batch needs whole-batch unit lists
         int pl = 0;
         rc = prep_range(ctx, ctx->all, ctx->lane[0], &pl);
-        if (rc != DINDEL_OK) return rc;
+        if (rc != DINDEL_OK) { drain(ctx); return rc; }
         CU(cudaStreamSynchronize(ctx->lane[0].st));
     }
     ctx->resident = true;
     ctx->ran = true;
+    if (job->cover || job->pair_sums || job->em) {
+        Nvtx nv("dindel_b200:stages(K4|K2|K3)");
+        const auto t0 = std::chrono::steady_clock::now();
+        if (job->cover) {
+            rc = coverage_resident(ctx, job->cover, job->cover_out);
+            if (rc != DINDEL_OK) { drain(ctx); return rc; }
+        }
+        if (job->pair_sums) {
+            rc = sums_resident(ctx, job, sum_off);
+            if (rc != DINDEL_OK) { drain(ctx); return rc; }
+        }
+        if (job->em) {
+            rc = em_resident(ctx, job->em, job->em_out, false);
+            if (rc != DINDEL_OK) { drain(ctx); return rc; }
+        }
+        t.post_ms += 1e3f * std::chrono::duration<float>(std::chrono::steady_clock::now() - t0).count();
+    }
     return DINDEL_OK;
+}
+
+// bytes of device memory windows [w0, w1) take as a resident range
+static size_t range_bytes(dindel_ctx *ctx, const dindel_batch_in *in, int w0, int w1, int hstride)
+{
+    const long long nw = w1 - w0, nh = in->win_hap[w1] - in->win_hap[w0], nr = in->win_read[w1] - in->win_read[w0];
+    const long long hb = in->n_haps ? in->hap_off[in->win_hap[w1]] - in->hap_off[in->win_hap[w0]] : 0;
+    const long long rb = in->n_reads ? in->read_off[in->win_read[w1]] - in->read_off[in->win_read[w0]] : 0;
+    const long long np = ctx->win_pair[w1] - ctx->win_pair[w0], nu = ctx->win_unit[w1] - ctx->win_unit[w0];
+    return (size_t)(nw * 32 + nh * 10 + 2 * hb + nr * 24 + 2 * rb + np * (64 + 2LL * hstride) + nu * 8);
+}
+
+// dindel_b200_process on windows [W0, W1) of the job's batch (the whole batch, or one device's shard)
+static int process_windows(dindel_ctx *ctx, const dindel_job *job, int W0, int W1, bool validated)
+{
+    if (!ctx || !job || !job->in || !job->out) return fail(ctx, DINDEL_E_INVALID, "null job / in / out");
+    const auto t_host0 = std::chrono::steady_clock::now();
+    TraceTimer tt(ctx->trace ? &ctx->t_submit : nullptr);
+    if (ctx->trace && ++ctx->n_submit % 50 == 0)
+        fprintf(stderr, "dindel_b200 trace: %ld submits %.3f s, %ld coverage calls %.3f s, create %.3f s\n", ctx->n_submit,
+                ctx->t_submit, ctx->n_cover, ctx->t_cover, ctx->t_create);
+    const dindel_batch_in *in = job->in;
+    dindel_batch_out *out = job->out;
+    int rc;
+    {
+        Nvtx nv("dindel_b200:index");
+        rc = index_batch(ctx, in, validated);
+        if (rc != DINDEL_OK) return rc;
+    }
+    memset(&ctx->timing, 0, sizeof(ctx->timing));
+    rc = check_out(ctx, out, !(job->cover || job->pair_sums || job->em));
+    if (rc != DINDEL_OK) return rc;
+    if ((job->cover && !job->cover_out) || (job->em && !job->em_out)) return fail(ctx, DINDEL_E_INVALID, "stage without its output struct");
+    if (job->pair_sums && job->n_groups > 0 && !job->read_group) return fail(ctx, DINDEL_E_INVALID, "n_groups without read_group");
+    if (job->n_groups < 0) return fail(ctx, DINDEL_E_INVALID, "n_groups");
+    const int nw = in->n_windows;
+    if (W0 < 0 || W1 > nw || W0 > W1) return fail(ctx, DINDEL_E_INVALID, "window range");
+    if (out->win_pair && W0 == 0 && W1 == nw) memcpy(out->win_pair, ctx->win_pair.data(), ((size_t)nw + 1) * 8);
+    std::vector<long long> sum_off;
+    if (job->pair_sums || job->win_sum_off) {
+        sum_off.assign((size_t)nw + 1, 0);
+        for (int w = 0; w < nw; w++) {
+            const long long nh = ctx->win_nh[w];
+            if (nh > 2048) return fail(ctx, DINDEL_E_UNSUPPORTED, "more than 2048 haplotypes in a window (pair sums)");
+            sum_off[w + 1] = sum_off[w] + nh * (nh + 1) / 2;
+        }
+        if (job->win_sum_off && W0 == 0 && W1 == nw) memcpy(job->win_sum_off, sum_off.data(), ((size_t)nw + 1) * 8);
+    }
+    if (W0 == W1) return DINDEL_OK;
+    const bool keep_hpos = (out->flags & DINDEL_OUT_KEEP_HPOS) != 0 || job->cover != nullptr; // rows stay in HBM for K4 / K5
+    const int want_hpos = (out->hpos != nullptr || keep_hpos) ? 1 : 0;
+    int hstride = 0;
+    if (want_hpos) {
+        if (out->hpos) hstride = out->hpos_stride;
+        else {
+            long long maxR = 0;
+            for (int r = in->win_read[W0]; r < in->win_read[W1]; r++) {
+                const long long l = in->read_off[r + 1] - in->read_off[r];
+                if (l > maxR) maxR = l;
+            }
+            hstride = (int)((maxR + 7) & ~7LL);
+            if (hstride < 8) hstride = 8;
+        }
+    }
+    // ranges: greedy, as many windows as fit the device-memory budget
+    std::vector<int> rb(1, W0);
+    {
+        int a = W0;
+        while (a < W1) {
+            int lo = a + 1, hi = W1; // largest b with bytes(a, b) <= budget (at least one window)
+            if (range_bytes(ctx, in, a, W1, hstride) > ctx->mem_budget) {
+                while (lo < hi) {
+                    const int mid = lo + (hi - lo + 1) / 2;
+                    if (range_bytes(ctx, in, a, mid, hstride) <= ctx->mem_budget) lo = mid; else hi = mid - 1;
+                }
+            } else lo = W1;
+            rb.push_back(lo);
+            a = lo;
+        }
+    }
+    const int n_ranges = (int)rb.size() - 1;
+    const bool whole = n_ranges == 1 && W0 == 0 && W1 == nw;
+    for (int k = 0; k < n_ranges; k++) {
+        rc = run_range(ctx, job, rb[k], rb[k + 1], want_hpos, hstride, sum_off, whole);
+        if (rc != DINDEL_OK) return rc;
+    }
+    ctx->timing.n_ranges = n_ranges;
+    if (!whole) { ctx->resident = false; ctx->ran = false; } // K2..K5 / run() need the whole batch in HBM
+    ctx->timing.host_ms = 1e3f * std::chrono::duration<float>(std::chrono::steady_clock::now() - t_host0).count();
+    return DINDEL_OK;
+}
+
+int dindel_b200_process(dindel_ctx *ctx, const dindel_job *job)
+{
+    if (!ctx || !job || !job->in) return fail(ctx, DINDEL_E_INVALID, "null job");
+    return process_windows(ctx, job, 0, job->in->n_windows, false);
+}
+
+// computeLikelihoods for a whole batch, host buffers in and out
+int dindel_b200_submit(dindel_ctx *ctx, const dindel_batch_in *in, dindel_batch_out *out)
+{
+    if (!ctx || !out || !in) return DINDEL_E_INVALID;
+    dindel_job job;
+    memset(&job, 0, sizeof(job));
+    job.in = in; job.out = out;
+    return process_windows(ctx, &job, 0, in->n_windows, false);
+}
+
+int64_t dindel_b200_count_sums(const dindel_batch_in *in)
+{
+    if (validate(in) != DINDEL_OK) return -1;
+    int64_t n = 0;
+    for (int w = 0; w < in->n_windows; w++) {
+        const int64_t nh = in->win_hap[w + 1] - in->win_hap[w];
+        n += nh * (nh + 1) / 2;
+    }
+    return n;
+}
+
+double dindel_b200_sum_error_bound(int64_t n_terms, double magnitude)
+{
+    return 4.0 * (double)(n_terms < 1 ? 1 : n_terms) * (2.22e-16 * fabs(magnitude) + 1e-15);
 }
 
 int dindel_b200_sync(dindel_ctx *ctx)
@@ -1025,101 +1291,234 @@ int dindel_b200_get_timing(const dindel_ctx *ctx, dindel_timing *t)
     return DINDEL_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// the stages on the resident range [base.w0, base.w1): caller arrays are indexed over the WHOLE batch, the
+// range's slices are uploaded and the device pointers rebased like the batch's own
+// ------------------------------------------------------------------------------------------
+static int launch_k2(dindel_ctx *ctx, const std::vector<int32_t> &jw, const std::vector<int32_t> &jg,
+                     const std::vector<long long> &joff, const double *start, const int32_t *read_group,
+                     double *out_host, int max_npairs)
+{
+    const K1Batch &B = ctx->B;
+    const Range &b = ctx->base;
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const size_t nj = jw.size(), nv = (size_t)joff[nj];
+    if (nj == 0) return DINDEL_OK;
+    CU(ctx->d_x[0].ensure(nj * 4)); CU(ctx->d_x[1].ensure(nj * 4)); CU(ctx->d_x[2].ensure((nj + 1) * 8));
+    CU(ctx->d_x[4].ensure(nv * 8 + 8));
+    CU(cudaMemcpyAsync(ctx->d_x[0].p, jw.data(), nj * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(ctx->d_x[1].p, jg.data(), nj * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(ctx->d_x[2].p, joff.data(), (nj + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (start && nv) {
+        CU(ctx->d_x[3].ensure(nv * 8 + 8));
+        CU(cudaMemcpyAsync(ctx->d_x[3].p, start, nv * 8, cudaMemcpyHostToDevice, st));
+    }
+    const size_t nr = (size_t)(b.r1 - b.r0);
+    if (read_group) {
+        CU(ctx->d_x[5].ensure(nr * 4 + 8));
+        if (nr) CU(cudaMemcpyAsync(ctx->d_x[5].p, read_group + b.r0, nr * 4, cudaMemcpyHostToDevice, st));
+    }
+    K2Args a;
+    a.n_jobs = (int)nj;
+    a.job_window = (const int32_t *)ctx->d_x[0].p; a.job_group = (const int32_t *)ctx->d_x[1].p;
+    a.job_off = (const long long *)ctx->d_x[2].p; a.start = start ? (const double *)ctx->d_x[3].p : nullptr;
+    a.read_group = read_group ? (const int32_t *)ctx->d_x[5].p - b.r0 : nullptr;
+    a.out = (double *)ctx->d_x[4].p;
+    a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.pairs = B.pairs;
+    volatile double half = 0.5;
+    a.log_half = log(half); // DInDel.cpp:3088 log(0.5), host libm
+    CU(cudaEventRecord(ctx->ev_k[0], st));
+    CU(k2_launch(&a, max_npairs, st));
+    CU(cudaEventRecord(ctx->ev_k[1], st));
+    if (nv) CU(cudaMemcpyAsync(out_host, a.out, nv * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev_k[0], ctx->ev_k[1]);
+    return DINDEL_OK;
+}
+
+__global__ void k_fill_ll(long long n, const double *ll, dindel_pair_out *pairs)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    dindel_pair_out o;
+    memset(&o, 0, sizeof(o));
+    o.ll = ll[i];
+    pairs[i] = o;
+}
+
+int dindel_b200_load_likelihoods(dindel_ctx *ctx, int32_t n_windows, const int32_t *win_hap, const int32_t *win_read,
+                                 const double *ll)
+{
+    if (!ctx || n_windows < 1 || !win_hap || !win_read || !ll) return fail(ctx, DINDEL_E_INVALID, "load_likelihoods");
+    if (win_hap[0] != 0 || win_read[0] != 0) return fail(ctx, DINDEL_E_INVALID, "win_hap / win_read must start at 0");
+    for (int w = 0; w < n_windows; w++)
+        if (win_hap[w + 1] < win_hap[w] || win_read[w + 1] < win_read[w]) return fail(ctx, DINDEL_E_INVALID, "CSR not monotone");
+    // a batch without sequences: only the window index arrays and the pair records exist on the device
+    const int nh = win_hap[n_windows], nr = win_read[n_windows];
+    std::vector<int64_t> hap_off((size_t)nh + 1, 0), read_off((size_t)nr + 1, 0);
+    std::vector<uint32_t> hs((size_t)n_windows, 0);
+    std::vector<uint8_t> z8((size_t)(nr ? nr : 1), 0);
+    std::vector<uint32_t> z32((size_t)(nr ? nr : 1), 0);
+    dindel_batch_in in;
+    memset(&in, 0, sizeof(in));
+    in.n_windows = n_windows; in.n_haps = nh; in.n_reads = nr;
+    in.hap_start = hs.data(); in.win_hap = win_hap; in.win_read = win_read;
+    in.hap_off = hap_off.data(); in.hap_seq = ""; in.read_off = read_off.data(); in.read_seq = ""; in.read_qual = z8.data();
+    in.read_mapq = z8.data(); in.read_start = z32.data(); in.read_flags = z8.data();
+    int rc = index_batch(ctx, &in, false);
+    if (rc != DINDEL_OK) return rc;
+    memset(&ctx->timing, 0, sizeof(ctx->timing));
+    rc = prepare_range(ctx, &in, 0, n_windows, 0, 0);
+    if (rc != DINDEL_OK) return rc;
+    cudaStream_t st = ctx->stream;
+    scan_range(ctx, &in, 0, n_windows, ctx->all);
+    rc = copy_in_range(ctx, &in, ctx->all, st);
+    if (rc != DINDEL_OK) { drain(ctx); return rc; }
+    const long long np = ctx->B.n_pairs;
+    if (np > 0) {
+        CU(ctx->d_x[7].ensure((size_t)np * 8));
+        CU(cudaMemcpyAsync(ctx->d_x[7].p, ll, (size_t)np * 8, cudaMemcpyHostToDevice, st));
+        k_fill_ll<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(np, (const double *)ctx->d_x[7].p, (dindel_pair_out *)ctx->d_pairs.p);
+        CU(cudaGetLastError());
+    }
+    CU(cudaStreamSynchronize(st));
+    ctx->resident = true;
+    ctx->ran = true;
+    return DINDEL_OK;
+}
+
 int dindel_b200_pair_sums(dindel_ctx *ctx, const dindel_pairsum_in *in, double *out)
 {
     if (!ctx || !in || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "pair_sums needs a resident, computed batch");
     if (in->n_jobs < 0) return fail(ctx, DINDEL_E_INVALID, "n_jobs");
     if (in->n_jobs == 0) return DINDEL_OK;
-    if (!in->job_window || !in->job_group || !in->job_off || !in->start || !out) return fail(ctx, DINDEL_E_INVALID, "null array");
-    const K1Batch &B = ctx->B;
+    if (!in->job_window || !in->job_group || !in->job_off || !out) return fail(ctx, DINDEL_E_INVALID, "null array");
+    const Range &b = ctx->base;
+    std::vector<int32_t> jw(in->job_window, in->job_window + in->n_jobs), jg(in->job_group, in->job_group + in->n_jobs);
+    std::vector<long long> joff((size_t)in->n_jobs + 1);
+    int max_np = 1;
     for (int j = 0; j < in->n_jobs; j++) {
         int w = in->job_window[j];
-        if (w < 0 || w >= B.n_windows) return fail(ctx, DINDEL_E_INVALID, "job_window out of range");
+        if (w < b.w0 || w >= b.w1) return fail(ctx, DINDEL_E_INVALID, "job_window outside the resident range");
         const long long nh = ctx->win_nh[w];
+        if (nh > 2048) return fail(ctx, DINDEL_E_UNSUPPORTED, "more than 2048 haplotypes in a window (pair sums)");
         if (in->job_off[j + 1] - in->job_off[j] != nh * (nh + 1) / 2) return fail(ctx, DINDEL_E_INVALID, "job_off does not match nh*(nh+1)/2");
+        if (nh * (nh + 1) / 2 > max_np) max_np = (int)(nh * (nh + 1) / 2);
+    }
+    if (in->job_off[0] != 0) return fail(ctx, DINDEL_E_INVALID, "job_off[0] != 0");
+    for (int j = 0; j <= in->n_jobs; j++) joff[j] = in->job_off[j];
+    return launch_k2(ctx, jw, jg, joff, in->start, in->read_group, out, max_np);
+}
+
+// job->pair_sums for the windows of the resident range
+static int sums_resident(dindel_ctx *ctx, const dindel_job *job, const std::vector<long long> &sum_off)
+{
+    const Range &b = ctx->base;
+    const int G = job->n_groups > 0 ? job->n_groups : 1;
+    std::vector<int32_t> jw, jg;
+    std::vector<long long> joff(1, 0);
+    jw.reserve((size_t)(b.w1 - b.w0) * G); jg.reserve(jw.capacity()); joff.reserve(jw.capacity() + 1);
+    int max_np = 1;
+    for (int w = b.w0; w < b.w1; w++) {
+        const long long np = sum_off[w + 1] - sum_off[w];
+        if (np > max_np) max_np = (int)np;
+        for (int g = 0; g < G; g++) {
+            jw.push_back(w);
+            jg.push_back(job->n_groups > 0 ? g : -1);
+            joff.push_back(joff.back() + np);
+        }
+    }
+    return launch_k2(ctx, jw, jg, joff, nullptr, job->n_groups > 0 ? job->read_group : nullptr,
+                     job->pair_sums + sum_off[b.w0] * G, max_np);
+}
+
+// sets [s0, s1) of `in` (all inside the resident range) through K3
+static int em_sets(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out *out, size_t s0, size_t s1)
+{
+    const K1Batch &B = ctx->B;
+    if (s1 <= s0) return DINDEL_OK;
+    int max_nh = 1, max_nr = 1;
+    for (size_t s = s0; s < s1; s++) {
+        const int w = in->set_window[s];
+        const long long nh = ctx->win_nh[w];
+        if (in->set_off[s + 1] - in->set_off[s] != nh) return fail(ctx, DINDEL_E_INVALID, "set_off does not match nh");
+        if (nh > k3_max_haps()) return fail(ctx, DINDEL_E_UNSUPPORTED, "more than 64 haplotypes in a window");
+        const long long np = ctx->win_pair[w + 1] - ctx->win_pair[w];
+        const int nr = nh ? (int)(np / nh) : 0;
+        if (nh > max_nh) max_nh = (int)nh;
+        if (nr > max_nr) max_nr = nr;
     }
     CU(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
-    const size_t nj = (size_t)in->n_jobs, nv = (size_t)in->job_off[in->n_jobs];
-    CU(ctx->d_x[0].ensure(nj * 4)); CU(ctx->d_x[1].ensure(nj * 4)); CU(ctx->d_x[2].ensure((nj + 1) * 8));
-    CU(ctx->d_x[3].ensure(nv * 8 + 8)); CU(ctx->d_x[4].ensure(nv * 8 + 8));
-    CU(cudaMemcpyAsync(ctx->d_x[0].p, in->job_window, nj * 4, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(ctx->d_x[1].p, in->job_group, nj * 4, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(ctx->d_x[2].p, in->job_off, (nj + 1) * 8, cudaMemcpyHostToDevice, st));
-    if (nv) CU(cudaMemcpyAsync(ctx->d_x[3].p, in->start, nv * 8, cudaMemcpyHostToDevice, st));
-    if (in->read_group) {
-        CU(ctx->d_x[5].ensure((size_t)B.n_reads * 4 + 8));
-        if (B.n_reads) CU(cudaMemcpyAsync(ctx->d_x[5].p, in->read_group, (size_t)B.n_reads * 4, cudaMemcpyHostToDevice, st));
-    }
-    K2Args a;
-    a.n_jobs = in->n_jobs;
-    a.job_window = (const int32_t *)ctx->d_x[0].p; a.job_group = (const int32_t *)ctx->d_x[1].p;
-    a.job_off = (const long long *)ctx->d_x[2].p; a.start = (const double *)ctx->d_x[3].p;
-    a.read_group = in->read_group ? (const int32_t *)ctx->d_x[5].p : nullptr;
-    a.out = (double *)ctx->d_x[4].p;
+    const size_t ns = s1 - s0, v0 = (size_t)in->set_off[s0], nv = (size_t)in->set_off[s1] - v0;
+    CU(ctx->d_x[0].ensure(ns * 4)); CU(ctx->d_x[1].ensure((ns + 1) * 8)); CU(ctx->d_x[2].ensure(nv + 8));
+    CU(ctx->d_x[3].ensure(ns * 8 * 3 + 8)); CU(ctx->d_x[4].ensure(ns * 4)); CU(ctx->d_x[5].ensure(nv * 8 + 8));
+    CU(ctx->d_x[6].ensure(nv * 8 + 8));
+    CU(cudaMemcpyAsync(ctx->d_x[0].p, in->set_window + s0, ns * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(ctx->d_x[1].p, in->set_off + s0, (ns + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (nv) CU(cudaMemcpyAsync(ctx->d_x[2].p, in->compatible + v0, nv, cudaMemcpyHostToDevice, st));
+    K3Args a;
+    a.n_sets = (int)ns;
+    a.set_window = (const int32_t *)ctx->d_x[0].p; a.set_off = (const long long *)ctx->d_x[1].p;
+    a.compatible = (const uint8_t *)ctx->d_x[2].p - v0;   // set_off values stay absolute
+    a.a0 = in->a0; a.tol = in->tol;
+    a.loglik = (double *)ctx->d_x[3].p; a.margin = a.loglik + ns; a.energy = a.margin + ns;
+    a.iters = (int32_t *)ctx->d_x[4].p;
+    a.pi = (double *)ctx->d_x[5].p - v0; a.freqs = (double *)ctx->d_x[6].p - v0;
     a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.pairs = B.pairs;
-    volatile double half = 0.5;
-    a.log_half = log(half); // DInDel.cpp:3091 log(0.5), host libm
     CU(cudaEventRecord(ctx->ev_k[0], st));
-    CU(k2_launch(&a, st));
+    CU(k3_launch(&a, max_nh, max_nr, ctx->smem_optin, st));
     CU(cudaEventRecord(ctx->ev_k[1], st));
-    if (nv) CU(cudaMemcpyAsync(out, a.out, nv * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out->loglik + s0, a.loglik, ns * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out->iters + s0, a.iters, ns * 4, cudaMemcpyDeviceToHost, st));
+    if (out->margin) CU(cudaMemcpyAsync(out->margin + s0, a.margin, ns * 8, cudaMemcpyDeviceToHost, st));
+    if (out->energy) CU(cudaMemcpyAsync(out->energy + s0, a.energy, ns * 8, cudaMemcpyDeviceToHost, st));
+    if (nv) {
+        CU(cudaMemcpyAsync(out->pi + v0, ctx->d_x[5].p, nv * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(out->freqs + v0, ctx->d_x[6].p, nv * 8, cudaMemcpyDeviceToHost, st));
+    }
     CU(cudaStreamSynchronize(st));
     cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev_k[0], ctx->ev_k[1]);
     return DINDEL_OK;
+}
+
+// need_all: every set must lie in the resident range (the stand-alone entry); else only the range's slice of the
+// (ascending) set list is run (dindel_b200_process)
+static int em_resident(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out *out, bool need_all)
+{
+    if (in->n_sets < 0) return fail(ctx, DINDEL_E_INVALID, "n_sets");
+    if (in->n_sets == 0) return DINDEL_OK;
+    if (!in->set_window || !in->set_off || !in->compatible || !out->loglik || !out->iters || !out->pi || !out->freqs)
+        return fail(ctx, DINDEL_E_INVALID, "null array");
+    const Range &b = ctx->base;
+    size_t s0 = 0, s1 = (size_t)in->n_sets;
+    if (need_all) {
+        for (int s = 0; s < in->n_sets; s++)
+            if (in->set_window[s] < b.w0 || in->set_window[s] >= b.w1) return fail(ctx, DINDEL_E_INVALID, "set_window outside the resident range");
+    } else {
+        for (int s = 1; s < in->n_sets; s++)
+            if (in->set_window[s] < in->set_window[s - 1]) return fail(ctx, DINDEL_E_INVALID, "set_window must be ascending in dindel_b200_process");
+        while (s0 < s1 && in->set_window[s0] < b.w0) s0++;
+        size_t e = s0;
+        while (e < s1 && in->set_window[e] < b.w1) e++;
+        s1 = e;
+    }
+    return em_sets(ctx, in, out, s0, s1);
 }
 
 int dindel_b200_bayes_em(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out *out)
 {
     if (!ctx || !in || !out || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "bayes_em needs a resident, computed batch");
-    if (in->n_sets < 0) return fail(ctx, DINDEL_E_INVALID, "n_sets");
-    if (in->n_sets == 0) return DINDEL_OK;
-    if (!in->set_window || !in->set_off || !in->compatible || !out->loglik || !out->iters || !out->pi || !out->freqs)
-        return fail(ctx, DINDEL_E_INVALID, "null array");
-    const K1Batch &B = ctx->B;
-    for (int s = 0; s < in->n_sets; s++) {
-        int w = in->set_window[s];
-        if (w < 0 || w >= B.n_windows) return fail(ctx, DINDEL_E_INVALID, "set_window out of range");
-        if (in->set_off[s + 1] - in->set_off[s] != ctx->win_nh[w]) return fail(ctx, DINDEL_E_INVALID, "set_off does not match nh");
-        if (in->set_off[s + 1] - in->set_off[s] > k3_max_haps()) return fail(ctx, DINDEL_E_UNSUPPORTED, "more than 64 haplotypes in a window");
-    }
-    CU(cudaSetDevice(ctx->device));
-    cudaStream_t st = ctx->stream;
-    const size_t ns = (size_t)in->n_sets, nv = (size_t)in->set_off[in->n_sets];
-    CU(ctx->d_x[0].ensure(ns * 4)); CU(ctx->d_x[1].ensure((ns + 1) * 8)); CU(ctx->d_x[2].ensure(nv + 8));
-    CU(ctx->d_x[3].ensure(ns * 8)); CU(ctx->d_x[4].ensure(ns * 4)); CU(ctx->d_x[5].ensure(nv * 8 + 8));
-    CU(ctx->d_x[6].ensure(nv * 8 + 8));
-    CU(cudaMemcpyAsync(ctx->d_x[0].p, in->set_window, ns * 4, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(ctx->d_x[1].p, in->set_off, (ns + 1) * 8, cudaMemcpyHostToDevice, st));
-    if (nv) CU(cudaMemcpyAsync(ctx->d_x[2].p, in->compatible, nv, cudaMemcpyHostToDevice, st));
-    K3Args a;
-    a.n_sets = in->n_sets;
-    a.set_window = (const int32_t *)ctx->d_x[0].p; a.set_off = (const long long *)ctx->d_x[1].p;
-    a.compatible = (const uint8_t *)ctx->d_x[2].p;
-    a.a0 = in->a0; a.tol = in->tol;
-    a.loglik = (double *)ctx->d_x[3].p; a.iters = (int32_t *)ctx->d_x[4].p;
-    a.pi = (double *)ctx->d_x[5].p; a.freqs = (double *)ctx->d_x[6].p;
-    a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.pairs = B.pairs;
-    CU(cudaEventRecord(ctx->ev_k[0], st));
-    CU(k3_launch(&a, st));
-    CU(cudaEventRecord(ctx->ev_k[1], st));
-    CU(cudaMemcpyAsync(out->loglik, a.loglik, ns * 8, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(out->iters, a.iters, ns * 4, cudaMemcpyDeviceToHost, st));
-    if (nv) {
-        CU(cudaMemcpyAsync(out->pi, a.pi, nv * 8, cudaMemcpyDeviceToHost, st));
-        CU(cudaMemcpyAsync(out->freqs, a.freqs, nv * 8, cudaMemcpyDeviceToHost, st));
-    }
-    CU(cudaStreamSynchronize(st));
-    cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev_k[0], ctx->ev_k[1]);
-    return DINDEL_OK;
+    return em_resident(ctx, in, out, true);
 }
 
-int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cover_out *out)
+static int coverage_resident(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cover_out *out)
 {
-    if (!ctx || !in || !out || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "coverage needs a resident, computed batch");
     TraceTimer tt(ctx->trace ? &ctx->t_cover : nullptr);
     ctx->n_cover++;
     const K1Batch &B = ctx->B;
+    const Range &b = ctx->base;
     if (!B.hpos) return fail(ctx, DINDEL_E_INVALID, "coverage needs the hpos rows resident (upload(want_hpos) or DINDEL_OUT_KEEP_HPOS)");
     if (in->n_entries < 0 || in->n_keys < 0) return fail(ctx, DINDEL_E_INVALID, "n_entries / n_keys");
     if (!in->win_entry || !in->win_key || !out->hap_filtered || (in->n_keys && (!out->key_nf || !out->key_nr)))
@@ -1127,11 +1526,11 @@ int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cove
     if (in->n_entries && (!in->entry_hap || !in->entry_key || !in->entry_type || !in->entry_left || !in->entry_right))
         return fail(ctx, DINDEL_E_INVALID, "null array");
     if (B.n_reads && !in->read_strand) return fail(ctx, DINDEL_E_INVALID, "read_strand");
-    const int nw = B.n_windows;
-    if (in->win_entry[0] != 0 || in->win_key[0] != 0 || in->win_entry[nw] != in->n_entries || in->win_key[nw] != in->n_keys)
+    const int nwt = ctx->idx_windows;
+    if (in->win_entry[0] != 0 || in->win_key[0] != 0 || in->win_entry[nwt] != in->n_entries || in->win_key[nwt] != in->n_keys)
         return fail(ctx, DINDEL_E_INVALID, "win_entry / win_key do not span the entries / keys");
     size_t smem = 0;
-    for (int w = 0; w < nw; w++) {
+    for (int w = b.w0; w < b.w1; w++) {
         const long long ne = in->win_entry[w + 1] - in->win_entry[w], nk = in->win_key[w + 1] - in->win_key[w];
         if (ne < 0 || nk < 0) return fail(ctx, DINDEL_E_INVALID, "win_entry / win_key not monotone");
         const int nh = ctx->win_nh[w];
@@ -1149,9 +1548,11 @@ int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cove
     if (smem > ctx->smem_optin) return fail(ctx, DINDEL_E_UNSUPPORTED, "window has too many (variant entries x reads) for one CTA's shared memory");
     CU(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
-    const size_t ne = (size_t)in->n_entries, nk = (size_t)in->n_keys, nh = (size_t)B.n_haps, nr = (size_t)B.n_reads;
+    const size_t nw = (size_t)(b.w1 - b.w0), nh = (size_t)(b.h1 - b.h0), nr = (size_t)(b.r1 - b.r0);
+    const size_t e0 = (size_t)in->win_entry[b.w0], ne = (size_t)in->win_entry[b.w1] - e0;
+    const size_t k0 = (size_t)in->win_key[b.w0], nk = (size_t)in->win_key[b.w1] - k0;
     // one staging buffer: [win_entry | win_key | entry_hap | entry_key | entry_left | entry_right | entry_type | read_strand]
-    const size_t o_we = 0, o_wk = o_we + ((size_t)nw + 1) * 8, o_eh = o_wk + ((size_t)nw + 1) * 8, o_ek = o_eh + ne * 4,
+    const size_t o_we = 0, o_wk = o_we + (nw + 1) * 8, o_eh = o_wk + (nw + 1) * 8, o_ek = o_eh + ne * 4,
                  o_el = o_ek + ne * 4, o_er = o_el + ne * 4, o_et = o_er + ne * 4, o_rs = o_et + ((ne + 7) & ~(size_t)7),
                  in_bytes = o_rs + ((nr + 7) & ~(size_t)7);
     // results: [key_nf | key_nr | hap_filtered | hap_uncovered]
@@ -1160,51 +1561,61 @@ int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cove
     CU(ctx->d_x[0].ensure(in_bytes + 16));
     CU(ctx->d_x[1].ensure(out_bytes + 16));
     char *d_in = (char *)ctx->d_x[0].p, *d_out = (char *)ctx->d_x[1].p;
-    CU(cudaMemcpyAsync(d_in + o_we, in->win_entry, ((size_t)nw + 1) * 8, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(d_in + o_wk, in->win_key, ((size_t)nw + 1) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_in + o_we, in->win_entry + b.w0, (nw + 1) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_in + o_wk, in->win_key + b.w0, (nw + 1) * 8, cudaMemcpyHostToDevice, st));
     if (ne) {
-        CU(cudaMemcpyAsync(d_in + o_eh, in->entry_hap, ne * 4, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(d_in + o_ek, in->entry_key, ne * 4, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(d_in + o_el, in->entry_left, ne * 4, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(d_in + o_er, in->entry_right, ne * 4, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(d_in + o_et, in->entry_type, ne, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_eh, in->entry_hap + e0, ne * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_ek, in->entry_key + e0, ne * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_el, in->entry_left + e0, ne * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_er, in->entry_right + e0, ne * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_et, in->entry_type + e0, ne, cudaMemcpyHostToDevice, st));
     }
-    if (nr) CU(cudaMemcpyAsync(d_in + o_rs, in->read_strand, nr, cudaMemcpyHostToDevice, st));
+    if (nr) CU(cudaMemcpyAsync(d_in + o_rs, in->read_strand + b.r0, nr, cudaMemcpyHostToDevice, st));
     K4Args a;
     a.maxMismatch = in->maxMismatch; a.doFilter = in->doFilter;
-    a.win_entry = (const long long *)(d_in + o_we); a.win_key = (const long long *)(d_in + o_wk);
-    a.entry_hap = (const int32_t *)(d_in + o_eh); a.entry_key = (const int32_t *)(d_in + o_ek);
-    a.entry_left = (const int32_t *)(d_in + o_el); a.entry_right = (const int32_t *)(d_in + o_er);
-    a.entry_type = (const uint8_t *)(d_in + o_et); a.read_strand = (const uint8_t *)(d_in + o_rs);
-    a.key_nf = (int32_t *)(d_out + r_nf); a.key_nr = (int32_t *)(d_out + r_nr);
-    a.hap_filtered = (uint8_t *)(d_out + r_hf); a.hap_uncovered = (uint8_t *)(d_out + r_hu);
+    a.w_begin = b.w0;
+    // win_entry / win_key values stay absolute: the arrays they index are rebased by e0 / k0
+    a.win_entry = (const long long *)(d_in + o_we) - b.w0; a.win_key = (const long long *)(d_in + o_wk) - b.w0;
+    a.entry_hap = (const int32_t *)(d_in + o_eh) - e0; a.entry_key = (const int32_t *)(d_in + o_ek) - e0;
+    a.entry_left = (const int32_t *)(d_in + o_el) - e0; a.entry_right = (const int32_t *)(d_in + o_er) - e0;
+    a.entry_type = (const uint8_t *)(d_in + o_et) - e0; a.read_strand = (const uint8_t *)(d_in + o_rs) - b.r0;
+    a.key_nf = (int32_t *)(d_out + r_nf) - k0; a.key_nr = (int32_t *)(d_out + r_nr) - k0;
+    a.hap_filtered = (uint8_t *)(d_out + r_hf) - b.h0; a.hap_uncovered = (uint8_t *)(d_out + r_hu) - b.h0;
     a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.hap_off = B.hap_off; a.read_off = B.read_off;
     a.hap_seq = B.hap_seq; a.read_seq = B.read_seq; a.pairs = B.pairs; a.hpos = B.hpos; a.hpos_stride = B.hpos_stride;
     CU(cudaEventRecord(ctx->ev_k[0], st));
-    CU(k4_launch(&a, nw, smem, st));
+    CU(k4_launch(&a, (int)nw, smem, st));
     CU(cudaEventRecord(ctx->ev_k[1], st));
     if (nk) {
-        CU(cudaMemcpyAsync(out->key_nf, a.key_nf, nk * 4, cudaMemcpyDeviceToHost, st));
-        CU(cudaMemcpyAsync(out->key_nr, a.key_nr, nk * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(out->key_nf + k0, d_out + r_nf, nk * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(out->key_nr + k0, d_out + r_nr, nk * 4, cudaMemcpyDeviceToHost, st));
     }
     if (nh) {
-        CU(cudaMemcpyAsync(out->hap_filtered, a.hap_filtered, nh, cudaMemcpyDeviceToHost, st));
-        if (out->hap_uncovered) CU(cudaMemcpyAsync(out->hap_uncovered, a.hap_uncovered, nh, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(out->hap_filtered + b.h0, d_out + r_hf, nh, cudaMemcpyDeviceToHost, st));
+        if (out->hap_uncovered) CU(cudaMemcpyAsync(out->hap_uncovered + b.h0, d_out + r_hu, nh, cudaMemcpyDeviceToHost, st));
     }
     CU(cudaStreamSynchronize(st));
     cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev_k[0], ctx->ev_k[1]);
     return DINDEL_OK;
 }
 
+int dindel_b200_coverage(dindel_ctx *ctx, const dindel_cover_in *in, dindel_cover_out *out)
+{
+    if (!ctx || !in || !out || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "coverage needs a resident, computed batch");
+    if (ctx->base.w0 != 0 || ctx->base.w1 != ctx->idx_windows) return fail(ctx, DINDEL_E_INVALID, "coverage needs the whole batch resident");
+    return coverage_resident(ctx, in, out);
+}
+
 int dindel_b200_cigars(dindel_ctx *ctx, const dindel_cigar_in *in, dindel_cigar_out *out)
 {
     if (!ctx || !in || !out || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "cigars needs a resident, computed batch");
+    if (ctx->base.w0 != 0 || ctx->base.w1 != ctx->idx_windows) return fail(ctx, DINDEL_E_INVALID, "cigars needs the whole batch resident");
     const K1Batch &B = ctx->B;
     if (!B.hpos) return fail(ctx, DINDEL_E_INVALID, "cigars needs the hpos rows resident (upload(want_hpos) or DINDEL_OUT_KEEP_HPOS)");
     if (in->mode != DINDEL_CIGAR_PAIR && in->mode != DINDEL_CIGAR_BEST) return fail(ctx, DINDEL_E_INVALID, "mode");
     if (in->cigar_cap < 1) return fail(ctx, DINDEL_E_INVALID, "cigar_cap");
     const size_t nw = (size_t)B.n_windows, nh = (size_t)B.n_haps, nr = (size_t)B.n_reads, cap = (size_t)in->cigar_cap;
-    const size_t nb = (size_t)ctx->hap_bases;
+    const size_t nb = (size_t)ctx->hap_bases_total;
     if (!in->win_ref_start || (nb && !in->hap_ref_pos)) return fail(ctx, DINDEL_E_INVALID, "null array");
     if (in->mode == DINDEL_CIGAR_PAIR && (!in->win_h1 || !in->win_h2 || (nh && !in->hap_n_indels)))
         return fail(ctx, DINDEL_E_INVALID, "PAIR mode needs win_h1 / win_h2 / hap_n_indels");
@@ -1237,9 +1648,9 @@ int dindel_b200_cigars(dindel_ctx *ctx, const dindel_cigar_in *in, dindel_cigar_
     a.hap_ref_pos = (const int32_t *)(d_in + o_rp);
     a.read_hap = (int32_t *)(d_out + r_h); a.read_ref_pos = (int32_t *)(d_out + r_p); a.read_n_ops = (int32_t *)(d_out + r_n);
     a.ops = (uint32_t *)(d_out + r_o);
-    a.n_windows = B.n_windows; a.n_reads = B.n_reads;
+    a.n_windows = B.n_windows; a.n_reads = B.n_reads; a.w_begin = 0; a.r_begin = 0;
     a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.hap_off = B.hap_off; a.read_off = B.read_off;
-    a.pairs = B.pairs; a.on_hap = (const uint8_t *)ctx->d_on_hap.p; a.hpos = B.hpos; a.hpos_stride = B.hpos_stride;
+    a.pairs = B.pairs; a.on_hap = ctx->p_on_hap; a.hpos = B.hpos; a.hpos_stride = B.hpos_stride;
     CU(cudaMemsetAsync(a.ops, 0, nr * cap * 4, st));
     CU(cudaEventRecord(ctx->ev_k[0], st));
     CU(k5_launch(&a, ctx->num_sms, smem, st));
@@ -1253,10 +1664,152 @@ int dindel_b200_cigars(dindel_ctx *ctx, const dindel_cigar_in *in, dindel_cigar_
     return DINDEL_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// the window scheduler over the GPUs of one box: one context + one worker thread per device
+// ------------------------------------------------------------------------------------------
+struct dindel_multi {
+    std::vector<dindel_ctx *> ctx;
+    std::vector<std::thread> workers;
+    std::mutex mu;
+    std::condition_variable cv_go, cv_done;
+    unsigned long generation = 0;
+    int pending = 0;
+    bool quit = false;
+    const dindel_job *job = nullptr;
+    std::vector<int32_t> first;      // shard k = windows [first[k], first[k+1])
+    std::vector<int> rc;
+    std::string err;
+};
+
+static void multi_worker(dindel_multi *m, int k)
+{
+    unsigned long seen = 0;
+    cudaSetDevice(m->ctx[k]->device);
+    for (;;) {
+        const dindel_job *job;
+        int w0, w1;
+        {
+            std::unique_lock<std::mutex> lk(m->mu);
+            m->cv_go.wait(lk, [&] { return m->quit || m->generation != seen; });
+            if (m->quit) return;
+            seen = m->generation;
+            job = m->job; w0 = m->first[k]; w1 = m->first[k + 1];
+        }
+        const int rc = process_windows(m->ctx[k], job, w0, w1, true);
+        {
+            std::lock_guard<std::mutex> lk(m->mu);
+            m->rc[k] = rc;
+            if (--m->pending == 0) m->cv_done.notify_all();
+        }
+    }
+}
+
+int dindel_b200_multi_create(const dindel_params *p, const int *devices, int ndev, dindel_multi **out)
+{
+    if (!p || !out || ndev < 1 || ndev > 64) return DINDEL_E_INVALID;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) { cudaGetLastError(); return DINDEL_E_NO_DEVICE; }
+    dindel_multi *m = new dindel_multi();
+    for (int k = 0; k < ndev; k++) {
+        dindel_ctx *c = nullptr;
+        const int rc = dindel_b200_create(p, devices ? devices[k] : k, &c);
+        if (rc != DINDEL_OK) {
+            for (dindel_ctx *x : m->ctx) dindel_b200_destroy(x);
+            delete m;
+            return rc;
+        }
+        m->ctx.push_back(c);
+    }
+    m->rc.assign((size_t)ndev, 0);
+    m->first.assign((size_t)ndev + 1, 0);
+    for (int k = 0; k < ndev; k++) m->workers.emplace_back(multi_worker, m, k);
+    *out = m;
+    return DINDEL_OK;
+}
+
+int dindel_b200_multi_destroy(dindel_multi *m)
+{
+    if (!m) return DINDEL_E_INVALID;
+    {
+        std::lock_guard<std::mutex> lk(m->mu);
+        m->quit = true;
+    }
+    m->cv_go.notify_all();
+    for (std::thread &t : m->workers) t.join();
+    for (dindel_ctx *c : m->ctx) dindel_b200_destroy(c);
+    delete m;
+    return DINDEL_OK;
+}
+
+int dindel_b200_multi_devices(const dindel_multi *m) { return m ? (int)m->ctx.size() : 0; }
+const char *dindel_b200_multi_last_error(const dindel_multi *m) { return m ? m->err.c_str() : ""; }
+
+int dindel_b200_multi_set_libraries(dindel_multi *m, int n_libs, const int64_t *lib_off, const double *probs,
+                                    const double *ninetyfifth_pct_prob)
+{
+    if (!m) return DINDEL_E_INVALID;
+    for (dindel_ctx *c : m->ctx) {
+        const int rc = dindel_b200_set_libraries(c, n_libs, lib_off, probs, ninetyfifth_pct_prob);
+        if (rc != DINDEL_OK) { m->err = c->err; return rc; }
+    }
+    return DINDEL_OK;
+}
+
+int dindel_b200_multi_process(dindel_multi *m, const dindel_job *job)
+{
+    if (!m || !job || !job->in || !job->out) return DINDEL_E_INVALID;
+    const dindel_batch_in *in = job->in;
+    if (validate(in) != DINDEL_OK) { m->err = "inconsistent batch"; return DINDEL_E_INVALID; }
+    const int ndev = (int)m->ctx.size(), nw = in->n_windows;
+    // whole-batch outputs the per-device runs leave to us: win_pair / win_sum_off prefixes
+    if (job->out->win_pair || job->win_sum_off) {
+        long long p = 0, s = 0;
+        for (int w = 0; w <= nw; w++) {
+            if (job->out->win_pair) job->out->win_pair[w] = p;
+            if (job->win_sum_off) job->win_sum_off[w] = s;
+            if (w < nw) {
+                const long long nh = in->win_hap[w + 1] - in->win_hap[w], nr = in->win_read[w + 1] - in->win_read[w];
+                p += nh * nr; s += nh * (nh + 1) / 2;
+            }
+        }
+    }
+    {
+        std::lock_guard<std::mutex> lk(m->mu);
+        if (nw > 0) plan_range(in, 0, nw, ndev, m->first.data());
+        else m->first.assign((size_t)ndev + 1, 0);
+        m->job = job;
+        m->pending = ndev;
+        m->generation++;
+    }
+    m->cv_go.notify_all();
+    {
+        std::unique_lock<std::mutex> lk(m->mu);
+        m->cv_done.wait(lk, [&] { return m->pending == 0; });
+    }
+    for (int k = 0; k < ndev; k++)
+        if (m->rc[k] != DINDEL_OK) {
+            char buf[64];
+            snprintf(buf, sizeof buf, "device %d: ", m->ctx[k]->device);
+            m->err = std::string(buf) + m->ctx[k]->err;
+            return m->rc[k];
+        }
+    return DINDEL_OK;
+}
+
+int dindel_b200_multi_get_shard(const dindel_multi *m, int k, int32_t *first_window, int32_t *last_window, dindel_timing *t)
+{
+    if (!m || k < 0 || k >= (int)m->ctx.size()) return DINDEL_E_INVALID;
+    if (first_window) *first_window = m->first[k];
+    if (last_window) *last_window = m->first[k + 1];
+    if (t) *t = m->ctx[k]->timing;
+    return DINDEL_OK;
+}
+
 void *dindel_b200_alloc_pinned(size_t bytes)
 {
     void *p = nullptr;
-    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) {
         cudaGetLastError();
         return nullptr;
     }

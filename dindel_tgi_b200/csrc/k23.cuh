@@ -6,7 +6,7 @@ struct K2Args {
     int n_jobs;
     const int32_t *job_window, *job_group;
     const long long *job_off;
-    const double *start;
+    const double *start;       // may be null (= zeros)
     const int32_t *read_group; // may be null
     double *out;
     const int32_t *win_hap, *win_read;
@@ -22,6 +22,7 @@ struct K3Args {
     const uint8_t *compatible;
     double a0, tol;
     double *loglik, *pi, *freqs;
+    double *margin, *energy; // may be null
     int32_t *iters;
     const int32_t *win_hap, *win_read;
     const long long *win_pair;

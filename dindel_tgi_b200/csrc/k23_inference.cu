@@ -4,16 +4,22 @@
 //
 //   K2  pair sums   acc <- start; for r in window (in order): acc += log(.5) + addLogs(rl[r,h1], rl[r,h2])
 //                   for every h1 <= h2: the inner loop of DetInDel::diploidGLF (DInDel.cpp:3085-3113,
-//                   :3349-3390, start = 0 resp. prior - sitePrior) and of the pooled genotype
-//                   likelihoods (DInDel.cpp:2683-2694, reads restricted to one pool member).
-//                   One CTA per job, one thread per haplotype pair, reads summed sequentially in r
-//                   like the CPU (same association; only exp/log differ from glibc at the ulp level).
-//   K3  Bayes EM    the variational-Bayes EM over haplotype frequencies for one set of active
-//                   variants (DetInDel::estimateHaplotypeFrequenciesBayesEM, DInDel.cpp:2431-2545):
-//                   E-step responsibilities by a chain of addLogs in h order per read, counts nk,
-//                   lpi = digamma(nk+a0) - digamma(sum), energy, <= 27 passes.  One CTA per set.
-// Tolerance (stated in tests/test_k23_gpu.py): 1e-9 relative against the CPU restatement; the
-// only arithmetic differences are CUDA libm vs glibc and the reduction tree over reads in K3.
+//                   :3349-3390) and of the pooled genotype likelihoods (DInDel.cpp:2683-2694, reads
+//                   restricted to one pool member).  One CTA per job.  The window's ll column block is staged
+//                   once per read tile from the 64-byte pair records into shared memory (one coalesced sweep,
+//                   no thread re-reads a record); one thread per haplotype pair then sums the tile's reads in
+//                   the CPU's order, so the only arithmetic difference to the reference is exp/log (CUDA libm
+//                   vs glibc, ulp level).
+//   K3  Bayes EM    the variational-Bayes EM over haplotype frequencies for one set of active variants
+//                   (DetInDel::estimateHaplotypeFrequenciesBayesEM, DInDel.cpp:2431-2545).  One CTA per set;
+//                   the ll matrix lives in shared memory (odd pitch: conflict-free column walks) for all <= 27
+//                   passes, one thread per read with its responsibilities in registers, warp-shuffle + fixed
+//                   cross-warp reductions (deterministic), digammas one per lane.  Responsibilities use the
+//                   max-shifted log-sum-exp (nh exp + 1 log per read instead of the reference's chain of nh
+//                   addLogs + nh exp): mathematically the same numbers, a few ulp apart.
+// Neither kernel can be bit-identical to glibc; both report what the host needs to keep the TEXT output identical:
+// K2's error bound is a closed form of (reads, magnitude) (dindel_b200_sum_error_bound); K3 returns per set the
+// margin min_pass ||dE| - tol| of the stopping rule (DInDel.cpp:2515) so that a knife-edge set is re-run on the host.
 #include "k1_common.cuh"
 #include "k23.cuh"
 
@@ -43,150 +49,248 @@ __device__ __forceinline__ double digamma_pos(double x)
     return r + log(x) - 0.5 / x + t;
 }
 
-__global__ void __launch_bounds__(128) k2_pair_sums(K2Args A)
+// ------------------------------------------------------------------------------------------------------------
+// K2
+// ------------------------------------------------------------------------------------------------------------
+#define K2_TILE_BYTES 32768
+
+__global__ void k2_pair_sums(K2Args A)
 {
+    extern __shared__ double s_rl[]; // [tile_r][nh] then uint8 keep[tile_r]
     const int j = blockIdx.x;
     if (j >= A.n_jobs) return;
     const int w = A.job_window[j], grp = A.job_group[j];
     const int nh = A.win_hap[w + 1] - A.win_hap[w];
     const int r0 = A.win_read[w], nr = A.win_read[w + 1] - r0;
     const int npairs = nh * (nh + 1) / 2;
+    if (nh <= 0) return;
     const dindel_pair_out *p = A.pairs + A.win_pair[w];
     const long long off = A.job_off[j];
-    for (int q = threadIdx.x; q < npairs; q += blockDim.x) {
-        // q -> (h1 <= h2), row-major upper triangle
+    int tile_r = K2_TILE_BYTES / (nh * 9);
+    if (tile_r > nr) tile_r = nr;
+    if (tile_r < 1) tile_r = 1;
+    uint8_t *s_keep = reinterpret_cast<uint8_t *>(s_rl + (size_t)tile_r * nh);
+    const bool grouped = grp >= 0 && A.read_group != nullptr;
+
+    // this thread's haplotype pairs: q -> (h1 <= h2), row-major upper triangle; up to 4 per thread in registers
+    int h1v[4], h2v[4];
+    double acc[4];
+    int nq = 0;
+    for (int q = threadIdx.x; q < npairs && nq < 4; q += blockDim.x, nq++) {
+        int h1 = 0, rem = q;
+        while (rem >= nh - h1) { rem -= nh - h1; h1++; }
+        h1v[nq] = h1; h2v[nq] = h1 + rem;
+        acc[nq] = A.start ? A.start[off + q] : 0.0;
+    }
+    for (int t0 = 0; t0 < nr; t0 += tile_r) {
+        const int tn = min(tile_r, nr - t0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < tn * nh; i += blockDim.x) s_rl[i] = p[(long long)t0 * nh + i].ll;
+        for (int i = threadIdx.x; i < tn; i += blockDim.x) s_keep[i] = grouped ? (A.read_group[r0 + t0 + i] == grp) : 1;
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k < nq) {
+                const int h1 = h1v[k], h2 = h2v[k];
+                double a = acc[k];
+                for (int r = 0; r < tn; r++) {
+                    if (!s_keep[r]) continue;
+                    a += A.log_half + addlogs(s_rl[r * nh + h1], s_rl[r * nh + h2]);
+                }
+                acc[k] = a;
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        if (k < nq) A.out[off + threadIdx.x + k * blockDim.x] = acc[k];
+    // more than 4 pairs per thread (nh > ~44 at 256 threads): the remaining pairs straight from the records
+    for (int q = threadIdx.x + 4 * blockDim.x; q < npairs; q += blockDim.x) {
         int h1 = 0, rem = q;
         while (rem >= nh - h1) { rem -= nh - h1; h1++; }
         const int h2 = h1 + rem;
-        double acc = A.start[off + q];
+        double a = A.start ? A.start[off + q] : 0.0;
         for (int r = 0; r < nr; r++) {
-            if (grp >= 0 && A.read_group && A.read_group[r0 + r] != grp) continue;
-            const double a = p[(long long)r * nh + h1].ll, b = p[(long long)r * nh + h2].ll;
-            acc += A.log_half + addlogs(a, b);
+            if (grouped && A.read_group[r0 + r] != grp) continue;
+            a += A.log_half + addlogs(p[(long long)r * nh + h1].ll, p[(long long)r * nh + h2].ll);
         }
-        A.out[off + q] = acc;
+        A.out[off + q] = a;
     }
 }
 
-#define K3_THREADS 128
+// ------------------------------------------------------------------------------------------------------------
+// K3
+// ------------------------------------------------------------------------------------------------------------
 #define K3_MAXH 64
+#define K3_MAX_WARPS 8
 
-__global__ void __launch_bounds__(K3_THREADS) k3_bayes_em(K3Args A)
+// NHP: haplotype slots unrolled per thread (nh <= NHP).  STAGE: the ll matrix fits shared memory.
+template <int NHP, bool STAGE>
+__global__ void __launch_bounds__(256) k3_bayes_em(K3Args A)
 {
+    extern __shared__ double s_mem[];
     __shared__ double s_lpi[K3_MAXH], s_pi[K3_MAXH], s_nk[K3_MAXH];
-    __shared__ double s_part[K3_THREADS];
-    __shared__ double s_loglik, s_B;
-    __shared__ int s_done;
-    const int s = blockIdx.x, tid = threadIdx.x;
+    __shared__ double s_wpart[K3_MAX_WARPS][K3_MAXH + 2];
+    __shared__ double s_scal[4]; // loglik, B, eNew
+    const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarps = blockDim.x >> 5;
     if (s >= A.n_sets) return;
     const int w = A.set_window[s];
     const int nh = A.win_hap[w + 1] - A.win_hap[w];
     const int nr = A.win_read[w + 1] - A.win_read[w];
     const dindel_pair_out *p = A.pairs + A.win_pair[w];
     const uint8_t *compat = A.compatible + A.set_off[s];
+    const int pitch = nh | 1; // odd number of doubles: the 32 lanes of a warp walk 32 rows without bank conflicts
+    if (STAGE) {
+        for (int i = tid; i < nr * nh; i += blockDim.x) {
+            const int r = i / nh, h = i - r * nh;
+            s_mem[r * pitch + h] = p[i].ll;
+        }
+    }
     int numah = 0;
     for (int h = 0; h < nh; h++) numah += compat[h] ? 1 : 0;
-    if (tid < nh) s_lpi[tid] = compat[tid] ? log(1.0 / (double)numah) : -100.0; // DInDel.cpp:2417
-    if (tid == 0) s_done = 0;
+    if (tid < nh) s_lpi[tid] = compat[tid] ? log(1.0 / (double)numah) : -100.0; // DInDel.cpp:2418
     __syncthreads();
-    double eOld = K1_NEG_INF;
+    double eOld = K1_NEG_INF, margin = __longlong_as_double(0x7ff0000000000000LL), loglik = 0.0;
     int iter = 0;
-    double z[K3_MAXH];
     for (;;) {
-        // E-step over this thread's reads (DInDel.cpp:2439-2457)
-        double nkp[K3_MAXH];
-        for (int h = 0; h < nh; h++) nkp[h] = 0.0;
+        // ---- E-step over this thread's reads (DInDel.cpp:2439-2457) ----
+        double nkp[NHP];
+#pragma unroll
+        for (int h = 0; h < NHP; h++) nkp[h] = 0.0;
         double ll = 0.0, Bp = 0.0;
-        for (int r = tid; r < nr; r += K3_THREADS) {
-            double lognorm = K1_NEG_INF;
-            for (int h = 0; h < nh; h++) {
-                z[h] = s_lpi[h] + p[(long long)r * nh + h].ll;
-                lognorm = addlogs(lognorm, z[h]);
+        for (int r = tid; r < nr; r += blockDim.x) {
+            double e[NHP];
+            double m = K1_NEG_INF;
+#pragma unroll
+            for (int h = 0; h < NHP; h++) {
+                if (h < nh) {
+                    e[h] = s_lpi[h] + (STAGE ? s_mem[r * pitch + h] : p[(long long)r * nh + h].ll);
+                    m = fmax(m, e[h]);
+                }
             }
-            for (int h = 0; h < nh; h++) {
-                const double zz = exp(z[h] - lognorm);
-                nkp[h] += zz;
-                Bp += zz * p[(long long)r * nh + h].ll;
+            double sum = 0.0;
+#pragma unroll
+            for (int h = 0; h < NHP; h++) {
+                if (h < nh) {
+                    e[h] = exp(e[h] - m);
+                    sum += e[h];
+                }
             }
-            ll += lognorm;
-        }
-        // deterministic block reductions (fixed tree)
-        for (int h = 0; h < nh; h++) {
-            s_part[tid] = nkp[h];
-            __syncthreads();
-            for (int o = K3_THREADS / 2; o > 0; o >>= 1) {
-                if (tid < o) s_part[tid] += s_part[tid + o];
-                __syncthreads();
+            const double inv = 1.0 / sum;
+#pragma unroll
+            for (int h = 0; h < NHP; h++) {
+                if (h < nh) {
+                    const double zz = e[h] * inv;
+                    nkp[h] += zz;
+                    Bp += zz * (STAGE ? s_mem[r * pitch + h] : p[(long long)r * nh + h].ll);
+                }
             }
-            if (tid == 0) s_nk[h] = s_part[0];
-            __syncthreads();
+            ll += m + log(sum);
         }
-        s_part[tid] = ll;
-        __syncthreads();
-        for (int o = K3_THREADS / 2; o > 0; o >>= 1) {
-            if (tid < o) s_part[tid] += s_part[tid + o];
-            __syncthreads();
+        // ---- deterministic reductions: xor tree inside the warp, then the warps in order ----
+#pragma unroll
+        for (int h = 0; h < NHP; h++) {
+            if (h < nh) {
+                double v = nkp[h];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) s_wpart[wid][h] = v;
+            }
         }
-        if (tid == 0) s_loglik = s_part[0];
-        __syncthreads();
-        s_part[tid] = Bp;
-        __syncthreads();
-        for (int o = K3_THREADS / 2; o > 0; o >>= 1) {
-            if (tid < o) s_part[tid] += s_part[tid + o];
-            __syncthreads();
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            ll += __shfl_xor_sync(0xffffffffu, ll, o);
+            Bp += __shfl_xor_sync(0xffffffffu, Bp, o);
         }
-        if (tid == 0) s_B = s_part[0];
+        if (lane == 0) { s_wpart[wid][K3_MAXH] = ll; s_wpart[wid][K3_MAXH + 1] = Bp; }
         __syncthreads();
-        // M-step (DInDel.cpp:2461-2480) and energy (:2484-2492), one thread
+        if (tid < nh) {
+            double v = 0.0;
+            for (int k = 0; k < nwarps; k++) v += s_wpart[k][tid];
+            s_nk[tid] = v;
+        }
         if (tid == 0) {
+            double v0 = 0.0, v1 = 0.0;
+            for (int k = 0; k < nwarps; k++) { v0 += s_wpart[k][K3_MAXH]; v1 += s_wpart[k][K3_MAXH + 1]; }
+            s_scal[0] = v0; s_scal[1] = v1;
+        }
+        __syncthreads();
+        // ---- M-step (DInDel.cpp:2461-2480), one haplotype per thread ----
+        if (tid < nh) {
             double ahat = 0.0;
             for (int h = 0; h < nh; h++)
                 if (compat[h]) ahat += s_nk[h] + A.a0;
-            const double dahat = digamma_pos(ahat);
-            double eNew = s_B;
-            for (int h = 0; h < nh; h++) {
-                if (compat[h]) {
-                    s_lpi[h] = digamma_pos(s_nk[h] + A.a0) - dahat;
-                    s_pi[h] = log((A.a0 + s_nk[h]) / ((double)numah * A.a0 + (double)nr));
-                } else {
-                    s_lpi[h] = -100.0;
-                    s_pi[h] = -100.0;
-                }
-                eNew += s_pi[h] * s_nk[h];
+            if (compat[tid]) {
+                s_lpi[tid] = digamma_pos(s_nk[tid] + A.a0) - digamma_pos(ahat);
+                s_pi[tid] = log((A.a0 + s_nk[tid]) / ((double)numah * A.a0 + (double)nr));
+            } else {
+                s_lpi[tid] = -100.0;
+                s_pi[tid] = -100.0;
             }
-            s_done = (fabs(eOld - eNew) < A.tol) || (iter > 25); // :2515
-            s_part[0] = eNew;
         }
         __syncthreads();
-        eOld = s_part[0];
+        // ---- energy (DInDel.cpp:2484-2492: sum z*(pi+rl) = sum z*rl + sum_h pi[h]*nk[h]) and stopping rule (:2515);
+        //      every thread evaluates the same expression on the same shared values ----
+        double eNew = s_scal[1];
+        for (int h = 0; h < nh; h++) eNew += s_pi[h] * s_nk[h];
+        loglik = s_scal[0];
+        const double dE = fabs(eOld - eNew);
+        if (iter <= 25) margin = fmin(margin, fabs(dE - A.tol));
+        const bool done = (dE < A.tol) || (iter > 25);
+        eOld = eNew;
         iter++;
-        const int done = s_done;
-        __syncthreads();
         if (done) break;
+        __syncthreads(); // s_scal / s_wpart are rewritten by the next pass
     }
     if (tid == 0) {
         double zs = 0.0;
-        for (int h = 0; h < nh; h++) zs += exp(s_pi[h]); // :2524-2527
+        for (int h = 0; h < nh; h++) zs += exp(s_pi[h]); // :2528-2531
         const long long off = A.set_off[s];
         for (int h = 0; h < nh; h++) {
             A.pi[off + h] = s_pi[h];
-            A.freqs[off + h] = exp(s_pi[h]) / zs; // :2539
+            A.freqs[off + h] = exp(s_pi[h]) / zs; // :2543
         }
-        A.loglik[s] = s_loglik;
+        A.loglik[s] = loglik;
         A.iters[s] = iter;
+        if (A.margin) A.margin[s] = margin;
+        if (A.energy) A.energy[s] = eOld;
     }
 }
 
-extern "C" cudaError_t k2_launch(const K2Args *a, cudaStream_t st)
+extern "C" cudaError_t k2_launch(const K2Args *a, int max_npairs, cudaStream_t st)
 {
     if (a->n_jobs <= 0) return cudaSuccess;
-    k2_pair_sums<<<a->n_jobs, 128, 0, st>>>(*a);
+    int threads = (max_npairs + 31) & ~31;
+    if (threads < 32) threads = 32;
+    if (threads > 256) threads = 256;
+    // tile of reads: at most K2_TILE_BYTES of ll values + 1 keep byte per read
+    k2_pair_sums<<<a->n_jobs, threads, K2_TILE_BYTES + 1024, st>>>(*a);
     return cudaGetLastError();
 }
-extern "C" cudaError_t k3_launch(const K3Args *a, cudaStream_t st)
+
+template <int NHP>
+static cudaError_t k3_launch_nhp(const K3Args *a, int threads, size_t smem, bool stage, cudaStream_t st)
+{
+    if (stage) {
+        cudaError_t e = cudaFuncSetAttribute(k3_bayes_em<NHP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        k3_bayes_em<NHP, true><<<a->n_sets, threads, smem, st>>>(*a);
+    } else {
+        k3_bayes_em<NHP, false><<<a->n_sets, threads, 0, st>>>(*a);
+    }
+    return cudaGetLastError();
+}
+
+// max_nh / max_nr: over the windows the sets refer to; smem_optin: the device's opt-in limit per CTA
+extern "C" cudaError_t k3_launch(const K3Args *a, int max_nh, int max_nr, size_t smem_optin, cudaStream_t st)
 {
     if (a->n_sets <= 0) return cudaSuccess;
-    k3_bayes_em<<<a->n_sets, K3_THREADS, 0, st>>>(*a);
-    return cudaGetLastError();
+    int threads = max_nr <= 64 ? 64 : (max_nr <= 128 ? 128 : 256);
+    const size_t need = (size_t)max_nr * (size_t)(max_nh | 1) * sizeof(double);
+    const bool stage = need + 8192 <= smem_optin;
+    if (max_nh <= 8) return k3_launch_nhp<8>(a, threads, need, stage, st);
+    if (max_nh <= 16) return k3_launch_nhp<16>(a, threads, need, stage, st);
+    if (max_nh <= 32) return k3_launch_nhp<32>(a, threads, need, stage, st);
+    return k3_launch_nhp<64>(a, threads, need, stage, st);
 }
 extern "C" int k3_max_haps(void) { return K3_MAXH; }

@@ -4,6 +4,7 @@
 
 struct K4Args {
     int maxMismatch, doFilter;
+    int w_begin; // CTA b works on window w_begin + b (the resident range; every pointer below is rebased)
     const long long *win_entry, *win_key;
     const int32_t *entry_hap, *entry_key, *entry_left, *entry_right;
     const uint8_t *entry_type, *read_strand;

@@ -18,7 +18,7 @@
 __global__ void __launch_bounds__(K4_THREADS) k4_coverage_kernel(K4Args a)
 {
     extern __shared__ uint32_t sm[];
-    const int w = blockIdx.x;
+    const int w = a.w_begin + blockIdx.x;
     const long long e0 = a.win_entry[w], e1 = a.win_entry[w + 1];
     const long long k0 = a.win_key[w], k1 = a.win_key[w + 1];
     const int ne = (int)(e1 - e0), nk = (int)(k1 - k0);

@@ -8,7 +8,8 @@ struct K5Args {
     int32_t *read_hap, *read_ref_pos, *read_n_ops;
     uint32_t *ops;
     // resident batch
-    int n_windows, n_reads;
+    int n_windows, n_reads; // of the resident range: windows [w_begin, w_begin + n_windows), reads [r_begin, ...)
+    int w_begin, r_begin;
     const int32_t *win_hap, *win_read;
     const long long *win_pair, *hap_off, *read_off;
     const dindel_pair_out *pairs;

@@ -49,14 +49,14 @@ __global__ void __launch_bounds__(K5_WARPS * 32) k5_cigar_kernel(K5Args a)
     int32_t *tile = k5_sm + (size_t)warp * 32 * a.pitch;
     const int ngroups = (a.n_reads + 31) >> 5;
     for (int g = blockIdx.x * K5_WARPS + warp; g < ngroups; g += gridDim.x * K5_WARPS) {
-        const int r_base = g << 5;
+        const int r_base = a.r_begin + (g << 5);   // reads [r_begin, r_begin + n_reads) of the resident range
         const int r = r_base + lane;
         // ---- choose: lane i resolves read r_base + i (window, pair row, haplotype): 32 dependent-load chains at once ----
         int my_R = 0, my_hap = -1, my_ref0 = 0, my_H = 0;
         const int16_t *my_hp = nullptr;
         const int32_t *my_ref = nullptr;
-        int w = k5_find_window(a.win_read, a.n_windows, r_base);   // same address in every lane: one search per warp
-        if (r < a.n_reads) {
+        int w = a.w_begin + k5_find_window(a.win_read + a.w_begin, a.n_windows, r_base);   // same address in every lane: one search per warp
+        if (r < a.r_begin + a.n_reads) {
             while (r >= a.win_read[w + 1]) w++;
             const int h0 = a.win_hap[w], nh = a.win_hap[w + 1] - h0;
             my_R = (int)(a.read_off[r + 1] - a.read_off[r]);
@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(K5_WARPS * 32) k5_cigar_kernel(K5Args a)
             if (b >= 0) { b = 0; while (np[b] < 0) b++; my_first = b; }
         }
         // ---- walk: lane i owns read r_base + i ----
-        if (r < a.n_reads) {
+        if (r < a.r_begin + a.n_reads) {
             int n = 0, ref_pos = -1;
             uint32_t *ops = a.ops + (size_t)r * a.cap;
 #define K5_PUSH(op, len) do { if (n < a.cap) ops[n] = ((uint32_t)(len) << 4) | (op); n++; } while (0)

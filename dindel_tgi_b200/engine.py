@@ -52,7 +52,8 @@ class _BatchOut(C.Structure):
 class Timing(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("prep_ms", C.c_float), ("k1_ms", C.c_float),
                 ("d2h_ms", C.c_float), ("total_ms", C.c_float), ("k1_launches", C.c_int32),
-                ("prep_launches", C.c_int32), ("n_pairs", C.c_int64), ("n_cells", C.c_int64)]
+                ("prep_launches", C.c_int32), ("n_pairs", C.c_int64), ("n_cells", C.c_int64),
+                ("post_ms", C.c_float), ("host_ms", C.c_float), ("n_ranges", C.c_int32), ("n_chunks", C.c_int32)]
 
 
 class _PairSumIn(C.Structure):
@@ -93,7 +94,14 @@ VAR_DEL, VAR_INS, VAR_OTHER = 0, 1, 2
 
 
 class _EmOut(C.Structure):
-    _fields_ = [("loglik", C.c_void_p), ("iters", C.c_void_p), ("pi", C.c_void_p), ("freqs", C.c_void_p)]
+    _fields_ = [("loglik", C.c_void_p), ("iters", C.c_void_p), ("pi", C.c_void_p), ("freqs", C.c_void_p),
+                ("margin", C.c_void_p), ("energy", C.c_void_p)]
+
+
+class _Job(C.Structure):
+    _fields_ = [("in_", C.c_void_p), ("out", C.c_void_p), ("cover", C.c_void_p), ("cover_out", C.c_void_p),
+                ("pair_sums", C.c_void_p), ("win_sum_off", C.c_void_p), ("n_groups", C.c_int32), ("reserved", C.c_int32),
+                ("read_group", C.c_void_p), ("em", C.c_void_p), ("em_out", C.c_void_p)]
 
 
 PAIR_DTYPE = np.dtype([
@@ -113,7 +121,10 @@ EXPORTS = [
     "dindel_b200_get_timing", "dindel_b200_hpos_stride", "dindel_b200_alloc_pinned",
     "dindel_b200_free_pinned", "dindel_b200_measure_fp64_peak", "dindel_b200_pair_sums",
     "dindel_b200_bayes_em", "dindel_b200_plan_shards", "dindel_b200_coverage", "dindel_b200_set_libraries",
-    "dindel_b200_last_kernel_ms", "dindel_b200_cigars",
+    "dindel_b200_last_kernel_ms", "dindel_b200_cigars", "dindel_b200_process", "dindel_b200_count_sums",
+    "dindel_b200_sum_error_bound", "dindel_b200_multi_create", "dindel_b200_multi_destroy", "dindel_b200_multi_devices",
+    "dindel_b200_multi_set_libraries", "dindel_b200_multi_process", "dindel_b200_multi_get_shard",
+    "dindel_b200_multi_last_error", "dindel_b200_load_likelihoods",
 ]
 
 _lib = None
@@ -156,6 +167,20 @@ def load_library():
     lib.dindel_b200_coverage.argtypes = [C.c_void_p, C.POINTER(_CoverIn), C.POINTER(_CoverOut)]
     lib.dindel_b200_set_libraries.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.dindel_b200_plan_shards.argtypes = [C.POINTER(_BatchIn), C.c_int, C.c_void_p]
+    lib.dindel_b200_process.argtypes = [C.c_void_p, C.POINTER(_Job)]
+    lib.dindel_b200_load_likelihoods.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.dindel_b200_count_sums.restype = C.c_int64
+    lib.dindel_b200_count_sums.argtypes = [C.POINTER(_BatchIn)]
+    lib.dindel_b200_sum_error_bound.restype = C.c_double
+    lib.dindel_b200_sum_error_bound.argtypes = [C.c_int64, C.c_double]
+    lib.dindel_b200_multi_create.argtypes = [C.POINTER(Params), C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+    lib.dindel_b200_multi_destroy.argtypes = [C.c_void_p]
+    lib.dindel_b200_multi_devices.argtypes = [C.c_void_p]
+    lib.dindel_b200_multi_process.argtypes = [C.c_void_p, C.POINTER(_Job)]
+    lib.dindel_b200_multi_get_shard.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(Timing)]
+    lib.dindel_b200_multi_last_error.restype = C.c_char_p
+    lib.dindel_b200_multi_last_error.argtypes = [C.c_void_p]
+    lib.dindel_b200_multi_set_libraries.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     _lib = lib
     return lib
 
@@ -396,6 +421,17 @@ class Engine:
         self._check(self.lib.dindel_b200_measure_fp64_peak(self.h, C.byref(v)), "measure_fp64_peak")
         return v.value
 
+    def load_likelihoods(self, rls, nhs):
+        """dindel_b200_load_likelihoods: rls = list of flat r-major ll matrices (one per window), nhs = haplotypes per
+        window.  Afterwards pair_sums / bayes_em run on them."""
+        wh = np.concatenate([[0], np.cumsum(nhs)]).astype(np.int32)
+        wr = np.concatenate([[0], np.cumsum([len(x) // h for x, h in zip(rls, nhs)])]).astype(np.int32)
+        ll = np.ascontiguousarray(np.concatenate(rls), dtype=np.float64)
+        self._check(self.lib.dindel_b200_load_likelihoods(self.h, len(rls), wh.ctypes.data, wr.ctypes.data, ll.ctypes.data),
+                    "load_likelihoods")
+        self._resident = None
+        self._n_haps, self._n_reads = int(wh[-1]), int(wr[-1])
+
     # ---- inference kernels over the resident likelihood matrix ----
     def pair_sums(self, job_window, starts, job_group=None, read_group=None):
         """K2 (diploidGLF / pooled genotype sums).  starts: list of float64 arrays, one per job, each
@@ -404,11 +440,12 @@ class Engine:
         jw = np.ascontiguousarray(job_window, dtype=np.int32)
         jg = np.full(nj, -1, dtype=np.int32) if job_group is None else np.ascontiguousarray(job_group, dtype=np.int32)
         off = np.concatenate([[0], np.cumsum([len(x) for x in starts])]).astype(np.int64)
+        zero_start = all(x is None or not np.any(x) for x in starts) and getattr(self, "null_start", False)
         st = np.ascontiguousarray(np.concatenate(starts) if nj else np.zeros(0), dtype=np.float64)
         out = np.zeros_like(st)
         rg = None if read_group is None else np.ascontiguousarray(read_group, dtype=np.int32)
         a = _PairSumIn()
-        a.n_jobs, a.job_window, a.job_group, a.job_off, a.start = nj, jw.ctypes.data, jg.ctypes.data, off.ctypes.data, st.ctypes.data
+        a.n_jobs, a.job_window, a.job_group, a.job_off, a.start = nj, jw.ctypes.data, jg.ctypes.data, off.ctypes.data, (None if zero_start else st.ctypes.data)
         a.read_group = rg.ctypes.data if rg is not None else None
         t0 = time.perf_counter()
         self._check(self.lib.dindel_b200_pair_sums(self.h, C.byref(a), out.ctypes.data), "pair_sums")
@@ -481,11 +518,153 @@ class Engine:
         comp = np.ascontiguousarray(np.concatenate(compatible) if ns else np.zeros(0), dtype=np.uint8)
         ll, it = np.zeros(ns), np.zeros(ns, dtype=np.int32)
         pi, fr = np.zeros(len(comp)), np.zeros(len(comp))
+        self.last_em_margin, self.last_em_energy = np.zeros(ns), np.zeros(ns)
         a, o = _EmIn(), _EmOut()
         a.n_sets, a.set_window, a.set_off, a.compatible, a.a0, a.tol = ns, sw.ctypes.data, off.ctypes.data, comp.ctypes.data, a0, tol
         o.loglik, o.iters, o.pi, o.freqs = ll.ctypes.data, it.ctypes.data, pi.ctypes.data, fr.ctypes.data
+        o.margin, o.energy = self.last_em_margin.ctypes.data, self.last_em_energy.ctypes.data
         t0 = time.perf_counter()
         self._check(self.lib.dindel_b200_bayes_em(self.h, C.byref(a), C.byref(o)), "bayes_em")
         self.last_call_ms = 1e3 * (time.perf_counter() - t0)
         self.last_kernel_ms = float(self.lib.dindel_b200_last_kernel_ms(self.h))
         return ll, it, [pi[off[j]:off[j + 1]] for j in range(ns)], [fr[off[j]:off[j + 1]] for j in range(ns)]
+
+
+class JobResults:
+    """What one dindel_b200_process / dindel_b200_multi_process call returned."""
+    pass
+
+
+def _build_job(batch, want_pairs, want_hpos, cover, pair_sums, n_groups, read_group, em, ins=None, pinned=None):
+    """Allocates the outputs of a job and fills the C structs.  cover: (win_entries, win_nkeys, read_strand,
+    max_mismatch, do_filter) as Engine.coverage takes them; em: (set_window, [compatible arrays], a0, tol).
+    Returns (job struct, keep-alive list, JobResults with numpy views)."""
+    keep, res = [], JobResults()
+    lib = load_library()
+    cb = batch._c(ins)
+    keep.append(cb)
+    n = batch.n_pairs()
+    o = _BatchOut()
+    res.win_pair = np.zeros(batch.n_windows + 1, dtype=np.int64)
+    res.win_status = np.zeros(max(batch.n_windows, 1), dtype=np.int32)
+    res.read_on_hap = np.zeros(max(batch.n_reads, 1), dtype=np.uint8)
+    res.pairs = res.hpos = None
+    if want_pairs:
+        res.pairs = np.zeros(n, dtype=PAIR_DTYPE) if pinned is None else pinned
+        o.n_pairs, o.pairs = n, res.pairs.ctypes.data
+    if want_hpos:
+        maxr = int(np.max(np.diff(batch.read_off))) if batch.n_reads else 0
+        stride = max(8, (maxr + 7) & ~7)
+        res.hpos = np.full((n, stride), -32768, dtype=np.int16)
+        o.hpos, o.hpos_stride = res.hpos.ctypes.data, stride
+    o.win_pair, o.win_status, o.read_on_hap = res.win_pair.ctypes.data, res.win_status.ctypes.data, res.read_on_hap.ctypes.data
+    keep.append(o)
+    job = _Job()
+    job.in_, job.out = C.addressof(cb), C.addressof(o)
+    if cover is not None:
+        win_entries, win_nkeys, read_strand, max_mismatch, do_filter = cover
+        we = np.concatenate([[0], np.cumsum([len(e) for e in win_entries])]).astype(np.int64)
+        wk = np.concatenate([[0], np.cumsum(win_nkeys)]).astype(np.int64)
+        flat = [x for e in win_entries for x in e]
+        e = np.array(flat, dtype=np.int64).reshape(len(flat), 5) if flat else np.zeros((0, 5), dtype=np.int64)
+        eh, ek, el, er = (np.ascontiguousarray(e[:, i], dtype=np.int32) for i in (0, 1, 3, 4))
+        et = np.ascontiguousarray(e[:, 2], dtype=np.uint8)
+        rs = np.ascontiguousarray(read_strand, dtype=np.uint8)
+        res.hap_filtered, res.hap_uncovered = np.zeros(max(batch.n_haps, 1), dtype=np.uint8), np.zeros(max(batch.n_haps, 1), dtype=np.uint8)
+        res.key_nf, res.key_nr = np.zeros(max(int(wk[-1]), 1), dtype=np.int32), np.zeros(max(int(wk[-1]), 1), dtype=np.int32)
+        res.win_key = wk
+        a, co = _CoverIn(), _CoverOut()
+        a.n_entries, a.n_keys, a.maxMismatch, a.doFilter = len(flat), int(wk[-1]), int(max_mismatch), int(bool(do_filter))
+        a.win_entry, a.win_key = we.ctypes.data, wk.ctypes.data
+        a.entry_hap, a.entry_key, a.entry_type = eh.ctypes.data, ek.ctypes.data, et.ctypes.data
+        a.entry_left, a.entry_right, a.read_strand = el.ctypes.data, er.ctypes.data, rs.ctypes.data
+        co.hap_filtered, co.hap_uncovered, co.key_nf, co.key_nr = (res.hap_filtered.ctypes.data, res.hap_uncovered.ctypes.data,
+                                                                  res.key_nf.ctypes.data, res.key_nr.ctypes.data)
+        keep += [we, wk, eh, ek, el, er, et, rs, a, co]
+        job.cover, job.cover_out = C.addressof(a), C.addressof(co)
+    if pair_sums:
+        ns = int(lib.dindel_b200_count_sums(C.byref(cb)))
+        g = max(int(n_groups), 1)
+        res.pair_sums = np.zeros(max(ns * g, 1), dtype=np.float64)
+        res.win_sum_off = np.zeros(batch.n_windows + 1, dtype=np.int64)
+        job.pair_sums, job.win_sum_off, job.n_groups = res.pair_sums.ctypes.data, res.win_sum_off.ctypes.data, int(n_groups)
+        if n_groups:
+            rg = np.ascontiguousarray(read_group, dtype=np.int32)
+            keep.append(rg)
+            job.read_group = rg.ctypes.data
+    if em is not None:
+        set_window, compatible, a0, tol = em
+        nsets = len(set_window)
+        sw = np.ascontiguousarray(set_window, dtype=np.int32)
+        off = np.concatenate([[0], np.cumsum([len(x) for x in compatible])]).astype(np.int64)
+        comp = np.ascontiguousarray(np.concatenate(compatible) if nsets else np.zeros(0), dtype=np.uint8)
+        res.em_loglik, res.em_iters = np.zeros(max(nsets, 1)), np.zeros(max(nsets, 1), dtype=np.int32)
+        res.em_pi, res.em_freqs = np.zeros(max(len(comp), 1)), np.zeros(max(len(comp), 1))
+        res.em_margin, res.em_energy, res.em_off = np.zeros(max(nsets, 1)), np.zeros(max(nsets, 1)), off
+        a, eo = _EmIn(), _EmOut()
+        a.n_sets, a.set_window, a.set_off, a.compatible, a.a0, a.tol = nsets, sw.ctypes.data, off.ctypes.data, comp.ctypes.data, a0, tol
+        eo.loglik, eo.iters, eo.pi, eo.freqs = res.em_loglik.ctypes.data, res.em_iters.ctypes.data, res.em_pi.ctypes.data, res.em_freqs.ctypes.data
+        eo.margin, eo.energy = res.em_margin.ctypes.data, res.em_energy.ctypes.data
+        keep += [sw, off, comp, a, eo]
+        job.em, job.em_out = C.addressof(a), C.addressof(eo)
+    return job, keep, res
+
+
+def _engine_process(self, batch, want_pairs=True, want_hpos=False, cover=None, pair_sums=False, n_groups=0,
+                    read_group=None, em=None, ins=None):
+    """dindel_b200_process: K1 and, on the still-resident results, K4 / K2 / K3, streamed through the device in
+    ranges of windows (any batch size).  See _build_job for the arguments."""
+    job, keep, res = _build_job(batch, want_pairs, want_hpos, cover, pair_sums, n_groups, read_group, em, ins)
+    self._check(self.lib.dindel_b200_process(self.h, C.byref(job)), "process")
+    res.timing = self.timing()
+    self._resident, self._n_haps = (batch, want_hpos or cover is not None), batch.n_haps
+    return res
+
+
+Engine.process = _engine_process
+
+
+def sum_error_bound(n_terms, magnitude):
+    return float(load_library().dindel_b200_sum_error_bound(int(n_terms), float(magnitude)))
+
+
+class MultiEngine:
+    """The window scheduler over several GPUs of one box (dindel_b200_multi_*): one context + one host worker
+    thread per device inside the library, windows sharded by cost, results in window order."""
+
+    def __init__(self, params=None, devices=(0,)):
+        self.lib = load_library()
+        self.params = params if params is not None else cli_params()
+        dev = np.ascontiguousarray(devices, dtype=np.int32)
+        h = C.c_void_p()
+        rc = self.lib.dindel_b200_multi_create(C.byref(self.params), dev.ctypes.data, len(dev), C.byref(h))
+        if rc != 0:
+            raise RuntimeError("dindel_b200_multi_create failed: %s" % self.lib.dindel_b200_strerror(rc).decode())
+        self.h, self.n_devices = h, len(dev)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.dindel_b200_multi_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def process(self, batch, want_pairs=True, want_hpos=False, cover=None, pair_sums=False, n_groups=0, read_group=None,
+                em=None, ins=None, pinned=None):
+        job, keep, res = _build_job(batch, want_pairs, want_hpos, cover, pair_sums, n_groups, read_group, em, ins, pinned)
+        t0 = time.perf_counter()
+        rc = self.lib.dindel_b200_multi_process(self.h, C.byref(job))
+        res.wall_ms = 1e3 * (time.perf_counter() - t0)
+        if rc != 0:
+            raise RuntimeError("multi_process failed: %s (%s)" % (self.lib.dindel_b200_strerror(rc).decode(),
+                                                                  self.lib.dindel_b200_multi_last_error(self.h).decode()))
+        res.shards = []
+        for k in range(self.n_devices):
+            a, b, t = C.c_int32(), C.c_int32(), Timing()
+            self.lib.dindel_b200_multi_get_shard(self.h, k, C.byref(a), C.byref(b), C.byref(t))
+            res.shards.append((a.value, b.value, t))
+        return res

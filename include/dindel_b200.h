@@ -19,12 +19,13 @@
  */
 #ifndef DINDEL_B200_H
 #define DINDEL_B200_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-#define DINDEL_B200_ABI_VERSION 3
+#define DINDEL_B200_ABI_VERSION 4
 
 /* error codes (batch-fatal) */
 #define DINDEL_OK 0
@@ -128,9 +129,16 @@ typedef struct dindel_batch_out {
 
 /* timings of the last submit/run on the context's stream, CUDA events, milliseconds */
 typedef struct dindel_timing {
+    /* submit / process: h2d_ms / d2h_ms = busy time of the two copy streams (summed over chunks; they run under the
+     * kernels), k1_ms = span from the first chunk's first kernel to the last chunk's last kernel, prep_ms = 0,
+     * total_ms = first copy in to last copy out.  upload / run / download: the four stages one after the other. */
     float h2d_ms, prep_ms, k1_ms, d2h_ms, total_ms;
     int32_t k1_launches, prep_launches;
     int64_t n_pairs, n_cells; /* cells = sum over pairs R*(H+2) */
+    float post_ms;            /* process: K4 / K2 / K3 stages incl. their copies, summed over ranges */
+    float host_ms;            /* process: host wall time of the whole call (pack / index / scan + waiting) */
+    int32_t n_ranges;         /* process: resident ranges the batch was streamed through (1 = whole batch resident) */
+    int32_t n_chunks;         /* pipeline chunks over all ranges */
 } dindel_timing;
 
 typedef struct dindel_ctx dindel_ctx;
@@ -162,7 +170,8 @@ int64_t dindel_b200_count_cells(const dindel_batch_in *in);
  * the range boundaries: shard k owns windows [first_window[k], first_window[k+1]). */
 int dindel_b200_plan_shards(const dindel_batch_in *in, int n_shards, int32_t *first_window);
 
-/* computeLikelihoods for a whole batch: host buffers in, host buffers out (H2D + kernels + D2H). */
+/* computeLikelihoods for a whole batch: host buffers in, host buffers out (H2D + kernels + D2H).
+ * Equivalent to dindel_b200_process with only `in` / `out` set. */
 int dindel_b200_submit(dindel_ctx *ctx, const dindel_batch_in *in, dindel_batch_out *out);
 
 /* the same split in three for callers that keep a batch resident in HBM */
@@ -174,6 +183,13 @@ int dindel_b200_get_timing(const dindel_ctx *ctx, dindel_timing *t);
 int dindel_b200_hpos_stride(const dindel_ctx *ctx);           /* stride of the resident hpos rows */
 /* device time (CUDA events) of the kernel of the last pair_sums / bayes_em / coverage call, ms */
 float dindel_b200_last_kernel_ms(const dindel_ctx *ctx);
+
+/* Inference only: makes a batch of caller-computed read x haplotype log-likelihoods the resident batch, as if K1 had
+ * produced them (rl[r*nh+h] of DInDel.cpp:2129 / :2953, r-major inside a window, windows back to back), so that
+ * dindel_b200_pair_sums / dindel_b200_bayes_em run on likelihoods from elsewhere (the reference's --faster model, a
+ * dump).  Every other field of the resident pair records is zero and there are no hpos rows. */
+int dindel_b200_load_likelihoods(dindel_ctx *ctx, int32_t n_windows, const int32_t *win_hap, const int32_t *win_read,
+                                 const double *ll);
 
 /* ---- K2: haplotype-pair sums over the RESIDENT likelihood matrix (after run/submit) ----------
  * Replaces the inner loops of DetInDel::diploidGLF (DInDel.cpp:3085-3113: start = 0;
@@ -188,10 +204,17 @@ typedef struct dindel_pairsum_in {
     const int32_t *job_window; /* [n_jobs] */
     const int32_t *job_group;  /* [n_jobs] -1 = all reads */
     const int64_t *job_off;    /* [n_jobs+1]; job_off[j+1]-job_off[j] == nh*(nh+1)/2 of its window */
-    const double *start;       /* [job_off[n_jobs]] */
+    const double *start;       /* [job_off[n_jobs]]; NULL = all zero */
     const int32_t *read_group; /* optional [n_reads] (Read::poolID) */
 } dindel_pairsum_in;
 int dindel_b200_pair_sums(dindel_ctx *ctx, const dindel_pairsum_in *in, double *out);
+/* Bound on |GPU sum - the reference's CPU sum| for a sum of n_terms reads whose partial sums stay below `magnitude`
+ * in absolute value (pass |start| + |sum| + 1): the terms differ by CUDA-libm-vs-glibc exp/log (<= 2 ulp of a term
+ * plus 1e-15 for the log(1+exp()) part) and every partial sum rounds once, in either order of summation, so
+ *   bound = 4 * n_terms * (2.22e-16 * magnitude + 1e-15)          (a factor 4 of head-room on the analysis).
+ * The host adapter (include/dindel_b200.hpp) treats every comparison closer than this and every printed field whose
+ * 6-digit text could change within it as undecided and re-evaluates that window with the reference's own CPU loop. */
+double dindel_b200_sum_error_bound(int64_t n_terms, double magnitude);
 
 /* ---- K3: variational-Bayes EM over haplotype frequencies (DInDel.cpp:2431-2545) --------------
  * One EM run per set of active variants: set s on window set_window[s] with compatible[] flags
@@ -211,6 +234,11 @@ typedef struct dindel_em_out {
     int32_t *iters;  /* [n_sets] */
     double *pi;      /* [set_off[n_sets]] */
     double *freqs;   /* [set_off[n_sets]] */
+    /* optional [n_sets]: min over the EM passes of | |eOld - eNew| - tol |, the distance of the stopping rule
+     * (DInDel.cpp:2515) from flipping.  The GPU's energy differs from the CPU's at the 1e-10 level (libm, reduction
+     * order over reads); a set whose margin is below the adapter's guard is re-run with the reference's own loop. */
+    double *margin;
+    double *energy;  /* optional [n_sets]: eNew of the last pass */
 } dindel_em_out;
 int dindel_b200_bayes_em(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out *out);
 
@@ -294,6 +322,63 @@ typedef struct dindel_cigar_out {
     uint32_t *ops;          /* [n_reads * cigar_cap] */
 } dindel_cigar_out;
 int dindel_b200_cigars(dindel_ctx *ctx, const dindel_cigar_in *in, dindel_cigar_out *out);
+
+/* ---- one pass over a batch of ANY size: K1 and, while the results are still in HBM, K4 / K2 / K3 --------------
+ * The batch is streamed through the device in RANGES of windows that fit a fixed memory budget
+ * ($DINDEL_B200_MEM_BUDGET bytes, default 48 GiB: inputs + 64 B per pair + the hpos rows); inside a range the
+ * chunked H2D / kernel / D2H pipeline of submit runs, then the optional stages on the range's resident results, and
+ * their (small) outputs come back before the next range reuses the buffers.  Device memory therefore does not grow
+ * with the batch: one call can take millions of windows (BASELINE configs[4]).  What replaces what:
+ *   out        computeLikelihoods (DInDel.cpp:1707-1739).  out->pairs may be NULL when only the stages below are
+ *              wanted (then no per-pair record crosses PCIe); out->win_pair / win_status / read_on_hap as in submit.
+ *   cover      filterHaplotypes (DInDel.cpp:1932-2100) for every window: same arrays as dindel_b200_coverage, over
+ *              the whole batch.  Implies the hpos rows are produced (and kept in HBM unless out->hpos is set).
+ *   pair_sums  the read sums of diploidGLF / the pooled genotype likelihoods (DInDel.cpp:3086-3089, :3369-3372,
+ *              :2687-2690) for every window and every h1 <= h2, started at 0:
+ *                n_groups == 0: pair_sums[sum_off[w] + q]                      = sum over all reads of the window
+ *                n_groups >= 1: pair_sums[sum_off[w] * n_groups + g * npairs(w) + q] = sum over reads with read_group == g
+ *              with sum_off[w] = sum over windows before w of nh(nh+1)/2 (returned in win_sum_off when non-NULL) and q
+ *              enumerating h1 <= h2 row-major.  The host adds its own start value (prior - sitePrior) and keeps the
+ *              printed text identical through dindel_b200_sum_error_bound (see there).
+ *   em         estimateHaplotypeFrequenciesBayesEM's EM (DInDel.cpp:2431-2545) for sets known up front; set_window
+ *              must be sorted ascending.
+ * After the call the batch is resident (K2..K5 entries usable) only if it went through as ONE range
+ * (dindel_timing.n_ranges == 1). */
+typedef struct dindel_job {
+    const dindel_batch_in *in;
+    dindel_batch_out *out;
+    const dindel_cover_in *cover;         /* optional */
+    dindel_cover_out *cover_out;
+    double *pair_sums;                     /* optional */
+    int64_t *win_sum_off;                  /* optional [n_windows+1] */
+    int32_t n_groups;
+    int32_t reserved;
+    const int32_t *read_group;             /* [n_reads] when n_groups >= 1 */
+    const dindel_em_in *em;         /* optional */
+    dindel_em_out *em_out;
+} dindel_job;
+int dindel_b200_process(dindel_ctx *ctx, const dindel_job *job);
+/* number of doubles pair_sums must hold for this batch (per group when n_groups >= 1: multiply) */
+int64_t dindel_b200_count_sums(const dindel_batch_in *in);
+
+/* ---- the window scheduler over the GPUs of one box (north star (3); replaces the per-file process fan-out of
+ * makeWindows.py, python/makeWindows.py:48-55) ----------------------------------------------------------------
+ * One dindel_multi owns one context and one host worker thread per listed device.  multi_process plans contiguous
+ * window shards of near-equal K1 cost (dindel_b200_plan_shards), runs dindel_b200_process on every shard
+ * concurrently (each device streams its own shard through its own ranges) and returns when all are done; results
+ * land in the caller's arrays in window order, byte-identical to a single-device run.  No collective: windows are
+ * independent (DInDel.cpp:1310-1411).  Use from one host thread at a time. */
+typedef struct dindel_multi dindel_multi;
+int dindel_b200_multi_create(const dindel_params *p, const int *devices, int ndev, dindel_multi **out);
+int dindel_b200_multi_destroy(dindel_multi *m);
+int dindel_b200_multi_devices(const dindel_multi *m);
+int dindel_b200_multi_set_libraries(dindel_multi *m, int n_libs, const int64_t *lib_off, const double *probs,
+                                    const double *ninetyfifth_pct_prob);
+int dindel_b200_multi_process(dindel_multi *m, const dindel_job *job);
+/* per device of the last multi_process: its window shard [first, last) and its timing */
+int dindel_b200_multi_get_shard(const dindel_multi *m, int k, int32_t *first_window, int32_t *last_window,
+                                dindel_timing *t);
+const char *dindel_b200_multi_last_error(const dindel_multi *m);
 
 /* pinned host memory for the caller's buffers */
 void *dindel_b200_alloc_pinned(size_t bytes);

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(engine.EXPORTS) == names
-    assert lib.dindel_b200_abi_version() == 3
+    assert lib.dindel_b200_abi_version() == 4
 
 
 def test_struct_layouts_match_header():
@@ -34,7 +34,8 @@ def test_struct_layouts_match_header():
     assert engine.PAIR_DTYPE.itemsize == 64
     assert C.sizeof(engine._BatchIn) == 16 + 14 * 8
     assert C.sizeof(engine._BatchOut) == 8 + 8 + 8 + 8 + 8 + 8 + 8
-    assert C.sizeof(engine.Timing) == 5 * 4 + 2 * 4 + 4 + 16  # 4 bytes padding before the int64s
+    assert C.sizeof(engine.Timing) == 5 * 4 + 2 * 4 + 4 + 16 + 4 * 4  # 4 bytes padding before the int64s
+    assert C.sizeof(engine._Job) == 6 * 8 + 8 + 3 * 8 and C.sizeof(engine._EmOut) == 6 * 8
 
 
 def test_param_presets_follow_reference_defaults():

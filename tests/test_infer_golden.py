@@ -128,3 +128,72 @@ def test_oracle_bayes_em_bit_exact_vs_reference(golden, port_oracle):
             for h1, h2, pr, ll in rows:
                 assert got[idx[(h1, h2)]] == ll
     assert n >= 60
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# GPU: K2 / K3 on the reference's own rl matrices (dindel_b200_load_likelihoods makes them the resident batch)
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+def test_gpu_k2_vs_reference_golden(golden, engine_cli):
+    from dindel_tgi_b200 import engine
+    dip = [w for w in golden if w["mode"] == "diploid"]
+    engine_cli.load_likelihoods([np.array(w["rl"]) for w in dip], [w["nh"] for w in dip])
+    jobs, starts, want = [], [], []
+    for k, w in enumerate(dip):
+        nh = w["nh"]
+        idx = {p: q for q, p in enumerate(_tri(nh))}
+        npairs = nh * (nh + 1) // 2
+        ref = np.full(npairs, np.nan)
+        for h1, h2, ll, prior, c1, c2 in w["pairs"]:
+            ref[idx[(h1, h2)]] = ll
+        jobs.append(k); starts.append(np.zeros(npairs)); want.append(ref)
+        by_pos = {}
+        for pos, h1, h2, v1, v2, pr, ll in w["site_pairs"]:
+            by_pos.setdefault(pos, []).append((h1, h2, pr, ll))
+        for pos, rows in by_pos.items():
+            st, ref = np.zeros(npairs), np.full(npairs, np.nan)
+            for h1, h2, pr, ll in rows:
+                st[idx[(h1, h2)]], ref[idx[(h1, h2)]] = pr, ll
+            jobs.append(k); starts.append(st); want.append(ref)
+    got = engine_cli.pair_sums(jobs, starts)
+    n = 0
+    worst = 0.0
+    for j, k in enumerate(jobs):
+        m = ~np.isnan(want[j])       # filtered pairs are not evaluated by the reference
+        g, r = got[j][m], want[j][m]
+        assert np.allclose(g, r, rtol=RTOL, atol=0), (j, np.abs(g - r).max())
+        # the library's own guard band covers the observed difference with room to spare
+        bound = np.array([engine.sum_error_bound(dip[k]["nr"], abs(x) + abs(s) + 1) for x, s in zip(r, starts[j][m])])
+        assert (np.abs(g - r) <= bound).all()
+        worst = max(worst, float((np.abs(g - r) / bound).max()))
+        assert int(np.argmax(g)) == int(np.argmax(r))          # strict-> arg-max pair (DInDel.cpp:3102-3110, :3384)
+        n += int(m.sum())
+    assert n > 1500
+    assert worst < 0.5, worst     # observed difference stays below half the bound
+
+
+@pytest.mark.gpu
+def test_gpu_k3_vs_reference_golden(golden, engine_cli):
+    poo = [w for w in golden if w["mode"] == "pooled"]
+    engine_cli.load_likelihoods([np.array(w["rl"]) for w in poo], [w["nh"] for w in poo])
+    sets, comps, ref = [], [], []
+    for k, w in enumerate(poo):
+        for th, s in enumerate(w["sets"]):
+            sets.append(k); comps.append(np.array(s["compatible"], dtype=np.uint8)); ref.append((w, th, s))
+    ll, it, pi, fr = engine_cli.bayes_em(sets, comps, poo[0]["a0"], poo[0]["tol"])
+    margin, energy = engine_cli.last_em_margin, engine_cli.last_em_energy
+    worst_e = 0.0
+    for j, (w, th, s) in enumerate(ref):
+        nh = w["nh"]
+        assert it[j] == s["iter"], (j, it[j], s["iter"], margin[j])
+        assert abs(ll[j] - s["loglik"]) <= RTOL * abs(s["loglik"])
+        assert np.allclose(pi[j], s["pi"], rtol=RTOL, atol=0)
+        assert np.allclose(fr[j], w["freqs"][th * nh:(th + 1) * nh], rtol=1e-8, atol=1e-300)
+        # energy of the last pass: the quantity the stopping rule compares (DInDel.cpp:2515); the adapter re-runs a set
+        # on the host when its margin is below 1e-7 * max(1, |E|): the observed GPU-vs-reference difference must stay
+        # far inside that guard
+        de = abs(energy[j] - s["energy"])
+        worst_e = max(worst_e, de / max(1.0, abs(s["energy"])))
+        assert margin[j] >= 0.0
+    assert len(ref) >= 60
+    assert worst_e < 1e-10, worst_e
