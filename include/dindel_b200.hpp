@@ -22,6 +22,8 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <iostream>
+#include <sstream>
+#include <math.h>
 #include <map>
 #include <string>
 #include <time.h>
@@ -44,6 +46,7 @@ struct ReadTraits {
 #endif
     static uint32_t start(const ReadT &r) { return uint32_t(r.posStat.first); }                      // ObservationModelFB.cpp:52
     static bool reverse(const ReadT &r) { return r.onReverseStrand; }
+    static int pool(const ReadT &r) { return r.poolID; }                                             // Read.hpp:73, DInDel.cpp:2580
 #ifdef BAM_BAM_H
     // insert-size prior of computeBMidPrior (ObservationModelFB.cpp:279-293): which formula applies to this read
     // (the caller ANDs it with params.mapUnmappedReads), its anchor coordinate, and its Library (Read.hpp:258)
@@ -99,7 +102,7 @@ inline int run_cigars(dindel_ctx *ctx, dindel_cigar_in &in, size_t nr, std::vect
 class Engine {
 public:
     template <class ObsParams>
-    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0), last_nh_(0), last_nr_(0), t_cl_(0.0), t_fh_(0.0), n_cl_(0), mapUnmapped_(false), libOff_(1, 0)
+    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0), last_nh_(0), last_nr_(0), t_cl_(0.0), t_fh_(0.0), n_cl_(0), mapUnmapped_(false), libOff_(1, 0), wantSums_(false), nPools_(0)
     {
         dindel_b200_default_params(&p_);
         p_.pError = op.pError; p_.pMut = op.pMut; p_.mapQualThreshold = op.mapQualThreshold;
@@ -113,6 +116,36 @@ public:
     ~Engine() { if (ctx_) dindel_b200_destroy(ctx_); }
     dindel_ctx *ctx() const { return ctx_; }
     const dindel_params &params() const { return p_; }
+    // Which read sums computeLikelihoods also brings back for the window (K2 inside the same dindel_b200_process call):
+    // NONE; ALL = one sum over all reads per haplotype pair (diploidGLF, DInDel.cpp:3086-3089 / :3369-3372);
+    // nPools >= 1 = one sum per pool member (estimateHaplotypeFrequenciesBayesEM, DInDel.cpp:2687-2690, myBams.size()).
+    void setInference(bool sums, int nPools) { wantSums_ = sums; nPools_ = nPools; }
+    bool wantSums() const { return wantSums_; }
+    // the sums of the window computeLikelihoods was last called with: [group][q], q enumerating h1 <= h2 row-major
+    const std::vector<double> &windowSums() const { return sums_; }
+    int windowPools() const { return nPools_ > 0 ? nPools_ : 0; }
+    size_t windowHaps() const { return last_nh_; }
+    size_t windowReads() const { return last_nr_; }
+    const std::vector<int> &windowPoolSizes() const { return poolSize_; }
+    // K3 on the resident window: one EM per row of `compatible` (nSets x nh).  Fills loglik[nSets], iters[nSets],
+    // pi[nSets*nh] (log frequencies, DInDel.cpp:2473), margin[nSets] (distance of the stopping rule from flipping).
+    void windowEM(const std::vector<uint8_t> &compatible, size_t nSets, double a0, double tol, std::vector<double> &loglik,
+                  std::vector<int32_t> &iters, std::vector<double> &pi, std::vector<double> &margin)
+    {
+        const size_t nh = last_nh_;
+        loglik.assign(nSets, 0.0); iters.assign(nSets, 0); pi.assign(nSets * nh, 0.0); margin.assign(nSets, 0.0);
+        if (nSets == 0) return;
+        std::vector<int32_t> sw(nSets, 0);
+        std::vector<int64_t> off(nSets + 1, 0);
+        for (size_t k = 0; k <= nSets; k++) off[k] = (int64_t)(k * nh);
+        std::vector<double> freqs(nSets * nh, 0.0);
+        dindel_em_in in; in.n_sets = (int32_t)nSets; in.reserved = 0; in.set_window = &sw[0]; in.set_off = &off[0];
+        in.compatible = &compatible[0]; in.a0 = a0; in.tol = tol;
+        dindel_em_out out; out.loglik = &loglik[0]; out.iters = &iters[0]; out.pi = &pi[0]; out.freqs = &freqs[0];
+        out.margin = &margin[0]; out.energy = 0;
+        int rc = dindel_b200_bayes_em(ctx_, &in, &out);
+        if (rc != DINDEL_OK) throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx_) + ")";
+    }
     bool mapUnmappedReads() const { return mapUnmapped_; }
     void setMapUnmappedReads(bool v) { mapUnmapped_ = v; } // the reference flips it after construction (DInDel.cpp:4270)
 
@@ -178,7 +211,175 @@ private:
     std::map<const void *, int> libIndex_;
     std::vector<int64_t> libOff_;
     std::vector<double> libProbs_, libP95_;
+    bool wantSums_;
+    int nPools_;
+    std::vector<double> sums_;
+    std::vector<int> poolSize_;
 };
+
+// ---------------------------------------------------------------------------------------------------------------
+// Inference: the numeric cores of DetInDel::diploidGLF (DInDel.cpp:3085-3120, :3240-3266, :3349-3390) and of
+// DetInDel::estimateHaplotypeFrequenciesBayesEM (:2431-2545, :2683-2694) take their read sums / EM results from the
+// GPU (K2 / K3) while the TEXT the reference writes stays byte-identical.  The GPU values differ from glibc's at the
+// ulp level (CUDA libm, summation order), so every place where such a value is COMPARED or PRINTED goes through a
+// guard: a comparison closer than the error bound, or a printed field whose 6-digit text (OutputData::Line::set
+// streams doubles at the default precision, OutputData.hpp:82-84) could change within the bound, marks the window
+// "undecided".  The patched function runs under DINDEL_B200_TWO_PASS: output is buffered; an undecided window is run
+// again with the reference's own CPU loops (mode CPU: every hook is transparent), so the result is the reference's
+// by construction.  Counters report how often that happened.
+class Inference {
+public:
+    enum Mode { IDLE, GPU, CPU };
+    Inference() : enabled_(false), mode_(IDLE), risky_(false), S_(0), nh_(0), nr_(0), G_(0), eps_(0.0), emErr_(0.0),
+                  nWindows(0), nRecheck(0), nEmSets(0), nEmMismatch(0) {}
+    void enable(bool on) { enabled_ = on; }
+    bool enabled() const { return enabled_; }
+    bool enter() { if (!enabled_ || mode_ != IDLE) return false; mode_ = GPU; risky_ = false; eps_ = 0.0; emErr_ = 0.0; nWindows++; return true; }
+    void leave() { mode_ = IDLE; }
+    bool gpu() const { return mode_ == GPU; }
+    bool risky() const { return risky_; }
+    void toCpu() { mode_ = CPU; risky_ = false; nRecheck++; }
+    void markRisky() { if (mode_ == GPU) risky_ = true; }
+    // the window's read sums (K2): S[g * npairs + q]; nGroups == 0: one block over all reads
+    void setSums(const double *S, size_t nh, size_t nr, int nGroups, const int *groupSize)
+    { S_ = S; nh_ = nh; nr_ = nr; G_ = nGroups; gsize_ = groupSize; }
+    static size_t tri(size_t h1, size_t h2, size_t nh) { return h1 * nh - h1 * (h1 - 1) / 2 + (h2 - h1); }
+    // start + sum over the window's reads of log(.5) + addLogs(rl[r,h1], rl[r,h2])      (DInDel.cpp:3086-3089, :3369-3372)
+    double sum(size_t h1, size_t h2, size_t nh, double start)
+    {
+        if (!S_ || nh != nh_) { markRisky(); return start; }
+        const double s = S_[tri(h1, h2, nh)];
+        widen(dindel_b200_sum_error_bound((int64_t)nr_ + 1, fabs(start) + fabs(s) + 1.0));
+        return start + s;
+    }
+    // the same over the reads of pool member b                                          (DInDel.cpp:2687-2690)
+    double sumGroup(int b, size_t h1, size_t h2, size_t nh, double start)
+    {
+        if (!S_ || nh != nh_ || b < 0 || b >= G_) { markRisky(); return start; }
+        const double s = S_[(size_t)b * (nh * (nh + 1) / 2) + tri(h1, h2, nh)];
+        widen(dindel_b200_sum_error_bound((int64_t)(gsize_ ? gsize_[b] : (int)nr_) + 1, fabs(start) + fabs(s) + 1.0));
+        return start + s;
+    }
+    // a > b as the reference evaluates it; undecided when the two are closer than the bound.  gt: log-domain values
+    // (sums, log-likelihoods: absolute bound); gtLin: probabilities / frequencies derived from the EM (relative bound)
+    bool gt(double a, double b)
+    {
+        if (mode_ == GPU && fabs(a - b) <= 2.0 * eps_ + 2.0 * emErr_) risky_ = true;
+        return a > b;
+    }
+    bool gtLin(double a, double b)
+    {
+        if (mode_ == GPU && fabs(a - b) <= 4.0 * emErr_ * (fabs(a) > fabs(b) ? fabs(a) : fabs(b))) risky_ = true;
+        return a > b;
+    }
+    // a value about to be printed: its text must not depend on where inside the bound the true value lies
+    double printed(double v)
+    {
+        if (mode_ == GPU) {
+            const double e = 2.0 * eps_ + 2.0 * emErr_;
+            if (text(v - e) != text(v + e)) risky_ = true;
+        }
+        return v;
+    }
+    double printedLin(double v)
+    {
+        if (mode_ == GPU) {
+            const double e = 4.0 * emErr_ * fabs(v);
+            if (text(v - e) != text(v + e)) risky_ = true;
+        }
+        return v;
+    }
+    // -10 * (ref - addLogs(alt, ref)) / log(10): qual (DInDel.cpp:3119) and genoqual (:3266), whose inputs are two
+    // maxima of sums; evaluated at the four corners of the bound (the formula cancels, so a plain interval on its
+    // output would not do)
+    void checkPhred(double ref, double alt)
+    {
+        if (mode_ != GPU) return;
+        const double e = 2.0 * eps_;
+        const std::string t = text(phred(ref, alt));
+        for (int i = 0; i < 4; i++)
+            if (text(phred(ref + ((i & 1) ? e : -e), alt + ((i & 2) ? e : -e))) != t) { risky_ = true; return; }
+    }
+    // ---- Bayes EM (K3) ----
+    // All EM runs of the window in one launch; em() then hands them out set by set and checks that the set it was
+    // computed for is the one the reference arrived at.
+    void emBegin(Engine &e, const std::vector<uint8_t> &compatible, size_t nSets, double a0, double tol)
+    {
+        emCompat_ = compatible; emSets_ = nSets;
+        if (mode_ != GPU) return;
+        e.windowEM(compatible, nSets, a0, tol, emLoglik_, emIters_, emPi_, emMargin_);
+    }
+    // returns true (converged) and fills loglik / pi / iter when the GPU's EM of set th stands; else the reference's
+    // own while-loop runs (returns false)
+    template <class IntVec, class DblVec>
+    bool em(int th, const IntVec &compatible, double tol, double &loglik, DblVec &pi, int &iter)
+    {
+        if (mode_ != GPU) return false;
+        nEmSets++;
+        const size_t nh = compatible.size();
+        if ((size_t)th >= emSets_ || emCompat_.size() != emSets_ * nh) { nEmMismatch++; risky_ = true; return false; }
+        for (size_t h = 0; h < nh; h++)
+            if ((compatible[h] != 0) != (emCompat_[th * nh + h] != 0)) { nEmMismatch++; risky_ = true; return false; }
+        // stopping rule |eOld - eNew| < tol (DInDel.cpp:2515): the GPU's energies differ from the CPU's by ~1e-13
+        // relative (measured 1e-15, tools/k23_deviation.py -> profiles/r2_k23_deviation.json); a pass that came closer to
+        // tol than 1e-10 * (1 + |loglik|) could have gone the other way on the CPU
+        const double guard = emGuardRel() * (1.0 + fabs(emLoglik_[th]));
+        if (emMargin_[th] < guard) { risky_ = true; return false; }
+        loglik = emLoglik_[th];
+        for (size_t h = 0; h < nh; h++) pi[h] = emPi_[th * nh + h];
+        iter = emIters_[th];
+        const double e = emValueRel() * (1.0 + fabs(loglik));
+        if (e > emErr_) emErr_ = e;
+        return true;
+    }
+    static double emGuardRel() { return 1e-10; }  // margin guard, relative to 1 + |loglik| (measured energy deviation: 1e-15)
+    static double emValueRel() { return 1e-12; }  // bound on the GPU EM's error, relative (measured: loglik 7e-16, pi 5e-14, freqs 5e-15)
+    static std::string text(double v) { std::ostringstream os; os << v; return os.str(); }
+    static double addLogsHost(double l1, double l2) // Utils.hpp:29-38
+    {
+        if (l1 > l2) { double diff = l2 - l1; return l1 + log(1.0 + exp(diff)); }
+        double diff = l1 - l2; return l2 + log(1.0 + exp(diff));
+    }
+    static double phred(double ref, double alt) { return -10.0 * (ref - addLogsHost(alt, ref)) / log(10.0); }
+    long nWindows, nRecheck, nEmSets, nEmMismatch;
+private:
+    void widen(double e) { if (e > eps_) eps_ = e; }
+    bool enabled_;
+    Mode mode_;
+    bool risky_;
+    const double *S_;
+    size_t nh_, nr_;
+    int G_;
+    const int *gsize_;
+    double eps_, emErr_;
+    std::vector<uint8_t> emCompat_;
+    size_t emSets_;
+    std::vector<double> emLoglik_, emPi_, emMargin_;
+    std::vector<int32_t> emIters_;
+};
+
+// Runs CALL (the function's own body, re-entered) with the glf output buffered: first with the GPU's numbers, and
+// when a guard tripped once more with the reference's CPU loops.  OUT = the OutputData whose `out` stream the body
+// writes to; RESET = statement(s) undoing what a discarded pass appended to output arguments.
+struct TwoPass {
+    Inference &inf; std::ostream **slot; std::ostream *real; std::ostringstream buf;
+    TwoPass(Inference &i, std::ostream **s) : inf(i), slot(s), real(*s) { *slot = &buf; }
+    ~TwoPass() { *slot = real; inf.leave(); }
+    bool retry() { if (inf.gpu() && inf.risky()) { buf.str(std::string()); buf.clear(); inf.toCpu(); return true; } return false; }
+    void commit() { *real << buf.str(); }
+};
+#define DINDEL_B200_TWO_PASS(INF, OUT, RESET, CALL)                                              \
+    if ((INF).enter()) {                                                                         \
+        dindel_b200::TwoPass _tp((INF), &(OUT).out);                                             \
+        for (;;) {                                                                               \
+            std::string _ex; bool _threw = false;                                                \
+            try { CALL; } catch (std::string &_s) { _threw = true; _ex = _s; }                   \
+            if (_tp.retry()) { RESET; continue; }                                                \
+            _tp.commit();                                                                        \
+            if (_threw) throw _ex;                                                               \
+            return;                                                                              \
+        }                                                                                        \
+    }
 
 // mapped types of MLA::indels and HapT::indels (C++98-friendly, the reference builds as gnu++98)
 template <class M> struct map_value;
@@ -326,7 +527,27 @@ void Engine::computeLikelihoods(const std::vector<HapT> &haps, const std::vector
     out.n_pairs = (int64_t)np; out.pairs = &pairs[0]; out.hpos = &hpos[0]; out.hpos_stride = stride;
     out.flags = DINDEL_OUT_KEEP_HPOS; out.win_pair = win_pair; out.win_status = &status; out.read_on_hap = &on[0];
     last_nh_ = last_nr_ = 0;
-    int rc = dindel_b200_submit(ctx_, &in, &out);
+    // one pass: K1 and, when the caller's inference runs on the GPU too, the read sums of the window (K2) while the
+    // likelihood matrix is still in HBM
+    dindel_job job;
+    job.in = &in; job.out = &out; job.cover = 0; job.cover_out = 0; job.pair_sums = 0; job.win_sum_off = 0;
+    job.n_groups = 0; job.reserved = 0; job.read_group = 0; job.em = 0; job.em_out = 0;
+    std::vector<int32_t> rgroup;
+    if (wantSums_) {
+        const int G = nPools_ > 0 ? nPools_ : 1;
+        sums_.assign(nh * (nh + 1) / 2 * (size_t)G, 0.0);
+        job.pair_sums = &sums_[0];
+        if (nPools_ > 0) {
+            rgroup.resize(nr);
+            poolSize_.assign((size_t)nPools_, 0);
+            for (size_t r = 0; r < nr; r++) {
+                rgroup[r] = RT::pool(reads[r]);
+                if (rgroup[r] >= 0 && rgroup[r] < nPools_) poolSize_[rgroup[r]]++;
+            }
+            job.n_groups = nPools_; job.read_group = &rgroup[0];
+        }
+    }
+    int rc = dindel_b200_process(ctx_, &job);
     if (rc != DINDEL_OK)
         throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx_) + ")";
     last_nh_ = nh; last_nr_ = nr;

@@ -20,7 +20,11 @@ text = open(src, encoding="latin-1").read()
 inc = '#include "Faster.hpp"\n'
 assert text.count(inc) == 1
 if not (len(sys.argv) > 3 and sys.argv[3] == "--dump"):
-    text = text.replace(inc, inc + '#include "dindel_b200.hpp"\nstatic dindel_b200::Engine *dindel_b200_gpu = 0;\n')
+    text = text.replace(inc, inc + '#include "dindel_b200.hpp"\nstatic dindel_b200::Engine *dindel_b200_gpu = 0;\n'
+                        'static dindel_b200::Inference dindel_b200_inf; // K2 / K3 with the guard band (INTEGRATION.md section 0b)\n'
+                        'static struct dindel_b200_report_t { ~dindel_b200_report_t() { if (dindel_b200_inf.nWindows) '
+                        'fprintf(stderr, "dindel_b200 inference: windows %ld rechecked_on_host %ld em_sets %ld em_set_mismatch %ld\\n", '
+                        'dindel_b200_inf.nWindows, dindel_b200_inf.nRecheck, dindel_b200_inf.nEmSets, dindel_b200_inf.nEmMismatch); } } dindel_b200_report;\n')
 
 sig = re.compile(r"\nvoid DetInDel::computeLikelihoods\(const vector<Haplotype> &haps, const vector<Read> & reads, "
                  r"vector<vector<MLAlignment> > & liks, uint32_t leftPos, uint32_t rightPos, vector<int> & onHap\)\n\{\n")
@@ -29,7 +33,13 @@ assert len(hits) == 2, len(hits)          # the first one sits inside a /* ... *
 m = hits[-1]
 fwd = ("\t{ // dindel_b200 drop-in (INTEGRATION.md section 0)\n"
        "\t\tdindel_b200::Engine *&gpu = dindel_b200_gpu;\n"
-       "\t\tif (!gpu) gpu = new dindel_b200::Engine(params.obsParams, getenv(\"DINDEL_B200_DEVICE\") ? atoi(getenv(\"DINDEL_B200_DEVICE\")) : 0);\n"
+       "\t\tif (!gpu) {\n"
+       "\t\t\tgpu = new dindel_b200::Engine(params.obsParams, getenv(\"DINDEL_B200_DEVICE\") ? atoi(getenv(\"DINDEL_B200_DEVICE\")) : 0);\n"
+       "\t\t\t// K2 / K3: the read sums of diploidGLF / the EM of estimateHaplotypeFrequenciesBayesEM on the GPU too\n"
+       "\t\t\tconst bool infer = !getenv(\"DINDEL_B200_HOST_INFERENCE\") && (params.doDiploid != params.estimateHapFreqs);\n"
+       "\t\t\tgpu->setInference(infer, params.estimateHapFreqs ? int(myBams.size()) : 0);\n"
+       "\t\t\tdindel_b200_inf.enable(infer);\n"
+       "\t\t}\n"
        "\t\tgpu->computeLikelihoods(haps, reads, liks, leftPos, rightPos, onHap);\n"
        "\t\treturn;\n"
        "\t}\n")
@@ -92,6 +102,73 @@ if not dump:
         call = "\t\t\t\t\t\tcigars[r]=getCIGAR(haps[%s], reads[r], liks[%s][r], refSeqPos);\n" % (hx, hx)
         assert text.count(call) == 1
         text = text.replace(call, "\t\t\t\t\t\tif (!gpuCigars.empty()) cigars[r]=gpuCigars[r]; else\n" + call)
+
+    # fifth part of the patch: the numeric cores of diploidGLF and of the Bayes EM take their
+    # read sums / EM results from K2 / K3; every comparison and printed field that depends on them goes through
+    # dindel_b200::Inference's guard band, and DINDEL_B200_TWO_PASS re-runs an undecided window with the reference's
+    # own CPU loops, so glf / VCF stay byte-identical.  Each entry: (anchor, how many times it occurs, which occurrence,
+    # "before" / "after" / "replace", new text).
+    INFER = [
+        # ---- diploidGLF (DInDel.cpp:2933-3662) ----
+        ("void DetInDel::diploidGLF(const vector<Haplotype> & haps, const vector<Read> & reads, const vector<vector<MLAlignment> > & liks, vector<double> & hapFreqs, vector <HapEstResult > & posteriors,  uint32_t candPos, uint32_t leftPos, uint32_t rightPos,  OutputData & glfData, int index, const AlignedCandidates & candidateVariants, string program=\"all\")\n\n{\n",
+         1, 0, "after",
+         "\tif (dindel_b200_gpu && dindel_b200_gpu->wantSums()) dindel_b200_inf.setSums(&dindel_b200_gpu->windowSums()[0], dindel_b200_gpu->windowHaps(), dindel_b200_gpu->windowReads(), 0, 0);\n"
+         "\tDINDEL_B200_TWO_PASS(dindel_b200_inf, glfData, ;, diploidGLF(haps, reads, liks, hapFreqs, posteriors, candPos, leftPos, rightPos, glfData, index, candidateVariants, program))\n"),
+        ("\t\tdouble ll=0.0;\n\t\tfor (size_t r=0;r<reads.size();r++){\n\t\t\tll+=log(0.5)+addLogs(rl[r*nh+h1],rl[r*nh+h2]);\n", 1, 0, "replace",
+         "\t\tdouble ll=0.0;\n\t\tif (dindel_b200_inf.gpu()) ll = dindel_b200_inf.sum(h1, h2, nh, ll); else\n\t\tfor (size_t r=0;r<reads.size();r++){\n\t\t\tll+=log(0.5)+addLogs(rl[r*nh+h1],rl[r*nh+h2]);\n"),
+        ("\t\tif (pairs_posterior[h1*nh+h2]>max_ll_indel && (", 1, 0, "replace",
+         "\t\tif (dindel_b200_inf.gt(pairs_posterior[h1*nh+h2], max_ll_indel) && ("),
+        ("\t\tif (pairs_posterior[h1*nh+h2]>max_ll_noindel && (", 1, 0, "replace",
+         "\t\tif (dindel_b200_inf.gt(pairs_posterior[h1*nh+h2], max_ll_noindel) && ("),
+        ("\tqual = - 10.0*( ll_ref - addLogs(max_ll_indel, ll_ref) )/log(10.0);\n", 1, 0, "after",
+         "\tdindel_b200_inf.checkPhred(ll_ref, max_ll_indel);\n"),
+        ("\t\t\tgenoqual = - 10.0*( max_ll_altgeno - addLogs(max_ll_indel, max_ll_altgeno) )/log(10.0);\n", 1, 0, "after",
+         "\t\t\tdindel_b200_inf.checkPhred(max_ll_altgeno, max_ll_indel);\n"),
+        ("\t\t\tdouble ll=pr;\n\t\t\tfor (size_t r=0;r<reads.size();r++){\n", 1, 0, "replace",
+         "\t\t\tdouble ll=pr;\n\t\t\tif (dindel_b200_inf.gpu()) ll = dindel_b200_inf.sum(h1, h2, nh, ll); else\n\t\t\tfor (size_t r=0;r<reads.size();r++){\n"),
+        ("\t\t\tif (ll>maxll) {\n", 2, 1, "replace", "\t\t\tif (dindel_b200_inf.gt(ll, maxll)) {\n"),   # the first one (:297) is in an unused function
+        ("\t\t\to << str << a1 << \"/\" << a2 << \":\" << git->second;\n", 1, 0, "replace",
+         "\t\t\to << str << a1 << \"/\" << a2 << \":\" << dindel_b200_inf.printed(git->second);\n"),
+        ("\t\t\tline.set(\"logZ\", maxll );\n", 1, 0, "replace", "\t\t\tline.set(\"logZ\", dindel_b200_inf.printed(maxll) );\n"),
+        # ---- estimateHaplotypeFrequenciesBayesEM (DInDel.cpp:2103-2930) ----
+        ("void DetInDel::estimateHaplotypeFrequenciesBayesEM(const vector<Haplotype> & haps, const vector<Read> & reads, const vector<vector<MLAlignment> > & liks, vector<double> & hapFreqs, vector <HapEstResult > & posteriors,  uint32_t candPos, uint32_t leftPos,   uint32_t rightPos, OutputData & glfData, int index, const AlignedCandidates & candidateVariants, string program=\"all\")\n\n{\n",
+         1, 0, "after",
+         "\tif (dindel_b200_gpu && dindel_b200_gpu->wantSums()) dindel_b200_inf.setSums(&dindel_b200_gpu->windowSums()[0], dindel_b200_gpu->windowHaps(), dindel_b200_gpu->windowReads(), dindel_b200_gpu->windowPools(), dindel_b200_gpu->windowPoolSizes().empty() ? 0 : &dindel_b200_gpu->windowPoolSizes()[0]);\n"
+         "\tDINDEL_B200_TWO_PASS(dindel_b200_inf, glfData, posteriors.clear(), estimateHaplotypeFrequenciesBayesEM(haps, reads, liks, hapFreqs, posteriors, candPos, leftPos, rightPos, glfData, index, candidateVariants, program))\n"),
+        ("\n\tfor (int th=0;th<nav;th++) {\n", 1, 0, "before",
+         "\n\tif (dindel_b200_inf.gpu()) { // every EM run of the window in one K3 launch: compatible[] of each set as at :2394-2408 (checked again set by set in em())\n"
+         "\t\tstd::vector<uint8_t> b200c(size_t(nav)*nh, 0);\n"
+         "\t\tfor (int th=0;th<nav;th++) for (size_t h=0;h<nh;h++) {\n"
+         "\t\t\tint c = filtered[h]==0;\n"
+         "\t\t\tif (c) for (It it=haps[h].indels.begin();it!=haps[h].indels.end();it++)\n"
+         "\t\t\t\tif (!it->second.isRef() && !(it->second.isSNP() && it->second.getString()[3]=='D') && activeVariants[th].find(PAV(it->first,it->second))==activeVariants[th].end()) { c=0; break; }\n"
+         "\t\t\tb200c[size_t(th)*nh+h]=c;\n"
+         "\t\t}\n"
+         "\t\tdindel_b200_inf.emBegin(*dindel_b200_gpu, b200c, nav, params.bayesa0, params.EMtol);\n"
+         "\t}\n"),
+        ("\t\twhile (!converged) {\n", 1, 0, "before",
+         "\t\tif (dindel_b200_inf.em(th, compatible, tol, loglik, pi, iter)) converged = true; // K3 ran this EM\n"),
+        ("\t\t\t\t\tBOOST_FOREACH(int r, readidx[b]) {\n\t\t\t\t\t\tll+=log5+addLogs(rl[r*nh+h1],rl[r*nh+h2]);\n", 1, 0, "before",
+         "\t\t\t\t\tif (dindel_b200_inf.gpu()) ll = dindel_b200_inf.sumGroup(int(b), h1, h2, nh, ll); else\n"),
+        ("\t\t\t\tline.set(\"post_prob_variant\", exp(logp));\n\t\t\t\tline.set(\"est_freq\", freq);\n\t\t\t\tline.set(\"logZ\", logz);\n", 1, 0, "replace",
+         "\t\t\t\tline.set(\"post_prob_variant\", dindel_b200_inf.printedLin(exp(logp)));\n\t\t\t\tline.set(\"est_freq\", dindel_b200_inf.printedLin(freq));\n\t\t\t\tline.set(\"logZ\", dindel_b200_inf.printed(logz));\n"),
+        ("\t\t\t\t\t\tif (hapFreqs[h]>1.0/double(2*reads.size())) {\n", 1, 0, "replace",
+         "\t\t\t\t\t\tif (dindel_b200_inf.gtLin(hapFreqs[h], 1.0/double(2*reads.size()))) {\n"),
+        ("\t\t\t\t\t\t\tos << \":\" << hapFreqs[h];\n", 1, 0, "replace",
+         "\t\t\t\t\t\t\tos << \":\" << dindel_b200_inf.printedLin(hapFreqs[h]);\n"),
+        ("\t\t\t\t\to << lik[n];\n", 1, 0, "replace", "\t\t\t\t\to << dindel_b200_inf.printed(lik[n]);\n"),
+    ]
+    for anchor, count, which, where, code in INFER:
+        assert text.count(anchor) == count, (anchor, text.count(anchor))
+        i = -1
+        for _ in range(which + 1):
+            i = text.index(anchor, i + 1)
+        if where == "before":
+            text = text[:i] + code + text[i:]
+        elif where == "after":
+            text = text[:i + len(anchor)] + code + text[i + len(anchor):]
+        else:
+            text = text[:i] + code + text[i + len(anchor):]
 
 # --dump: oracle/_ref/dindel_ref_dump = the STOCK CPU driver whose filterHaplotypes (DInDel.cpp:1932-2100)
 # appends, at its end, its inputs and outputs as text to the file named by $DINDEL_B200_DUMP_COVER.  This is

@@ -124,6 +124,19 @@ def check_totals(glfs):
     return pairs, bad
 
 
+def inference_totals(glfs):
+    """`dindel_b200 inference:` lines of the GPU-backed binary (one per process, at exit): windows whose diploidGLF /
+    Bayes EM numeric cores ran on K2 / K3, and how many of them the guard band sent back to the reference's CPU loops."""
+    tot = {"windows": 0, "rechecked_on_host": 0, "em_sets": 0, "em_set_mismatch": 0}
+    for g in glfs:
+        for line in open(g[:-len(".glf.txt")] + ".log", errors="replace"):
+            if line.startswith("dindel_b200 inference:"):
+                t = line.split()
+                for k in tot:
+                    tot[k] += int(t[t.index(k) + 1])
+    return tot
+
+
 def diff_lines(a_files, b_files, limit=5):
     out = []
     for x, y in zip(a_files, b_files):
@@ -236,6 +249,8 @@ def main():
             ok, err = glf_stats(glfs)
             out[arm] = (glfs, vcf)
             r[arm] = {"stage3_wall_s": round(wall, 3), "vcf_calls": n_calls, "windows_ok": ok, "windows_skipped": err}
+            if arm == "gpu":
+                r[arm]["inference"] = inference_totals(glfs)
             if arm == "check":
                 r[arm]["pairs_compared"], r[arm]["pair_mismatches"] = check_totals(glfs)
                 verdict = verdict and r[arm]["pair_mismatches"] == 0 and r[arm]["pairs_compared"] > 0

@@ -50,6 +50,7 @@ template <> struct ReadTraits<MockRead> {
     static bool unmapped(const MockRead &r) { return r.unmapped; }
     static uint32_t start(const MockRead &r) { return r.start; }
     static bool reverse(const MockRead &r) { return r.reverse; }
+    static int pool(const MockRead &) { return 0; }
     static bool coverReverse(const MockRead &r) { return r.reverse; }
     static int insertMode(const MockRead &) { return DINDEL_INS_NONE; }
     static int32_t insertAnchor(const MockRead &, int) { return 0; }

@@ -5,8 +5,8 @@ synthetic chr20 FASTA + 30x BAM -> `--analysis getCIGARindels` -> windows -> `--
   * CPU: the window scripts' restatements (oracle/e2e/make_windows.py, merge_diploid.py), and the stock
     reference binary (oracle/_ref/dindel_ref, built where /root/reference exists) recovering the planted
     indels from the synthetic BAM -- this pins the fixture generator and the harness.
-  * GPU: the reference binary with INTEGRATION.md's three-line patch (oracle/_ref/dindel_b200: K1 and K4 run on
-    the B200 through include/dindel_b200.hpp) produces `.glf.txt` files and a VCF that are byte-identical
+  * GPU: the reference binary with INTEGRATION.md's patch (oracle/_ref/dindel_b200: K1, K4 and the inference cores
+    K2 / K3 run on the B200 through include/dindel_b200.hpp) produces `.glf.txt` files and a VCF that are byte-identical
     to the stock CPU binary's (north star: "final VCF indel calls and genotypes must be bit-exact").
 """
 import json
@@ -128,6 +128,10 @@ def test_glf_and_vcf_identical_to_cpu_reference(tmp_path):
     hn = res["heap_neutral"]
     assert hn["glf_identical"] and hn["vcf_identical"], res
     assert hn["cpu"]["vcf_calls"] >= 20 and hn["cpu"]["windows_ok"] >= 40, res
+    # diploidGLF's read sums came from K2 (dindel_b200_process); the guard band sent few windows back to the CPU loops
+    inf = hn["gpu"]["inference"]
+    assert inf["windows"] >= 40 and inf["rechecked_on_host"] <= inf["windows"] // 2, inf
+    print("K2 inference:", inf)
 
 
 @pytest.mark.gpu
@@ -165,8 +169,8 @@ def test_glf_identical_with_lib_file(tmp_path):
 
 @pytest.mark.gpu
 def test_glf_identical_pooled(tmp_path):
-    """--doPooled (estimateHaplotypeFrequenciesBayesEM, the path of configs[2]): K1 and K4 feed the reference's own EM;
-    glf byte-identical to the stock CPU binary (both arms use the same digamma shim)."""
+    """--doPooled (estimateHaplotypeFrequenciesBayesEM, the path of configs[2]): K1, K4, the EM (K3) and the pooled
+    genotype sums (K2) on the GPU; glf byte-identical to the stock CPU binary (both arms use the same digamma shim)."""
     if not run_e2e.have_binaries(("cpu", "gpu")):
         pytest.skip("oracle/_ref binaries not built (reference sources absent at build time)")
     r = subprocess.run([sys.executable, os.path.join(E2E, "run_e2e.py"), "--work", str(tmp_path), "--length", "50000",
@@ -176,6 +180,11 @@ def test_glf_identical_pooled(tmp_path):
     res = json.loads(r.stdout.strip().splitlines()[-1])
     hn = res["heap_neutral"]
     assert hn["glf_identical"] and hn["cpu"]["windows_ok"] >= 15, res
+    # the EM ran on K3 and the pooled genotype sums on K2; knife-edge sets / fields went back to the CPU loops
+    inf = hn["gpu"]["inference"]
+    assert inf["windows"] >= 15 and inf["em_sets"] >= 30 and inf["em_set_mismatch"] == 0, inf
+    assert inf["rechecked_on_host"] <= inf["windows"] // 2, inf
+    print("K3 inference:", inf)
 
 
 @pytest.mark.gpu
