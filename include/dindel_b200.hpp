@@ -230,8 +230,8 @@ private:
 class Inference {
 public:
     enum Mode { IDLE, GPU, CPU };
-    Inference() : enabled_(false), mode_(IDLE), risky_(false), S_(0), nh_(0), nr_(0), G_(0), eps_(0.0), emErr_(0.0),
-                  nWindows(0), nRecheck(0), nEmSets(0), nEmMismatch(0) {}
+    Inference() : nWindows(0), nRecheck(0), nEmSets(0), nEmMismatch(0), enabled_(false), mode_(IDLE), risky_(false), S_(0),
+                  nh_(0), nr_(0), G_(0), gsize_(0), eps_(0.0), emErr_(0.0), emSets_(0) {}
     void enable(bool on) { enabled_ = on; }
     bool enabled() const { return enabled_; }
     bool enter() { if (!enabled_ || mode_ != IDLE) return false; mode_ = GPU; risky_ = false; eps_ = 0.0; emErr_ = 0.0; nWindows++; return true; }
