@@ -303,7 +303,10 @@ public:
     // ---- Bayes EM (K3) ----
     // All EM runs of the window in one launch; em() then hands them out set by set and checks that the set it was
     // computed for is the one the reference arrived at.
-    void emBegin(Engine &e, const std::vector<uint8_t> &compatible, size_t nSets, double a0, double tol)
+    // Provider: anything with windowEM(compatible, nSets, a0, tol, loglik, iters, pi, margin) for the current window
+    // (Engine: the resident window; the batched driver: one window of the flushed batch)
+    template <class Provider>
+    void emBegin(Provider &e, const std::vector<uint8_t> &compatible, size_t nSets, double a0, double tol)
     {
         emCompat_ = compatible; emSets_ = nSets;
         if (mode_ != GPU) return;
@@ -595,7 +598,7 @@ public:
         hap_seq_.clear(); read_seq_.clear(); qual_.clear(); mapq_.clear(); flags_.clear(); strand_.clear(); start_.clear();
         win_entry_.assign(1, 0); win_key_.assign(1, 0); e_hap_.clear(); e_key_.clear(); e_left_.clear(); e_right_.clear();
         e_type_.clear(); keys_.clear(); maxR_ = 0; flushed_ = false;
-        insMode_.clear(); insAnchor_.clear(); insLib_.clear(); anyIns_ = false;
+        insMode_.clear(); insAnchor_.clear(); insLib_.clear(); anyIns_ = false; pool_.clear();
     }
     size_t size() const { return hap_start_.size(); }
     // copies what the engine needs of one window (DetInDel::computeLikelihoods' arguments + the variant entries of
@@ -626,6 +629,7 @@ public:
             mapq_.push_back(RT::mapq(reads[r])); start_.push_back(RT::start(reads[r]));
             flags_.push_back((uint8_t)((RT::unmapped(reads[r]) ? DINDEL_READ_UNMAPPED : 0) | (RT::reverse(reads[r]) ? DINDEL_READ_REVERSE : 0)));
             strand_.push_back(RT::coverReverse(reads[r]) ? 1 : 0);
+            pool_.push_back(RT::pool(reads[r]));
             if (sq.size() > maxR_) maxR_ = sq.size();
             const int mode = eng_.mapUnmappedReads() ? RT::insertMode(reads[r]) : DINDEL_INS_NONE;
             insMode_.push_back((uint8_t)mode);
@@ -645,6 +649,33 @@ public:
                 std::vector<std::vector<MLA> > &liks, std::vector<int> &onHap) const;
     template <class CovMap>
     int filterResult(int w, std::vector<int> &filtered, CovMap &varCoverage) const;
+    // K2 results of window w (flush() computes them when the engine's setInference asked for sums): hands them to the
+    // window's Inference guard
+    void bindSums(int w, Inference &inf) const
+    {
+        if (!flushed_ || sums_.empty() || w < 0 || (size_t)w >= size()) { inf.setSums(0, 0, 0, 0, 0); return; }
+        const int G = G_ > 0 ? G_ : 1;
+        inf.setSums(&sums_[(size_t)sum_off_[w] * G], (size_t)(win_hap_[w + 1] - win_hap_[w]), (size_t)(win_read_[w + 1] - win_read_[w]),
+                    G_, G_ > 0 ? &poolSize_[(size_t)w * G_] : 0);
+    }
+    // K3 for window w of the flushed (still resident) batch: one EM per row of `compatible` (nSets x nh)
+    void windowEM(int w, const std::vector<uint8_t> &compatible, size_t nSets, double a0, double tol, std::vector<double> &loglik,
+                  std::vector<int32_t> &iters, std::vector<double> &pi, std::vector<double> &margin) const
+    {
+        const size_t nh = (size_t)(win_hap_[w + 1] - win_hap_[w]);
+        loglik.assign(nSets, 0.0); iters.assign(nSets, 0); pi.assign(nSets * nh, 0.0); margin.assign(nSets, 0.0);
+        if (nSets == 0) return;
+        std::vector<int32_t> sw(nSets, (int32_t)w);
+        std::vector<int64_t> off(nSets + 1, 0);
+        for (size_t k = 0; k <= nSets; k++) off[k] = (int64_t)(k * nh);
+        std::vector<double> freqs(nSets * nh, 0.0);
+        dindel_em_in in; in.n_sets = (int32_t)nSets; in.reserved = 0; in.set_window = &sw[0]; in.set_off = &off[0];
+        in.compatible = &compatible[0]; in.a0 = a0; in.tol = tol;
+        dindel_em_out out; out.loglik = &loglik[0]; out.iters = &iters[0]; out.pi = &pi[0]; out.freqs = &freqs[0];
+        out.margin = &margin[0]; out.energy = 0;
+        int rc = dindel_b200_bayes_em(eng_.ctx(), &in, &out);
+        if (rc != DINDEL_OK) throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(eng_.ctx()) + ")";
+    }
     // Realigned-read CIGARs of EVERY window of the flushed batch in one K5 call (see Engine::realignedCigars).
     // allHaps[w] = the haplotypes window w was added with (their ml.hpos / countIndels() are read here: the
     // haplotype-to-reference alignment is not part of add()); refSeqPos[w]; h1[w] / h2[w] = the MAP pair of window w
@@ -668,6 +699,11 @@ private:
     std::vector<std::vector<PAV> > keys_;
     std::vector<dindel_pair_out> pairs_;
     std::vector<int16_t> hpos_;
+    std::vector<int32_t> pool_;
+    std::vector<double> sums_;          // K2: [sum_off_[w] * G + g * npairs + q]
+    std::vector<int64_t> sum_off_;
+    std::vector<int> poolSize_;         // [w * G + g] reads of window w in pool g
+    int G_;
 };
 
 
@@ -694,10 +730,7 @@ void WindowBatch<HapT, ReadT>::flush()
     dindel_batch_out out;
     out.n_pairs = np; out.pairs = &pairs_[0]; out.hpos = full_ ? &hpos_[0] : 0; out.hpos_stride = full_ ? stride_ : 0;
     out.flags = DINDEL_OUT_KEEP_HPOS; out.win_pair = &win_pair_[0]; out.win_status = &status_[0]; out.read_on_hap = &on_[0];
-    int rc = dindel_b200_submit(eng_.ctx(), &in, &out);
-    if (rc != DINDEL_OK)
-        throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(eng_.ctx()) + ")";
-    // K4 over the rows K1 left in HBM
+    // K4 over the rows K1 leaves in HBM, and the read sums of the inference (K2), in the same pass over the batch
     dindel_cover_in ci;
     ci.n_entries = (int32_t)e_hap_.size(); ci.n_keys = (int32_t)win_key_.back(); ci.maxMismatch = maxMismatch_; ci.doFilter = doFilter_ ? 1 : 0;
     ci.win_entry = &win_entry_[0]; ci.win_key = &win_key_[0];
@@ -709,7 +742,29 @@ void WindowBatch<HapT, ReadT>::flush()
     nf_.assign(ci.n_keys ? ci.n_keys : 1, 0); nr_.assign(ci.n_keys ? ci.n_keys : 1, 0);
     dindel_cover_out co;
     co.hap_filtered = &filt_[0]; co.hap_uncovered = 0; co.key_nf = &nf_[0]; co.key_nr = &nr_[0];
-    rc = dindel_b200_coverage(eng_.ctx(), &ci, &co);
+    dindel_job job;
+    job.in = &in; job.out = &out; job.cover = &ci; job.cover_out = &co; job.pair_sums = 0; job.win_sum_off = 0;
+    job.n_groups = 0; job.reserved = 0; job.read_group = 0; job.em = 0; job.em_out = 0;
+    sums_.clear(); G_ = 0;
+    if (eng_.wantSums()) {
+        G_ = eng_.windowPools();
+        const int G = G_ > 0 ? G_ : 1;
+        sum_off_.assign(nw + 1, 0);
+        for (size_t w = 0; w < nw; w++) {
+            const int64_t nh = win_hap_[w + 1] - win_hap_[w];
+            sum_off_[w + 1] = sum_off_[w] + nh * (nh + 1) / 2;
+        }
+        sums_.assign((size_t)(sum_off_[nw] ? sum_off_[nw] : 1) * (size_t)G, 0.0);
+        job.pair_sums = &sums_[0];
+        if (G_ > 0) {
+            job.n_groups = G_; job.read_group = pool_.empty() ? &zero32 : &pool_[0];
+            poolSize_.assign(nw * (size_t)G_, 0);
+            for (size_t w = 0; w < nw; w++)
+                for (int32_t r = win_read_[w]; r < win_read_[w + 1]; r++)
+                    if (pool_[r] >= 0 && pool_[r] < G_) poolSize_[w * (size_t)G_ + (size_t)pool_[r]]++;
+        }
+    }
+    int rc = dindel_b200_process(eng_.ctx(), &job);
     if (rc != DINDEL_OK)
         throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(eng_.ctx()) + ")";
     flushed_ = true;

@@ -20,11 +20,30 @@ text = open(src, encoding="latin-1").read()
 inc = '#include "Faster.hpp"\n'
 assert text.count(inc) == 1
 if not (len(sys.argv) > 3 and sys.argv[3] == "--dump"):
-    text = text.replace(inc, inc + '#include "dindel_b200.hpp"\nstatic dindel_b200::Engine *dindel_b200_gpu = 0;\n'
+    text = text.replace(inc, inc + '#include "dindel_b200_driver.hpp"\nstatic dindel_b200::Engine *dindel_b200_gpu = 0;\n'
                         'static dindel_b200::Inference dindel_b200_inf; // K2 / K3 with the guard band (INTEGRATION.md section 0b)\n'
+                        '#define DINDEL_B200_INF (dindel_b200_replay ? dindel_b200_replay->inf : dindel_b200_inf)\n'
+                        'static std::string dindel_b200_bam_arg; static int dindel_b200_multiple_files = 0; // main() -> batched driver\n'
                         'static struct dindel_b200_report_t { ~dindel_b200_report_t() { if (dindel_b200_inf.nWindows) '
                         'fprintf(stderr, "dindel_b200 inference: windows %ld rechecked_on_host %ld em_sets %ld em_set_mismatch %ld\\n", '
-                        'dindel_b200_inf.nWindows, dindel_b200_inf.nRecheck, dindel_b200_inf.nEmSets, dindel_b200_inf.nEmMismatch); } } dindel_b200_report;\n')
+                        'dindel_b200_inf.nWindows, dindel_b200_inf.nRecheck, dindel_b200_inf.nEmSets, dindel_b200_inf.nEmMismatch); } } dindel_b200_report;\n'
+                        '// the one engine of the process; K2 / K3 (the read sums of diploidGLF / the EM of estimateHaplotypeFrequenciesBayesEM) on the GPU too\n'
+                        'static dindel_b200::Engine *dindel_b200_engine(const DetInDel::Parameters & params, size_t nBams)\n{\n'
+                        '\tif (!dindel_b200_gpu) {\n'
+                        '\t\tdindel_b200_gpu = new dindel_b200::Engine(params.obsParams, getenv("DINDEL_B200_DEVICE") ? atoi(getenv("DINDEL_B200_DEVICE")) : 0);\n'
+                        '\t\tconst bool infer = !getenv("DINDEL_B200_HOST_INFERENCE") && (params.doDiploid != params.estimateHapFreqs);\n'
+                        '\t\tdindel_b200_gpu->setInference(infer, params.estimateHapFreqs ? int(nBams) : 0);\n'
+                        '\t\tdindel_b200_inf.enable(infer);\n'
+                        '\t}\n\treturn dindel_b200_gpu;\n}\n')
+    # the class gets one friend (a patched copy of DInDel.hpp next to the patched DInDel.cpp; the class layout is unchanged)
+    hdr = open(src[:-len("DInDel.cpp")] + "DInDel.hpp", encoding="latin-1").read()
+    cls = "class DetInDel\n{\npublic:\n"
+    assert hdr.count(cls) == 1
+    hdr = hdr.replace(cls, cls + "\tfriend struct dindel_b200_driver; // the batched window loop (include/dindel_b200_driver.hpp)\n")
+    open(dst[:-len(".cpp")] + ".hpp", "w", encoding="latin-1").write(hdr)
+    own = '#include "DInDel.hpp"\n'
+    assert text.count(own) == 1
+    text = text.replace(own, '#include "%s"\n' % (dst[:-len(".cpp")].split("/")[-1] + ".hpp"))
 
 sig = re.compile(r"\nvoid DetInDel::computeLikelihoods\(const vector<Haplotype> &haps, const vector<Read> & reads, "
                  r"vector<vector<MLAlignment> > & liks, uint32_t leftPos, uint32_t rightPos, vector<int> & onHap\)\n\{\n")
@@ -32,14 +51,12 @@ hits = list(sig.finditer(text))
 assert len(hits) == 2, len(hits)          # the first one sits inside a /* ... */ block (DInDel.cpp:1652)
 m = hits[-1]
 fwd = ("\t{ // dindel_b200 drop-in (INTEGRATION.md section 0)\n"
-       "\t\tdindel_b200::Engine *&gpu = dindel_b200_gpu;\n"
-       "\t\tif (!gpu) {\n"
-       "\t\t\tgpu = new dindel_b200::Engine(params.obsParams, getenv(\"DINDEL_B200_DEVICE\") ? atoi(getenv(\"DINDEL_B200_DEVICE\")) : 0);\n"
-       "\t\t\t// K2 / K3: the read sums of diploidGLF / the EM of estimateHaplotypeFrequenciesBayesEM on the GPU too\n"
-       "\t\t\tconst bool infer = !getenv(\"DINDEL_B200_HOST_INFERENCE\") && (params.doDiploid != params.estimateHapFreqs);\n"
-       "\t\t\tgpu->setInference(infer, params.estimateHapFreqs ? int(myBams.size()) : 0);\n"
-       "\t\t\tdindel_b200_inf.enable(infer);\n"
+       "\t\tif (dindel_b200_replay) { // batched driver: the window's results are in the flushed batch\n"
+       "\t\t\tif (dindel_b200_replay->w < 0) { liks = vector<vector<MLAlignment> >(haps.size(), vector<MLAlignment>(reads.size())); onHap = vector<int>(reads.size(), 0); return; }\n"
+       "\t\t\tdindel_b200_replay->batch->result(dindel_b200_replay->w, haps, reads, liks, onHap);\n"
+       "\t\t\treturn;\n"
        "\t\t}\n"
+       "\t\tdindel_b200::Engine *gpu = dindel_b200_engine(params, myBams.size());\n"
        "\t\tgpu->computeLikelihoods(haps, reads, liks, leftPos, rightPos, onHap);\n"
        "\t\treturn;\n"
        "\t}\n")
@@ -81,7 +98,12 @@ if not dump:
     fsig = ("void DetInDel::filterHaplotypes(const vector<Haplotype> & haps, const vector<Read> & reads, const vector<vector<MLAlignment> > & liks,"
             "  vector<int> & filtered, map<pair<int, AlignedVariant>, VariantCoverage> & varCoverage, bool doFilter)\n{\n")
     assert text.count(fsig) == 1
-    ffwd = ("\tif (params.slower && dindel_b200_gpu && !getenv(\"DINDEL_B200_HOST_FILTER\")) { // dindel_b200 drop-in (INTEGRATION.md section 0)\n"
+    ffwd = ("\tif (dindel_b200_replay && dindel_b200_replay->w >= 0) { // batched driver: K4 ran with the batch\n"
+            "\t\tint nf = dindel_b200_replay->batch->filterResult(dindel_b200_replay->w, filtered, varCoverage);\n"
+            "\t\tcout << \"Filtered \" << nf << \" haplotypes.\" << endl;\n"
+            "\t\treturn;\n"
+            "\t}\n"
+            "\tif (params.slower && dindel_b200_gpu && !dindel_b200_replay && !getenv(\"DINDEL_B200_HOST_FILTER\")) { // dindel_b200 drop-in (INTEGRATION.md section 0)\n"
             "\t\tint nf = dindel_b200_gpu->filterHaplotypes(haps, reads, liks, filtered, varCoverage, doFilter, params.obsParams.maxMismatch);\n"
             "\t\tcout << \"Filtered \" << nf << \" haplotypes.\" << endl;\n"
             "\t\treturn;\n"
@@ -112,31 +134,33 @@ if not dump:
         # ---- diploidGLF (DInDel.cpp:2933-3662) ----
         ("void DetInDel::diploidGLF(const vector<Haplotype> & haps, const vector<Read> & reads, const vector<vector<MLAlignment> > & liks, vector<double> & hapFreqs, vector <HapEstResult > & posteriors,  uint32_t candPos, uint32_t leftPos, uint32_t rightPos,  OutputData & glfData, int index, const AlignedCandidates & candidateVariants, string program=\"all\")\n\n{\n",
          1, 0, "after",
-         "\tif (dindel_b200_gpu && dindel_b200_gpu->wantSums()) dindel_b200_inf.setSums(&dindel_b200_gpu->windowSums()[0], dindel_b200_gpu->windowHaps(), dindel_b200_gpu->windowReads(), 0, 0);\n"
-         "\tDINDEL_B200_TWO_PASS(dindel_b200_inf, glfData, ;, diploidGLF(haps, reads, liks, hapFreqs, posteriors, candPos, leftPos, rightPos, glfData, index, candidateVariants, program))\n"),
+         "\tif (dindel_b200_replay) dindel_b200_replay->batch->bindSums(dindel_b200_replay->w, dindel_b200_replay->inf);\n"
+         "\telse if (dindel_b200_gpu && dindel_b200_gpu->wantSums()) DINDEL_B200_INF.setSums(&dindel_b200_gpu->windowSums()[0], dindel_b200_gpu->windowHaps(), dindel_b200_gpu->windowReads(), 0, 0);\n"
+         "\tDINDEL_B200_TWO_PASS(DINDEL_B200_INF, glfData, ;, diploidGLF(haps, reads, liks, hapFreqs, posteriors, candPos, leftPos, rightPos, glfData, index, candidateVariants, program))\n"),
         ("\t\tdouble ll=0.0;\n\t\tfor (size_t r=0;r<reads.size();r++){\n\t\t\tll+=log(0.5)+addLogs(rl[r*nh+h1],rl[r*nh+h2]);\n", 1, 0, "replace",
-         "\t\tdouble ll=0.0;\n\t\tif (dindel_b200_inf.gpu()) ll = dindel_b200_inf.sum(h1, h2, nh, ll); else\n\t\tfor (size_t r=0;r<reads.size();r++){\n\t\t\tll+=log(0.5)+addLogs(rl[r*nh+h1],rl[r*nh+h2]);\n"),
+         "\t\tdouble ll=0.0;\n\t\tif (DINDEL_B200_INF.gpu()) ll = DINDEL_B200_INF.sum(h1, h2, nh, ll); else\n\t\tfor (size_t r=0;r<reads.size();r++){\n\t\t\tll+=log(0.5)+addLogs(rl[r*nh+h1],rl[r*nh+h2]);\n"),
         ("\t\tif (pairs_posterior[h1*nh+h2]>max_ll_indel && (", 1, 0, "replace",
-         "\t\tif (dindel_b200_inf.gt(pairs_posterior[h1*nh+h2], max_ll_indel) && ("),
+         "\t\tif (DINDEL_B200_INF.gt(pairs_posterior[h1*nh+h2], max_ll_indel) && ("),
         ("\t\tif (pairs_posterior[h1*nh+h2]>max_ll_noindel && (", 1, 0, "replace",
-         "\t\tif (dindel_b200_inf.gt(pairs_posterior[h1*nh+h2], max_ll_noindel) && ("),
+         "\t\tif (DINDEL_B200_INF.gt(pairs_posterior[h1*nh+h2], max_ll_noindel) && ("),
         ("\tqual = - 10.0*( ll_ref - addLogs(max_ll_indel, ll_ref) )/log(10.0);\n", 1, 0, "after",
-         "\tdindel_b200_inf.checkPhred(ll_ref, max_ll_indel);\n"),
+         "\tDINDEL_B200_INF.checkPhred(ll_ref, max_ll_indel);\n"),
         ("\t\t\tgenoqual = - 10.0*( max_ll_altgeno - addLogs(max_ll_indel, max_ll_altgeno) )/log(10.0);\n", 1, 0, "after",
-         "\t\t\tdindel_b200_inf.checkPhred(max_ll_altgeno, max_ll_indel);\n"),
+         "\t\t\tDINDEL_B200_INF.checkPhred(max_ll_altgeno, max_ll_indel);\n"),
         ("\t\t\tdouble ll=pr;\n\t\t\tfor (size_t r=0;r<reads.size();r++){\n", 1, 0, "replace",
-         "\t\t\tdouble ll=pr;\n\t\t\tif (dindel_b200_inf.gpu()) ll = dindel_b200_inf.sum(h1, h2, nh, ll); else\n\t\t\tfor (size_t r=0;r<reads.size();r++){\n"),
-        ("\t\t\tif (ll>maxll) {\n", 2, 1, "replace", "\t\t\tif (dindel_b200_inf.gt(ll, maxll)) {\n"),   # the first one (:297) is in an unused function
+         "\t\t\tdouble ll=pr;\n\t\t\tif (DINDEL_B200_INF.gpu()) ll = DINDEL_B200_INF.sum(h1, h2, nh, ll); else\n\t\t\tfor (size_t r=0;r<reads.size();r++){\n"),
+        ("\t\t\tif (ll>maxll) {\n", 2, 1, "replace", "\t\t\tif (DINDEL_B200_INF.gt(ll, maxll)) {\n"),   # the first one (:297) is in an unused function
         ("\t\t\to << str << a1 << \"/\" << a2 << \":\" << git->second;\n", 1, 0, "replace",
-         "\t\t\to << str << a1 << \"/\" << a2 << \":\" << dindel_b200_inf.printed(git->second);\n"),
-        ("\t\t\tline.set(\"logZ\", maxll );\n", 1, 0, "replace", "\t\t\tline.set(\"logZ\", dindel_b200_inf.printed(maxll) );\n"),
+         "\t\t\to << str << a1 << \"/\" << a2 << \":\" << DINDEL_B200_INF.printed(git->second);\n"),
+        ("\t\t\tline.set(\"logZ\", maxll );\n", 1, 0, "replace", "\t\t\tline.set(\"logZ\", DINDEL_B200_INF.printed(maxll) );\n"),
         # ---- estimateHaplotypeFrequenciesBayesEM (DInDel.cpp:2103-2930) ----
         ("void DetInDel::estimateHaplotypeFrequenciesBayesEM(const vector<Haplotype> & haps, const vector<Read> & reads, const vector<vector<MLAlignment> > & liks, vector<double> & hapFreqs, vector <HapEstResult > & posteriors,  uint32_t candPos, uint32_t leftPos,   uint32_t rightPos, OutputData & glfData, int index, const AlignedCandidates & candidateVariants, string program=\"all\")\n\n{\n",
          1, 0, "after",
-         "\tif (dindel_b200_gpu && dindel_b200_gpu->wantSums()) dindel_b200_inf.setSums(&dindel_b200_gpu->windowSums()[0], dindel_b200_gpu->windowHaps(), dindel_b200_gpu->windowReads(), dindel_b200_gpu->windowPools(), dindel_b200_gpu->windowPoolSizes().empty() ? 0 : &dindel_b200_gpu->windowPoolSizes()[0]);\n"
-         "\tDINDEL_B200_TWO_PASS(dindel_b200_inf, glfData, posteriors.clear(), estimateHaplotypeFrequenciesBayesEM(haps, reads, liks, hapFreqs, posteriors, candPos, leftPos, rightPos, glfData, index, candidateVariants, program))\n"),
+         "\tif (dindel_b200_replay) dindel_b200_replay->batch->bindSums(dindel_b200_replay->w, dindel_b200_replay->inf);\n"
+         "\telse if (dindel_b200_gpu && dindel_b200_gpu->wantSums()) DINDEL_B200_INF.setSums(&dindel_b200_gpu->windowSums()[0], dindel_b200_gpu->windowHaps(), dindel_b200_gpu->windowReads(), dindel_b200_gpu->windowPools(), dindel_b200_gpu->windowPoolSizes().empty() ? 0 : &dindel_b200_gpu->windowPoolSizes()[0]);\n"
+         "\tDINDEL_B200_TWO_PASS(DINDEL_B200_INF, glfData, posteriors.clear(), estimateHaplotypeFrequenciesBayesEM(haps, reads, liks, hapFreqs, posteriors, candPos, leftPos, rightPos, glfData, index, candidateVariants, program))\n"),
         ("\n\tfor (int th=0;th<nav;th++) {\n", 1, 0, "before",
-         "\n\tif (dindel_b200_inf.gpu()) { // every EM run of the window in one K3 launch: compatible[] of each set as at :2394-2408 (checked again set by set in em())\n"
+         "\n\tif (DINDEL_B200_INF.gpu()) { // every EM run of the window in one K3 launch: compatible[] of each set as at :2394-2408 (checked again set by set in em())\n"
          "\t\tstd::vector<uint8_t> b200c(size_t(nav)*nh, 0);\n"
          "\t\tfor (int th=0;th<nav;th++) for (size_t h=0;h<nh;h++) {\n"
          "\t\t\tint c = filtered[h]==0;\n"
@@ -144,20 +168,44 @@ if not dump:
          "\t\t\t\tif (!it->second.isRef() && !(it->second.isSNP() && it->second.getString()[3]=='D') && activeVariants[th].find(PAV(it->first,it->second))==activeVariants[th].end()) { c=0; break; }\n"
          "\t\t\tb200c[size_t(th)*nh+h]=c;\n"
          "\t\t}\n"
-         "\t\tdindel_b200_inf.emBegin(*dindel_b200_gpu, b200c, nav, params.bayesa0, params.EMtol);\n"
+         "\t\tif (dindel_b200_replay) dindel_b200_replay->inf.emBegin(*dindel_b200_replay, b200c, nav, params.bayesa0, params.EMtol);\n"
+         "\t\telse DINDEL_B200_INF.emBegin(*dindel_b200_gpu, b200c, nav, params.bayesa0, params.EMtol);\n"
          "\t}\n"),
         ("\t\twhile (!converged) {\n", 1, 0, "before",
-         "\t\tif (dindel_b200_inf.em(th, compatible, tol, loglik, pi, iter)) converged = true; // K3 ran this EM\n"),
+         "\t\tif (DINDEL_B200_INF.em(th, compatible, tol, loglik, pi, iter)) converged = true; // K3 ran this EM\n"),
         ("\t\t\t\t\tBOOST_FOREACH(int r, readidx[b]) {\n\t\t\t\t\t\tll+=log5+addLogs(rl[r*nh+h1],rl[r*nh+h2]);\n", 1, 0, "before",
-         "\t\t\t\t\tif (dindel_b200_inf.gpu()) ll = dindel_b200_inf.sumGroup(int(b), h1, h2, nh, ll); else\n"),
+         "\t\t\t\t\tif (DINDEL_B200_INF.gpu()) ll = DINDEL_B200_INF.sumGroup(int(b), h1, h2, nh, ll); else\n"),
         ("\t\t\t\tline.set(\"post_prob_variant\", exp(logp));\n\t\t\t\tline.set(\"est_freq\", freq);\n\t\t\t\tline.set(\"logZ\", logz);\n", 1, 0, "replace",
-         "\t\t\t\tline.set(\"post_prob_variant\", dindel_b200_inf.printedLin(exp(logp)));\n\t\t\t\tline.set(\"est_freq\", dindel_b200_inf.printedLin(freq));\n\t\t\t\tline.set(\"logZ\", dindel_b200_inf.printed(logz));\n"),
+         "\t\t\t\tline.set(\"post_prob_variant\", DINDEL_B200_INF.printedLin(exp(logp)));\n\t\t\t\tline.set(\"est_freq\", DINDEL_B200_INF.printedLin(freq));\n\t\t\t\tline.set(\"logZ\", DINDEL_B200_INF.printed(logz));\n"),
         ("\t\t\t\t\t\tif (hapFreqs[h]>1.0/double(2*reads.size())) {\n", 1, 0, "replace",
-         "\t\t\t\t\t\tif (dindel_b200_inf.gtLin(hapFreqs[h], 1.0/double(2*reads.size()))) {\n"),
+         "\t\t\t\t\t\tif (DINDEL_B200_INF.gtLin(hapFreqs[h], 1.0/double(2*reads.size()))) {\n"),
         ("\t\t\t\t\t\t\tos << \":\" << hapFreqs[h];\n", 1, 0, "replace",
-         "\t\t\t\t\t\t\tos << \":\" << dindel_b200_inf.printedLin(hapFreqs[h]);\n"),
-        ("\t\t\t\t\to << lik[n];\n", 1, 0, "replace", "\t\t\t\t\to << dindel_b200_inf.printed(lik[n]);\n"),
+         "\t\t\t\t\t\t\tos << \":\" << DINDEL_B200_INF.printedLin(hapFreqs[h]);\n"),
+        ("\t\t\t\t\to << lik[n];\n", 1, 0, "replace", "\t\t\t\t\to << DINDEL_B200_INF.printed(lik[n]);\n"),
     ]
+    if not check:
+        INFER += [
+            ("bool DetInDel::getHaplotypes(vector<Haplotype> &haps, const vector<Read> & reads,uint32_t pos, uint32_t & leftPos, uint32_t & rightPos, const AlignedCandidates & candidateVariants)\n{\n", 1, 0, "after",
+             "\tif (dindel_b200_replay) { // batched driver: prepared before the batch was flushed\n"
+             "\t\thaps = *dindel_b200_replay->haps; leftPos = dindel_b200_replay->leftPos; rightPos = dindel_b200_replay->rightPos;\n"
+             "\t\treturn dindel_b200_replay->skip;\n"
+             "\t}\n"),
+            ("void DetInDel::detectIndels(const string & variantsFileName)\n{\n", 1, 0, "after",
+             "\t// dindel_b200: the window loop batched (prepare on host threads -> one GPU pass per batch -> finish on host threads)\n"
+             "\tif (params.slower && params.inferenceMethod==\"empirical\" && !params.outputRealignedBAM && !params.outputPooledLikelihoods && !params.showHapAlignments && !getenv(\"DINDEL_B200_NO_BATCH\")) {\n"
+             "\t\tdindel_b200::Engine *eng = 0;\n"
+             "\t\ttry { eng = dindel_b200_engine(params, myBams.size()); } catch (string s) { eng = 0; } // no device: the loop below reports it window by window\n"
+             "\t\tif (eng) {\n"
+             "\t\t\tdindel_b200_driver drv(*this, *eng, dindel_b200_bam_arg, dindel_b200_multiple_files, dindel_b200_inf.enabled());\n"
+             "\t\t\tint nt = getenv(\"DINDEL_B200_THREADS\") ? atoi(getenv(\"DINDEL_B200_THREADS\")) : int(sysconf(_SC_NPROCESSORS_ONLN));\n"
+             "\t\t\tif (nt < 1) nt = 1; if (nt > 64) nt = 64;\n"
+             "\t\t\tdrv.run(variantsFileName, nt, getenv(\"DINDEL_B200_BATCH\") ? size_t(atol(getenv(\"DINDEL_B200_BATCH\"))) : size_t(4096));\n"
+             "\t\t\treturn;\n"
+             "\t\t}\n"
+             "\t}\n"),
+            ("\t\t\tdetInDel.detectIndels(varFile);\n", 1, 0, "before",
+             "\t\t\tdindel_b200_bam_arg = file; dindel_b200_multiple_files = multipleFiles; // the batched driver opens one DetInDel per worker thread\n"),
+        ]
     for anchor, count, which, where, code in INFER:
         assert text.count(anchor) == count, (anchor, text.count(anchor))
         i = -1

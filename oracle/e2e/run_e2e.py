@@ -71,8 +71,18 @@ def prepare(work, length, seed, coverage=30.0, per_file=1000, min_count=2):
             "n_candidates": sum(1 for _ in open(sel))}
 
 
-def run_arm(arm, prep, work, procs, extra=(), env=None, tag="", mode="--doDiploid"):
-    """stage 3 + 4 for one arm.  Returns (glf paths, vcf path, wall seconds of stage 3, VCF calls)."""
+def run_arm(arm, prep, work, procs, extra=(), env=None, tag="", mode="--doDiploid", one_file=False):
+    """stage 3 + 4 for one arm.  Returns (glf paths, vcf path, wall seconds of stage 3, VCF calls).
+    one_file: every window file concatenated into one and handled by ONE process (the GPU-backed binary batches the
+    window loop itself: host threads for the CPU stages, one GPU pass per batch of windows)."""
+    window_files = prep["window_files"]
+    if one_file:
+        allw = os.path.join(work, "win.all.txt")
+        with open(allw, "w") as f:
+            for wf in window_files:
+                f.write(open(wf).read())
+        window_files = [allw]
+
     def one(k_f):
         k, wf = k_f
         out = os.path.join(work, "%s%s.%d" % (arm, tag, k))
@@ -81,7 +91,7 @@ def run_arm(arm, prep, work, procs, extra=(), env=None, tag="", mode="--doDiploi
         return out + ".glf.txt"
     t0 = time.perf_counter()
     with ThreadPoolExecutor(max(1, procs)) as ex:
-        glfs = list(ex.map(one, enumerate(prep["window_files"], 1)))
+        glfs = list(ex.map(one, enumerate(window_files, 1)))
     wall = time.perf_counter() - t0
     vcf = os.path.join(work, arm + tag + ".vcf")
     if mode == "--doDiploid":
@@ -139,6 +149,24 @@ def inference_totals(glfs):
 
 def diff_lines(a_files, b_files, limit=5):
     out = []
+    if len(a_files) != len(b_files):
+        # one arm ran every window in one process: compare the concatenated bodies with the `index` column (the window's
+        # line number inside ITS window file, DInDel.cpp:1345) masked
+        def body(files):
+            rows = []
+            for f in files:
+                for line in open(f).read().splitlines()[1:]:
+                    d = line.split(" ")
+                    d[1] = "*"
+                    rows.append(" ".join(d))
+            return rows
+        la, lb = body(a_files), body(b_files)
+        if len(la) != len(lb):
+            out.append("%d vs %d lines" % (len(la), len(lb)))
+        for i, (p, q) in enumerate(zip(la, lb)):
+            if p != q:
+                out.append("line %d cols %s" % (i + 1, [k for k, (u, v) in enumerate(zip(p.split(" "), q.split(" "))) if u != v]))
+        return len(out), out[:limit]
     for x, y in zip(a_files, b_files):
         la, lb = open(x).read().splitlines(), open(y).read().splitlines()
         if len(la) != len(lb):
@@ -226,6 +254,11 @@ def main():
     ap.add_argument("--realigned-bam", action="store_true", help="pass --outputRealignedBAM to stage 3 (all arms) and "
                     "compare the per-window realigned BAMs (the gpu arm's CIGARs come from K5, dindel_b200_cigars)")
     ap.add_argument("--heap-neutral", action="store_true", help="also compare with the allocator poisoning freed memory")
+    ap.add_argument("--gpu-one-file", action="store_true", help="gpu arm: ONE process over all windows (its batched driver "
+                    "uses host threads + one GPU pass per batch) instead of one process per window file")
+    ap.add_argument("--gpu-threads", type=int, default=0, help="DINDEL_B200_THREADS of the gpu arm (0 = host cores)")
+    ap.add_argument("--gpu-no-batch", action="store_true", help="gpu arm: the window-at-a-time loop (DINDEL_B200_NO_BATCH)")
+    ap.add_argument("--host-inference", action="store_true", help="gpu arm: diploidGLF / EM sums on the host (DINDEL_B200_HOST_INFERENCE)")
     a = ap.parse_args()
     arms = a.arms.split(",")
     procs = a.procs or len(os.sched_getaffinity(0))
@@ -241,16 +274,27 @@ def main():
         for arm in arms:
             if arm == "check" and env:
                 continue
+            aenv = dict(env or {})
+            if arm != "cpu":
+                if a.gpu_threads:
+                    aenv["DINDEL_B200_THREADS"] = str(a.gpu_threads)
+                if a.gpu_no_batch:
+                    aenv["DINDEL_B200_NO_BATCH"] = "1"
+                if a.host_inference:
+                    aenv["DINDEL_B200_HOST_INFERENCE"] = "1"
             glfs, vcf, wall, n_calls = run_arm(arm, prep, a.work, procs if arm == "cpu" else a.gpu_procs,
                                                extra=(["--filterHaplotypes"] if a.filter_haplotypes else []) +
                                                (["--libFile", prep["libraries"]] if a.lib_file else []) +
-                                               (["--outputRealignedBAM"] if a.realigned_bam else []), env=env, tag=tag,
-                                               mode="--doPooled" if a.pooled else "--doDiploid")
+                                               (["--outputRealignedBAM"] if a.realigned_bam else []), env=aenv or None, tag=tag,
+                                               mode="--doPooled" if a.pooled else "--doDiploid",
+                                               one_file=a.gpu_one_file and arm == "gpu")
             ok, err = glf_stats(glfs)
             out[arm] = (glfs, vcf)
             r[arm] = {"stage3_wall_s": round(wall, 3), "vcf_calls": n_calls, "windows_ok": ok, "windows_skipped": err}
             if arm == "gpu":
                 r[arm]["inference"] = inference_totals(glfs)
+                r[arm]["batched"] = [l.strip() for g in glfs for l in open(g[:-len(".glf.txt")] + ".log", errors="replace")
+                                     if l.startswith("dindel_b200 batched:")][:4]
             if arm == "check":
                 r[arm]["pairs_compared"], r[arm]["pair_mismatches"] = check_totals(glfs)
                 verdict = verdict and r[arm]["pair_mismatches"] == 0 and r[arm]["pairs_compared"] > 0

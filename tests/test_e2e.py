@@ -204,3 +204,46 @@ def test_realigned_bams_identical(tmp_path, pooled):
     rb = d["realigned_bam"]
     assert rb["mismatches"] == 0 and rb["files"] >= 10 and rb["records"] >= 500 and rb["records_with_indel_or_clip"] >= 50, res
     assert d["glf_identical"], res
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("extra", [[], ["--filter-haplotypes"], ["--lib-file"], ["--pooled"]])
+def test_batched_driver_one_process_identical(tmp_path, extra):
+    """The batched window loop (include/dindel_b200_driver.hpp): ONE GPU-backed process over every window -- getReads /
+    getHaplotypes on host threads, one dindel_b200_process (K1 + K4 + K2) per batch of windows, the reference's own
+    empiricalDistributionMethod replayed per window on host threads -- writes the glf lines of the stock binary run one
+    process per window file (the `index` column, a window's line number inside its file, aside) and the same VCF.  Small
+    batches (DINDEL_B200_BATCH) force several flushes."""
+    if not run_e2e.have_binaries(("cpu", "gpu")):
+        pytest.skip("oracle/_ref binaries not built (reference sources absent at build time)")
+    env = dict(os.environ, DINDEL_B200_BATCH="23")
+    r = subprocess.run([sys.executable, os.path.join(E2E, "run_e2e.py"), "--work", str(tmp_path), "--length", "80000",
+                        "--seed", "21", "--arms", "cpu,gpu", "--windows-per-file", "15", "--heap-neutral", "--gpu-one-file",
+                        "--gpu-threads", "5"] + extra, capture_output=True, text=True, timeout=1500, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    hn = res["heap_neutral"]
+    assert hn["glf_identical"] and hn["cpu"]["windows_ok"] >= 25, res
+    if "--pooled" not in extra:
+        assert hn["vcf_identical"] and hn["cpu"]["vcf_calls"] >= 15, res
+    assert hn["gpu"]["batched"] and "batches" in hn["gpu"]["batched"][0], res
+    nb = int(hn["gpu"]["batched"][0].split("batches")[1].split()[0])
+    assert nb >= 2, hn["gpu"]["batched"]
+    assert hn["gpu"]["inference"]["windows"] >= 25, res
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pooled", [False, True])
+def test_window_at_a_time_loop_still_identical(tmp_path, pooled):
+    """DINDEL_B200_NO_BATCH: the reference's own window loop with one GPU call per window,
+    K2 / K3 through Engine::computeLikelihoods / Engine::windowEM."""
+    if not run_e2e.have_binaries(("cpu", "gpu")):
+        pytest.skip("oracle/_ref binaries not built (reference sources absent at build time)")
+    r = subprocess.run([sys.executable, os.path.join(E2E, "run_e2e.py"), "--work", str(tmp_path), "--length", "40000",
+                        "--seed", "23", "--arms", "cpu,gpu", "--windows-per-file", "20", "--heap-neutral", "--gpu-no-batch"] +
+                       (["--pooled"] if pooled else []), capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout + r.stderr
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    hn = res["heap_neutral"]
+    assert hn["glf_identical"] and hn["cpu"]["windows_ok"] >= 12, res
+    assert hn["gpu"]["inference"]["windows"] >= 12 and not hn["gpu"]["batched"], res
