@@ -85,7 +85,18 @@ struct dindel_b200_driver {
     };
 
     DetInDel &master;
-    dindel_b200::Engine &gpu;
+    // The engine (CUDA context: ~1.4 s) is created on a helper thread while the workers already fetch reads and build
+    // haplotypes; a worker parks its prepared windows until the engine is there and adds them to the batch then.
+    typedef dindel_b200::Engine *(*EngineFactory)(void *);
+    EngineFactory makeEngine;
+    void *makeEngineArg;
+    dindel_b200::Engine *gpu;
+    volatile int engineState;              // 0 = being created, 1 = ready, -1 = failed (engineError)
+    std::string engineError;
+    pthread_t engineThread;
+    bool engineThreadStarted, engineJoined;
+    pthread_mutex_t engineLock;
+    double tEngine;
     std::string bamArg;
     int multipleFiles;
     std::vector<Worker> workers;
@@ -97,15 +108,49 @@ struct dindel_b200_driver {
     long nWindows, nBatches, nLateFail;
     dindel_b200::Inference totals;
 
-    dindel_b200_driver(DetInDel &m, dindel_b200::Engine &g, const std::string &bam, int multi, bool infer)
-        : master(m), gpu(g), bamArg(bam), multipleFiles(multi), batch(0), inferOnGpu(infer), tFlush(0.0), tRead(0.0), tWrite(0.0),
+    dindel_b200_driver(DetInDel &m, EngineFactory f, void *farg, const std::string &bam, int multi, bool infer)
+        : master(m), makeEngine(f), makeEngineArg(farg), gpu(0), engineState(0), engineThreadStarted(false), engineJoined(false),
+          tEngine(0.0), bamArg(bam), multipleFiles(multi), batch(0), inferOnGpu(infer), tFlush(0.0), tRead(0.0), tWrite(0.0),
           nWindows(0), nBatches(0), nLateFail(0)
     {
         pthread_mutex_init(&addLock, 0);
         pthread_mutex_init(&gpuLock, 0);
+        pthread_mutex_init(&engineLock, 0);
+    }
+    static void *engineMain(void *arg)
+    {
+        dindel_b200_driver &d = *(dindel_b200_driver *)arg;
+        const double t0 = now();
+        try {
+            d.gpu = d.makeEngine(d.makeEngineArg);
+            d.batch = new Batch(*d.gpu, d.master.params.obsParams.maxMismatch, d.master.params.filterHaplotypes, true);
+            d.tEngine = now() - t0;
+            __sync_synchronize();
+            d.engineState = 1;
+        } catch (std::string s) {
+            d.engineError = s;
+            __sync_synchronize();
+            d.engineState = -1;
+        }
+        return 0;
+    }
+    void startEngine()
+    {
+        if (pthread_create(&engineThread, 0, engineMain, this) == 0) engineThreadStarted = true;
+        else engineMain(this);
+    }
+    // blocks until the engine exists (or failed); true when it is usable
+    bool waitEngine()
+    {
+        pthread_mutex_lock(&engineLock);
+        if (engineThreadStarted && !engineJoined) { pthread_join(engineThread, 0); engineJoined = true; }
+        pthread_mutex_unlock(&engineLock);
+        __sync_synchronize();
+        return engineState == 1;
     }
     ~dindel_b200_driver()
     {
+        waitEngine();
         for (size_t k = 1; k < workers.size(); k++) delete workers[k].det;
         delete batch;
     }
@@ -138,6 +183,7 @@ struct dindel_b200_driver {
         uint32_t oldLeftPos = 0, oldRightFetchReadPos = 0;
         bool reset = true;
         std::string oldTid("-1");
+        std::vector<size_t> parked;
         for (size_t i = wk.first; i < wk.last; i++) {
             Win &x = d.wins[i];
             if (x.prepared) continue;
@@ -152,12 +198,8 @@ struct dindel_b200_driver {
                 x.skipHaps = det.getHaplotypes(x.haps, x.reads, x.pos, x.hLeft, x.hRight, x.cand);
                 // windows the reference refuses after getHaplotypes (:395-399) or skips (:403) never reach the GPU
                 const bool tooLarge = int(x.reads.size() * x.haps.size()) > det.params.maxHapReadProd; // thrown at :395-399
-                if (!x.skipHaps && !tooLarge && !x.haps.empty()) {
-                    pthread_mutex_lock(&d.addLock);
-                    try { x.bw = d.batch->add(x.haps, x.reads, x.hLeft); }
-                    catch (...) { pthread_mutex_unlock(&d.addLock); throw; }
-                    pthread_mutex_unlock(&d.addLock);
-                }
+                if (!x.skipHaps && !tooLarge && !x.haps.empty()) parked.push_back(i);
+                if (d.engineState == 1) { addParked(d, parked); }
                 reset = tooLarge; // a skipped window restarts the read buffer (:1405)
             } catch (std::string s) { x.failed = true; x.message = s; x.stringThrown = true; reset = true; }
             catch (std::bad_alloc) { x.failed = true; x.message = "bad_alloc"; x.stringThrown = false; reset = true; }
@@ -166,6 +208,24 @@ struct dindel_b200_driver {
             oldLeftPos = x.leftPos;
         }
         for (size_t r = 0; r < readBuffer.size(); r++) if (readBuffer[r] != NULL) delete readBuffer[r];
+        if (d.waitEngine()) addParked(d, parked);
+        else for (size_t k = 0; k < parked.size(); k++) { // no device: what the engine's constructor threw, window by window
+            Win &x = d.wins[parked[k]];
+            x.failed = true; x.stringThrown = true; x.message = d.engineError;
+        }
+    }
+    // the prepared windows a worker parked while the engine was being created -> the batch
+    static void addParked(dindel_b200_driver &d, std::vector<size_t> &parked)
+    {
+        for (size_t k = 0; k < parked.size(); k++) {
+            Win &x = d.wins[parked[k]];
+            pthread_mutex_lock(&d.addLock);
+            try { x.bw = d.batch->add(x.haps, x.reads, x.hLeft); }
+            catch (std::string s) { x.failed = true; x.stringThrown = true; x.message = s; }
+            catch (...) { pthread_mutex_unlock(&d.addLock); throw; }
+            pthread_mutex_unlock(&d.addLock);
+        }
+        parked.clear();
     }
 
     // the "error_<msg>" line of a skipped window (DInDel.cpp:1389-1402)
@@ -262,8 +322,8 @@ struct dindel_b200_driver {
         glfData.outputLine(glfData.headerString());
         VariantFile vf(variantsFileName);
         const bool oneBam = master.myBams.size() == 1;
+        startEngine();
         makeWorkers(oneBam ? nThreads : 1);
-        batch = new Batch(gpu, master.params.obsParams.maxMismatch, master.params.filterHaplotypes, true);
         int index = 0;
         uint32_t oldLeftPos = 0;
         std::string oldTid("-1");
@@ -293,10 +353,10 @@ struct dindel_b200_driver {
             tRead += now() - t0;
             if (wins.empty()) break;
             nBatches++;
-            batch->clear();
+            if (nBatches > 1 && waitEngine()) batch->clear();
             runPhase(0, 0, wins.size());
             t0 = now();
-            batch->flush();
+            if (waitEngine()) batch->flush();
             tFlush += now() - t0;
             runPhase(1, 0, wins.size());
             // ---- write in window order; several BAM files: a late failure restarts the read buffer for what follows ----
@@ -322,7 +382,7 @@ struct dindel_b200_driver {
         double tp = 0.0, tf = 0.0;
         for (size_t k = 0; k < workers.size(); k++) { tp += workers[k].tPrepare; tf += workers[k].tFinish; }
         fprintf(stderr, "dindel_b200 batched: windows %ld batches %ld threads %d late_failures %ld; wall: read %.3f s, flush(GPU) %.3f s, write %.3f s; "
-                        "thread-seconds: prepare %.3f finish %.3f\n", nWindows, nBatches, (int)workers.size(), nLateFail, tRead, tFlush, tWrite, tp, tf);
+                        "thread-seconds: prepare %.3f finish %.3f; engine created in %.3f s (under the first prepare)\n", nWindows, nBatches, (int)workers.size(), nLateFail, tRead, tFlush, tWrite, tp, tf, tEngine);
         if (totals.nWindows)
             fprintf(stderr, "dindel_b200 inference: windows %ld rechecked_on_host %ld em_sets %ld em_set_mismatch %ld\n",
                     totals.nWindows, totals.nRecheck, totals.nEmSets, totals.nEmMismatch);

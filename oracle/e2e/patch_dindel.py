@@ -34,7 +34,9 @@ if not (len(sys.argv) > 3 and sys.argv[3] == "--dump"):
                         '\t\tconst bool infer = !getenv("DINDEL_B200_HOST_INFERENCE") && (params.doDiploid != params.estimateHapFreqs);\n'
                         '\t\tdindel_b200_gpu->setInference(infer, params.estimateHapFreqs ? int(nBams) : 0);\n'
                         '\t\tdindel_b200_inf.enable(infer);\n'
-                        '\t}\n\treturn dindel_b200_gpu;\n}\n')
+                        '\t}\n\treturn dindel_b200_gpu;\n}\n'
+                        '// the batched driver creates the engine on a helper thread (context creation under the first prepare phase)\n'
+                        'static dindel_b200::Engine *dindel_b200_engine_factory(void *det) { return dindel_b200_engine(((DetInDel *)det)->params, ((DetInDel *)det)->getMyBams().size()); }\n')
     # the class gets one friend (a patched copy of DInDel.hpp next to the patched DInDel.cpp; the class layout is unchanged)
     hdr = open(src[:-len("DInDel.cpp")] + "DInDel.hpp", encoding="latin-1").read()
     cls = "class DetInDel\n{\npublic:\n"
@@ -193,15 +195,12 @@ if not dump:
             ("void DetInDel::detectIndels(const string & variantsFileName)\n{\n", 1, 0, "after",
              "\t// dindel_b200: the window loop batched (prepare on host threads -> one GPU pass per batch -> finish on host threads)\n"
              "\tif (params.slower && params.inferenceMethod==\"empirical\" && !params.outputRealignedBAM && !params.outputPooledLikelihoods && !params.showHapAlignments && !getenv(\"DINDEL_B200_NO_BATCH\")) {\n"
-             "\t\tdindel_b200::Engine *eng = 0;\n"
-             "\t\ttry { eng = dindel_b200_engine(params, myBams.size()); } catch (string s) { eng = 0; } // no device: the loop below reports it window by window\n"
-             "\t\tif (eng) {\n"
-             "\t\t\tdindel_b200_driver drv(*this, *eng, dindel_b200_bam_arg, dindel_b200_multiple_files, dindel_b200_inf.enabled());\n"
-             "\t\t\tint nt = getenv(\"DINDEL_B200_THREADS\") ? atoi(getenv(\"DINDEL_B200_THREADS\")) : int(sysconf(_SC_NPROCESSORS_ONLN));\n"
-             "\t\t\tif (nt < 1) nt = 1; if (nt > 64) nt = 64;\n"
-             "\t\t\tdrv.run(variantsFileName, nt, getenv(\"DINDEL_B200_BATCH\") ? size_t(atol(getenv(\"DINDEL_B200_BATCH\"))) : size_t(4096));\n"
-             "\t\t\treturn;\n"
-             "\t\t}\n"
+             "\t\tconst bool infer = !getenv(\"DINDEL_B200_HOST_INFERENCE\") && (params.doDiploid != params.estimateHapFreqs);\n"
+             "\t\tdindel_b200_driver drv(*this, dindel_b200_engine_factory, this, dindel_b200_bam_arg, dindel_b200_multiple_files, infer);\n"
+             "\t\tint nt = getenv(\"DINDEL_B200_THREADS\") ? atoi(getenv(\"DINDEL_B200_THREADS\")) : int(sysconf(_SC_NPROCESSORS_ONLN));\n"
+             "\t\tif (nt < 1) nt = 1; if (nt > 64) nt = 64;\n"
+             "\t\tdrv.run(variantsFileName, nt, getenv(\"DINDEL_B200_BATCH\") ? size_t(atol(getenv(\"DINDEL_B200_BATCH\"))) : size_t(4096));\n"
+             "\t\treturn;\n"
              "\t}\n"),
             ("\t\t\tdetInDel.detectIndels(varFile);\n", 1, 0, "before",
              "\t\t\tdindel_b200_bam_arg = file; dindel_b200_multiple_files = multipleFiles; // the batched driver opens one DetInDel per worker thread\n"),
