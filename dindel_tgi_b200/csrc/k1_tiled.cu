@@ -17,6 +17,7 @@
 //   * clamped duplicates of LO / RO can never be taken -> offered as -inf
 // Requires: sequence bytes in [A-Z=] (one-hot accept masks), forceReadOnHaplotype off; other
 // batches take the generic kernel (k1_generic.cu).
+#include <stdlib.h>
 #include <type_traits>
 #include "k1_common.cuh"
 #include "k1_tail.cuh"
@@ -690,7 +691,20 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
 // J = 11 (maxLengthDel 10, configs[3]): three wide classes up to S = 352, back-pointers in global memory.
 static const int kClassC6[6] = {2, 3, 4, 5, 6, 8};
 static const int kClassC11[6] = {8, 10, 11, 0, 0, 0};
-static const int *class_table(int J) { return J == 6 ? kClassC6 : (J == 11 ? kClassC11 : nullptr); }
+// J = 11 through the strip kernel (k1_strip.cu): classes = 1, 2, 3 strips of 128 columns (4 per lane and strip)
+static const int kClassStrip11[6] = {4, 8, 12, 0, 0, 0};
+extern "C" size_t k1_strip_slot_bytes(int maxR);
+extern "C" size_t k1_strip_slots(int num_sms);
+extern "C" int k1_strip_supported(int maxS, int maxR);
+extern "C" cudaError_t k1_strip_launch_class(const K1Batch *B, int num_sms, int cls, int J, cudaStream_t st);
+// $DINDEL_B200_J11_TILED=1 keeps the 8/10/11-columns-per-lane classes of this file for J = 11 (A/B runs)
+static bool use_strip(int J)
+{
+    static int tiled11 = -1;
+    if (tiled11 < 0) { const char *e = getenv("DINDEL_B200_J11_TILED"); tiled11 = (e && e[0] == '1') ? 1 : 0; }
+    return J == 11 && !tiled11;
+}
+static const int *class_table(int J) { return J == 6 ? kClassC6 : (J == 11 ? (use_strip(J) ? kClassStrip11 : kClassC11) : nullptr); }
 extern "C" void k1_tiled_class_table(int J, int32_t out[6])
 {
     const int *t = class_table(J);
@@ -791,17 +805,23 @@ static cudaError_t launch_one_ins(const K1Batch *B, int num_sms, int cls, cudaSt
 extern "C" size_t k1_tiled_bt_slot_bytes(int maxR, int J)
 {
     if (J <= 7) return 0;
+    if (use_strip(J)) return k1_strip_slot_bytes(maxR);
     const int *t = class_table(J);
     int C = 0;
     for (int i = 0; t && i < 6; i++) if (t[i] > C) C = t[i];
     return (((size_t)maxR + 1) * ((C + 1) / 2) * 64 + 255) & ~(size_t)255;
 }
-extern "C" size_t k1_tiled_bt_slots(int num_sms) { return (size_t)num_sms * K1_TILED_BTG_MAX_CTAS * K1_TILED_WPC; }
+extern "C" size_t k1_tiled_bt_slots(int num_sms)
+{
+    const size_t a = (size_t)num_sms * K1_TILED_BTG_MAX_CTAS * K1_TILED_WPC, b = k1_strip_slots(num_sms);
+    return a > b ? a : b;
+}
 
 extern "C" int k1_tiled_supported(int maxS, int maxR, int J)
 {
     const int *t = class_table(J);
     if (!t) return 0;
+    if (use_strip(J)) return k1_strip_supported(maxS, maxR);
     int C = 0;
     for (int i = 0; i < 6; i++)
         if (t[i] > 0 && maxS <= 32 * t[i]) { C = t[i]; break; }
@@ -834,6 +854,8 @@ extern "C" cudaError_t k1_tiled_launch(const K1Batch *B, int num_sms, cudaStream
             case 6: e = launch_one<6, 6, K1_TILED_MINB, false>(B, num_sms, i, st); break;
             case 8: e = launch_one<8, 6, K1_TILED_MINB, false>(B, num_sms, i, st); break;
             }
+        } else if (use_strip(J)) {
+            e = k1_strip_launch_class(B, num_sms, i, J, st);
         } else {
             switch (t[i]) {
             case 8: e = launch_one<8, 11, K1_TILED_J11_MINB, true>(B, num_sms, i, st); break;
