@@ -4,14 +4,15 @@
 // A pair's 2*(H+2) states do not fit a warp at 4 columns per lane once H+2 > 128, and at 10-11 columns per lane the
 // row loops of k1_tiled.cu become 20 KB of straight-line code holding 250 registers (profiles/r1_k1_tiled_j11.md:
 // two warps per scheduler, instruction-fetch and latency bound, 0.46 of the FP64-issue roofline).  Here a warp still
-// owns one (read, haplotype) pair but walks the haplotype in strips of 128 columns (4 per lane): for the left half
-// (rows 1..bMid, dependencies point left) strip 0 runs all its rows, then strip 1, ...; for the right half (rows
-// R-1..bMid+1, dependencies point right) the last strip runs first.  Inside a strip the code is the 4-column row loop
-// (~1/3 of the code, ~half the registers); what a strip needs from its neighbour -- the previous row's values of the
-// J columns across the boundary (+ one plane-1 value) -- the neighbour left in a per-warp, per-row EDGE buffer (L2
-// resident; the last three lanes write 12 doubles per row, the first three lanes of the next strip read them back).
-// One buffer serves every boundary: strip s stores row b's edge in slot b - s + 2, which is exactly the slot strip
-// s + 1 reads (and then overwrites with its own edge) when it computes row b + 1.
+// owns one (read, haplotype) pair but walks the haplotype in strips of 128 columns (4 per lane), KS_RB rows at a
+// time: block of rows by block of rows, strip 0 runs its rows, then strip 1, then strip 2 (left half: rows 1..bMid,
+// dependencies point left; the right half, rows R-1..bMid+1, runs the strips right to left).  Inside a strip the code
+// is the 4-column row loop (~1/3 of the code, half the registers).  What a strip needs from its neighbour -- the
+// previous row's values of the J columns across the boundary (+ one plane-1 value) -- the neighbour left, row by row,
+// in a small per-warp EDGE buffer in shared memory (KS_RB + 1 rows x 13 doubles per boundary); between two blocks a
+// strip's own row (8 doubles per lane) is parked in the warp's global scratch slot (L2: re-read ~40 us later).
+// (A first version ran every strip over ALL rows with the edges in global memory: 250 rows later they had left the
+// L2 and every strip-row waited for DRAM: 67 GCUPS against the tiled classes' 133.)
 //
 // Back-pointers: 4-bit winner code per column (16 bits per lane and row) + the plane-1 bit of the lane's 4 columns
 // gathered by 4 ballots (16 bytes per row): 80 bytes per strip-row in a per-warp slot of global memory.
@@ -27,21 +28,13 @@
 #define KS_W 128          // columns per strip
 #define KS_WPC 4          // warps per CTA
 #define KS_MAX_STRIPS 3   // S <= 384
-#define KS_EDGE 16        // doubles per edge-buffer row: [0..11] plane-0 values of the 12 boundary columns, [12] plane 1 of the last
-#ifndef K1_STRIP_MINB
-#define K1_STRIP_MINB 4
+#define KS_EDGE 13        // doubles per edge-buffer row: [0..11] plane-0 values of the 12 boundary columns, [12] plane 1 of the last
+#ifndef KS_RB
+#define KS_RB 16          // rows per block
 #endif
-
-template <int I = 0, class F>
-__device__ __forceinline__ void ks_static_for_cro(int cro, F &f)
-{
-    if constexpr (I < KS_C) {
-        if (cro == I) f(std::integral_constant<int, I>{});
-        else ks_static_for_cro<I + 1>(cro, f);
-    } else {
-        f(std::integral_constant<int, -1>{}); // no RO in this strip
-    }
-}
+#ifndef K1_STRIP_MINB
+#define K1_STRIP_MINB 3
+#endif
 
 __device__ __forceinline__ double ks_up(double v, int d) { return __shfl_up_sync(FULLMASK, v, d); }
 __device__ __forceinline__ double ks_down(double v, int d) { return __shfl_down_sync(FULLMASK, v, d); }
@@ -65,17 +58,18 @@ __host__ __device__ inline size_t ks_smem_per_warp(int maxR)
 {
     size_t b = (size_t)maxR * 16                       // eq / uq
                + (size_t)2 * KS_MAX_STRIPS * KS_W * 8  // alpha[bMid]+obs[bMid], then the meeting-row sums, by state column
+               + (size_t)2 * (KS_RB + 1) * KS_EDGE * 8 // edge rows of the (at most two) strips that have a successor
                + (size_t)maxR * 2                      // map state
                + (size_t)maxR * 2;                     // read chars + phreds
     return (b + 15) & ~(size_t)15;
 }
-// per-warp global scratch: back-pointer rows of every strip + the edge buffer
+// per-warp global scratch: back-pointer rows of every strip + the strips' parked rows
 __host__ __device__ inline size_t ks_bt_rows(int maxR) { return (size_t)maxR + 1; }
 __host__ __device__ inline size_t ks_slot_bytes(int maxR)
 {
     const size_t bt = (size_t)KS_MAX_STRIPS * ks_bt_rows(maxR) * 80;
-    const size_t edge = ((size_t)maxR + 4) * KS_EDGE * 8;
-    return (bt + edge + 255) & ~(size_t)255;
+    const size_t save = (size_t)KS_MAX_STRIPS * 2 * KS_C * 32 * 8; // a strip's row between two blocks
+    return (bt + save + 255) & ~(size_t)255;
 }
 
 // prior of the meeting row for state column x (cpp:268-305 through the LUTs; insert-size term when INS)
@@ -180,7 +174,8 @@ __global__ void __launch_bounds__(32 * KS_WPC, MINB) k1_strip_kernel(K1Batch B, 
     double *sm_uq = sm_eq + maxR;
     double *sm_ao = sm_uq + maxR; // [2][KS_MAX_STRIPS * KS_W]
     constexpr int AO1 = KS_MAX_STRIPS * KS_W;
-    int16_t *sm_ms = reinterpret_cast<int16_t *>(sm_ao + 2 * AO1);
+    double *sm_edge = sm_ao + 2 * AO1; // [2][KS_RB + 1][KS_EDGE]
+    int16_t *sm_ms = reinterpret_cast<int16_t *>(sm_edge + 2 * (KS_RB + 1) * KS_EDGE);
     uint8_t *sm_ch = reinterpret_cast<uint8_t *>(sm_ms + maxR);
     uint8_t *sm_ph = sm_ch + maxR;
     // per-warp global scratch
@@ -188,7 +183,7 @@ __global__ void __launch_bounds__(32 * KS_WPC, MINB) k1_strip_kernel(K1Batch B, 
     const size_t btRows = ks_bt_rows(maxR);
     uint16_t *g_codes = reinterpret_cast<uint16_t *>(slot);                                                  // [strip][row][32]
     uint32_t *g_bits = reinterpret_cast<uint32_t *>(slot + (size_t)KS_MAX_STRIPS * btRows * 64);              // [strip][row][4]
-    double *g_edge = reinterpret_cast<double *>(slot + (size_t)KS_MAX_STRIPS * btRows * 80);                 // [slot][KS_EDGE]
+    double *g_save = reinterpret_cast<double *>(slot + (size_t)KS_MAX_STRIPS * btRows * 80);                 // [strip][plane][c][32]
 
     const double lLOgLO = L->lLOgLO, lFirstgLO = L->lFirstgLO, lInsgIns = L->lInsgIns,
                  lNoInsgIns = L->lNoInsgIns, lNoInsgNoIns = L->lNoInsgNoIns;
@@ -246,6 +241,8 @@ __global__ void __launch_bounds__(32 * KS_WPC, MINB) k1_strip_kernel(K1Batch B, 
             __syncwarp();
 
             // =================== left half: rows 1..bMid (passMessageTwoDec), strips left to right ===================
+            for (int b0 = 0; b0 < bMid || b0 == 0; b0 += KS_RB) {
+            const int b1 = min(bMid, b0 + KS_RB);
             for (int s = 0; s < NS; s++) {
                 const int xs = s * KS_W, c0 = xs + lane * C;
                 const bool first = (s == 0), last = (s == NS - 1);
@@ -261,37 +258,46 @@ __global__ void __launch_bounds__(32 * KS_WPC, MINB) k1_strip_kernel(K1Batch B, 
                     lpe[c] = s_hp_lpe[code];
                     lpn[c] = s_hp_lpn[code];
                     offL[c] = code * (J - 1);
-                    P0[c] = 0.0; // alpha[0] = 0 (cpp:335-338)
-                    P1[c] = 0.0;
+                    if (b0 == 0) { // alpha[0] = 0 (cpp:335-338)
+                        P0[c] = 0.0;
+                        P1[c] = 0.0;
+                    } else {       // the strip's row b0, parked at the end of the previous block
+                        P0[c] = __ldcg(g_save + ((s * 2 + 0) * C + c) * 32 + lane);
+                        P1[c] = __ldcg(g_save + ((s * 2 + 1) * C + c) * 32 + lane);
+                    }
                 }
 #pragma unroll
                 for (int j = 1; j <= J; j++) amH[j] = ks_accept(hap, c0 - j, H); // columns across the strip boundary (lanes 0..2)
                 const double lpeLm1 = s_hp_lpe[hp[(c0 >= 1 && c0 - 1 <= RO) ? c0 - 1 : 0]];
-                double *edgeW = g_edge + (size_t)(2 - s) * KS_EDGE; // slot of row b: edgeW + b * KS_EDGE (b - s + 2)
-                if (!last && lane >= 29) { // row 0 of this strip's right edge
+                // edge rows: strip s writes row b at edgeW[b - b0]; strip s+1 reads row b-1 at edgeR[b - 1 - b0]
+                double *edgeW = sm_edge + (size_t)(s & 1) * (KS_RB + 1) * KS_EDGE;
+                const double *edgeR = sm_edge + (size_t)((s + 1) & 1) * (KS_RB + 1) * KS_EDGE;
+                if (!last && lane >= 29) { // row b0 of this strip's right edge
 #pragma unroll
-                    for (int c = 0; c < C; c++) edgeW[(lane - 29) * C + c] = 0.0;
-                    if (lane == 31) edgeW[12] = 0.0;
+                    for (int c = 0; c < C; c++) edgeW[(lane - 29) * C + c] = P0[c];
+                    if (lane == 31) edgeW[12] = P1[C - 1];
                 }
                 __syncwarp();
 
-                auto left_rows = [&](auto cro_tag) {
-                constexpr int CRO = decltype(cro_tag)::value;
-                for (int b = 1; b <= bMid; b++) {
+                // ONE copy of the row loop per half: RO's slot is tested at run time (a warp-uniform branch per column
+                // slot).  Per-slot instantiations (as k1_tiled.cu has them) multiply the code the warps of an SM -- each
+                // in another strip, half and slot at any time -- pull through the instruction cache: with five copies
+                // per half ncu showed 8.8 warps waiting for instructions per issue (profiles/r2_k1_strip.md).
+                {
+                for (int b = b0 + 1; b <= b1; b++) {
                     const double eq = sm_eq[b - 1], uq = sm_uq[b - 1];
                     const uint32_t rbit = 1u << (sm_ch[b - 1] & 31);
-                    // previous row's values of the 11 columns left of the strip (+ plane 1 of the nearest one): the
-                    // slot strip s-1 filled for row b-1 is b-1-(s-1)+2 = edgeW + b * KS_EDGE of THIS strip
-                    const double *er = edgeW + (size_t)b * KS_EDGE;
+                    // previous row's values of the 11 columns left of the strip (+ plane 1 of the nearest one)
+                    const double *er = edgeR + (size_t)(b - 1 - b0) * KS_EDGE;
                     double hv[J + 1];
                     double hp1 = 0.0;
                     if (!first && lane < 3) {
 #pragma unroll
                         for (int j = 1; j <= J; j++) {
                             const int rel = 12 + lane * C - j; // boundary block = columns xs-12 .. xs-1
-                            hv[j] = (rel < 12) ? __ldcg(er + rel) : 0.0;
+                            hv[j] = (rel < 12) ? er[rel < 12 ? rel : 0] : 0.0;
                         }
-                        if (lane == 0) hp1 = __ldcg(er + 12);
+                        if (lane == 0) hp1 = er[12];
                     } else {
 #pragma unroll
                         for (int j = 1; j <= J; j++) hv[j] = K1_NEG_INF; // a source left of LO can never win
@@ -368,8 +374,9 @@ __global__ void __launch_bounds__(32 * KS_WPC, MINB) k1_strip_kernel(K1Batch B, 
                         }
                     }
                     // RO (cpp:1780-1782, 1804-1805)
-                    if constexpr (CRO >= 0) {
-                        constexpr int c = CRO;
+#pragma unroll
+                    for (int c = 0; c < C; c++)
+                    if (last && c == cRO) {
                         const double uH = WO[J + c - 1] + WP[J + c - 1];
                         double rv = (u[c] + lLOgLO) + lNoInsgNoIns;
                         uint32_t rcode = 0;
@@ -397,20 +404,16 @@ __global__ void __launch_bounds__(32 * KS_WPC, MINB) k1_strip_kernel(K1Batch B, 
                         const unsigned m = __ballot_sync(FULLMASK, bit1[c] != 0);
                         if (lane == c) g_bits[((size_t)s * btRows + b) * 4 + c] = m;
                     }
-                    __syncwarp(); // the first lanes' loads of this slot come before the last lanes' stores to it
                     if (!last && lane >= 29) {
-                        double *ew = edgeW + (size_t)b * KS_EDGE;
+                        double *ew = edgeW + (size_t)(b - b0) * KS_EDGE;
 #pragma unroll
                         for (int c = 0; c < C; c++) ew[(lane - 29) * C + c] = P0[c];
                         if (lane == 31) ew[12] = P1[C - 1];
                     }
-                    __syncwarp();
                 }
-                }; // left_rows
-                if (last) ks_static_for_cro(cRO, left_rows);
-                else left_rows(std::integral_constant<int, -1>{});
-                // alpha[bMid] + obs[bMid] (first add of cpp:1098) -> shared, by state column
-                {
+                } // rows of the block
+                if (b1 >= bMid) {
+                    // alpha[bMid] + obs[bMid] (first add of cpp:1098) -> shared, by state column
                     const double eq = sm_eq[bMid], uq = sm_uq[bMid];
                     const uint32_t rbit = 1u << (sm_ch[bMid] & 31);
 #pragma unroll
@@ -418,10 +421,20 @@ __global__ void __launch_bounds__(32 * KS_WPC, MINB) k1_strip_kernel(K1Batch B, 
                         sm_ao[c0 + c] = P0[c] + ((am[c] & rbit) ? eq : uq);
                         sm_ao[AO1 + c0 + c] = P1[c] + eq;
                     }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < C; c++) { // park row b1 until the next block
+                        __stcg(g_save + ((s * 2 + 0) * C + c) * 32 + lane, P0[c]);
+                        __stcg(g_save + ((s * 2 + 1) * C + c) * 32 + lane, P1[c]);
+                    }
                 }
                 __syncwarp();
             }
+            }
             // =================== right half: rows R-2..bMid (passMessageTwoInc), strips right to left ===================
+            const int nRight = R - 1 - bMid; // rows t = 1 .. nRight (row t holds beta[R-1-t])
+            for (int t0 = 0; t0 < nRight || t0 == 0; t0 += KS_RB) {
+            const int t1 = min(nRight, t0 + KS_RB);
             for (int s = NS - 1; s >= 0; s--) {
                 const int xs = s * KS_W, c0 = xs + lane * C;
                 const int k = NS - 1 - s; // order of processing
@@ -437,34 +450,39 @@ __global__ void __launch_bounds__(32 * KS_WPC, MINB) k1_strip_kernel(K1Batch B, 
                     const int x = c0 + c;
                     am[c] = ks_accept(hap, x, H);
                     lpeN[c] = s_hp_lpe[hp[(x + 1 <= RO) ? x + 1 : RO]]; // logProbError[x+1] (cpp:1748)
-                    P0[c] = (x <= RO) ? 0.0 : K1_NEG_INF; // beta[R-1] = 0; columns beyond RO never win
-                    P1[c] = (x <= RO) ? 0.0 : K1_NEG_INF;
+                    if (t0 == 0) {
+                        P0[c] = (x <= RO) ? 0.0 : K1_NEG_INF; // beta[R-1] = 0; columns beyond RO never win
+                        P1[c] = (x <= RO) ? 0.0 : K1_NEG_INF;
+                    } else {
+                        P0[c] = __ldcg(g_save + ((s * 2 + 0) * C + c) * 32 + lane);
+                        P1[c] = __ldcg(g_save + ((s * 2 + 1) * C + c) * 32 + lane);
+                    }
                 }
 #pragma unroll
                 for (int j = 1; j <= J; j++) amH[j] = ks_accept(hap, c0 + C - 1 + j, H); // columns right of the strip (lanes 29..31)
                 const double lpnRO = s_hp_lpn[hp[RO]];
-                // edge slots: row index t = R-1-b (t = 0: beta[R-1]); strip of order k stores row t at slot t - k + 2
-                double *edgeW = g_edge + (size_t)(2 - k) * KS_EDGE;
+                // edge rows: the strip of order k writes row t at edgeW[t - t0]; the next one reads row t at edgeR[t - t0]
+                double *edgeW = sm_edge + (size_t)(k & 1) * (KS_RB + 1) * KS_EDGE;
+                const double *edgeR = sm_edge + (size_t)((k + 1) & 1) * (KS_RB + 1) * KS_EDGE;
                 if (!first && lane < 3) {
 #pragma unroll
                     for (int c = 0; c < C; c++) edgeW[lane * C + c] = P0[c];
                 }
                 __syncwarp();
 
-                auto right_rows = [&](auto cro_tag) {
-                constexpr int CRO = decltype(cro_tag)::value;
-                for (int b = R - 1; b > bMid; b--) {
-                    const int t = R - 1 - b; // row of the values being read
+                {
+                for (int t = t0; t < t1; t++) {
+                    const int b = R - 1 - t; // beta[b] (row t) -> beta[b-1] (row t+1)
                     const double eq = sm_eq[b], uq = sm_uq[b];
                     const uint32_t rbit = 1u << (sm_ch[b] & 31);
-                    // beta[b] of the 11 columns right of the strip: stored by strip s+1 (order k-1) at slot t-(k-1)+2
-                    const double *er = edgeW + (size_t)(t + 1) * KS_EDGE;
+                    // beta[b] of the 11 columns right of the strip
+                    const double *er = edgeR + (size_t)(t - t0) * KS_EDGE;
                     double hv[J + 1];
                     if (!last && lane >= 29) {
 #pragma unroll
                         for (int j = 1; j <= J; j++) {
                             const int rel = lane * C + C - 1 + j - KS_W; // column xs+128+rel
-                            hv[j] = (rel >= 0) ? __ldcg(er + rel) : 0.0;
+                            hv[j] = (rel >= 0) ? er[rel >= 0 ? rel : 0] : 0.0;
                         }
                     } else {
 #pragma unroll
@@ -530,8 +548,9 @@ __global__ void __launch_bounds__(32 * KS_WPC, MINB) k1_strip_kernel(K1Batch B, 
                         code[0] = isLane0 ? rcode : code[0];
                         f[0] = isLane0 ? f0 : f[0];
                     }
-                    if constexpr (CRO >= 0) { // RO (cpp:1741-1742, 1750, 1764)
-                        constexpr int c = CRO;
+#pragma unroll
+                    for (int c = 0; c < C; c++)
+                    if (last && c == cRO) { // RO (cpp:1741-1742, 1750, 1764)
                         double rv = uw[c] + lpnRO;
                         uint32_t rcode = 0;
                         if (t1[c] > rv + K1_EPS) { rv = t1[c]; rcode = J; }
@@ -559,24 +578,29 @@ __global__ void __launch_bounds__(32 * KS_WPC, MINB) k1_strip_kernel(K1Batch B, 
                         const unsigned m = __ballot_sync(FULLMASK, bit1[c] != 0);
                         if (lane == c) g_bits[((size_t)s * btRows + b) * 4 + c] = m;
                     }
-                    __syncwarp(); // the last lanes' loads of this slot come before the first lanes' stores to it
-                    if (!first && lane < 3) { // beta[b-1] of this strip's left edge: row t+1 at slot t+1-k+2
-                        double *ew = edgeW + (size_t)(t + 1) * KS_EDGE;
+                    if (!first && lane < 3) { // beta[b-1] of this strip's left edge
+                        double *ew = edgeW + (size_t)(t + 1 - t0) * KS_EDGE;
 #pragma unroll
                         for (int c = 0; c < C; c++) ew[lane * C + c] = P0[c];
                     }
-                    __syncwarp();
                 }
-                }; // right_rows
-                if (last) ks_static_for_cro(cRO, right_rows);
-                else right_rows(std::integral_constant<int, -1>{});
-                // meeting-row sums by state column: (alpha[bMid] + obs[bMid]) + beta[bMid]  (cpp:1098), in place
+                } // rows of the block
+                if (t1 >= nRight) {
+                    // meeting-row sums by state column: (alpha[bMid] + obs[bMid]) + beta[bMid]  (cpp:1098), in place
 #pragma unroll
-                for (int c = 0; c < C; c++) {
-                    sm_ao[c0 + c] = sm_ao[c0 + c] + P0[c];
-                    sm_ao[AO1 + c0 + c] = sm_ao[AO1 + c0 + c] + P1[c];
+                    for (int c = 0; c < C; c++) {
+                        sm_ao[c0 + c] = sm_ao[c0 + c] + P0[c];
+                        sm_ao[AO1 + c0 + c] = sm_ao[AO1 + c0 + c] + P1[c];
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < C; c++) {
+                        __stcg(g_save + ((s * 2 + 0) * C + c) * 32 + lane, P0[c]);
+                        __stcg(g_save + ((s * 2 + 1) * C + c) * 32 + lane, P1[c]);
+                    }
                 }
                 __syncwarp();
+            }
             }
             // =================== meeting row (cpp:1075-1144) ===================
             KsPrior Q;

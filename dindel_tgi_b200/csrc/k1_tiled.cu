@@ -697,12 +697,15 @@ extern "C" size_t k1_strip_slot_bytes(int maxR);
 extern "C" size_t k1_strip_slots(int num_sms);
 extern "C" int k1_strip_supported(int maxS, int maxR);
 extern "C" cudaError_t k1_strip_launch_class(const K1Batch *B, int num_sms, int cls, int J, cudaStream_t st);
-// $DINDEL_B200_J11_TILED=1 keeps the 8/10/11-columns-per-lane classes of this file for J = 11 (A/B runs)
+// J = 11 runs on the 8/10/11-columns-per-lane classes of this file; $DINDEL_B200_J11_STRIP=1 (read at every call, so a
+// test can switch between two engines of one process) takes the strip kernel instead.  Measured on configs[3]
+// (profiles/r2_k1_strip.md): strip 106.5 GCUPS against 133.6 here -- its strips pad S ~ 302 to 384 columns and pay
+// the boundary selects every row, 6.9 warp instructions per cell against 4.7.
 static bool use_strip(int J)
 {
-    static int tiled11 = -1;
-    if (tiled11 < 0) { const char *e = getenv("DINDEL_B200_J11_TILED"); tiled11 = (e && e[0] == '1') ? 1 : 0; }
-    return J == 11 && !tiled11;
+    if (J != 11) return false;
+    const char *e = getenv("DINDEL_B200_J11_STRIP");
+    return e && e[0] == '1';
 }
 static const int *class_table(int J) { return J == 6 ? kClassC6 : (J == 11 ? (use_strip(J) ? kClassStrip11 : kClassC11) : nullptr); }
 extern "C" void k1_tiled_class_table(int J, int32_t out[6])

@@ -1,7 +1,8 @@
 mkdir -p gpurun_out
-B="python bench.py --cfg 2 --windows 6000 --steps 3 --warmup 3 --no-cpu-baseline"
+B="python bench.py --cfg 4 --windows 600 --steps 2 --warmup 3 --no-cpu-baseline --no-extra --no-strong"
 for v in "" _alt; do
   [ -f dindel_tgi_b200/libdindel_b200$v.so ] || continue
-  DINDEL_B200_LIB=$PWD/dindel_tgi_b200/libdindel_b200$v.so $B > gpurun_out/b6k$v.log 2>&1
-  echo "variant '$v'"; grep -h -o '"gcups": [0-9.]*' gpurun_out/b6k$v.log | head -1; grep -h -o '"ll_checksum": [-0-9.e]*' gpurun_out/b6k$v.log
+  DINDEL_B200_LIB=$PWD/dindel_tgi_b200/libdindel_b200$v.so timeout 300 $B > gpurun_out/cfg4$v.json 2> gpurun_out/cfg4$v.err
+  echo "variant '$v'"; python -c "
+import json; r=json.load(open('gpurun_out/cfg4$v.json')); print(r['gcups'], r['roofline']['frac'], r['e2e']['ll_checksum'])"
 done
