@@ -102,7 +102,7 @@ inline int run_cigars(dindel_ctx *ctx, dindel_cigar_in &in, size_t nr, std::vect
 class Engine {
 public:
     template <class ObsParams>
-    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0), last_nh_(0), last_nr_(0), t_cl_(0.0), t_fh_(0.0), n_cl_(0), mapUnmapped_(false), libOff_(1, 0), wantSums_(false), nPools_(0)
+    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0), last_nh_(0), last_nr_(0), t_cl_(0.0), t_fh_(0.0), n_cl_(0), mapUnmapped_(false), libOff_(1, 0), wantSums_(false), nPools_(0), multi_(0)
     {
         dindel_b200_default_params(&p_);
         p_.pError = op.pError; p_.pMut = op.pMut; p_.mapQualThreshold = op.mapQualThreshold;
@@ -113,7 +113,17 @@ public:
         int rc = dindel_b200_create(&p_, device, &ctx_);
         if (rc != DINDEL_OK) throw std::string("dindel_b200: ") + dindel_b200_strerror(rc);
     }
-    ~Engine() { if (ctx_) dindel_b200_destroy(ctx_); }
+    ~Engine() { if (multi_) dindel_b200_multi_destroy(multi_); if (ctx_) dindel_b200_destroy(ctx_); }
+    // The window scheduler over several GPUs (dindel_b200_multi_*): WindowBatch::flush then shards every batch over
+    // these devices; the per-window entries (computeLikelihoods, windowEM, ...) stay on the engine's own device.
+    void enableMulti(const std::vector<int> &devices)
+    {
+        if (multi_ || devices.size() < 2) return;
+        int rc = dindel_b200_multi_create(&p_, &devices[0], (int)devices.size(), &multi_);
+        if (rc != DINDEL_OK) { multi_ = 0; throw std::string("dindel_b200: ") + dindel_b200_strerror(rc); }
+        if (!libP95_.empty()) dindel_b200_multi_set_libraries(multi_, (int)libP95_.size(), &libOff_[0], &libProbs_[0], &libP95_[0]);
+    }
+    dindel_multi *multi() const { return multi_; }
     dindel_ctx *ctx() const { return ctx_; }
     const dindel_params &params() const { return p_; }
     // Which read sums computeLikelihoods also brings back for the window (K2 inside the same dindel_b200_process call):
@@ -162,6 +172,7 @@ public:
         libP95_.push_back(lib->getNinetyFifthPctProb());
         libIndex_[(const void *)lib] = idx;
         int rc = dindel_b200_set_libraries(ctx_, (int)libP95_.size(), &libOff_[0], &libProbs_[0], &libP95_[0]);
+        if (rc == DINDEL_OK && multi_) rc = dindel_b200_multi_set_libraries(multi_, (int)libP95_.size(), &libOff_[0], &libProbs_[0], &libP95_[0]);
         if (rc != DINDEL_OK) throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx_) + ")";
         return idx;
     }
@@ -215,6 +226,7 @@ private:
     int nPools_;
     std::vector<double> sums_;
     std::vector<int> poolSize_;
+    dindel_multi *multi_;
 };
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -764,9 +776,16 @@ void WindowBatch<HapT, ReadT>::flush()
                     if (pool_[r] >= 0 && pool_[r] < G_) poolSize_[w * (size_t)G_ + (size_t)pool_[r]]++;
         }
     }
-    int rc = dindel_b200_process(eng_.ctx(), &job);
-    if (rc != DINDEL_OK)
-        throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(eng_.ctx()) + ")";
+    int rc;
+    if (eng_.multi()) { // the batch sharded over the GPUs of the box; results land in window order
+        rc = dindel_b200_multi_process(eng_.multi(), &job);
+        if (rc != DINDEL_OK)
+            throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_multi_last_error(eng_.multi()) + ")";
+    } else {
+        rc = dindel_b200_process(eng_.ctx(), &job);
+        if (rc != DINDEL_OK)
+            throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(eng_.ctx()) + ")";
+    }
     flushed_ = true;
 }
 

@@ -34,6 +34,13 @@ if not (len(sys.argv) > 3 and sys.argv[3] == "--dump"):
                         '\t\tconst bool infer = !getenv("DINDEL_B200_HOST_INFERENCE") && (params.doDiploid != params.estimateHapFreqs);\n'
                         '\t\tdindel_b200_gpu->setInference(infer, params.estimateHapFreqs ? int(nBams) : 0);\n'
                         '\t\tdindel_b200_inf.enable(infer);\n'
+                        '\t\t// $DINDEL_B200_DEVICES=0,1,..: the batched driver shards every batch over these GPUs (dindel_b200_multi_process);\n'
+                        '\t\t// the pooled path keeps one device (its per-window K3 calls need the batch resident on the engine\'s own)\n'
+                        '\t\tif (getenv("DINDEL_B200_DEVICES") && !params.estimateHapFreqs) {\n'
+                        '\t\t\tstd::vector<int> devs; std::string l(getenv("DINDEL_B200_DEVICES")); size_t a = 0;\n'
+                        '\t\t\twhile (a <= l.size()) { size_t b = l.find(\',\', a); if (b == std::string::npos) b = l.size(); if (b > a) devs.push_back(atoi(l.substr(a, b - a).c_str())); a = b + 1; }\n'
+                        '\t\t\tdindel_b200_gpu->enableMulti(devs);\n'
+                        '\t\t}\n'
                         '\t}\n\treturn dindel_b200_gpu;\n}\n'
                         '// the batched driver creates the engine on a helper thread (context creation under the first prepare phase)\n'
                         'static dindel_b200::Engine *dindel_b200_engine_factory(void *det) { return dindel_b200_engine(((DetInDel *)det)->params, ((DetInDel *)det)->getMyBams().size()); }\n')

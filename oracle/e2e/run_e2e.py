@@ -257,6 +257,8 @@ def main():
     ap.add_argument("--gpu-one-file", action="store_true", help="gpu arm: ONE process over all windows (its batched driver "
                     "uses host threads + one GPU pass per batch) instead of one process per window file")
     ap.add_argument("--gpu-threads", type=int, default=0, help="DINDEL_B200_THREADS of the gpu arm (0 = host cores)")
+    ap.add_argument("--gpu-devices", default="", help="DINDEL_B200_DEVICES of the gpu arm: its batched driver shards every batch "
+                    "over these CUDA devices through the in-process scheduler (e.g. 0,1)")
     ap.add_argument("--gpu-no-batch", action="store_true", help="gpu arm: the window-at-a-time loop (DINDEL_B200_NO_BATCH)")
     ap.add_argument("--host-inference", action="store_true", help="gpu arm: diploidGLF / EM sums on the host (DINDEL_B200_HOST_INFERENCE)")
     a = ap.parse_args()
@@ -278,6 +280,8 @@ def main():
             if arm != "cpu":
                 if a.gpu_threads:
                     aenv["DINDEL_B200_THREADS"] = str(a.gpu_threads)
+                if a.gpu_devices:
+                    aenv["DINDEL_B200_DEVICES"] = a.gpu_devices
                 if a.gpu_no_batch:
                     aenv["DINDEL_B200_NO_BATCH"] = "1"
                 if a.host_inference:

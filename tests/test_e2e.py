@@ -247,3 +247,25 @@ def test_window_at_a_time_loop_still_identical(tmp_path, pooled):
     hn = res["heap_neutral"]
     assert hn["glf_identical"] and hn["cpu"]["windows_ok"] >= 12, res
     assert hn["gpu"]["inference"]["windows"] >= 12 and not hn["gpu"]["batched"], res
+
+
+@pytest.mark.gpu
+def test_batched_driver_over_several_devices(tmp_path):
+    """configs[4] in the small: the patched binary's batched driver shards every batch of windows over several CUDA
+    devices through the in-process scheduler (DINDEL_B200_DEVICES -> Engine::enableMulti -> dindel_b200_multi_process);
+    glf and VCF byte-identical to the stock CPU binary.  Two contexts on device 0 where there is one GPU, every visible
+    device (up to 8) otherwise."""
+    import torch
+    if not run_e2e.have_binaries(("cpu", "gpu")):
+        pytest.skip("oracle/_ref binaries not built (reference sources absent at build time)")
+    n = min(torch.cuda.device_count(), 8)
+    devs = ",".join(str(i) for i in range(n)) if n >= 2 else "0,0"
+    env = dict(os.environ, DINDEL_B200_BATCH="40")
+    r = subprocess.run([sys.executable, os.path.join(E2E, "run_e2e.py"), "--work", str(tmp_path), "--length", "150000",
+                        "--seed", "31", "--arms", "cpu,gpu", "--windows-per-file", "25", "--heap-neutral", "--gpu-one-file",
+                        "--gpu-devices", devs], capture_output=True, text=True, timeout=1500, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    hn = res["heap_neutral"]
+    assert hn["glf_identical"] and hn["vcf_identical"] and hn["cpu"]["windows_ok"] >= 50 and hn["cpu"]["vcf_calls"] >= 30, res
+    assert hn["gpu"]["inference"]["windows"] >= 50, res
