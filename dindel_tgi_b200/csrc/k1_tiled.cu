@@ -35,6 +35,9 @@
 #ifndef K1_LEFT_TREE
 #define K1_LEFT_TREE 1
 #endif
+#ifndef K1_FMAX
+#define K1_FMAX 0 // 1: the 'take iff v >= best' value selects as DMNMX (one FP64-pipe instruction instead of two ALU selects)
+#endif
 #ifndef K1_TILED_J11_MINB
 #define K1_TILED_J11_MINB 3
 #endif
@@ -341,7 +344,11 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                             if (y + 1 <= J) {
                                 const double vb = ((WO[J + c - (y + 1)] + LPD(c, y - 1)) + WP[J + c - (y + 1)]) + lpn[c];
                                 const bool pb = (vb >= va);
+#if K1_FMAX
+                                pm = fmax(va, vb); // == pb ? vb : va bit for bit (no NaN, no zero of either sign among these sums)
+#else
                                 pm = pb ? vb : va;
+#endif
                                 pc = pb ? (uint32_t)y : (uint32_t)(y - 1);
                             }
                             if (y == 1) {
@@ -349,7 +356,11 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                                 code[c] = pc;
                             } else {
                                 const bool p = (pm >= best[c]);
+#if K1_FMAX
+                                best[c] = fmax(best[c], pm);
+#else
                                 best[c] = p ? pm : best[c];
+#endif
                                 code[c] = p ? pc : code[c];
                             }
                         }
@@ -385,7 +396,11 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                         const double stay = t1w[c + 1] + lInsgIns;
                         const double f = u[c] + lNoInsgIns;
                         const bool p = (f >= stay);
+#if K1_FMAX
+                        a1[c] = fmax(stay, f);
+#else
                         a1[c] = p ? f : stay;
+#endif
                         bit1[c] = p ? 1u : 0u;
                         if (c == 0) { // LO (cpp:1798-1799); plane 1 only stays (loop from x=1)
                             const double lo = u[0] + lNoInsgNoIns;
@@ -572,7 +587,11 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                     for (int c = 0; c < C; c++) {
                         const double stay = t1[c] + lInsgIns;
                         const bool p = (f[c] >= stay);
+#if K1_FMAX
+                        a1[c] = fmax(stay, f[c]);
+#else
                         a1[c] = p ? f[c] : stay;
+#endif
                         bit1[c] = p ? 1u : 0u;
                     }
 #pragma unroll

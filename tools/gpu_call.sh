@@ -1,4 +1,8 @@
 mkdir -p gpurun_out
-P=$(cat gpurun_out/r2_pipe_explog.json 2>/dev/null || tools/pipe_explog)
-python tools/k23probe.py "$P" > gpurun_out/r2_k23probe_new512.json 2> gpurun_out/k23probe_new.err; cat gpurun_out/r2_k23probe_new512.json
-python -m pytest tests/test_k23.py tests/test_infer_golden.py tests/test_process_gpu.py -m gpu -x -q 2>&1 | tail -3
+B="python bench.py --cfg 2 --windows 6000 --steps 3 --warmup 3 --no-cpu-baseline --no-extra --no-strong"
+for v in "" _alt; do
+  [ -f dindel_tgi_b200/libdindel_b200$v.so ] || continue
+  DINDEL_B200_LIB=$PWD/dindel_tgi_b200/libdindel_b200$v.so timeout 300 $B > gpurun_out/b6k$v.json 2> gpurun_out/b6k$v.err
+  echo "variant '$v'"; python -c "
+import json; r=json.load(open('gpurun_out/b6k$v.json')); print(r['gcups'], r['roofline']['frac'], r['e2e']['ll_checksum'])"
+done
