@@ -79,9 +79,9 @@ struct dindel_b200_driver {
         int id;
         size_t first, last;                // its run of windows inside the current batch
         int phase;
-        double tPrepare, tFinish;
+        double tPrepare, tFinish, tReads, tHaps, tAdd;   // thread-seconds: phases; getReads / getHaplotypes / batch add
         dindel_b200_replay_t replay;
-        Worker() : drv(0), det(0), id(0), first(0), last(0), phase(0), tPrepare(0.0), tFinish(0.0) {}
+        Worker() : drv(0), det(0), id(0), first(0), last(0), phase(0), tPrepare(0.0), tFinish(0.0), tReads(0.0), tHaps(0.0), tAdd(0.0) {}
     };
 
     DetInDel &master;
@@ -191,11 +191,17 @@ struct dindel_b200_driver {
             if (det.params.tid != oldTid) { reset = true; oldTid = det.params.tid; oldLeftPos = 0; }
             x.failed = false; x.bw = -1; x.message = "ok";
             try {
-                det.getReads(x.leftPos, x.rightPos, x.reads, oldLeftPos, oldRightFetchReadPos, readBuffer, reset);
+                const double tr0 = now();
+                try { det.getReads(x.leftPos, x.rightPos, x.reads, oldLeftPos, oldRightFetchReadPos, readBuffer, reset); }
+                catch (...) { wk.tReads += now() - tr0; throw; }
+                const double tr1 = now();
+                wk.tReads += tr1 - tr0;
                 if (det.params.inferenceMethod != "empirical") throw std::string("Unknown inference method");
                 x.hLeft = x.leftPos; x.hRight = x.rightPos;
                 x.haps.clear();
-                x.skipHaps = det.getHaplotypes(x.haps, x.reads, x.pos, x.hLeft, x.hRight, x.cand);
+                try { x.skipHaps = det.getHaplotypes(x.haps, x.reads, x.pos, x.hLeft, x.hRight, x.cand); }
+                catch (...) { wk.tHaps += now() - tr1; throw; }
+                wk.tHaps += now() - tr1;
                 // windows the reference refuses after getHaplotypes (:395-399) or skips (:403) never reach the GPU
                 const bool tooLarge = int(x.reads.size() * x.haps.size()) > det.params.maxHapReadProd; // thrown at :395-399
                 if (!x.skipHaps && !tooLarge && !x.haps.empty()) parked.push_back(i);
@@ -379,8 +385,9 @@ struct dindel_b200_driver {
             totals.nWindows += workers[k].replay.inf.nWindows; totals.nRecheck += workers[k].replay.inf.nRecheck;
             totals.nEmSets += workers[k].replay.inf.nEmSets; totals.nEmMismatch += workers[k].replay.inf.nEmMismatch;
         }
-        double tp = 0.0, tf = 0.0;
-        for (size_t k = 0; k < workers.size(); k++) { tp += workers[k].tPrepare; tf += workers[k].tFinish; }
+        double tp = 0.0, tf = 0.0, trd = 0.0, thp = 0.0;
+        for (size_t k = 0; k < workers.size(); k++) { tp += workers[k].tPrepare; tf += workers[k].tFinish; trd += workers[k].tReads; thp += workers[k].tHaps; }
+        fprintf(stderr, "dindel_b200 host stages (thread-seconds): getReads %.3f getHaplotypes %.3f (of prepare %.3f, the rest waits for the engine / adds to the batch)\n", trd, thp, tp);
         fprintf(stderr, "dindel_b200 batched: windows %ld batches %ld threads %d late_failures %ld; wall: read %.3f s, flush(GPU) %.3f s, write %.3f s; "
                         "thread-seconds: prepare %.3f finish %.3f; engine created in %.3f s (under the first prepare)\n", nWindows, nBatches, (int)workers.size(), nLateFail, tRead, tFlush, tWrite, tp, tf, tEngine);
         if (totals.nWindows)

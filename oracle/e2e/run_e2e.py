@@ -298,7 +298,7 @@ def main():
             if arm == "gpu":
                 r[arm]["inference"] = inference_totals(glfs)
                 r[arm]["batched"] = [l.strip() for g in glfs for l in open(g[:-len(".glf.txt")] + ".log", errors="replace")
-                                     if l.startswith("dindel_b200 batched:")][:4]
+                                     if l.startswith("dindel_b200 batched:") or l.startswith("dindel_b200 host stages")][:8]
             if arm == "check":
                 r[arm]["pairs_compared"], r[arm]["pair_mismatches"] = check_totals(glfs)
                 verdict = verdict and r[arm]["pair_mismatches"] == 0 and r[arm]["pairs_compared"] > 0
