@@ -133,6 +133,7 @@ public:
     bool wantSums() const { return wantSums_; }
     // the sums of the window computeLikelihoods was last called with: [group][q], q enumerating h1 <= h2 row-major
     const std::vector<double> &windowSums() const { return sums_; }
+    const double *windowSumsPtr() const { return sums_.empty() ? 0 : &sums_[0]; }
     int windowPools() const { return nPools_ > 0 ? nPools_ : 0; }
     size_t windowHaps() const { return last_nh_; }
     size_t windowReads() const { return last_nr_; }
@@ -495,6 +496,8 @@ void Engine::computeLikelihoods(const std::vector<HapT> &haps, const std::vector
     const size_t nh = haps.size(), nr = reads.size();
     onHap = std::vector<int>(nr, 0);
     liks = std::vector<std::vector<MLA> >(nh, std::vector<MLA>(nr));
+    last_nh_ = last_nr_ = 0; // nothing of an earlier window may answer for this one
+    sums_.clear();
     if (nh == 0 || nr == 0) return;
     std::vector<int64_t> hap_off(1, 0), read_off(1, 0);
     std::string hap_seq, read_seq;

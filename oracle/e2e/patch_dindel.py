@@ -144,7 +144,7 @@ if not dump:
         ("void DetInDel::diploidGLF(const vector<Haplotype> & haps, const vector<Read> & reads, const vector<vector<MLAlignment> > & liks, vector<double> & hapFreqs, vector <HapEstResult > & posteriors,  uint32_t candPos, uint32_t leftPos, uint32_t rightPos,  OutputData & glfData, int index, const AlignedCandidates & candidateVariants, string program=\"all\")\n\n{\n",
          1, 0, "after",
          "\tif (dindel_b200_replay) dindel_b200_replay->batch->bindSums(dindel_b200_replay->w, dindel_b200_replay->inf);\n"
-         "\telse if (dindel_b200_gpu && dindel_b200_gpu->wantSums()) DINDEL_B200_INF.setSums(&dindel_b200_gpu->windowSums()[0], dindel_b200_gpu->windowHaps(), dindel_b200_gpu->windowReads(), 0, 0);\n"
+         "\telse if (dindel_b200_gpu && dindel_b200_gpu->wantSums()) DINDEL_B200_INF.setSums(dindel_b200_gpu->windowSumsPtr(), dindel_b200_gpu->windowHaps(), dindel_b200_gpu->windowReads(), 0, 0);\n"
          "\tDINDEL_B200_TWO_PASS(DINDEL_B200_INF, glfData, ;, diploidGLF(haps, reads, liks, hapFreqs, posteriors, candPos, leftPos, rightPos, glfData, index, candidateVariants, program))\n"),
         ("\t\tdouble ll=0.0;\n\t\tfor (size_t r=0;r<reads.size();r++){\n\t\t\tll+=log(0.5)+addLogs(rl[r*nh+h1],rl[r*nh+h2]);\n", 1, 0, "replace",
          "\t\tdouble ll=0.0;\n\t\tif (DINDEL_B200_INF.gpu()) ll = DINDEL_B200_INF.sum(h1, h2, nh, ll); else\n\t\tfor (size_t r=0;r<reads.size();r++){\n\t\t\tll+=log(0.5)+addLogs(rl[r*nh+h1],rl[r*nh+h2]);\n"),
@@ -166,7 +166,7 @@ if not dump:
         ("void DetInDel::estimateHaplotypeFrequenciesBayesEM(const vector<Haplotype> & haps, const vector<Read> & reads, const vector<vector<MLAlignment> > & liks, vector<double> & hapFreqs, vector <HapEstResult > & posteriors,  uint32_t candPos, uint32_t leftPos,   uint32_t rightPos, OutputData & glfData, int index, const AlignedCandidates & candidateVariants, string program=\"all\")\n\n{\n",
          1, 0, "after",
          "\tif (dindel_b200_replay) dindel_b200_replay->batch->bindSums(dindel_b200_replay->w, dindel_b200_replay->inf);\n"
-         "\telse if (dindel_b200_gpu && dindel_b200_gpu->wantSums()) DINDEL_B200_INF.setSums(&dindel_b200_gpu->windowSums()[0], dindel_b200_gpu->windowHaps(), dindel_b200_gpu->windowReads(), dindel_b200_gpu->windowPools(), dindel_b200_gpu->windowPoolSizes().empty() ? 0 : &dindel_b200_gpu->windowPoolSizes()[0]);\n"
+         "\telse if (dindel_b200_gpu && dindel_b200_gpu->wantSums()) DINDEL_B200_INF.setSums(dindel_b200_gpu->windowSumsPtr(), dindel_b200_gpu->windowHaps(), dindel_b200_gpu->windowReads(), dindel_b200_gpu->windowPools(), dindel_b200_gpu->windowPoolSizes().empty() ? 0 : &dindel_b200_gpu->windowPoolSizes()[0]);\n"
          "\tDINDEL_B200_TWO_PASS(DINDEL_B200_INF, glfData, posteriors.clear(), estimateHaplotypeFrequenciesBayesEM(haps, reads, liks, hapFreqs, posteriors, candPos, leftPos, rightPos, glfData, index, candidateVariants, program))\n"),
         ("\n\tfor (int th=0;th<nav;th++) {\n", 1, 0, "before",
          "\n\tif (DINDEL_B200_INF.gpu()) { // every EM run of the window in one K3 launch: compatible[] of each set as at :2394-2408 (checked again set by set in em())\n"

@@ -226,8 +226,9 @@ def test_batched_driver_one_process_identical(tmp_path, extra):
     assert hn["glf_identical"] and hn["cpu"]["windows_ok"] >= 25, res
     if "--pooled" not in extra:
         assert hn["vcf_identical"] and hn["cpu"]["vcf_calls"] >= 15, res
-    assert hn["gpu"]["batched"] and "batches" in hn["gpu"]["batched"][0], res
-    nb = int(hn["gpu"]["batched"][0].split("batches")[1].split()[0])
+    lines = [l for l in hn["gpu"]["batched"] if l.startswith("dindel_b200 batched:")]
+    assert lines and any(l.startswith("dindel_b200 host stages") for l in hn["gpu"]["batched"]), res
+    nb = int(lines[0].split("batches")[1].split()[0])
     assert nb >= 2, hn["gpu"]["batched"]
     assert hn["gpu"]["inference"]["windows"] >= 25, res
 

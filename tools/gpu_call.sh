@@ -1,8 +1,6 @@
 mkdir -p gpurun_out
-B="python bench.py --cfg 2 --windows 6000 --steps 3 --warmup 3 --no-cpu-baseline --no-extra --no-strong"
-for v in "" _alt; do
-  [ -f dindel_tgi_b200/libdindel_b200$v.so ] || continue
-  DINDEL_B200_LIB=$PWD/dindel_tgi_b200/libdindel_b200$v.so timeout 300 $B > gpurun_out/b6k$v.json 2> gpurun_out/b6k$v.err
-  echo "variant '$v'"; python -c "
-import json; r=json.load(open('gpurun_out/b6k$v.json')); print(r['gcups'], r['roofline']['frac'], r['e2e']['ll_checksum'])"
-done
+python -m pytest tests -m gpu -x -q > gpurun_out/r2_gputests_full.log 2>&1; tail -4 gpurun_out/r2_gputests_full.log
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r2_smoke.log 2>&1; tail -2 gpurun_out/r2_smoke.log
+python oracle/e2e/run_e2e.py --work /tmp/e2e1 --length 1000000 --seed 1 --arms cpu,gpu --windows-per-file 35 --procs 16 --gpu-one-file --heap-neutral > gpurun_out/r2_e2e_1mb.json 2> gpurun_out/r2_e2e_1mb.err
+python -c "
+import json; r=json.load(open('gpurun_out/r2_e2e_1mb.json')); print({k:(r[k]['cpu']['stage3_wall_s'], r[k]['gpu']['stage3_wall_s'], r[k]['glf_identical'], r[k]['vcf_identical'], r[k]['gpu']['batched']) for k in ('default','heap_neutral')})"
