@@ -13,7 +13,20 @@
 //              J = plane-1 x;  x == 0: 0 -> 0, 1 -> 1, J -> S;  x == RO: 0 RO, J S+RO
 //              plane 1: bit1 -> plane-0 min(x+1, RO)  (x == 0: plane-0 0)
 #pragma once
+#include <type_traits>
 #include "k1_common.cuh"
+
+// Back-pointer rows that live in global memory (J = 11 classes): the walk reads ONE entry per row, each on its own
+// 128-byte line that left the L1 long ago, so every step would wait a full L2 / DRAM round trip.  The walk follows
+// the alignment's diagonal almost everywhere (x moves by one per row), so the entry K1_TAIL_PF_AHEAD rows further
+// down the diagonal is prefetched; a wrong guess (indel in between) costs one useless line.  8 rows measured best
+// (32 and 96 slightly worse: profiles/r2_k1_j11.md).
+#ifndef K1_TAIL_PF_AHEAD
+#define K1_TAIL_PF_AHEAD 8
+#endif
+struct K1NoPrefetch {
+    __device__ __forceinline__ void operator()(int, int) const {}
+};
 
 __device__ __forceinline__ int k1_prev_state_dec(int s, int code0, int bit1, int S, int H, int J)
 {
@@ -45,8 +58,8 @@ __device__ __forceinline__ int k1_next_state_inc(int s, int code0, int bit1, int
 // Everything after ms[bMid] is known.  `bt(row, x)` returns code0 | bit1 << 7 of state column x;
 // rows 1..bMid hold the left half (btf[b]), rows bMid+1..R-1 hold btb[row-1].
 // sm_ms: int16[R] scratch; sm_ch / sm_ph: the read's bases and phred bytes; sm_acc: double[R].
-template <class Bt>
-__device__ __forceinline__ void k1_tail(const Bt &bt, int lane, int R, int H, int J, int bMid,
+template <class Bt, class Pf>
+__device__ __forceinline__ void k1_tail(const Bt &bt, const Pf &pf, int lane, int R, int H, int J, int bMid,
                                         int msMid, const uint8_t *hap, const uint8_t *sm_ch,
                                         const uint8_t *sm_ph, int16_t *sm_ms, double *sm_acc,
                                         const K1Luts *__restrict__ L, double ll, double llOn,
@@ -62,9 +75,22 @@ __device__ __forceinline__ void k1_tail(const Bt &bt, int lane, int R, int H, in
         const int n = left ? bMid : (R - 1 - bMid);
         int s = msMid, b = bMid;
         if (left) sm_ms[bMid] = (int16_t)s;
+        if constexpr (!std::is_same<Pf, K1NoPrefetch>::value) { // the first rows of the diagonal
+            const int x0 = s >= S ? s - S : s;
+            for (int k = 1; k < K1_TAIL_PF_AHEAD && k < n; k++) {
+                const int xp = left ? x0 - k : x0 + k;
+                pf(left ? b - k : b + 1 + k, xp < 0 ? 0 : (xp > RO ? RO : xp));
+            }
+        }
         for (int i = 0; i < n; i++) {
             const bool plane1 = s >= S;
             const int x = plane1 ? s - S : s;
+            if constexpr (!std::is_same<Pf, K1NoPrefetch>::value) {
+                if (i + K1_TAIL_PF_AHEAD < n) {
+                    const int xp = left ? x - K1_TAIL_PF_AHEAD : x + K1_TAIL_PF_AHEAD;
+                    pf(left ? b - K1_TAIL_PF_AHEAD : b + 1 + K1_TAIL_PF_AHEAD, xp < 0 ? 0 : (xp > RO ? RO : xp));
+                }
+            }
             const int c = bt(left ? b : b + 1, x);
             const int code = c & 127;
             const bool bit1 = (c >> 7) != 0;
@@ -161,6 +187,16 @@ __device__ __forceinline__ void k1_tail(const Bt &bt, int lane, int R, int H, in
         dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2]; dst[3] = src[3];
     }
     __syncwarp();
+}
+
+template <class Bt>
+__device__ __forceinline__ void k1_tail(const Bt &bt, int lane, int R, int H, int J, int bMid, int msMid, const uint8_t *hap,
+                                        const uint8_t *sm_ch, const uint8_t *sm_ph, int16_t *sm_ms, double *sm_acc,
+                                        const K1Luts *__restrict__ L, double ll, double llOn, double llOff, int offHap,
+                                        int offHapHMQ, dindel_pair_out *out, int16_t *hpos_out)
+{
+    k1_tail(bt, K1NoPrefetch(), lane, R, H, J, bMid, msMid, hap, sm_ch, sm_ph, sm_ms, sm_acc, L, ll, llOn, llOff, offHap,
+            offHapHMQ, out, hpos_out);
 }
 
 // A pair that the reference refuses with "hapSize error." (cpp:47).

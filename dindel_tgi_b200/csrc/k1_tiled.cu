@@ -38,6 +38,12 @@
 #ifndef K1_FMAX
 #define K1_FMAX 0 // 1: the 'take iff v >= best' value selects as DMNMX (one FP64-pipe instruction instead of two ALU selects)
 #endif
+#ifndef K1_LEFT_ADD
+// shared-table classes: the left half's jump entries logProbError + (y-1)*lInsgIns (cpp:1791) are rebuilt by one DADD
+// from the column's lpe and the compile-time constant (y-1) * -0.5 (lInsgIns is the constant -.5: api.cu, cpp:1664;
+// the product is exact, so the sum is the table's) instead of a shared load per candidate: +2.9 % at J = 11
+#define K1_LEFT_ADD 1
+#endif
 #ifndef K1_TILED_J11_MINB
 #define K1_TILED_J11_MINB 3
 #endif
@@ -170,7 +176,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
     constexpr bool TBL = (J > 7) || (C > K1_TILED_TBL_MINC);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double s_hp_lpe[K1_HP_LUT], s_hp_lpn[K1_HP_LUT];
-    __shared__ double s_tl[TBL ? K1_HP_LUT * (J - 1) : 1]; // [code][y-2] = logProbError + (y-1)*lInsgIns (cpp:1791)
+    __shared__ double s_tl[(TBL && !K1_LEFT_ADD) ? K1_HP_LUT * (J - 1) : 1]; // [code][y-2] = logProbError + (y-1)*lInsgIns (cpp:1791)
     __shared__ double s_tr[TBL ? K1_HP_LUT * J : 1];       // [code][y-1] = lp(y) + logProbNoError    (cpp:1732-1735)
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
@@ -181,7 +187,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
         s_hp_lpn[i] = L->hp_lpn[i];
     }
     if constexpr (TBL) {
-        for (int i = threadIdx.x; i < K1_HP_LUT * (J - 1); i += blockDim.x) {
+        for (int i = threadIdx.x; !K1_LEFT_ADD && i < K1_HP_LUT * (J - 1); i += blockDim.x) {
             const int code = i / (J - 1), y = i % (J - 1) + 2;
             s_tl[i] = L->hp_lpe[code] + (double)(y - 1) * L->lInsgIns;
         }
@@ -300,7 +306,11 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                 const double lpeLm1 = s_hp_lpe[hp[(c0 >= 1 && c0 - 1 <= RO) ? c0 - 1 : 0]];
 
                 auto LPD = [&](int c, int k) -> double {
+#if K1_LEFT_ADD
+                    if constexpr (TBL) return lpe[c] + (-0.5 * (double)(k + 1));
+#else
                     if constexpr (TBL) return s_tl[offL[c] + k];
+#endif
                     else return lpD[c][k];
                 };
                 auto left_rows = [&](auto cro_tag) {
@@ -697,8 +707,17 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                     return (int)((u16 >> (8 * (c & 1))) & 255u);
                 }
             };
-            k1_tail(btf, lane, R, H, J, bMid, msH, hap, sm_ch, sm_ph, sm_ms, sm_eq, L, ll, llOn, llOff,
-                    offHap, offHapHMQ, out, B.hpos ? B.hpos + pair * (long long)B.hpos_stride : nullptr);
+            int16_t *hrow = B.hpos ? B.hpos + pair * (long long)B.hpos_stride : nullptr;
+            if constexpr (BTG) { // rows in global memory: prefetch down the diagonal (k1_tail.cuh)
+                auto pff = [btp](int row, int x) {
+                    const int ln = x / C, c = x - ln * C;
+                    const uint16_t *a = btp + ((size_t)row * U16 + (Cfg::NIB ? (c >> 2) : (c >> 1))) * 32 + ln;
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(a));
+                };
+                k1_tail(btf, pff, lane, R, H, J, bMid, msH, hap, sm_ch, sm_ph, sm_ms, sm_eq, L, ll, llOn, llOff, offHap, offHapHMQ, out, hrow);
+            } else {
+                k1_tail(btf, lane, R, H, J, bMid, msH, hap, sm_ch, sm_ph, sm_ms, sm_eq, L, ll, llOn, llOff, offHap, offHapHMQ, out, hrow);
+            }
         }
     }
 }
