@@ -1840,4 +1840,108 @@ int dindel_b200_measure_fp64_peak(dindel_ctx *ctx, double *dadd_per_s)
     return DINDEL_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// dindel_b200_run_static: K1 over the resident batch without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  It is the generic kernel in its "back-pointer rows in a per-warp global slot"
+// plan (k1_generic.cu; the plan tests force with DINDEL_B200_FORCE_BT_GLOBAL) with BOTH pieces of scratch that plan
+// needs -- the work-queue head and the back-pointer slots of every resident warp -- in ONE file-scope device array:
+//
+//   [0, 256)                         work-queue head (unsigned long long); cleared by a memset node before every launch
+//   [256, 256 + warps * slot_bytes)  back-pointer slots, slot_bytes = align256((maxH + 2) * maxR); NOT cleared: every
+//                                    row a pair's back-trace reads was written by the same warp for that pair
+//
+// Every GPU that loads the library holds the array (DINDEL_B200_STATIC_SCRATCH_BYTES) until the process exits.  All
+// calls on a device share it and it keeps the last call's contents: two calls that overlap on the GPU (two contexts,
+// two streams, two host threads) race on the queue head and the slots.  One call at a time per device.
+//
+// In host code `g_static_scratch` is only the host-side stand-in of the symbol, not a device address: the address is
+// resolved once per device, with that device current, by cudaGetSymbolAddress (static_scratch_ptr) and that pointer
+// is what the kernel receives.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[DINDEL_B200_STATIC_SCRATCH_BYTES];
+#define DINDEL_STATIC_HEAD_BYTES 256
+#define DINDEL_STATIC_MAX_DEVICES 64
+static std::mutex g_static_lock;
+static unsigned char *g_static_ptr[DINDEL_STATIC_MAX_DEVICES]; // device address of g_static_scratch, per device ordinal
+
+static int static_scratch_ptr(dindel_ctx *ctx, unsigned char **out)
+{
+    if (ctx->device < 0 || ctx->device >= DINDEL_STATIC_MAX_DEVICES)
+        return fail(ctx, DINDEL_E_UNSUPPORTED, "run_static: device ordinal beyond the static scratch table");
+    std::lock_guard<std::mutex> g(g_static_lock);
+    if (!g_static_ptr[ctx->device]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch); // the ctx's device is current (caller)
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return fail(ctx, DINDEL_E_CUDA, std::string("run_static: cudaGetSymbolAddress(g_static_scratch): ") + cudaGetErrorString(e));
+        }
+        g_static_ptr[ctx->device] = (unsigned char *)p;
+    }
+    *out = g_static_ptr[ctx->device];
+    return DINDEL_OK;
+}
+
+size_t dindel_b200_static_scratch_bytes(void) { return (size_t)DINDEL_B200_STATIC_SCRATCH_BYTES; }
+
+int dindel_b200_run_static(dindel_ctx *ctx, dindel_batch_out *out)
+{
+    if (!ctx || !ctx->resident) return fail(ctx, DINDEL_E_INVALID, "run_static: no resident batch (call upload first)");
+    if (ctx->base.w0 != 0 || ctx->base.w1 != ctx->idx_windows)
+        return fail(ctx, DINDEL_E_INVALID, "run_static needs the whole batch resident");
+    CU(cudaSetDevice(ctx->device));
+    unsigned char *scratch = nullptr;
+    int rc = static_scratch_ptr(ctx, &scratch);
+    if (rc != DINDEL_OK) return rc;
+    Lane &ln = ctx->lane[0];
+    cudaStream_t st = ln.st;
+    const Range &g = ctx->all;
+    K1Batch b = range_batch(ctx, g, ln);
+    // the plan of k1_range's generic branch with the back-pointer rows in global memory
+    const size_t pw = k1_generic_smem_per_warp(b.max_S, b.max_R, 0);
+    int warps = 4;
+    while (warps > 1 && pw * warps > ctx->smem_optin) warps >>= 1;
+    if (pw * warps > ctx->smem_optin) return fail(ctx, DINDEL_E_UNSUPPORTED, "run_static: shape exceeds shared memory");
+    int cps = (int)((size_t)(228 * 1024 - 1024) / (pw * warps + 1024));
+    if (cps < 1) cps = 1;
+    if (cps * warps > 32) cps = 32 / warps;
+    const long long slot = (((long long)b.max_S * b.max_R) + 255) & ~255LL;
+    const long long room = (long long)DINDEL_B200_STATIC_SCRATCH_BYTES - DINDEL_STATIC_HEAD_BYTES;
+    const long long need = slot * warps * ctx->num_sms; // one CTA per SM at least
+    if (need > room) {
+        char msg[320];
+        snprintf(msg, sizeof(msg), "run_static: batch too large for the static scratch: (maxH+2) x maxR = %d x %d needs %lld bytes "
+                 "(%lld per warp x %d warps x %d SMs), the maximum is %lld; use dindel_b200_run", b.max_S, b.max_R, need, slot,
+                 warps, ctx->num_sms, room);
+        return fail(ctx, DINDEL_E_UNSUPPORTED, msg);
+    }
+    long long max_ctas = room / (slot * warps);
+    long long grid = (long long)ctx->num_sms * cps;
+    if (grid > max_ctas) grid = max_ctas;
+    const long long want = (g.u1 - g.u0 + warps - 1) / warps;
+    if (grid > want) grid = want;
+    b.counter = (unsigned long long *)scratch;
+    b.bt_scratch = scratch + DINDEL_STATIC_HEAD_BYTES;
+    b.bt_slot_bytes = slot;
+    CU(cudaEventRecord(ctx->ev[3], st));
+    int launches = 0;
+    if (g.u1 > g.u0) {
+        CU(cudaMemsetAsync(scratch, 0, DINDEL_STATIC_HEAD_BYTES, st)); // the queue head must start at zero
+        CU(k1_generic_launch(&b, (int)grid, warps, 0, pw * warps, st));
+        launches++;
+    }
+    if (g.w1 > g.w0) {
+        const int threads = 128, wpb = threads / 32;
+        k1_window_summary<<<(g.w1 - g.w0 + wpb - 1) / wpb, threads, 0, st>>>(g.w0, g.w1, b.win_hap, b.win_read, b.win_pair, b.pairs,
+                                                                            ctx->p_win_status, ctx->p_on_hap);
+        CU(cudaGetLastError());
+        launches++;
+    }
+    CU(cudaEventRecord(ctx->ev[4], st));
+    ctx->timing.k1_launches = launches;
+    ctx->ran = true;
+    return out ? dindel_b200_download(ctx, out) : DINDEL_OK;
+}
+
 } // extern "C"

@@ -124,7 +124,8 @@ EXPORTS = [
     "dindel_b200_last_kernel_ms", "dindel_b200_cigars", "dindel_b200_process", "dindel_b200_count_sums",
     "dindel_b200_sum_error_bound", "dindel_b200_multi_create", "dindel_b200_multi_destroy", "dindel_b200_multi_devices",
     "dindel_b200_multi_set_libraries", "dindel_b200_multi_process", "dindel_b200_multi_get_shard",
-    "dindel_b200_multi_last_error", "dindel_b200_load_likelihoods",
+    "dindel_b200_multi_last_error", "dindel_b200_load_likelihoods", "dindel_b200_run_static",
+    "dindel_b200_static_scratch_bytes",
 ]
 
 _lib = None
@@ -181,6 +182,8 @@ def load_library():
     lib.dindel_b200_multi_last_error.restype = C.c_char_p
     lib.dindel_b200_multi_last_error.argtypes = [C.c_void_p]
     lib.dindel_b200_multi_set_libraries.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.dindel_b200_run_static.argtypes = [C.c_void_p, C.POINTER(_BatchOut)]
+    lib.dindel_b200_static_scratch_bytes.restype = C.c_size_t
     _lib = lib
     return lib
 
@@ -414,6 +417,15 @@ class Engine:
         stride = self.lib.dindel_b200_hpos_stride(self.h) if want_hpos else None
         o, pairs, win_pair, win_status, on_hap, hpos = self._alloc_out(batch, want_hpos, stride)
         self._check(self.lib.dindel_b200_download(self.h, C.byref(o)), "download")
+        return PairResults(pairs, win_pair, win_status, on_hap, hpos, self.timing())
+
+    def run_static(self):
+        """dindel_b200_run_static: K1 over the resident batch with the kernel's scratch in the library's static device
+        array (no allocation inside the call), results copied into host arrays allocated HERE before the call."""
+        batch, want_hpos = self._resident
+        stride = self.lib.dindel_b200_hpos_stride(self.h) if want_hpos else None
+        o, pairs, win_pair, win_status, on_hap, hpos = self._alloc_out(batch, want_hpos, stride)
+        self._check(self.lib.dindel_b200_run_static(self.h, C.byref(o)), "run_static")
         return PairResults(pairs, win_pair, win_status, on_hap, hpos, self.timing())
 
     def measure_fp64_peak(self):

@@ -388,6 +388,24 @@ void dindel_b200_free_pinned(void *p);
  * the denominator of the K1 roofline. */
 int dindel_b200_measure_fp64_peak(dindel_ctx *ctx, double *dadd_per_s);
 
+/* K1 over the resident batch WITHOUT ANY ALLOCATION.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Inputs: the batch made resident by dindel_b200_upload (which may allocate: set-up).
+ * Outputs: `out` as for dindel_b200_download, or NULL to leave the results resident (dindel_b200_download later).
+ * The call itself issues one memset, the generic K1 kernel with its back-pointer rows in global memory, the window
+ * summary and (out != NULL) the device-to-host copies; it calls no cudaMalloc / cudaFree / allocating routine.  The
+ * kernel's scratch (work-queue head + one back-pointer slot per resident warp) is a file-scope device array of
+ * DINDEL_B200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until the process exits.
+ * Limit: align256((maxH + 2) * maxR) * 4 warps * SM count <= DINDEL_B200_STATIC_SCRATCH_BYTES - 256 (B200, 148 SMs:
+ * (maxH + 2) * maxR <= 28 160, e.g. 100-base reads on haplotypes up to 279 bases); a larger batch is refused with
+ * DINDEL_E_UNSUPPORTED and a message naming both sizes -- use dindel_b200_run.  Results are byte-identical to
+ * dindel_b200_run's.  All calls on a device share the array, which keeps the last call's contents (the queue head is
+ * cleared by the call; the slots need no clearing): calls that OVERLAP on the GPU (two contexts, streams or threads
+ * on one device) race -- issue one at a time per device. */
+#define DINDEL_B200_STATIC_SCRATCH_BYTES (16u << 20)
+int dindel_b200_run_static(dindel_ctx *ctx, dindel_batch_out *out);
+size_t dindel_b200_static_scratch_bytes(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,4 +1,3 @@
 mkdir -p gpurun_out
-python -m pytest tests/test_k1_gpu.py -x -q > gpurun_out/r2b_k1tests.log 2>&1; tail -4 gpurun_out/r2b_k1tests.log
-python bench.py --cfg 4 --windows 600 --steps 2 --warmup 3 --no-cpu-baseline --no-extra --no-strong > gpurun_out/r2b_cfg4.json 2> gpurun_out/r2b_cfg4.err; tail -c 1500 gpurun_out/r2b_cfg4.json
-python bench.py --cfg 2 --windows 6000 --steps 3 --warmup 3 --no-cpu-baseline --no-extra --no-strong > gpurun_out/r2b_cfg2.json 2> gpurun_out/r2b_cfg2.err; tail -c 1500 gpurun_out/r2b_cfg2.json
+python -m pytest tests/test_zz_no_alloc.py -x -q > gpurun_out/r2c_noalloc_alone.log 2>&1; tail -15 gpurun_out/r2c_noalloc_alone.log
+python -m pytest tests -m gpu -x -q > gpurun_out/r2c_gputests_full.log 2>&1; tail -6 gpurun_out/r2c_gputests_full.log
