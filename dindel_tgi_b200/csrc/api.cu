@@ -18,6 +18,7 @@
 #include "k23.cuh"
 #include "k4.cuh"
 #include "k5.cuh"
+#include "k6.cuh"
 
 extern "C" size_t k1_generic_smem_per_warp(int maxS, int maxR, int bt_in_smem);
 extern "C" cudaError_t k1_generic_launch(const K1Batch *B, int grid, int warps_per_cta,
@@ -38,6 +39,7 @@ extern "C" cudaError_t k4_launch(const K4Args *a, int n_windows, size_t smem, cu
 extern "C" size_t k5_smem_bytes(int pitch);
 extern "C" int k5_pitch(int max_R);
 extern "C" cudaError_t k5_launch(const K5Args *a, int n_sms, size_t smem, cudaStream_t st);
+extern "C" cudaError_t k6_launch(const K6Args *a, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------------
 // small device kernels owned by the API layer
@@ -1388,6 +1390,43 @@ int dindel_b200_load_likelihoods(dindel_ctx *ctx, int32_t n_windows, const int32
     return DINDEL_OK;
 }
 
+// As load_likelihoods, with whole pair records and the per-read bytes the stage kernels read (K6: mapping-quality
+// phred and DINDEL_READ_* flags).
+int dindel_b200_load_records(dindel_ctx *ctx, int32_t n_windows, const int32_t *win_hap, const int32_t *win_read,
+                             const dindel_pair_out *records, const uint8_t *read_mapq, const uint8_t *read_flags)
+{
+    if (!ctx || n_windows < 1 || !win_hap || !win_read || !records) return fail(ctx, DINDEL_E_INVALID, "load_records");
+    if (win_hap[0] != 0 || win_read[0] != 0) return fail(ctx, DINDEL_E_INVALID, "win_hap / win_read must start at 0");
+    for (int w = 0; w < n_windows; w++)
+        if (win_hap[w + 1] < win_hap[w] || win_read[w + 1] < win_read[w]) return fail(ctx, DINDEL_E_INVALID, "CSR not monotone");
+    const int nh = win_hap[n_windows], nr = win_read[n_windows];
+    std::vector<int64_t> hap_off((size_t)nh + 1, 0), read_off((size_t)nr + 1, 0);
+    std::vector<uint32_t> hs((size_t)n_windows, 0);
+    std::vector<uint8_t> z8((size_t)(nr ? nr : 1), 0);
+    std::vector<uint32_t> z32((size_t)(nr ? nr : 1), 0);
+    dindel_batch_in in;
+    memset(&in, 0, sizeof(in));
+    in.n_windows = n_windows; in.n_haps = nh; in.n_reads = nr;
+    in.hap_start = hs.data(); in.win_hap = win_hap; in.win_read = win_read;
+    in.hap_off = hap_off.data(); in.hap_seq = ""; in.read_off = read_off.data(); in.read_seq = ""; in.read_qual = z8.data();
+    in.read_mapq = read_mapq ? read_mapq : z8.data(); in.read_start = z32.data(); in.read_flags = read_flags ? read_flags : z8.data();
+    int rc = index_batch(ctx, &in, false);
+    if (rc != DINDEL_OK) return rc;
+    memset(&ctx->timing, 0, sizeof(ctx->timing));
+    rc = prepare_range(ctx, &in, 0, n_windows, 0, 0);
+    if (rc != DINDEL_OK) return rc;
+    cudaStream_t st = ctx->stream;
+    scan_range(ctx, &in, 0, n_windows, ctx->all);
+    rc = copy_in_range(ctx, &in, ctx->all, st);
+    if (rc != DINDEL_OK) { drain(ctx); return rc; }
+    const long long np = ctx->B.n_pairs;
+    if (np > 0) CU(cudaMemcpyAsync(ctx->d_pairs.p, records, (size_t)np * sizeof(dindel_pair_out), cudaMemcpyHostToDevice, st));
+    CU(cudaStreamSynchronize(st));
+    ctx->resident = true;
+    ctx->ran = true;
+    return DINDEL_OK;
+}
+
 int dindel_b200_pair_sums(dindel_ctx *ctx, const dindel_pairsum_in *in, double *out)
 {
     if (!ctx || !in || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "pair_sums needs a resident, computed batch");
@@ -1659,6 +1698,79 @@ int dindel_b200_cigars(dindel_ctx *ctx, const dindel_cigar_in *in, dindel_cigar_
     CU(cudaMemcpyAsync(out->read_ref_pos, a.read_ref_pos, nr * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(out->read_n_ops, a.read_n_ops, nr * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(out->ops, a.ops, nr * cap * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev_k[0], ctx->ev_k[1]);
+    return DINDEL_OK;
+}
+
+// K6: read statistics of called sites over the resident records (k6_read_stats.cu)
+int dindel_b200_read_stats(dindel_ctx *ctx, const dindel_stats_in *in, dindel_read_stats *out)
+{
+    if (!ctx || !in || !ctx->resident || !ctx->ran) return fail(ctx, DINDEL_E_INVALID, "read_stats needs a resident, computed batch");
+    if (in->n_jobs < 0) return fail(ctx, DINDEL_E_INVALID, "n_jobs");
+    if (in->n_jobs == 0) return DINDEL_OK;
+    if (!in->job_window || !in->job_mode || !in->job_group || !in->job_cand || !out) return fail(ctx, DINDEL_E_INVALID, "null array");
+    const Range &b = ctx->base;
+    const K1Batch &B = ctx->B;
+    const size_t nj = (size_t)in->n_jobs;
+    if (in->job_cand[0] != 0) return fail(ctx, DINDEL_E_INVALID, "job_cand[0] != 0");
+    bool any_group = false;
+    for (size_t j = 0; j < nj; j++) {
+        const int w = in->job_window[j], mode = in->job_mode[j];
+        if (w < b.w0 || w >= b.w1) return fail(ctx, DINDEL_E_INVALID, "job_window outside the resident range");
+        const long long nc = in->job_cand[j + 1] - in->job_cand[j];
+        if (nc < 0) return fail(ctx, DINDEL_E_INVALID, "job_cand not monotone");
+        if (mode != DINDEL_STATS_SITE && mode != DINDEL_STATS_MAP && mode != DINDEL_STATS_POOL) return fail(ctx, DINDEL_E_INVALID, "job_mode");
+        if (mode != DINDEL_STATS_POOL && nc != 2) return fail(ctx, DINDEL_E_INVALID, "SITE / MAP jobs take exactly two candidates");
+        const int nh = ctx->win_nh[w];
+        for (long long c = in->job_cand[j]; c < in->job_cand[j + 1]; c++)
+            if (in->cand_hap[c] < 0 || in->cand_hap[c] >= nh) return fail(ctx, DINDEL_E_INVALID, "cand_hap outside the window");
+        any_group = any_group || in->job_group[j] >= 0;
+    }
+    if (any_group && !in->read_group) return fail(ctx, DINDEL_E_INVALID, "job_group >= 0 without read_group");
+    const size_t ncand = (size_t)in->job_cand[nj];
+    if (ncand && (!in->cand_hap || !in->cand_start || !in->cand_end || !in->cand_flags)) return fail(ctx, DINDEL_E_INVALID, "null array");
+    static double mq_lut[256];
+    static std::once_flag mq_once;
+    std::call_once(mq_once, [] {
+        for (int ph = 0; ph < 256; ph++) mq_lut[ph] = -10 * log10(1.0 - phred_to_prob(ph)); // DInDel.cpp:3505 on Read.hpp:127-131
+    });
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const size_t nr = (size_t)(b.r1 - b.r0);
+    // staging: [job_cand (8) | job_window | job_mode | job_group | cand_hap | cand_start | cand_end | cand_flags | read_group]
+    const size_t o_jc = 0, o_jw = o_jc + (nj + 1) * 8, o_jm = o_jw + nj * 4, o_jg = o_jm + nj * 4, o_ch = o_jg + nj * 4,
+                 o_cs = o_ch + ncand * 4, o_ce = o_cs + ncand * 4, o_cf = o_ce + ncand * 4, o_rg = (o_cf + ncand + 7) & ~(size_t)7,
+                 in_bytes = o_rg + (any_group ? nr * 4 : 0);
+    CU(ctx->d_x[0].ensure(in_bytes + 16));
+    CU(ctx->d_x[1].ensure(nj * sizeof(dindel_read_stats) + 16));
+    char *d_in = (char *)ctx->d_x[0].p;
+    CU(cudaMemcpyAsync(d_in + o_jc, in->job_cand, (nj + 1) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_in + o_jw, in->job_window, nj * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_in + o_jm, in->job_mode, nj * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_in + o_jg, in->job_group, nj * 4, cudaMemcpyHostToDevice, st));
+    if (ncand) {
+        CU(cudaMemcpyAsync(d_in + o_ch, in->cand_hap, ncand * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_cs, in->cand_start, ncand * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_ce, in->cand_end, ncand * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_in + o_cf, in->cand_flags, ncand, cudaMemcpyHostToDevice, st));
+    }
+    if (any_group && nr) CU(cudaMemcpyAsync(d_in + o_rg, in->read_group + b.r0, nr * 4, cudaMemcpyHostToDevice, st));
+    K6Args a;
+    a.n_jobs = (int)nj; a.pad = ctx->params.padCover;
+    a.job_cand = (const long long *)(d_in + o_jc); a.job_window = (const int32_t *)(d_in + o_jw);
+    a.job_mode = (const int32_t *)(d_in + o_jm); a.job_group = (const int32_t *)(d_in + o_jg);
+    a.cand_hap = (const int32_t *)(d_in + o_ch); a.cand_start = (const int32_t *)(d_in + o_cs);
+    a.cand_end = (const int32_t *)(d_in + o_ce); a.cand_flags = (const uint8_t *)(d_in + o_cf);
+    a.read_group = any_group ? (const int32_t *)(d_in + o_rg) - b.r0 : nullptr;
+    a.out = (dindel_read_stats *)ctx->d_x[1].p;
+    a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.pairs = B.pairs;
+    a.read_mapq = B.read_mapq; a.read_flags = B.read_flags;
+    memcpy(a.mq, mq_lut, sizeof(mq_lut));
+    CU(cudaEventRecord(ctx->ev_k[0], st));
+    CU(k6_launch(&a, st));
+    CU(cudaEventRecord(ctx->ev_k[1], st));
+    CU(cudaMemcpyAsync(out, a.out, nj * sizeof(dindel_read_stats), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev_k[0], ctx->ev_k[1]);
     return DINDEL_OK;

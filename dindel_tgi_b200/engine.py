@@ -104,6 +104,20 @@ class _Job(C.Structure):
                 ("read_group", C.c_void_p), ("em", C.c_void_p), ("em_out", C.c_void_p)]
 
 
+class _StatsIn(C.Structure):
+    _fields_ = [("n_jobs", C.c_int32), ("reserved", C.c_int32), ("job_window", C.c_void_p), ("job_mode", C.c_void_p),
+                ("job_group", C.c_void_p), ("job_cand", C.c_void_p), ("cand_hap", C.c_void_p), ("cand_start", C.c_void_p),
+                ("cand_end", C.c_void_p), ("cand_flags", C.c_void_p), ("read_group", C.c_void_p)]
+
+
+STATS_DTYPE = np.dtype([
+    ("msq", "<f8"), ("allmsq", "<f8"), ("mLogBQ", "<f8"), ("n", "<i4"), ("nf", "<i4"), ("nr", "<i4"), ("numOffBoth", "<i4"),
+    ("numIndels", "<i4"), ("nBQT", "<i4"), ("nmmBQT", "<i4"), ("nMMLeft", "<i4"), ("nMMRight", "<i4"),
+    ("numUnmappedRealigned", "<i4"), ("n_reads", "<i4"), ("reserved", "<i4")])
+assert STATS_DTYPE.itemsize == 72
+STATS_SITE, STATS_MAP, STATS_POOL = 0, 1, 2
+CAND_PRESENT, CAND_HAS_VAR = 1, 2
+
 PAIR_DTYPE = np.dtype([
     ("ll", "<f8"), ("llOn", "<f8"), ("llOff", "<f8"), ("mLogBQ", "<f8"),
     ("firstBase", "<i4"), ("lastBase", "<i4"),
@@ -125,7 +139,7 @@ EXPORTS = [
     "dindel_b200_sum_error_bound", "dindel_b200_multi_create", "dindel_b200_multi_destroy", "dindel_b200_multi_devices",
     "dindel_b200_multi_set_libraries", "dindel_b200_multi_process", "dindel_b200_multi_get_shard",
     "dindel_b200_multi_last_error", "dindel_b200_load_likelihoods", "dindel_b200_run_static",
-    "dindel_b200_static_scratch_bytes",
+    "dindel_b200_static_scratch_bytes", "dindel_b200_read_stats", "dindel_b200_load_records",
 ]
 
 _lib = None
@@ -182,6 +196,8 @@ def load_library():
     lib.dindel_b200_multi_last_error.restype = C.c_char_p
     lib.dindel_b200_multi_last_error.argtypes = [C.c_void_p]
     lib.dindel_b200_multi_set_libraries.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.dindel_b200_read_stats.argtypes = [C.c_void_p, C.POINTER(_StatsIn), C.c_void_p]
+    lib.dindel_b200_load_records.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.dindel_b200_run_static.argtypes = [C.c_void_p, C.POINTER(_BatchOut)]
     lib.dindel_b200_static_scratch_bytes.restype = C.c_size_t
     _lib = lib
@@ -443,6 +459,46 @@ class Engine:
                     "load_likelihoods")
         self._resident = None
         self._n_haps, self._n_reads = int(wh[-1]), int(wr[-1])
+
+    def load_records(self, recs, nhs, mapq=None, flags=None):
+        """dindel_b200_load_records: recs = list of PAIR_DTYPE arrays (one per window, r-major), nhs = haplotypes per
+        window, mapq / flags = per-read bytes over the whole batch."""
+        wh = np.concatenate([[0], np.cumsum(nhs)]).astype(np.int32)
+        wr = np.concatenate([[0], np.cumsum([len(x) // h for x, h in zip(recs, nhs)])]).astype(np.int32)
+        flat = np.ascontiguousarray(np.concatenate(recs), dtype=PAIR_DTYPE)
+        mq = None if mapq is None else np.ascontiguousarray(mapq, dtype=np.uint8)
+        fl = None if flags is None else np.ascontiguousarray(flags, dtype=np.uint8)
+        self._check(self.lib.dindel_b200_load_records(self.h, len(recs), wh.ctypes.data, wr.ctypes.data, flat.ctypes.data,
+                                                      mq.ctypes.data if mq is not None else None,
+                                                      fl.ctypes.data if fl is not None else None), "load_records")
+        self._resident = None
+        self._n_haps, self._n_reads = int(wh[-1]), int(wr[-1])
+
+    def read_stats(self, jobs, read_group=None):
+        """K6 (dindel_b200_read_stats) over the resident batch.  jobs: list of (window, mode, group, cands) with
+        cands = [(hap, startRead, endRead, flags)]; returns a STATS_DTYPE array, one row per job."""
+        nj = len(jobs)
+        jw = np.array([j[0] for j in jobs], dtype=np.int32)
+        jm = np.array([j[1] for j in jobs], dtype=np.int32)
+        jg = np.array([j[2] for j in jobs], dtype=np.int32)
+        jc = np.concatenate([[0], np.cumsum([len(j[3]) for j in jobs])]).astype(np.int64)
+        flat = [c for j in jobs for c in j[3]]
+        ch = np.array([c[0] for c in flat], dtype=np.int32)
+        cs = np.array([c[1] for c in flat], dtype=np.int32)
+        ce = np.array([c[2] for c in flat], dtype=np.int32)
+        cf = np.array([c[3] for c in flat], dtype=np.uint8)
+        rg = None if read_group is None else np.ascontiguousarray(read_group, dtype=np.int32)
+        a = _StatsIn()
+        a.n_jobs = nj
+        a.job_window, a.job_mode, a.job_group, a.job_cand = jw.ctypes.data, jm.ctypes.data, jg.ctypes.data, jc.ctypes.data
+        a.cand_hap, a.cand_start, a.cand_end, a.cand_flags = ch.ctypes.data, cs.ctypes.data, ce.ctypes.data, cf.ctypes.data
+        a.read_group = rg.ctypes.data if rg is not None else None
+        out = np.zeros(nj, dtype=STATS_DTYPE)
+        t0 = time.perf_counter()
+        self._check(self.lib.dindel_b200_read_stats(self.h, C.byref(a), out.ctypes.data), "read_stats")
+        self.last_call_ms = 1e3 * (time.perf_counter() - t0)
+        self.last_kernel_ms = float(self.lib.dindel_b200_last_kernel_ms(self.h))
+        return out
 
     # ---- inference kernels over the resident likelihood matrix ----
     def pair_sums(self, job_window, starts, job_group=None, read_group=None):

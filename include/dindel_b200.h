@@ -190,6 +190,11 @@ float dindel_b200_last_kernel_ms(const dindel_ctx *ctx);
  * dump).  Every other field of the resident pair records is zero and there are no hpos rows. */
 int dindel_b200_load_likelihoods(dindel_ctx *ctx, int32_t n_windows, const int32_t *win_hap, const int32_t *win_read,
                                  const double *ll);
+/* The same with whole pair records (r-major per window, like dindel_batch_out.pairs) and the per-read bytes the stage
+ * kernels read (mapping-quality phred, DINDEL_READ_* flags; NULL = zeros): K2 / K3 / K6 then run on records that were
+ * computed elsewhere (tests load the reference's own MLAlignment fields this way). */
+int dindel_b200_load_records(dindel_ctx *ctx, int32_t n_windows, const int32_t *win_hap, const int32_t *win_read,
+                             const dindel_pair_out *records, const uint8_t *read_mapq, const uint8_t *read_flags);
 
 /* ---- K2: haplotype-pair sums over the RESIDENT likelihood matrix (after run/submit) ----------
  * Replaces the inner loops of DetInDel::diploidGLF (DInDel.cpp:3085-3113: start = 0;
@@ -322,6 +327,55 @@ typedef struct dindel_cigar_out {
     uint32_t *ops;          /* [n_reads * cigar_cap] */
 } dindel_cigar_out;
 int dindel_b200_cigars(dindel_ctx *ctx, const dindel_cigar_in *in, dindel_cigar_out *out);
+
+/* ---- K6: read statistics of a called site over the RESIDENT K1 records ---------------------------
+ * Replaces the per-read aggregation loops that follow the arg-max in DetInDel::diploidGLF and in
+ * DetInDel::estimateHaplotypeFrequenciesBayesEM: everything they read of liks[h][r] is a field of the 64-byte pair
+ * record (hapIndelCovered / hapSNPCovered[pos] are AlignedVariant::isCovered(padCover, firstBase, lastBase),
+ * ObservationModelFB.cpp:1465-1472 = firstBase + pad <= startRead && lastBase - pad >= endRead, Variant.hpp:125-128),
+ * everything they read of reads[r] is resident too (mapping-quality phred, DINDEL_READ_* flags).
+ * One JOB = one (window, site) with its CANDIDATE haplotypes; per candidate the host gives the window-relative
+ * haplotype index, startRead / endRead of the haplotype's variant at the site and DINDEL_CAND_PRESENT when the
+ * coverage map the reference consults has the site at all (`find(pos) != end()`), DINDEL_CAND_HAS_VAR = hapHasVar.
+ * With mq(r) = -10*log10(1 - mapQual(r)) (host libm, by phred byte) and reads taken in window order, restricted to
+ * read_group[r] == job_group when job_group >= 0:
+ *   DINDEL_STATS_SITE (DInDel.cpp:3396-3404, :3504-3554; candidates = the site's arg-max pair hx1, hx2):
+ *     numUnmappedRealigned = #unmapped reads with !offHap on hx1 or hx2; allmsq += mq^2; numOffBoth = #reads offHap on
+ *     both; h = hx1 if ll[hx1][r] >= ll[hx2][r] else hx2; numIndels / nBQT / nmmBQT / mLogBQ summed over the chosen
+ *     records, nMMLeft / nMMRight = #reads whose chosen record has >= 2; when the chosen record covers the site:
+ *     nf or nr (Read::onReverseStrand) + 1, msq += mq^2, n + 1.
+ *   DINDEL_STATS_MAP (:3126-3132, :3148-3170; candidates = max_indel_pair[0..1], PRESENT = it is one of the m
+ *     haplotypes looped over and has an indel at the site): numUnmappedRealigned as above; for every PRESENT candidate
+ *     in turn, for every read covering the site on it: nf or nr + 1, msq += mq^2, n + 1.
+ *   DINDEL_STATS_POOL (:2697-2742; candidates = all haplotypes of the window in order): per read ml = max ll,
+ *     the haplotypes with ll >= ml - 1e-7 that are PRESENT, cover the site and HAS_VAR set the read's strand flag;
+ *     nf / nr = #reads with a forward / reverse flag; msq += mq^2 and n + 1 for every read.
+ * The FP64 sums run in the reference's order (read order; MAP: candidate-major), so msq / allmsq / mLogBQ are
+ * bit-identical to the CPU's; the caller applies sqrt(msq / n) etc.  n_reads = |readidx|.
+ * Needs a resident, computed batch (the job windows inside the resident range). */
+#define DINDEL_STATS_SITE 0
+#define DINDEL_STATS_MAP 1
+#define DINDEL_STATS_POOL 2
+#define DINDEL_CAND_PRESENT 1u
+#define DINDEL_CAND_HAS_VAR 2u
+typedef struct dindel_stats_in {
+    int32_t n_jobs;
+    int32_t reserved;
+    const int32_t *job_window;  /* [n_jobs] */
+    const int32_t *job_mode;    /* [n_jobs] DINDEL_STATS_* */
+    const int32_t *job_group;   /* [n_jobs] -1 = every read of the window */
+    const int64_t *job_cand;    /* [n_jobs+1] job -> its candidates (SITE / MAP: exactly 2) */
+    const int32_t *cand_hap;    /* haplotype index inside the window */
+    const int32_t *cand_start;  /* AlignedVariant::startRead of the haplotype's variant at the site */
+    const int32_t *cand_end;    /* AlignedVariant::endRead */
+    const uint8_t *cand_flags;  /* DINDEL_CAND_* */
+    const int32_t *read_group;  /* [n_reads] of the batch (Read::poolID); may be NULL when every job_group is -1 */
+} dindel_stats_in;
+typedef struct dindel_read_stats {
+    double msq, allmsq, mLogBQ;   /* plain sums (no sqrt, no division) */
+    int32_t n, nf, nr, numOffBoth, numIndels, nBQT, nmmBQT, nMMLeft, nMMRight, numUnmappedRealigned, n_reads, reserved;
+} dindel_read_stats;
+int dindel_b200_read_stats(dindel_ctx *ctx, const dindel_stats_in *in, dindel_read_stats *out /* [n_jobs] */);
 
 /* ---- one pass over a batch of ANY size: K1 and, while the results are still in HBM, K4 / K2 / K3 --------------
  * The batch is streamed through the device in RANGES of windows that fit a fixed memory budget

@@ -694,3 +694,102 @@ int ora_get_cigar(int R, const int32_t *hpos, int H, const int32_t *hml, int ref
 #undef NPOS
     return n;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * K6: the per-read aggregation loops behind a called site.  recs is r-major [nr*nh] like rl; mapQual is
+ * Read::mapQual; cand_* describe, per candidate haplotype, what the reference's map lookups find at the site
+ * (present = `find(pos) != end()` of the coverage map it consults, start / end = startRead / endRead of that
+ * haplotype's variant: hapIndelCovered / hapSNPCovered[pos] = isCovered(padCover, firstBase, lastBase),
+ * ObservationModelFB.cpp:1465-1472, Variant.hpp:125-128).  Sums are left as sums (the caller's sqrt / divide
+ * are at DInDel.cpp:2744, :3173, :3557, :3561, :3626).
+ *   mode 0  DInDel.cpp:3396-3404 + :3504-3554 (candidates = hx1, hx2)
+ *   mode 1  DInDel.cpp:3126-3132 + :3148-3170 (candidates = max_indel_pair; present = looped over and isIndel)
+ *   mode 2  DInDel.cpp:2697-2742 (candidates = every haplotype; has_var = hapHasVar[h*nv+idx])
+ * ------------------------------------------------------------------------------------------ */
+static int covered(const ora_pair_out *p, int pad, int start, int end)
+{
+    return (p->firstBase + pad <= start && p->lastBase - pad >= end) ? 1 : 0;
+}
+
+void ora_read_stats(int mode, int nh, int nr, const ora_pair_out *recs, const double *mapQual, const uint8_t *reverse,
+                    const uint8_t *unmapped, const int32_t *read_group, int group, int ncand, const int32_t *cand_hap,
+                    const int32_t *cand_start, const int32_t *cand_end, const uint8_t *cand_flags, int pad,
+                    ora_read_stats_t *o)
+{
+    int r, i, h;
+    memset(o, 0, sizeof(*o));
+#define IN_GROUP(r) (!(group >= 0 && read_group) || read_group[r] == group)
+#define REC(h, r) (&recs[(size_t)(r) * nh + (h)])
+    if (mode == 0) {
+        const int hx1 = cand_hap[0], hx2 = cand_hap[1];
+        for (r = 0; r < nr; r++)                                                        /* :3396-3404 */
+            if (unmapped[r] && (!REC(hx1, r)->offHap || !REC(hx2, r)->offHap)) o->numUnmappedRealigned++;
+        for (r = 0; r < nr; r++) {                                                      /* :3504 */
+            double mq;
+            int k, nrt = 0, nft = 0;
+            const ora_pair_out *p;
+            if (!IN_GROUP(r)) continue;
+            o->n_reads++;
+            mq = -10 * log10(1.0 - mapQual[r]);
+            o->allmsq += (mq * mq);
+            if (REC(hx1, r)->offHap && REC(hx2, r)->offHap) o->numOffBoth++;
+            k = (REC(hx1, r)->ll >= REC(hx2, r)->ll) ? 0 : 1;                          /* :3514-3520 */
+            p = REC(cand_hap[k], r);
+            o->numIndels += p->numIndels;
+            o->nBQT += p->nBQT;
+            o->nmmBQT += p->nmmBQT;
+            o->mLogBQ += p->mLogBQ;
+            if (p->nMMLeft >= 2) o->nMMLeft++;
+            if (p->nMMRight >= 2) o->nMMRight++;
+            if ((cand_flags[k] & 1) && covered(p, pad, cand_start[k], cand_end[k])) {   /* :3537-3550 */
+                double mq2 = -10 * log10(1.0 - mapQual[r]);
+                if (reverse[r]) nrt = 1; else nft = 1;
+                o->msq += mq2 * mq2;
+                o->n++;
+            }
+            if (nft) o->nf++;
+            if (nrt) o->nr++;
+        }
+    } else if (mode == 1) {
+        for (r = 0; r < nr; r++)                                                        /* :3126-3132 */
+            if (ncand >= 2 && unmapped[r] && (!REC(cand_hap[0], r)->offHap || !REC(cand_hap[1], r)->offHap))
+                o->numUnmappedRealigned++;
+        for (r = 0; r < nr; r++) if (IN_GROUP(r)) o->n_reads++;
+        for (i = 0; i < ncand && i < 2; i++) {                                          /* :3152 */
+            if (!(cand_flags[i] & 1)) continue;                                         /* :3155 */
+            h = cand_hap[i];
+            for (r = 0; r < nr; r++) {
+                if (!IN_GROUP(r)) continue;
+                if (covered(REC(h, r), pad, cand_start[i], cand_end[i])) {              /* :3160-3166 */
+                    double mq = -10 * log10(1.0 - mapQual[r]);
+                    if (reverse[r]) o->nr++; else o->nf++;
+                    o->msq += mq * mq;
+                    o->n++;
+                }
+            }
+        }
+    } else {
+        for (r = 0; r < nr; r++) {                                                      /* :2697 */
+            double ml = -HUGE_VAL, mq;
+            int nrt = 0, nft = 0;
+            if (!IN_GROUP(r)) continue;
+            o->n_reads++;
+            for (i = 0; i < ncand; i++)                                                 /* :2702-2707 */
+                if (REC(cand_hap[i], r)->ll >= ml) ml = REC(cand_hap[i], r)->ll;
+            for (i = 0; i < ncand; i++) {                                               /* :2708-2734 */
+                const ora_pair_out *p = REC(cand_hap[i], r);
+                if (!(p->ll >= ml - 1e-7)) continue;
+                if ((cand_flags[i] & 1) && covered(p, pad, cand_start[i], cand_end[i]) && (cand_flags[i] & 2)) {
+                    if (reverse[r]) nrt = 1; else nft = 1;
+                }
+            }
+            mq = -10 * log10(1.0 - mapQual[r]);                                         /* :2736-2738 */
+            o->msq += mq * mq;
+            o->n++;
+            if (nft) o->nf++;
+            if (nrt) o->nr++;
+        }
+    }
+#undef IN_GROUP
+#undef REC
+}

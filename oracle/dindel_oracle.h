@@ -52,6 +52,15 @@ void ora_filter_haplotypes(int nh, int nr, const char *hap_seq, const int32_t *h
 int ora_choose_hap(int mode, int nh, const double *ll, const int32_t *n_indels, int h1, int h2);
 int ora_get_cigar(int R, const int32_t *hpos, int H, const int32_t *hml, int refSeqStart, int32_t *refPos,
                   int32_t *ops, int cap);
+/* K6: read statistics of a called site (DInDel.cpp:3126-3170, :3396-3404, :3504-3554, :2697-2742) */
+typedef struct ora_read_stats_t {
+    double msq, allmsq, mLogBQ;
+    int32_t n, nf, nr, numOffBoth, numIndels, nBQT, nmmBQT, nMMLeft, nMMRight, numUnmappedRealigned, n_reads, reserved;
+} ora_read_stats_t;
+void ora_read_stats(int mode, int nh, int nr, const ora_pair_out *recs, const double *mapQual, const uint8_t *reverse,
+                    const uint8_t *unmapped, const int32_t *read_group, int group, int ncand, const int32_t *cand_hap,
+                    const int32_t *cand_start, const int32_t *cand_end, const uint8_t *cand_flags, int pad,
+                    ora_read_stats_t *o);
 double ora_addlogs(double a, double b);
 double ora_digamma(double x);
 

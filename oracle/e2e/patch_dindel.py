@@ -311,13 +311,50 @@ DUMP_INF = [
     ("\t\t\t\t\tlik[genotype]=addLogs(lik[genotype],ll);\n", "before", 1, 0,
      DF('fprintf(df, "PG %d %d %d %d %.17g %.17g\\n", idx, int(b), int(h1), int(h2), pr, ll);')),
 ]
+# --dump, fourth hook: the per-read aggregation loops behind a called site (DInDel.cpp:3126-3170 "dip.map" sites,
+# :3396-3404 + :3504-3554 per variant position, :2697-2742 pooled per variant and pool member) append what they read
+# (per read: mapQual / strand / unmapped / poolID; per (haplotype, read): the MLAlignment fields; per candidate
+# haplotype: whether the coverage map has the site and startRead / endRead of its variant) and what they computed to
+# the same file: golden vectors for K6 (tests/golden/make_stats_golden.py -> tests/golden/stats_golden.json.gz).
+PEEK = ('struct dindel_b200_peek : AlignedVariant { static int end_read(const AlignedVariant & a) '
+        '{ int AlignedVariant::*p = &dindel_b200_peek::endRead; return a.*p; } };\n')
+RDLK = ('for (size_t r=0;r<reads.size();r++) fprintf(df, "RD %d %.17g %d %d %d\\n", int(r), reads[r].mapQual, int(reads[r].onReverseStrand), int(reads[r].isUnmapped()), reads[r].poolID); '
+        'for (size_t h=0;h<haps.size();h++) for (size_t r=0;r<reads.size();r++) { const MLAlignment & m_ = liks[h][r]; '
+        'fprintf(df, "LK %d %d %.17g %d %d %d %d %.17g %d %d %d %d\\n", int(h), int(r), m_.ll, int(m_.offHap), int(m_.indels.size()), m_.nBQT, m_.nmmBQT, m_.mLogBQ, m_.nMMLeft, m_.nMMRight, m_.firstBase, m_.lastBase); }')
+CAND = ('{ int pres_=0, st_=0, en_=0; map<int,AlignedVariant>::const_iterator f_; '
+        'if (KIND==1) { f_=haps[H_].indels.find(POS_); if (f_!=haps[H_].indels.end()) { pres_=1; st_=f_->second.getStartRead(); en_=dindel_b200_peek::end_read(f_->second); } } '
+        'else if (KIND==2) { f_=haps[H_].snps.find(POS_); if (f_!=haps[H_].snps.end()) { pres_=1; st_=f_->second.getStartRead(); en_=dindel_b200_peek::end_read(f_->second); } } '
+        'fprintf(df, " %d %d %d %d %d", int(H_), pres_, st_, en_, int(HV_)); }')
+def cand(h, pos, kind, hv="0"):
+    return CAND.replace("H_", h).replace("POS_", pos).replace("KIND", kind).replace("HV_", hv)
+SITE_KIND = "(haps[H_].indels.find(pos)==haps[H_].indels.end() ? -1 : (haps[H_].indels.find(pos)->second.isIndel() ? 1 : (haps[H_].indels.find(pos)->second.isSNP() ? 2 : 0)))"
+DUMP_STATS = [
+    ("\t// get all variants\n", "before", 1, 0, DF(RDLK)),
+    ("\tcout << \"ALWAYS CALLING ::filterHaplotypes\" << endl;\n", "before", 1, 0, DF(RDLK)),
+    ("\n\t\t\tif (n!=0) msq=sqrt(msq/double(n)); else msq=0.0;\n", "before", 1, 0,
+     DF('fprintf(df, "RSM %d %d", it->first, m); for (int i_=0;i_<2;i_++) { int h_=max_indel_pair[i_]; It q_=haps[h_].indels.find(it->first); '
+        'int g_=(i_<m && q_!=haps[h_].indels.end() && q_->second.isIndel())?1:0; '
+        'fprintf(df, " %d %d %d %d 0", h_, g_, g_?q_->second.getStartRead():0, g_?dindel_b200_peek::end_read(q_->second):0); } '
+        'fprintf(df, " O %d %d %d %.17g %d\\n", numf, numr, n, msq, numUnmappedRealigned);')),
+    ("\n\t\tif (n!=0) msq=sqrt(msq/double(n)); else msq=0.0;\n", "before", 1, 0,
+     DF('fprintf(df, "RSS %d", pos); for (int i_=0;i_<2;i_++) { int h_=i_?hx2:hx1; ' + cand("h_", "pos", SITE_KIND.replace("H_", "h_")) + ' } '
+        'fprintf(df, " O %d %d %d %.17g %.17g %d %d %d %d %.17g %d %d %d\\n", nf, nr, n, msq, allmsq, numOffBoth, numMappedIndels, nBQT, nmmBQT, mLogBQ, nMMLeft, nMMRight, numUnmappedRealigned);')),
+    ("\n\t\t\t\tif (n!=0) msq=sqrt(msq/double(n)); else msq=0.0;\n", "before", 1, 0,
+     DF('fprintf(df, "RSP %d %d %d", idx, int(b), pos); for (size_t h_=0;h_<nh;h_++) ' + cand("h_", "pos", "(pav.second.isIndel()?1:(pav.second.isSNP()?2:0))", "hapHasVar[h_*nv+idx]") +
+        ' fprintf(df, " O %d %d %d %.17g\\n", nf, nr, n, msq);')),
+]
 if dump:
-    for anchor, where, count, which, code in DUMP_INF:
+    assert text.count(inc) == 1
+    text = text.replace(inc, inc + PEEK.replace("\\n", "\n"))
+    for anchor, where, count, which, code in DUMP_INF + DUMP_STATS:
         assert text.count(anchor) == count, (anchor, text.count(anchor))
         i = -1
         for _ in range(which + 1):
             i = text.index(anchor, i + 1)
-        text = text[:i] + (code + anchor if where == "before" else anchor + code) + text[i + len(anchor):]
+        if where == "before" and anchor.startswith("\n"):   # on a line of its own (the line before may end in a // comment)
+            text = text[:i + 1] + code + text[i + 1:]
+        else:
+            text = text[:i] + (code + anchor if where == "before" else anchor + code) + text[i + len(anchor):]
     anchor = "\t\tvarCoverage[pav]=VariantCoverage(int(rf.size()), int(rr.size()));\n\t}\n"
     assert text.count(anchor) == 1
     text = text.replace(anchor, anchor + DUMP)

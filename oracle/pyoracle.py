@@ -29,6 +29,13 @@ ORA_DTYPE = np.dtype([
 assert ORA_DTYPE.itemsize == 80
 
 
+STATS_DTYPE = np.dtype([
+    ("msq", "<f8"), ("allmsq", "<f8"), ("mLogBQ", "<f8"), ("n", "<i4"), ("nf", "<i4"), ("nr", "<i4"), ("numOffBoth", "<i4"),
+    ("numIndels", "<i4"), ("nBQT", "<i4"), ("nmmBQT", "<i4"), ("nMMLeft", "<i4"), ("nMMRight", "<i4"),
+    ("numUnmappedRealigned", "<i4"), ("n_reads", "<i4"), ("reserved", "<i4")])
+assert STATS_DTYPE.itemsize == 72
+
+
 def build(which="port"):
     subprocess.check_call(["make", "-s", "-C", HERE, "oracle" if which == "port" else "ref"])
 
@@ -152,6 +159,25 @@ class Oracle:
         vp = lambda a: a.ctypes.data_as(C.c_void_p)
         it = self.lib.ora_bayes_em(vp(rl), nr, nh, vp(comp), C.c_double(a0), C.c_double(tol), C.byref(ll), vp(pi), vp(fr))
         return ll.value, it, pi, fr
+
+    # ---- K6: read statistics of a called site (port only) ----
+    def read_stats(self, mode, recs, nh, map_qual, reverse, unmapped, cands, pad, read_group=None, group=-1):
+        """recs: ORA_DTYPE records r-major [nr*nh]; cands: list of (hap, startRead, endRead, flags)."""
+        recs = np.ascontiguousarray(recs, dtype=ORA_DTYPE)
+        nr = len(recs) // nh
+        mqv = np.ascontiguousarray(map_qual, dtype=np.float64)
+        rev = np.ascontiguousarray(reverse, dtype=np.uint8)
+        unm = np.ascontiguousarray(unmapped, dtype=np.uint8)
+        rg = None if read_group is None else np.ascontiguousarray(read_group, dtype=np.int32)
+        ch = np.array([c[0] for c in cands], dtype=np.int32)
+        cs = np.array([c[1] for c in cands], dtype=np.int32)
+        ce = np.array([c[2] for c in cands], dtype=np.int32)
+        cf = np.array([c[3] for c in cands], dtype=np.uint8)
+        out = np.zeros(1, dtype=STATS_DTYPE)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        self.lib.ora_read_stats(int(mode), int(nh), int(nr), vp(recs), vp(mqv), vp(rev), vp(unm), vp(rg) if rg is not None else None,
+                                int(group), len(cands), vp(ch), vp(cs), vp(ce), vp(cf), int(pad), vp(out))
+        return out[0]
 
     def addlogs(self, a, b):
         self.lib.ora_addlogs.restype = C.c_double
