@@ -589,6 +589,21 @@ def main():
         infer = {"k5_cigars_ms": k5_ms, "k5_kernel_ms": k5_kernel_ms, "k5_max_ops": k5_max,
                  "k5_reads_per_s": batch.n_reads / (k5_ms * 1e-3), "k5_frac_of_k1_step": k5_ms / rec["ms_per_step"],
                  "k5_ops_checksum": int(k5n.sum())}
+        # ---- K6: the read statistics of three called sites per window (one dip.map site on the first / last haplotype,
+        # two variant positions on haplotype pairs) for the whole resident batch in ONE call ----
+        nwb = batch.n_windows
+        H0 = np.diff(batch.hap_off)[batch.win_hap[:-1]].astype(np.int32)       # length of each window's first haplotype
+        jw = np.repeat(np.arange(nwb, dtype=np.int32), 3)
+        jm = np.tile(np.array([engine.STATS_MAP, engine.STATS_SITE, engine.STATS_SITE], np.int32), nwb)
+        jc = np.arange(3 * nwb + 1, dtype=np.int64) * 2
+        last = (nh_w - 1).astype(np.int32)
+        ch = np.stack([np.zeros(nwb, np.int32), last, np.zeros(nwb, np.int32), np.minimum(1, last), np.minimum(1, last), last], 1).ravel()
+        cs = np.repeat(np.stack([H0 // 2, H0 // 3, 2 * H0 // 3], 1).ravel(), 2).astype(np.int32)
+        k6 = eng.read_stats_flat(jw, jm, np.full(3 * nwb, -1, np.int32), jc, ch, cs, cs + 2, np.ones(6 * nwb, np.uint8))   # warm-up
+        k6 = eng.read_stats_flat(jw, jm, np.full(3 * nwb, -1, np.int32), jc, ch, cs, cs + 2, np.ones(6 * nwb, np.uint8))
+        infer.update({"k6_read_stats_ms": eng.last_call_ms, "k6_kernel_ms": eng.last_kernel_ms, "k6_jobs": int(3 * nwb),
+                      "k6_jobs_per_s": 3 * nwb / (eng.last_call_ms * 1e-3), "k6_frac_of_k1_step": eng.last_call_ms / rec["ms_per_step"],
+                      "k6_covered_checksum": int(k6["n"].sum()), "k6_reads_checksum": int(k6["n_reads"].sum())})
     parity = None
     if rank == 0 and not args.no_cpu_baseline:
         parity = parity_gate(batch, params, hj.pairs, hj.win_pair, 32 if args.cfg == 2 else 8)

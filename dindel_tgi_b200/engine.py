@@ -477,7 +477,6 @@ class Engine:
     def read_stats(self, jobs, read_group=None):
         """K6 (dindel_b200_read_stats) over the resident batch.  jobs: list of (window, mode, group, cands) with
         cands = [(hap, startRead, endRead, flags)]; returns a STATS_DTYPE array, one row per job."""
-        nj = len(jobs)
         jw = np.array([j[0] for j in jobs], dtype=np.int32)
         jm = np.array([j[1] for j in jobs], dtype=np.int32)
         jg = np.array([j[2] for j in jobs], dtype=np.int32)
@@ -487,6 +486,15 @@ class Engine:
         cs = np.array([c[1] for c in flat], dtype=np.int32)
         ce = np.array([c[2] for c in flat], dtype=np.int32)
         cf = np.array([c[3] for c in flat], dtype=np.uint8)
+        return self.read_stats_flat(jw, jm, jg, jc, ch, cs, ce, cf, read_group)
+
+    def read_stats_flat(self, jw, jm, jg, jc, ch, cs, ce, cf, read_group=None):
+        """The same on the C ABI's own flat arrays (dindel_stats_in)."""
+        nj = len(jw)
+        jw, jm, jg = (np.ascontiguousarray(x, dtype=np.int32) for x in (jw, jm, jg))
+        jc = np.ascontiguousarray(jc, dtype=np.int64)
+        ch, cs, ce = (np.ascontiguousarray(x, dtype=np.int32) for x in (ch, cs, ce))
+        cf = np.ascontiguousarray(cf, dtype=np.uint8)
         rg = None if read_group is None else np.ascontiguousarray(read_group, dtype=np.int32)
         a = _StatsIn()
         a.n_jobs = nj

@@ -97,12 +97,122 @@ inline int run_cigars(dindel_ctx *ctx, dindel_cigar_in &in, size_t nr, std::vect
 }
 } // namespace detail
 
+// ---------------------------------------------------------------------------------------------------------------
+// K6 (dindel_b200_read_stats): the per-read aggregation loops behind a called site (DInDel.cpp:3126-3170, :3396-3404,
+// :3504-3554, :2697-2742) on the GPU, over the records K1 left there.  Bit-identical to the loops (integer counts and
+// read-order FP64 sums), so no guard band is involved.  A JOB is one execution of one of the loops; its candidates
+// carry what the loop's map lookups would find at the site for each haplotype it looks at.
+// ---------------------------------------------------------------------------------------------------------------
+struct StatsCand {
+    int32_t hap, start, end; uint8_t flags;
+    StatsCand() : hap(0), start(0), end(0), flags(0) {}
+    StatsCand(int h, int s, int e, unsigned f) : hap(h), start(s), end(e), flags((uint8_t)f) {}
+};
+struct StatsJob {
+    int mode, group; std::vector<StatsCand> cands;
+    StatsJob(int m, int g) : mode(m), group(g) {}
+};
+// AlignedVariant::endRead is protected and has no getter (Variant.hpp:148, :170): read through a pointer to member
+// formed in a derived class (the one access the language grants), not through a cast.
+template <class AV> struct VariantPeek : AV {
+    static int endOf(const AV &a) { int AV::*p = &VariantPeek::endRead; return a.*p; }
+};
+template <class HapT> struct HapT_variant; // mapped type of HapT::indels / snps (defined below)
+// what `m.find(pos)` + isCovered() of the reference reads: present, startRead, endRead of the map's variant at pos
+template <class Map>
+inline StatsCand statsLookup(const Map &m, int pos, int hap, unsigned extraFlags)
+{
+    typename Map::const_iterator it = m.find(pos);
+    if (it == m.end()) return StatsCand(hap, 0, 0, extraFlags);
+    return StatsCand(hap, it->second.getStartRead(), VariantPeek<typename Map::mapped_type>::endOf(it->second), DINDEL_CAND_PRESENT | extraFlags);
+}
+// DInDel.cpp:3536-3543: the map consulted for haplotype h at a variant position depends on what h carries there
+template <class HapT>
+inline StatsCand siteCand(const HapT &hap, int h, int pos)
+{
+    typename std::map<int, typename HapT_variant<HapT>::type>::const_iterator hit = hap.indels.find(pos);
+    if (hit == hap.indels.end()) return StatsCand(h, 0, 0, 0);            // (the reference dereferences end() here)
+    if (hit->second.isIndel()) return statsLookup(hap.indels, pos, h, 0); // hapIndelCovered[pos], ObservationModelFB.cpp:1465-1468
+    if (hit->second.isSNP()) return statsLookup(hap.snps, pos, h, 0);     // hapSNPCovered[pos], :1469-1472
+    return StatsCand(h, 0, 0, 0);
+}
+// DInDel.cpp:3152-3160: haplotype h is looped over (i < m) and has an indel at the site
+template <class HapT>
+inline StatsCand mapCand(const HapT &hap, int h, int pos, bool looped)
+{
+    typename std::map<int, typename HapT_variant<HapT>::type>::const_iterator it = hap.indels.find(pos);
+    if (!looped || it == hap.indels.end() || !it->second.isIndel()) return StatsCand(h, 0, 0, 0);
+    return statsLookup(hap.indels, pos, h, 0);
+}
+// DInDel.cpp:2716-2724: the variant's own kind picks the map; hapHasVar gates the strand flags (:2726)
+template <class HapT, class AV>
+inline StatsCand poolCand(const HapT &hap, int h, int pos, const AV &var, bool hasVar)
+{
+    const unsigned f = hasVar ? DINDEL_CAND_HAS_VAR : 0u;
+    if (var.isIndel()) return statsLookup(hap.indels, pos, h, f);
+    if (var.isSNP()) return statsLookup(hap.snps, pos, h, f);
+    return StatsCand(h, 0, 0, f);
+}
+// $DINDEL_B200_DEVICE_STATS: 0 = the reference's host loops always, 1 = K6 always, unset = K6 when the loops would
+// touch at least DINDEL_B200_STATS_MIN_WORK (read, candidate) records (a K6 call costs ~50 us: a loss on 50-read
+// diploid windows whose records are on the host anyway, a gain on deep pooled windows)
+#ifndef DINDEL_B200_STATS_MIN_WORK
+#define DINDEL_B200_STATS_MIN_WORK 8192
+#endif
+inline int statsPolicy()
+{
+    static int p = -2;
+    if (p == -2) { const char *e = getenv("DINDEL_B200_DEVICE_STATS"); p = e ? atoi(e) : -1; }
+    return p;
+}
+namespace detail {
+inline void runStats(dindel_ctx *ctx, int w, const std::vector<StatsJob> &jobs, const int32_t *readGroup, std::vector<dindel_read_stats> &out)
+{
+    const size_t nj = jobs.size();
+    std::vector<int32_t> jw(nj, (int32_t)w), jm(nj), jg(nj), ch, cs, ce;
+    std::vector<int64_t> jc(nj + 1, 0);
+    std::vector<uint8_t> cf;
+    for (size_t j = 0; j < nj; j++) {
+        jm[j] = jobs[j].mode; jg[j] = readGroup ? jobs[j].group : -1;
+        for (size_t c = 0; c < jobs[j].cands.size(); c++) {
+            const StatsCand &k = jobs[j].cands[c];
+            ch.push_back(k.hap); cs.push_back(k.start); ce.push_back(k.end); cf.push_back(k.flags);
+        }
+        jc[j + 1] = (int64_t)ch.size();
+    }
+    static const int32_t z32 = 0; static const uint8_t z8 = 0;
+    dindel_stats_in in;
+    in.n_jobs = (int32_t)nj; in.reserved = 0; in.job_window = &jw[0]; in.job_mode = &jm[0]; in.job_group = &jg[0]; in.job_cand = &jc[0];
+    in.cand_hap = ch.empty() ? &z32 : &ch[0]; in.cand_start = cs.empty() ? &z32 : &cs[0]; in.cand_end = ce.empty() ? &z32 : &ce[0];
+    in.cand_flags = cf.empty() ? &z8 : &cf[0]; in.read_group = readGroup;
+    out.resize(nj);
+    int rc = dindel_b200_read_stats(ctx, &in, &out[0]);
+    if (rc != DINDEL_OK) throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx) + ")";
+}
+} // namespace detail
+// Provider: Engine (the resident window), WindowBatch through the batched driver's replay slot (one window of the
+// flushed batch).  false = the caller's own loops run.
+template <class Provider>
+inline bool deviceStats(Provider &p, const std::vector<StatsJob> &jobs, size_t nReads, std::vector<dindel_read_stats> &out)
+{
+    if (jobs.empty() || !p.statsResident()) return false;
+    const int pol = statsPolicy();
+    if (pol == 0) return false;
+    if (pol < 0) {
+        size_t work = 0;
+        for (size_t j = 0; j < jobs.size(); j++) work += nReads * jobs[j].cands.size();
+        if (work < (size_t)DINDEL_B200_STATS_MIN_WORK) return false;
+    }
+    p.windowStats(jobs, out);
+    return true;
+}
+
 // RAII owner of one dindel_ctx (one device).  Construct from anything with the fields of
 // ObservationModelParameters (ObservationModel.hpp:28-99) that the path reads.
 class Engine {
 public:
     template <class ObsParams>
-    explicit Engine(const ObsParams &op, int device = 0) : ctx_(0), last_nh_(0), last_nr_(0), t_cl_(0.0), t_fh_(0.0), n_cl_(0), mapUnmapped_(false), libOff_(1, 0), wantSums_(false), nPools_(0), multi_(0)
+    explicit Engine(const ObsParams &op, int device = 0) : nStatsCalls(0), nStatsJobs(0), ctx_(0), last_nh_(0), last_nr_(0), t_cl_(0.0), t_fh_(0.0), n_cl_(0), mapUnmapped_(false), libOff_(1, 0), wantSums_(false), nPools_(0), multi_(0)
     {
         dindel_b200_default_params(&p_);
         p_.pError = op.pError; p_.pMut = op.pMut; p_.mapQualThreshold = op.mapQualThreshold;
@@ -157,6 +267,14 @@ public:
         int rc = dindel_b200_bayes_em(ctx_, &in, &out);
         if (rc != DINDEL_OK) throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(ctx_) + ")";
     }
+    // K6 on the resident window (the one computeLikelihoods was last called with)
+    bool statsResident() const { return last_nh_ > 0 && last_nr_ > 0; }
+    void windowStats(const std::vector<StatsJob> &jobs, std::vector<dindel_read_stats> &out)
+    {
+        detail::runStats(ctx_, 0, jobs, rgroup_.empty() ? 0 : &rgroup_[0], out);
+        nStatsCalls++; nStatsJobs += (long)jobs.size();
+    }
+    long nStatsCalls, nStatsJobs;
     bool mapUnmappedReads() const { return mapUnmapped_; }
     void setMapUnmappedReads(bool v) { mapUnmapped_ = v; } // the reference flips it after construction (DInDel.cpp:4270)
 
@@ -227,6 +345,7 @@ private:
     int nPools_;
     std::vector<double> sums_;
     std::vector<int> poolSize_;
+    std::vector<int32_t> rgroup_;  // Read::poolID of the resident window's reads
     dindel_multi *multi_;
 };
 
@@ -550,16 +669,16 @@ void Engine::computeLikelihoods(const std::vector<HapT> &haps, const std::vector
     dindel_job job;
     job.in = &in; job.out = &out; job.cover = 0; job.cover_out = 0; job.pair_sums = 0; job.win_sum_off = 0;
     job.n_groups = 0; job.reserved = 0; job.read_group = 0; job.em = 0; job.em_out = 0;
-    std::vector<int32_t> rgroup;
+    std::vector<int32_t> &rgroup = rgroup_;
+    rgroup.resize(nr);
+    for (size_t r = 0; r < nr; r++) rgroup[r] = RT::pool(reads[r]);
     if (wantSums_) {
         const int G = nPools_ > 0 ? nPools_ : 1;
         sums_.assign(nh * (nh + 1) / 2 * (size_t)G, 0.0);
         job.pair_sums = &sums_[0];
         if (nPools_ > 0) {
-            rgroup.resize(nr);
             poolSize_.assign((size_t)nPools_, 0);
             for (size_t r = 0; r < nr; r++) {
-                rgroup[r] = RT::pool(reads[r]);
                 if (rgroup[r] >= 0 && rgroup[r] < nPools_) poolSize_[rgroup[r]]++;
             }
             job.n_groups = nPools_; job.read_group = &rgroup[0];
@@ -606,7 +725,7 @@ public:
     // scalar MLAlignment fields and the hapIndelCovered / hapSNPCovered maps but leaves hpos / align / indels / snps
     // empty (nothing in the calling pipeline reads them once filterResult() replaces filterHaplotypes).
     explicit WindowBatch(Engine &e, int maxMismatch = 2, bool doFilter = false, bool fullAlignments = true)
-        : eng_(e), maxMismatch_(maxMismatch), doFilter_(doFilter), flushed_(false), full_(fullAlignments) { clear(); }
+        : eng_(e), maxMismatch_(maxMismatch), doFilter_(doFilter), flushed_(false), full_(fullAlignments), resident_(false) { clear(); }
     void clear()
     {
         hap_start_.clear(); win_hap_.assign(1, 0); win_read_.assign(1, 0); hap_off_.assign(1, 0); read_off_.assign(1, 0);
@@ -691,6 +810,14 @@ public:
         int rc = dindel_b200_bayes_em(eng_.ctx(), &in, &out);
         if (rc != DINDEL_OK) throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(eng_.ctx()) + ")";
     }
+    // K6 for window w of the flushed batch, while it is still resident on the engine's own device (not when the batch
+    // was sharded over several GPUs or streamed in more than one range)
+    bool statsResident() const { return flushed_ && resident_; }
+    void windowStats(int w, const std::vector<StatsJob> &jobs, std::vector<dindel_read_stats> &out) const
+    {
+        detail::runStats(eng_.ctx(), w, jobs, pool_.empty() ? 0 : &pool_[0], out);
+        eng_.nStatsCalls++; eng_.nStatsJobs += (long)jobs.size(); // callers serialise GPU calls (the driver's gpuLock)
+    }
     // Realigned-read CIGARs of EVERY window of the flushed batch in one K5 call (see Engine::realignedCigars).
     // allHaps[w] = the haplotypes window w was added with (their ml.hpos / countIndels() are read here: the
     // haplotype-to-reference alignment is not part of add()); refSeqPos[w]; h1[w] / h2[w] = the MAP pair of window w
@@ -701,7 +828,7 @@ public:
 private:
     Engine &eng_;
     int maxMismatch_;
-    bool doFilter_, flushed_, full_, anyIns_;
+    bool doFilter_, flushed_, full_, anyIns_, resident_;
     size_t maxR_;
     std::vector<uint8_t> insMode_;
     std::vector<int32_t> insAnchor_, insLib_;
@@ -726,6 +853,7 @@ template <class HapT, class ReadT>
 void WindowBatch<HapT, ReadT>::flush()
 {
     const size_t nw = size();
+    resident_ = false;
     if (nw == 0) { flushed_ = true; return; }
     static const uint8_t none8 = 0;
     static const uint32_t none32 = 0;
@@ -788,6 +916,8 @@ void WindowBatch<HapT, ReadT>::flush()
         rc = dindel_b200_process(eng_.ctx(), &job);
         if (rc != DINDEL_OK)
             throw std::string("dindel_b200: ") + dindel_b200_strerror(rc) + " (" + dindel_b200_last_error(eng_.ctx()) + ")";
+        dindel_timing t;
+        resident_ = dindel_b200_get_timing(eng_.ctx(), &t) == DINDEL_OK && t.n_ranges == 1;
     }
     flushed_ = true;
 }

@@ -52,6 +52,15 @@ struct Replay {
         catch (...) { pthread_mutex_unlock(gpuLock); throw; }
         pthread_mutex_unlock(gpuLock);
     }
+    // K6 for this window (dindel_b200::deviceStats' provider)
+    bool statsResident() const { return w >= 0 && batch && batch->statsResident(); }
+    void windowStats(const std::vector<StatsJob> &jobs, std::vector<dindel_read_stats> &out)
+    {
+        pthread_mutex_lock(gpuLock);
+        try { batch->windowStats(w, jobs, out); }
+        catch (...) { pthread_mutex_unlock(gpuLock); throw; }
+        pthread_mutex_unlock(gpuLock);
+    }
 };
 } // namespace dindel_b200
 
@@ -393,6 +402,8 @@ struct dindel_b200_driver {
         if (totals.nWindows)
             fprintf(stderr, "dindel_b200 inference: windows %ld rechecked_on_host %ld em_sets %ld em_set_mismatch %ld\n",
                     totals.nWindows, totals.nRecheck, totals.nEmSets, totals.nEmMismatch);
+        if (gpu && gpu->nStatsCalls)
+            { fprintf(stderr, "dindel_b200 read stats: device_calls %ld jobs %ld\n", gpu->nStatsCalls, gpu->nStatsJobs); gpu->nStatsCalls = 0; }
     }
 };
 #endif

@@ -23,10 +23,13 @@ if not (len(sys.argv) > 3 and sys.argv[3] == "--dump"):
     text = text.replace(inc, inc + '#include "dindel_b200_driver.hpp"\nstatic dindel_b200::Engine *dindel_b200_gpu = 0;\n'
                         'static dindel_b200::Inference dindel_b200_inf; // K2 / K3 with the guard band (INTEGRATION.md section 0b)\n'
                         '#define DINDEL_B200_INF (dindel_b200_replay ? dindel_b200_replay->inf : dindel_b200_inf)\n'
+                        '// K6: the read statistics of called sites from the GPU when the policy says so (dindel_b200::deviceStats); false = the loop below it runs\n'
+                        '#define DINDEL_B200_STATS(JOBS, NREADS, OUT) (dindel_b200_replay ? dindel_b200::deviceStats(*dindel_b200_replay, JOBS, NREADS, OUT) : (dindel_b200_gpu ? dindel_b200::deviceStats(*dindel_b200_gpu, JOBS, NREADS, OUT) : false))\n'
                         'static std::string dindel_b200_bam_arg; static int dindel_b200_multiple_files = 0; // main() -> batched driver\n'
                         'static struct dindel_b200_report_t { ~dindel_b200_report_t() { if (dindel_b200_inf.nWindows) '
                         'fprintf(stderr, "dindel_b200 inference: windows %ld rechecked_on_host %ld em_sets %ld em_set_mismatch %ld\\n", '
-                        'dindel_b200_inf.nWindows, dindel_b200_inf.nRecheck, dindel_b200_inf.nEmSets, dindel_b200_inf.nEmMismatch); } } dindel_b200_report;\n'
+                        'dindel_b200_inf.nWindows, dindel_b200_inf.nRecheck, dindel_b200_inf.nEmSets, dindel_b200_inf.nEmMismatch); '
+                        'if (dindel_b200_gpu && dindel_b200_gpu->nStatsCalls) fprintf(stderr, "dindel_b200 read stats: device_calls %ld jobs %ld\\n", dindel_b200_gpu->nStatsCalls, dindel_b200_gpu->nStatsJobs); } } dindel_b200_report;\n'
                         '// the one engine of the process; K2 / K3 (the read sums of diploidGLF / the EM of estimateHaplotypeFrequenciesBayesEM) on the GPU too\n'
                         'static dindel_b200::Engine *dindel_b200_engine(const DetInDel::Parameters & params, size_t nBams)\n{\n'
                         '\tif (!dindel_b200_gpu) {\n'
@@ -162,6 +165,52 @@ if not dump:
         ("\t\t\to << str << a1 << \"/\" << a2 << \":\" << git->second;\n", 1, 0, "replace",
          "\t\t\to << str << a1 << \"/\" << a2 << \":\" << DINDEL_B200_INF.printed(git->second);\n"),
         ("\t\t\tline.set(\"logZ\", maxll );\n", 1, 0, "replace", "\t\t\tline.set(\"logZ\", DINDEL_B200_INF.printed(maxll) );\n"),
+        # ---- K6: the per-read aggregation loops behind a called site ----
+        # dip.map sites (DInDel.cpp:3126-3170): every site of the window in one K6 call before the site loop
+        ("\t\tfor (map<int, std::set<AlignedVariant> >::const_iterator it = indels.begin();it!=indels.end();it++) {\n\t\t\t\n\t\t\tdouble msq = 0;\n", 1, 0, "before",
+         "\t\tstd::vector<dindel_read_stats> b200_ms; bool b200_map = false; size_t b200_mi = 0;\n"
+         "\t\t{\n"
+         "\t\t\tstd::vector<dindel_b200::StatsJob> jobs_;\n"
+         "\t\t\tconst int m_ = (max_indel_pair[0]==max_indel_pair[1]) ? 1 : 2;\n"
+         "\t\t\tfor (map<int, std::set<AlignedVariant> >::const_iterator it = indels.begin();it!=indels.end();it++) {\n"
+         "\t\t\t\tjobs_.push_back(dindel_b200::StatsJob(DINDEL_STATS_MAP, -1));\n"
+         "\t\t\t\tfor (int i=0;i<2;i++) jobs_.back().cands.push_back(dindel_b200::mapCand(haps[max_indel_pair[i]], max_indel_pair[i], it->first, i<m_));\n"
+         "\t\t\t}\n"
+         "\t\t\tb200_map = DINDEL_B200_STATS(jobs_, reads.size(), b200_ms);\n"
+         "\t\t\tif (b200_map && !b200_ms.empty()) numUnmappedRealigned = b200_ms[0].numUnmappedRealigned;\n"
+         "\t\t}\n"),
+        ("\t\t\tfor (int i=0;i<m;i++) {\n\t\t\t\tint h=max_indel_pair[i];\n\t\t\t\tIt iter = haps[h].indels.find(it->first);\n", 1, 0, "before",
+         "\t\t\tif (b200_map) { const dindel_read_stats & s_ = b200_ms[b200_mi++]; msq = s_.msq; numf = s_.nf; numr = s_.nr; n = s_.n; } else\n"),
+        # variant positions (:3396-3404, :3504-3554): one K6 call per position, once its arg-max pair is known
+        ("\t\tint numUnmappedRealigned = 0;\n\t\tfor (size_t r=0;r<reads.size();r++) {\n", 1, 0, "replace",
+         "\t\tint numUnmappedRealigned = 0;\n"
+         "\t\tstd::vector<dindel_read_stats> b200_ss; bool b200_site = false;\n"
+         "\t\t{\n"
+         "\t\t\tstd::vector<dindel_b200::StatsJob> jobs_(1, dindel_b200::StatsJob(DINDEL_STATS_SITE, -1));\n"
+         "\t\t\tjobs_[0].cands.push_back(dindel_b200::siteCand(haps[hx1], hx1, pos)); jobs_[0].cands.push_back(dindel_b200::siteCand(haps[hx2], hx2, pos));\n"
+         "\t\t\tb200_site = DINDEL_B200_STATS(jobs_, reads.size(), b200_ss);\n"
+         "\t\t\tif (b200_site) numUnmappedRealigned = b200_ss[0].numUnmappedRealigned;\n"
+         "\t\t}\n"
+         "\t\tif (!b200_site) for (size_t r=0;r<reads.size();r++) {\n"),
+        ("\t\tBOOST_FOREACH(int r, readidx) {\n\t\t\tdouble mq=-10*log10(1.0-reads[r].mapQual);\n\t\t\tallmsq+=(mq*mq);\n", 1, 0, "before",
+         "\t\tif (b200_site) { const dindel_read_stats & s_ = b200_ss[0]; allmsq = s_.allmsq; numMappedIndels = s_.numIndels; nBQT = s_.nBQT; nmmBQT = s_.nmmBQT; "
+         "mLogBQ = s_.mLogBQ; nMMLeft = s_.nMMLeft; nMMRight = s_.nMMRight; numOffBoth = s_.numOffBoth; nf = s_.nf; nr = s_.nr; msq = s_.msq; n = s_.n; } else\n"),
+        # pooled variants (:2697-2742): every pool member of the variant in one K6 call
+        ("\t\tif (1) for (size_t b=0;b<myBams.size();b++) {\n\t\t\tdouble msq=0.0;\n", 1, 0, "before",
+         "\t\tstd::vector<dindel_read_stats> b200_ps; std::vector<int> b200_pj(myBams.size(), -1); bool b200_pool = false;\n"
+         "\t\t{\n"
+         "\t\t\tstd::vector<dindel_b200::StatsJob> jobs_;\n"
+         "\t\t\tsize_t most_ = 0;\n"
+         "\t\t\tfor (size_t b=0;b<myBams.size();b++) if (readidx[b].size()) {\n"
+         "\t\t\t\tb200_pj[b] = int(jobs_.size());\n"
+         "\t\t\t\tjobs_.push_back(dindel_b200::StatsJob(DINDEL_STATS_POOL, int(b)));\n"
+         "\t\t\t\tfor (size_t h=0;h<nh;h++) jobs_.back().cands.push_back(dindel_b200::poolCand(haps[h], int(h), pav.first, pav.second, hapHasVar[h*nv+idx]!=0));\n"
+         "\t\t\t\tif (readidx[b].size() > most_) most_ = readidx[b].size();\n"
+         "\t\t\t}\n"
+         "\t\t\tb200_pool = DINDEL_B200_STATS(jobs_, most_, b200_ps);\n"
+         "\t\t}\n"),
+        ("\t\t\t\tBOOST_FOREACH(int r, readidx[b]) {\n\t\t\t\t\t//cout << \" \" << 10*log10(1-reads[r].mapQual);\n\n\t\t\t\t\tsize_t mlidx;", 1, 0, "before",
+         "\t\t\t\tif (b200_pool && b200_pj[b] >= 0) { const dindel_read_stats & s_ = b200_ps[b200_pj[b]]; msq = s_.msq; n = s_.n; nf = s_.nf; nr = s_.nr; } else\n"),
         # ---- estimateHaplotypeFrequenciesBayesEM (DInDel.cpp:2103-2930) ----
         ("void DetInDel::estimateHaplotypeFrequenciesBayesEM(const vector<Haplotype> & haps, const vector<Read> & reads, const vector<vector<MLAlignment> > & liks, vector<double> & hapFreqs, vector <HapEstResult > & posteriors,  uint32_t candPos, uint32_t leftPos,   uint32_t rightPos, OutputData & glfData, int index, const AlignedCandidates & candidateVariants, string program=\"all\")\n\n{\n",
          1, 0, "after",

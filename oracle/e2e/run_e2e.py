@@ -147,6 +147,18 @@ def inference_totals(glfs):
     return tot
 
 
+def read_stats_totals(glfs):
+    """`dindel_b200 read stats:` lines: K6 calls of the GPU-backed binary and the jobs (site loops) they served."""
+    tot = {"device_calls": 0, "jobs": 0}
+    for g in glfs:
+        for line in open(g[:-len(".glf.txt")] + ".log", errors="replace"):
+            if line.startswith("dindel_b200 read stats:"):
+                t = line.split()
+                for k in tot:
+                    tot[k] += int(t[t.index(k) + 1])
+    return tot
+
+
 def diff_lines(a_files, b_files, limit=5):
     out = []
     if len(a_files) != len(b_files):
@@ -260,6 +272,8 @@ def main():
     ap.add_argument("--gpu-devices", default="", help="DINDEL_B200_DEVICES of the gpu arm: its batched driver shards every batch "
                     "over these CUDA devices through the in-process scheduler (e.g. 0,1)")
     ap.add_argument("--gpu-no-batch", action="store_true", help="gpu arm: the window-at-a-time loop (DINDEL_B200_NO_BATCH)")
+    ap.add_argument("--gpu-device-stats", default="", help="DINDEL_B200_DEVICE_STATS of the gpu arm: 1 = the read statistics of every "
+                    "called site from K6, 0 = always the reference's host loops (default: by size)")
     ap.add_argument("--host-inference", action="store_true", help="gpu arm: diploidGLF / EM sums on the host (DINDEL_B200_HOST_INFERENCE)")
     a = ap.parse_args()
     arms = a.arms.split(",")
@@ -286,6 +300,8 @@ def main():
                     aenv["DINDEL_B200_NO_BATCH"] = "1"
                 if a.host_inference:
                     aenv["DINDEL_B200_HOST_INFERENCE"] = "1"
+                if a.gpu_device_stats:
+                    aenv["DINDEL_B200_DEVICE_STATS"] = a.gpu_device_stats
             glfs, vcf, wall, n_calls = run_arm(arm, prep, a.work, procs if arm == "cpu" else a.gpu_procs,
                                                extra=(["--filterHaplotypes"] if a.filter_haplotypes else []) +
                                                (["--libFile", prep["libraries"]] if a.lib_file else []) +
@@ -297,6 +313,7 @@ def main():
             r[arm] = {"stage3_wall_s": round(wall, 3), "vcf_calls": n_calls, "windows_ok": ok, "windows_skipped": err}
             if arm == "gpu":
                 r[arm]["inference"] = inference_totals(glfs)
+                r[arm]["read_stats"] = read_stats_totals(glfs)
                 r[arm]["batched"] = [l.strip() for g in glfs for l in open(g[:-len(".glf.txt")] + ".log", errors="replace")
                                      if l.startswith("dindel_b200 batched:") or l.startswith("dindel_b200 host stages")][:8]
             if arm == "check":

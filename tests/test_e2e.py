@@ -251,6 +251,30 @@ def test_window_at_a_time_loop_still_identical(tmp_path, pooled):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("extra", [["--gpu-one-file"], ["--gpu-one-file", "--pooled"], ["--gpu-no-batch"], ["--gpu-no-batch", "--pooled"]])
+def test_device_read_stats_identical(tmp_path, extra):
+    """K6 in the pipeline (DINDEL_B200_DEVICE_STATS=1: every site, whatever its size): the read statistics behind every
+    called site -- dip.map sites, variant positions, pooled variants (DInDel.cpp:3126-3170, :3396-3404, :3504-3554,
+    :2697-2742) -- come from dindel_b200_read_stats instead of the reference's loops; the glf columns they feed (msq,
+    num_cover_forward / reverse, nBQT, nmmBQT, mLogBQ, nMMLeft, nMMRight, numOffAll, num_indel, num_unmapped_realigned)
+    and the VCF stay byte-identical, in the batched driver and in the window-at-a-time loop."""
+    if not run_e2e.have_binaries(("cpu", "gpu")):
+        pytest.skip("oracle/_ref binaries not built (reference sources absent at build time)")
+    env = dict(os.environ, DINDEL_B200_BATCH="30")
+    r = subprocess.run([sys.executable, os.path.join(E2E, "run_e2e.py"), "--work", str(tmp_path), "--length", "60000",
+                        "--seed", "41", "--arms", "cpu,gpu", "--windows-per-file", "15", "--heap-neutral", "--gpu-threads", "4",
+                        "--gpu-device-stats", "1"] + extra, capture_output=True, text=True, timeout=1500, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    hn = res["heap_neutral"]
+    assert hn["glf_identical"] and hn["cpu"]["windows_ok"] >= 18, res
+    if "--pooled" not in extra:
+        assert hn["vcf_identical"] and hn["cpu"]["vcf_calls"] >= 10, res
+    rs = hn["gpu"]["read_stats"]
+    assert rs["device_calls"] >= 18 and rs["jobs"] >= rs["device_calls"], res
+
+
+@pytest.mark.gpu
 def test_batched_driver_over_several_devices(tmp_path):
     """configs[4] in the small: the patched binary's batched driver shards every batch of windows over several CUDA
     devices through the in-process scheduler (DINDEL_B200_DEVICES -> Engine::enableMulti -> dindel_b200_multi_process);
