@@ -44,6 +44,9 @@
 // the product is exact, so the sum is the table's) instead of a shared load per candidate: +2.9 % at J = 11
 #define K1_LEFT_ADD 1
 #endif
+#ifndef K1_ROW_UNROLL
+#define K1_ROW_UNROLL 1 // J = 6 classes: row loops unrolled by this factor (experiment (b) of profiles/r2_k1_j6_experiments.md)
+#endif
 #ifndef K1_TILED_J11_MINB
 #define K1_TILED_J11_MINB 3
 #endif
@@ -174,6 +177,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
     // (C*(2J-1) doubles); they are kept once per CTA in shared memory, indexed by the homopolymer code of the
     // column that owns the entry, and the "-inf outside the haplotype" entries become -inf halo columns instead.
     constexpr bool TBL = (J > 7) || (C > K1_TILED_TBL_MINC);
+    constexpr int kRowUnroll = (J <= 7) ? K1_ROW_UNROLL : 1; // the J = 11 loops are 20 KB each as they are
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double s_hp_lpe[K1_HP_LUT], s_hp_lpn[K1_HP_LUT];
     __shared__ double s_tl[(TBL && !K1_LEFT_ADD) ? K1_HP_LUT * (J - 1) : 1]; // [code][y-2] = logProbError + (y-1)*lInsgIns (cpp:1791)
@@ -315,6 +319,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                 };
                 auto left_rows = [&](auto cro_tag) {
                 constexpr int CRO = decltype(cro_tag)::value;
+#pragma unroll kRowUnroll
                 for (int b = 1; b <= bMid; b++) {
                     const double eq = sm_eq[b - 1], uq = sm_uq[b - 1];
                     const uint32_t rbit = 1u << (sm_ch[b - 1] & 31);
@@ -517,6 +522,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                 };
                 auto right_rows = [&](auto cro_tag) {
                 constexpr int CRO = decltype(cro_tag)::value;
+#pragma unroll kRowUnroll
                 for (int b = R - 1; b > bMid; b--) {
                     const double eq = sm_eq[b], uq = sm_uq[b];
                     const uint32_t rbit = 1u << (sm_ch[b] & 31);

@@ -38,6 +38,24 @@ def test_struct_layouts_match_header():
     assert C.sizeof(engine._Job) == 6 * 8 + 8 + 3 * 8 and C.sizeof(engine._EmOut) == 6 * 8
 
 
+def test_struct_sizes_against_the_compiled_header(tmp_path):
+    """The ctypes mirrors in engine.py against sizeof() of the header itself, compiled as plain C (the boundary is a C ABI)."""
+    import subprocess
+    names = ["dindel_params", "dindel_batch_in", "dindel_batch_out", "dindel_pair_out", "dindel_timing", "dindel_job",
+             "dindel_em_out", "dindel_stats_in", "dindel_read_stats"]
+    src = '#include <stdio.h>\n#include "dindel_b200.h"\nint main(void){' + "".join(
+        'printf("%%zu\\n", sizeof(%s));' % n for n in names) + "return 0;}\n"
+    c = tmp_path / "sizes.c"
+    c.write_text(src)
+    exe = str(tmp_path / "sizes")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(c), "-o", exe])
+    got = [int(x) for x in subprocess.check_output([exe]).split()]
+    want = [C.sizeof(engine.Params), C.sizeof(engine._BatchIn), C.sizeof(engine._BatchOut), engine.PAIR_DTYPE.itemsize,
+            C.sizeof(engine.Timing), C.sizeof(engine._Job), C.sizeof(engine._EmOut), C.sizeof(engine._StatsIn),
+            engine.STATS_DTYPE.itemsize]
+    assert got == want, list(zip(names, got, want))
+
+
 def test_param_presets_follow_reference_defaults():
     d, c = engine.default_params(), engine.cli_params()
     assert (d.pError, d.pMut, d.maxLengthDel, d.padCover, d.bMid) == (1e-4, 1e-4, 10, 5, -1)   # ObservationModel.hpp:39-62

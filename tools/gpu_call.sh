@@ -1,4 +1,7 @@
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q > gpurun_out/r2g_gputests_full.log 2>&1; tail -5 gpurun_out/r2g_gputests_full.log
-python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r2g_smoke.log 2>&1; tail -2 gpurun_out/r2g_smoke.log
-python bench.py > gpurun_out/r2g_bench_n1.json 2> gpurun_out/r2g_bench_n1.err; tail -c 600 gpurun_out/r2g_bench_n1.json; tail -3 gpurun_out/r2g_bench_n1.err
+for rep in 1 2; do for v in "" "_alt"; do
+DINDEL_B200_LIB=$PWD/dindel_tgi_b200/libdindel_b200$v.so python bench.py --cfg 2 --windows 6000 --steps 3 --warmup 3 --no-cpu-baseline --no-extra --no-strong > gpurun_out/r2h_cfg2$v.$rep.json 2> gpurun_out/r2h_cfg2$v.$rep.err
+python -c "
+import json; r=json.loads(open('gpurun_out/r2h_cfg2$v.$rep.json').read().strip().splitlines()[-1]); print('variant [$v] rep $rep', r['gcups'], r['roofline']['frac'], r['e2e']['ll_checksum'])"
+done; done
+DINDEL_B200_LIB=$PWD/dindel_tgi_b200/libdindel_b200_alt.so python -m pytest tests/test_k1_gpu.py -x -q -k "every_shape_class or golden or random" 2>&1 | tail -2
