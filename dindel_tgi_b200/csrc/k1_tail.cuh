@@ -68,7 +68,8 @@ __device__ __forceinline__ void k1_tail(const Bt &bt, const Pf &pf, int lane, in
 {
     const int S = H + 2;
     // --- back-trace, cpp:1148-1165: lane 0 walks left (btf), lane 1 walks right (btb), in the same
-    //     instruction stream (one loop, both decodes evaluated, the lane's own one selected) ---
+    //     instruction stream.  The walk was 10 % of the J = 6 kernel's issued instructions (profiles/r2_k1_regions.md):
+    //     nearly every step sits on an interior plane-0 column, which now takes a short path of its own ---
     if (lane < 2) {
         const bool left = (lane == 0);
         const int RO = H + 1;
@@ -82,35 +83,68 @@ __device__ __forceinline__ void k1_tail(const Bt &bt, const Pf &pf, int lane, in
                 pf(left ? b - k : b + 1 + k, xp < 0 ? 0 : (xp > RO ? RO : xp));
             }
         }
-        for (int i = 0; i < n; i++) {
-            const bool plane1 = s >= S;
-            const int x = plane1 ? s - S : s;
-            if constexpr (!std::is_same<Pf, K1NoPrefetch>::value) {
+        if constexpr (std::is_same<Pf, K1NoPrefetch>::value) {
+            // rows in shared memory (J = 6 classes, generic kernel): nearly every step sits on an interior plane-0
+            // column, which takes a short path of its own (+2.0 % on configs[1])
+            for (int i = 0; i < n; i++) {
+                const bool plane1 = s >= S;
+                const int x = plane1 ? s - S : s;
+                const int c = bt(left ? b : b + 1, x);
+                const int code = c & 127;
+                if ((unsigned)(s - 1) < (unsigned)H) {
+                    // a jump of code+1 columns, or into / out of the insertion plane (k1_prev_state_dec /
+                    // k1_next_state_inc, 1 <= s <= H)
+                    const int t = left ? x - code - 1 : x + code + 1;
+                    const int jump = left ? (t < 0 ? 0 : t) : (t > H ? RO : t);
+                    s = (code >= J) ? (left ? S + x - 1 : S + x) : jump;
+                } else {
+                    const bool bit1 = (c >> 7) != 0;
+                    // plane 1 (s >= S)
+                    const int p1d = bit1 ? x : s;
+                    const int xi = (x + 1 > RO) ? RO : x + 1;
+                    const int p1i = !bit1 ? s : (x == 0 ? 0 : xi);
+                    // plane 0, LO and RO
+                    const int i0 = (code == 0) ? 0 : (code == 1) ? 1 : S;
+                    const int dR = (code == 0) ? RO : (code == 1) ? H : (code == 2) ? S + RO : S + H;
+                    const int iR = (code == 0) ? RO : S + RO;
+                    const int d = plane1 ? p1d : (x == 0 ? 0 : dR);
+                    const int u = plane1 ? p1i : (x == 0 ? i0 : iR);
+                    s = left ? d : u;
+                }
+                b += left ? -1 : 1;
+                sm_ms[b] = (int16_t)s;
+            }
+        } else {
+            // rows in global memory (J = 11 classes): the walk waits for the load, the branch-free form (both decodes
+            // evaluated, the lane's own one selected) measured 1.8 % faster there than the short path
+            for (int i = 0; i < n; i++) {
+                const bool plane1 = s >= S;
+                const int x = plane1 ? s - S : s;
                 if (i + K1_TAIL_PF_AHEAD < n) {
                     const int xp = left ? x - K1_TAIL_PF_AHEAD : x + K1_TAIL_PF_AHEAD;
                     pf(left ? b - K1_TAIL_PF_AHEAD : b + 1 + K1_TAIL_PF_AHEAD, xp < 0 ? 0 : (xp > RO ? RO : xp));
                 }
+                const int c = bt(left ? b : b + 1, x);
+                const int code = c & 127;
+                const bool bit1 = (c >> 7) != 0;
+                // plane 1 (k1_prev_state_dec / k1_next_state_inc, s >= S)
+                const int p1d = bit1 ? x : s;
+                const int xi = (x + 1 > RO) ? RO : x + 1;
+                const int p1i = !bit1 ? s : (x == 0 ? 0 : xi);
+                // plane 0, interior column
+                const int jd0 = x - code - 1, ji0 = x + code + 1;
+                const int gd = (code >= J) ? S + x - 1 : (jd0 < 0 ? 0 : jd0);
+                const int gi = (code >= J) ? S + x : (ji0 > H ? RO : ji0);
+                // plane 0, LO and RO
+                const int i0 = (code == 0) ? 0 : (code == 1) ? 1 : S;
+                const int dR = (code == 0) ? RO : (code == 1) ? H : (code == 2) ? S + RO : S + H;
+                const int iR = (code == 0) ? RO : S + RO;
+                const int d = plane1 ? p1d : (x == 0 ? 0 : (x == RO ? dR : gd));
+                const int u = plane1 ? p1i : (x == 0 ? i0 : (x == RO ? iR : gi));
+                s = left ? d : u;
+                b += left ? -1 : 1;
+                sm_ms[b] = (int16_t)s;
             }
-            const int c = bt(left ? b : b + 1, x);
-            const int code = c & 127;
-            const bool bit1 = (c >> 7) != 0;
-            // plane 1 (k1_prev_state_dec / k1_next_state_inc, s >= S)
-            const int p1d = bit1 ? x : s;
-            const int xi = (x + 1 > RO) ? RO : x + 1;
-            const int p1i = !bit1 ? s : (x == 0 ? 0 : xi);
-            // plane 0, interior column
-            const int jd0 = x - code - 1, ji0 = x + code + 1;
-            const int gd = (code >= J) ? S + x - 1 : (jd0 < 0 ? 0 : jd0);
-            const int gi = (code >= J) ? S + x : (ji0 > H ? RO : ji0);
-            // plane 0, LO and RO
-            const int i0 = (code == 0) ? 0 : (code == 1) ? 1 : S;
-            const int dR = (code == 0) ? RO : (code == 1) ? H : (code == 2) ? S + RO : S + H;
-            const int iR = (code == 0) ? RO : S + RO;
-            const int d = plane1 ? p1d : (x == 0 ? 0 : (x == RO ? dR : gd));
-            const int u = plane1 ? p1i : (x == 0 ? i0 : (x == RO ? iR : gi));
-            s = left ? d : u;
-            b += left ? -1 : 1;
-            sm_ms[b] = (int16_t)s;
         }
     }
     __syncwarp();

@@ -44,6 +44,9 @@
 // the product is exact, so the sum is the table's) instead of a shared load per candidate: +2.9 % at J = 11
 #define K1_LEFT_ADD 1
 #endif
+#ifndef K1_DIAG
+#define K1_DIAG 0 // timing diagnostics only (WRONG results): bit 0 skips the left-half rows, bit 1 the right-half rows, bit 2 the back-trace + summary
+#endif
 #ifndef K1_ROW_UNROLL
 #define K1_ROW_UNROLL 1 // J = 6 classes: row loops unrolled by this factor (experiment (b) of profiles/r2_k1_j6_experiments.md)
 #endif
@@ -320,7 +323,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                 auto left_rows = [&](auto cro_tag) {
                 constexpr int CRO = decltype(cro_tag)::value;
 #pragma unroll kRowUnroll
-                for (int b = 1; b <= bMid; b++) {
+                for (int b = 1; b <= ((K1_DIAG & 1) ? 0 : bMid); b++) {
                     const double eq = sm_eq[b - 1], uq = sm_uq[b - 1];
                     const uint32_t rbit = 1u << (sm_ch[b - 1] & 31);
                     double WO[C + J], WP[C + J], u[C], t1w[C + 1];
@@ -523,7 +526,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                 auto right_rows = [&](auto cro_tag) {
                 constexpr int CRO = decltype(cro_tag)::value;
 #pragma unroll kRowUnroll
-                for (int b = R - 1; b > bMid; b--) {
+                for (int b = ((K1_DIAG & 2) ? bMid : R - 1); b > bMid; b--) {
                     const double eq = sm_eq[b], uq = sm_uq[b];
                     const uint32_t rbit = 1u << (sm_ch[b] & 31);
                     double WO[C + J], WP[C + J], uw[C + 1], t1[C];
@@ -703,17 +706,32 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
 
             const uint16_t *btp = sm_bt;
             auto btf = [btp](int row, int x) -> int {
-                const int ln = x / C, c = x - ln * C;
-                if (Cfg::NIB) {
-                    const uint32_t u16 = btp[((size_t)row * U16 + (c >> 2)) * 32 + ln];
-                    const uint32_t v = (u16 >> (4 * (c & 3))) & 15u;
-                    return (int)((v & 7u) | ((v >> 3) << 7));
-                } else {
-                    const uint32_t u16 = btp[((size_t)row * U16 + (c >> 1)) * 32 + ln];
-                    return (int)((u16 >> (8 * (c & 1))) & 255u);
+                if constexpr (BTG) { // rows in global memory: 64-bit row offsets
+                    const int ln = x / C, c = x - ln * C;
+                    if (Cfg::NIB) {
+                        const uint32_t u16 = btp[((size_t)row * U16 + (c >> 2)) * 32 + ln];
+                        const uint32_t v = (u16 >> (4 * (c & 3))) & 15u;
+                        return (int)((v & 7u) | ((v >> 3) << 7));
+                    } else {
+                        const uint32_t u16 = btp[((size_t)row * U16 + (c >> 1)) * 32 + ln];
+                        return (int)((u16 >> (8 * (c & 1))) & 255u);
+                    }
+                } else {             // rows in shared memory: unsigned 32-bit index arithmetic (x >= 0)
+                    const unsigned ln = (unsigned)x / (unsigned)C, c = (unsigned)x - ln * (unsigned)C;
+                    if (Cfg::NIB) {
+                        const uint32_t u16 = btp[((unsigned)row * U16 + (c >> 2)) * 32 + ln];
+                        const uint32_t v = (u16 >> (4 * (c & 3))) & 15u;
+                        return (int)((v & 7u) | ((v >> 3) << 7));
+                    } else {
+                        const uint32_t u16 = btp[((unsigned)row * U16 + (c >> 1)) * 32 + ln];
+                        return (int)((u16 >> (8 * (c & 1))) & 255u);
+                    }
                 }
             };
             int16_t *hrow = B.hpos ? B.hpos + pair * (long long)B.hpos_stride : nullptr;
+            if constexpr ((K1_DIAG & 4) != 0) { // diagnostics: no back-trace / summary
+                if (lane == 0) { out->ll = ll; out->llOn = llOn; out->llOff = llOff; out->mapState0 = (uint16_t)msH; out->offHap = (uint8_t)offHap; out->offHapHMQ = (uint8_t)offHapHMQ; }
+            } else
             if constexpr (BTG) { // rows in global memory: prefetch down the diagonal (k1_tail.cuh)
                 auto pff = [btp](int row, int x) {
                     const int ln = x / C, c = x - ln * C;

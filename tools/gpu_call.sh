@@ -1,7 +1,10 @@
 mkdir -p gpurun_out
-for rep in 1 2; do for v in "" "_alt"; do
-DINDEL_B200_LIB=$PWD/dindel_tgi_b200/libdindel_b200$v.so python bench.py --cfg 2 --windows 6000 --steps 3 --warmup 3 --no-cpu-baseline --no-extra --no-strong > gpurun_out/r2h_cfg2$v.$rep.json 2> gpurun_out/r2h_cfg2$v.$rep.err
+python -m pytest tests/test_k1_gpu.py -x -q > gpurun_out/r2m_k1tests.log 2>&1; tail -3 gpurun_out/r2m_k1tests.log
+for rep in 1 2; do
+python bench.py --cfg 2 --windows 6000 --steps 3 --warmup 3 --no-cpu-baseline --no-extra --no-strong > gpurun_out/r2m_cfg2.$rep.json 2> gpurun_out/r2m_cfg2.$rep.err
 python -c "
-import json; r=json.loads(open('gpurun_out/r2h_cfg2$v.$rep.json').read().strip().splitlines()[-1]); print('variant [$v] rep $rep', r['gcups'], r['roofline']['frac'], r['e2e']['ll_checksum'])"
-done; done
-DINDEL_B200_LIB=$PWD/dindel_tgi_b200/libdindel_b200_alt.so python -m pytest tests/test_k1_gpu.py -x -q -k "every_shape_class or golden or random" 2>&1 | tail -2
+import json; r=json.loads(open('gpurun_out/r2m_cfg2.$rep.json').read().strip().splitlines()[-1]); print('cfg2 rep $rep', r['ms_per_step'], r['gcups'], r['roofline']['frac'], r['e2e']['ll_checksum'])"
+done
+python bench.py --cfg 4 --windows 600 --steps 2 --warmup 3 --no-cpu-baseline --no-extra --no-strong > gpurun_out/r2m_cfg4.json 2> gpurun_out/r2m_cfg4.err
+python -c "
+import json; r=json.loads(open('gpurun_out/r2m_cfg4.json').read().strip().splitlines()[-1]); print('cfg4', r['ms_per_step'], r['gcups'], r['roofline']['frac'], r['e2e']['ll_checksum'])"
