@@ -24,6 +24,14 @@
 #ifndef K1_TAIL_PF_AHEAD
 #define K1_TAIL_PF_AHEAD 8
 #endif
+// speculative parallel back-trace (k1_backtrace_parallel) for callers with their rows in shared / global memory; 0 = the
+// sequential 2-lane walk.  Measured (profiles/r2_k1_regions.md): configs[1] 289.3 -> 306.9 GCUPS, configs[3] 141.2 -> 153.2
+#ifndef K1_TAIL_PAR_SMEM
+#define K1_TAIL_PAR_SMEM 1
+#endif
+#ifndef K1_TAIL_PAR_GLOBAL
+#define K1_TAIL_PAR_GLOBAL 1
+#endif
 struct K1NoPrefetch {
     __device__ __forceinline__ void operator()(int, int) const {}
 };
@@ -55,6 +63,82 @@ __device__ __forceinline__ int k1_next_state_inc(int s, int code0, int bit1, int
     return nx > H ? RO : nx;
 }
 
+// ---- speculative parallel back-trace -------------------------------------------------------------------------
+// The back-trace (cpp:1148-1165) is a chain of R-1 dependent steps, but an alignment follows a diagonal almost
+// everywhere, so its states can be GUESSED: each of the 32 lanes takes K consecutive steps of one walk, starts them
+// from the state the diagonal predicts, and the warp then checks that every lane's entry state is the previous lane's
+// exit state.  Lane 0's entry is known; the first lane whose guess was wrong gets the true state (the exit of the lane
+// before it, right by induction), the lanes after it a new guess along the diagonal from there, and the round is
+// repeated.  Every round settles at least one more lane (at most 32 rounds; an alignment without indels: one), and the
+// last round, in which all entries are right, writes the final states.  The guess only steers speed; what is stored
+// is always produced by the same decode as the sequential walk.
+template <class Bt>
+__device__ __forceinline__ int k1_bt_step(const Bt &bt, bool left, int row, int s, int S, int H, int J)
+{
+    const int RO = H + 1;
+    const bool plane1 = s >= S;
+    const int x = plane1 ? s - S : s;
+    const int c = bt(row, x);
+    const int code = c & 127;
+    if ((unsigned)(s - 1) < (unsigned)H) { // plane 0, interior column (k1_prev_state_dec / k1_next_state_inc, 1 <= s <= H)
+        const int t = left ? x - code - 1 : x + code + 1;
+        const int jump = left ? (t < 0 ? 0 : t) : (t > H ? RO : t);
+        return (code >= J) ? (left ? S + x - 1 : S + x) : jump;
+    }
+    const bool bit1 = (c >> 7) != 0;
+    const int p1d = bit1 ? x : s;
+    const int xi = (x + 1 > RO) ? RO : x + 1;
+    const int p1i = !bit1 ? s : (x == 0 ? 0 : xi);
+    const int i0 = (code == 0) ? 0 : (code == 1) ? 1 : S;
+    const int dR = (code == 0) ? RO : (code == 1) ? H : (code == 2) ? S + RO : S + H;
+    const int iR = (code == 0) ? RO : S + RO;
+    const int d = plane1 ? p1d : (x == 0 ? 0 : dR);
+    const int u = plane1 ? p1i : (x == 0 ? i0 : iR);
+    return left ? d : u;
+}
+// the state k steps further along the diagonal (a guess: LO / RO / insertion states are assumed to stay)
+__device__ __forceinline__ int k1_bt_guess(bool left, int s, int k, int S, int H)
+{
+    if ((unsigned)(s - 1) >= (unsigned)H) return s;
+    const int t = left ? s - k : s + k;
+    return left ? (t < 0 ? 0 : t) : (t > H ? H + 1 : t);
+}
+template <class Bt>
+__device__ __forceinline__ void k1_backtrace_parallel(const Bt &bt, int lane, int R, int H, int J, int bMid, int msMid, int16_t *sm_ms)
+{
+    const int S = H + 2;
+    if (lane == 0) sm_ms[bMid] = (int16_t)msMid;
+#pragma unroll 1
+    for (int dir = 0; dir < 2; dir++) {
+        const bool left = dir == 0;
+        const int n = left ? bMid : (R - 1 - bMid);       // steps of this walk
+        if (n <= 0) continue;
+        const int K = (n + 31) >> 5;                       // steps per lane
+        const int nl = (n + K - 1) / K;                    // lanes that have steps
+        const int j0 = lane * K;                           // this lane's first step
+        int e = k1_bt_guess(left, msMid, j0, S, H);        // entry state (lane 0: msMid itself)
+        int settled = 1;                                   // lanes below this have right entries
+        for (;;) {
+            int s = e;
+            for (int j = 0; j < K; j++) {
+                const int st = j0 + j;
+                if (st < n) {
+                    // left: from read base bMid-st to bMid-st-1 through btf[bMid-st]; right: from bMid+st to bMid+st+1 through btb[bMid+st]
+                    s = k1_bt_step(bt, left, left ? bMid - st : bMid + st + 1, s, S, H, J);
+                    sm_ms[left ? bMid - st - 1 : bMid + st + 1] = (int16_t)s;
+                }
+            }
+            const int prev = __shfl_up_sync(0xffffffffu, s, 1);
+            const unsigned bad = __ballot_sync(0xffffffffu, lane >= settled && lane < nl && e != prev);
+            if (!bad) break;
+            const int f = __ffs(bad) - 1;                  // first lane with a wrong entry; the lanes before it are right
+            const int tru = __shfl_sync(0xffffffffu, s, f - 1);
+            if (lane >= f) e = k1_bt_guess(left, tru, (lane - f) * K, S, H);
+            settled = f + 1;
+        }
+    }
+}
+
 // Everything after ms[bMid] is known.  `bt(row, x)` returns code0 | bit1 << 7 of state column x;
 // rows 1..bMid hold the left half (btf[b]), rows bMid+1..R-1 hold btb[row-1].
 // sm_ms: int16[R] scratch; sm_ch / sm_ph: the read's bases and phred bytes; sm_acc: double[R].
@@ -67,9 +151,13 @@ __device__ __forceinline__ void k1_tail(const Bt &bt, const Pf &pf, int lane, in
                                         dindel_pair_out *out, int16_t *hpos_out)
 {
     const int S = H + 2;
-    // --- back-trace, cpp:1148-1165: lane 0 walks left (btf), lane 1 walks right (btb), in the same
-    //     instruction stream.  The walk was 10 % of the J = 6 kernel's issued instructions (profiles/r2_k1_regions.md):
-    //     nearly every step sits on an interior plane-0 column, which now takes a short path of its own ---
+    // --- back-trace, cpp:1148-1165.  As a 2-lane sequential walk (lane 0 left through btf, lane 1 right through btb) it
+    //     was 10 % of the J = 6 kernel's issued instructions (profiles/r2_k1_regions.md); the default is the speculative
+    //     32-lane walk above, the sequential loops below stay as the measured alternative (K1_TAIL_PAR_* = 0) ---
+    constexpr bool kParallel = std::is_same<Pf, K1NoPrefetch>::value ? (K1_TAIL_PAR_SMEM != 0) : (K1_TAIL_PAR_GLOBAL != 0);
+    if constexpr (kParallel) {
+        k1_backtrace_parallel(bt, lane, R, H, J, bMid, msMid, sm_ms);
+    } else
     if (lane < 2) {
         const bool left = (lane == 0);
         const int RO = H + 1;

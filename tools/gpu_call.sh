@@ -1,10 +1,4 @@
 mkdir -p gpurun_out
-python -m pytest tests/test_k1_gpu.py -x -q > gpurun_out/r2m_k1tests.log 2>&1; tail -3 gpurun_out/r2m_k1tests.log
-for rep in 1 2; do
-python bench.py --cfg 2 --windows 6000 --steps 3 --warmup 3 --no-cpu-baseline --no-extra --no-strong > gpurun_out/r2m_cfg2.$rep.json 2> gpurun_out/r2m_cfg2.$rep.err
-python -c "
-import json; r=json.loads(open('gpurun_out/r2m_cfg2.$rep.json').read().strip().splitlines()[-1]); print('cfg2 rep $rep', r['ms_per_step'], r['gcups'], r['roofline']['frac'], r['e2e']['ll_checksum'])"
-done
-python bench.py --cfg 4 --windows 600 --steps 2 --warmup 3 --no-cpu-baseline --no-extra --no-strong > gpurun_out/r2m_cfg4.json 2> gpurun_out/r2m_cfg4.err
-python -c "
-import json; r=json.loads(open('gpurun_out/r2m_cfg4.json').read().strip().splitlines()[-1]); print('cfg4', r['ms_per_step'], r['gcups'], r['roofline']['frac'], r['e2e']['ll_checksum'])"
+python -m pytest tests -m gpu -x -q > gpurun_out/r2o_gputests_full.log 2>&1; tail -5 gpurun_out/r2o_gputests_full.log
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r2o_smoke.log 2>&1; tail -2 gpurun_out/r2o_smoke.log
+python bench.py > gpurun_out/r2o_bench_n1.json 2> gpurun_out/r2o_bench_n1.err; tail -c 300 gpurun_out/r2o_bench_n1.json; tail -2 gpurun_out/r2o_bench_n1.err
