@@ -1020,8 +1020,12 @@ static int run_range(dindel_ctx *ctx, const dindel_job *job, int a, int b, int w
     }
     if (out->hpos && out->hpos_stride != ctx->B.hpos_stride) return fail(ctx, DINDEL_E_INVALID, "hpos_stride mismatch");
     const long long cells = range_cells(in, a, b);
-    // chunk plan: about 8e9 cells (~30 ms of K1) per chunk, at most 64 chunks
-    int n_chunks = ctx->force_chunks > 0 ? ctx->force_chunks : (int)(cells / 8000000000LL);
+    // chunk plan.  More chunks expose less of the first H2D / last D2H copy (~ T_copy / n), every chunk costs ~0.6 ms of
+    // launch tails (its persistent kernels drain before the lane's next chunk starts): n ~ sqrt(T_copy / 0.6 ms), and
+    // T_copy grows with the cells.  Measured e2e (bench.py, ms per step at 6 k / 25 k / 100 k windows = 2.0e10 / 8.4e10 /
+    // 3.4e11 cells): 2 chunks 72.9, 4: 73.7, 8: 75.2, 16: 79.1 | 4: 290.3, 8: 290.5, 10: 292.6, 16: 297.4 |
+    // 8: 1146.6, 16: 1138.4, 24: 1165.3, 41: 1161.9, 64: 1185.7  ->  n = sqrt(cells / 1.6e9): 4 / 7 / 14
+    int n_chunks = ctx->force_chunks > 0 ? ctx->force_chunks : (int)(sqrt((double)cells / 1.6e9) + 0.5);
     if (n_chunks > 64) n_chunks = 64;
     if (n_chunks > b - a) n_chunks = b - a;
     if (n_chunks < 1) n_chunks = 1;

@@ -1,5 +1,4 @@
 mkdir -p gpurun_out
-python -m pytest tests/test_k1_gpu.py -x -q -k "breaks" > gpurun_out/r2p_breaks.log 2>&1; tail -3 gpurun_out/r2p_breaks.log
-CMD2="python bench.py --windows 3000 --steps 2 --warmup 3 --no-cpu-baseline --no-extra --no-strong"
-$CMD2 > gpurun_out/r2p_plain2.json 2> gpurun_out/r2p_plain2.err || exit 1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k1_tiled_kernel -s 6 -c 1 -o gpurun_out/r2_k1_j6_v5 $CMD2 > gpurun_out/r2p_ncu_j6.log 2>&1; echo "j6 rc $?"
+python -m pytest tests -m gpu -x -q > gpurun_out/r2s_gputests_full.log 2>&1; tail -4 gpurun_out/r2s_gputests_full.log
+python bench.py > gpurun_out/r2s_bench_n1.json 2> gpurun_out/r2s_bench_n1.err; python -c "
+import json; r=json.loads(open('gpurun_out/r2s_bench_n1.json').read().strip().splitlines()[-1]); print(r['value'], r['gcups'], r['roofline']['frac'], 'e2e', r['e2e']['value'], r['e2e']['ms_per_step']); print({k:(v['value'], v['e2e']['value']) for k,v in r['extra_configs'].items()}); print(r['strong']['n1']['ms'])"
