@@ -36,7 +36,8 @@
 #define K1_LEFT_TREE 1
 #endif
 #ifndef K1_FMAX
-#define K1_FMAX 0 // 1: the 'take iff v >= best' value selects as DMNMX (one FP64-pipe instruction instead of two ALU selects)
+#define K1_FMAX 0 // bit mask: 'take iff v >= best' value selects as DMNMX (one FP64-pipe instruction instead of two ALU selects):
+                  // 1 left-half pair leaves, 2 left-half tree nodes, 4 plane 1 of the left half, 8 plane 1 of the right half
 #endif
 #ifndef K1_LEFT_ADD
 // shared-table classes: the left half's jump entries logProbError + (y-1)*lInsgIns (cpp:1791) are rebuilt by one DADD
@@ -362,7 +363,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                             if (y + 1 <= J) {
                                 const double vb = ((WO[J + c - (y + 1)] + LPD(c, y - 1)) + WP[J + c - (y + 1)]) + lpn[c];
                                 const bool pb = (vb >= va);
-#if K1_FMAX
+#if K1_FMAX & 1
                                 pm = fmax(va, vb); // == pb ? vb : va bit for bit (no NaN, no zero of either sign among these sums)
 #else
                                 pm = pb ? vb : va;
@@ -374,7 +375,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                                 code[c] = pc;
                             } else {
                                 const bool p = (pm >= best[c]);
-#if K1_FMAX
+#if K1_FMAX & 2
                                 best[c] = fmax(best[c], pm);
 #else
                                 best[c] = p ? pm : best[c];
@@ -414,7 +415,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                         const double stay = t1w[c + 1] + lInsgIns;
                         const double f = u[c] + lNoInsgIns;
                         const bool p = (f >= stay);
-#if K1_FMAX
+#if K1_FMAX & 4
                         a1[c] = fmax(stay, f);
 #else
                         a1[c] = p ? f : stay;
@@ -606,7 +607,7 @@ __global__ void __launch_bounds__(32 * K1_TILED_WPC, MINB) k1_tiled_kernel(K1Bat
                     for (int c = 0; c < C; c++) {
                         const double stay = t1[c] + lInsgIns;
                         const bool p = (f[c] >= stay);
-#if K1_FMAX
+#if K1_FMAX & 8
                         a1[c] = fmax(stay, f[c]);
 #else
                         a1[c] = p ? f[c] : stay;
