@@ -468,6 +468,41 @@ static int validate(const dindel_batch_in *in)
     return DINDEL_OK;
 }
 
+// validate() for the multi-device call: the three monotonicity sweeps (O(windows + haplotypes + reads): 7 ms per 100 k
+// windows on one core) are the serial part in front of the shards, so they are cut into `parts` slices run on short-lived
+// host threads.
+static int validate_parallel(const dindel_batch_in *in, int parts)
+{
+    if (!in || in->n_windows < 0 || in->n_haps < 0 || in->n_reads < 0) return DINDEL_E_INVALID;
+    if (in->n_windows == 0) return DINDEL_OK;
+    if (parts < 2 || in->n_reads < 200000) return validate(in);
+    if (!in->hap_start || !in->win_hap || !in->win_read || !in->hap_off || !in->read_off) return DINDEL_E_INVALID;
+    if (in->win_hap[0] != 0 || in->win_read[0] != 0 || in->win_hap[in->n_windows] != in->n_haps ||
+        in->win_read[in->n_windows] != in->n_reads)
+        return DINDEL_E_INVALID;
+    if (in->hap_off[0] != 0 || in->read_off[0] != 0) return DINDEL_E_INVALID;
+    std::vector<int> bad((size_t)parts, 0);
+    std::vector<std::thread> th;
+    for (int k = 0; k < parts; k++)
+        th.emplace_back([in, parts, k, &bad] {
+            const long long w0 = (long long)in->n_windows * k / parts, w1 = (long long)in->n_windows * (k + 1) / parts;
+            const long long h0 = (long long)in->n_haps * k / parts, h1 = (long long)in->n_haps * (k + 1) / parts;
+            const long long r0 = (long long)in->n_reads * k / parts, r1 = (long long)in->n_reads * (k + 1) / parts;
+            int b = 0;
+            for (long long w = w0; w < w1; w++) b |= (in->win_hap[w + 1] < in->win_hap[w]) | (in->win_read[w + 1] < in->win_read[w]);
+            for (long long h = h0; h < h1; h++) b |= in->hap_off[h + 1] < in->hap_off[h];
+            for (long long r = r0; r < r1; r++) b |= in->read_off[r + 1] < in->read_off[r];
+            bad[(size_t)k] = b;
+        });
+    for (size_t k = 0; k < th.size(); k++) th[k].join();
+    for (int k = 0; k < parts; k++)
+        if (bad[(size_t)k]) return DINDEL_E_INVALID;
+    if (in->n_haps && (!in->hap_seq) && in->hap_off[in->n_haps] > 0) return DINDEL_E_INVALID;
+    if (in->n_reads && in->read_off[in->n_reads] > 0 && (!in->read_seq || !in->read_qual)) return DINDEL_E_INVALID;
+    if (in->n_reads && (!in->read_mapq || !in->read_start || !in->read_flags)) return DINDEL_E_INVALID;
+    return DINDEL_OK;
+}
+
 int dindel_b200_set_libraries(dindel_ctx *ctx, int n_libs, const int64_t *lib_off, const double *probs,
                               const double *ninetyfifth_pct_prob)
 {
@@ -1876,8 +1911,8 @@ int dindel_b200_multi_process(dindel_multi *m, const dindel_job *job)
 {
     if (!m || !job || !job->in || !job->out) return DINDEL_E_INVALID;
     const dindel_batch_in *in = job->in;
-    if (validate(in) != DINDEL_OK) { m->err = "inconsistent batch"; return DINDEL_E_INVALID; }
     const int ndev = (int)m->ctx.size(), nw = in->n_windows;
+    if (validate_parallel(in, ndev < 8 ? ndev * 2 : 16) != DINDEL_OK) { m->err = "inconsistent batch"; return DINDEL_E_INVALID; }
     // whole-batch outputs the per-device runs leave to us: win_pair / win_sum_off prefixes
     if (job->out->win_pair || job->win_sum_off) {
         long long p = 0, s = 0;

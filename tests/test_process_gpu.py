@@ -199,6 +199,37 @@ def test_multi_process_two_contexts_one_device():
 
 
 @pytest.mark.gpu
+def test_multi_process_validates_large_batches_in_slices():
+    """Above 200 k reads the multi-device call checks the CSR arrays on several host threads (validate_parallel): a valid
+    batch gives the single-context records, a batch whose read_off / hap_off / win_read is not monotone somewhere in the
+    middle of a slice is refused as a whole, whichever slice holds the defect."""
+    from dindel_tgi_b200 import engine, synth
+    batch = synth.make_batch(2, 4000, seed=12)
+    assert batch.n_reads >= 200000
+    e = engine.Engine(engine.cli_params(), 0)
+    single = e.compute_likelihoods(batch, want_hpos=False)
+    e.close()
+    m = engine.MultiEngine(engine.cli_params(), (0, 0, 0))
+    try:
+        multi = m.process(batch, want_pairs=True, want_hpos=False)
+        assert multi.pairs.tobytes() == single.pairs.tobytes()
+        for field, pos in (("read_off", 0.9), ("read_off", 0.1), ("hap_off", 0.5), ("win_read", 0.7)):
+            arr = getattr(batch, field).copy()
+            k = int(len(arr) * pos)
+            arr[k], arr[k + 1] = arr[k + 1], arr[k]
+            bad = engine.Batch(batch.hap_start, batch.win_hap, batch.win_read if field != "win_read" else arr,
+                               batch.hap_off if field != "hap_off" else arr, batch.hap_seq,
+                               batch.read_off if field != "read_off" else arr, batch.read_seq, batch.read_qual, batch.read_mapq,
+                               batch.read_start, batch.read_flags)
+            with pytest.raises(RuntimeError, match="inconsistent batch|bad argument"):
+                m.process(bad, want_pairs=True, want_hpos=False)
+        again = m.process(batch, want_pairs=True, want_hpos=False)   # the scheduler survives the refusals
+        assert again.pairs.tobytes() == single.pairs.tobytes()
+    finally:
+        m.close()
+
+
+@pytest.mark.gpu
 def test_multi_process_two_devices():
     import torch
     if torch.cuda.device_count() < 2:
