@@ -579,7 +579,7 @@ int dindel_b200_plan_shards(const dindel_batch_in *in, int n_shards, int32_t *fi
 // ------------------------------------------------------------------------------------------
 static int index_batch(dindel_ctx *ctx, const dindel_batch_in *in, bool validated)
 {
-    if (!validated && validate(in) != DINDEL_OK) return fail(ctx, DINDEL_E_INVALID, "inconsistent batch");
+    if (!validated && validate_parallel(in, 4) != DINDEL_OK) return fail(ctx, DINDEL_E_INVALID, "inconsistent batch");
     CU(cudaSetDevice(ctx->device));
     ctx->resident = false;
     ctx->ran = false;

@@ -16,6 +16,21 @@ struct MockAV { // Variant.hpp:78-175: the members this path touches
     MockAV(const std::string &s, int sh, int eh, int sr, int er) : str(s), startHap(sh), endHap(eh), startRead(sr), endRead(er) {}
     bool isCovered(int pad, int firstBase, int lastBase) const { return firstBase + pad <= startRead && lastBase - pad >= endRead; }
 };
+// AlignedVariant as the K6 helpers see it (Variant.hpp:41-43, :148, :170): endRead is PROTECTED and has no getter
+class MockAV2 {
+public:
+    enum { REF, INS, DEL, SNP };
+    MockAV2() : kind(REF), startRead(-1), endRead(-1) {}
+    MockAV2(int k, int sr, int er) : kind(k), startRead(sr), endRead(er) {}
+    bool isIndel() const { return kind == INS || kind == DEL; }
+    bool isSNP() const { return kind == SNP; }
+    bool isRef() const { return kind == REF; }
+    int getStartRead() const { return startRead; }
+    bool isCovered(int pad, int firstBase, int lastBase) const { return firstBase + pad <= startRead && lastBase - pad >= endRead; }
+protected:
+    int kind, startRead, endRead;
+};
+struct MockHap2 { std::string seq; std::map<int, MockAV2> indels, snps; };
 struct MockHapML { std::vector<int> hpos; };
 struct MockHap { // Haplotype.hpp:40-70, countIndels :254-261, ml = its alignment to the reference segment
     std::string seq;
@@ -147,6 +162,38 @@ int main()
                   cig[2][0].second + cig[2][2].second == 60 && cig[2].refPos == 7015);
             CHECK(cig[3].size() == 1 && cig[3][0] == std::make_pair(0, 50) && cig[3].refPos == 7030);
         }
+    }
+    { // K6 through the adapter: candidates from the variant maps (protected endRead through VariantPeek), the site's
+      // read statistics from the GPU against the reference's loop (DInDel.cpp:3504-3554) run here on the mock records
+        eng->computeLikelihoods(haps, reads, liks, leftPos, leftPos + 100, onHap);
+        std::vector<MockHap2> h2(2);
+        h2[0].indels[50] = MockAV2(MockAV2::REF, -1, -1);
+        h2[1].indels[50] = MockAV2(MockAV2::DEL, 50, 50);
+        h2[0].snps[20] = MockAV2(MockAV2::SNP, 20, 20);
+        const dindel_b200::StatsCand c0 = dindel_b200::siteCand(h2[0], 0, 50), c1 = dindel_b200::siteCand(h2[1], 1, 50);
+        CHECK(c0.flags == 0 && c1.flags == DINDEL_CAND_PRESENT && c1.start == 50 && c1.end == 50 && c1.hap == 1);
+        CHECK(dindel_b200::siteCand(h2[0], 0, 77).flags == 0);                       // no entry at the site
+        const dindel_b200::StatsCand m1 = dindel_b200::mapCand(h2[1], 1, 50, true);
+        CHECK(m1.flags == DINDEL_CAND_PRESENT && dindel_b200::mapCand(h2[1], 1, 50, false).flags == 0 && dindel_b200::mapCand(h2[0], 0, 50, true).flags == 0);
+        const dindel_b200::StatsCand p0 = dindel_b200::poolCand(h2[0], 0, 20, MockAV2(MockAV2::SNP, 0, 0), true);
+        CHECK(p0.flags == (DINDEL_CAND_PRESENT | DINDEL_CAND_HAS_VAR) && p0.start == 20 && p0.end == 20);
+        CHECK(dindel_b200::poolCand(h2[1], 1, 20, MockAV2(MockAV2::SNP, 0, 0), false).flags == 0);
+        std::vector<dindel_b200::StatsJob> jobs(1, dindel_b200::StatsJob(DINDEL_STATS_SITE, -1));
+        jobs[0].cands.push_back(c0); jobs[0].cands.push_back(c1);
+        std::vector<dindel_read_stats> st;
+        eng->windowStats(jobs, st);
+        CHECK(st.size() == 1);
+        int nf = 0, n = 0, nBQT = 0, nInd = 0;
+        double mLogBQ = 0.0;
+        for (size_t r = 0; r < reads.size(); r++) {
+            const int h = (liks[0][r].ll >= liks[1][r].ll) ? 0 : 1;
+            const MockMLA &m = liks[h][r];
+            nBQT += m.nBQT; nInd += m.numIndels; mLogBQ += m.mLogBQ;
+            if (h == 1 && m.firstBase + p.padCover <= 50 && m.lastBase - p.padCover >= 50) { nf++; n++; }
+        }
+        CHECK(st[0].n_reads == 4 && st[0].nBQT == nBQT && st[0].numIndels == nInd && st[0].mLogBQ == mLogBQ);
+        CHECK(st[0].n == n && st[0].nf == nf && st[0].nr == 0 && n >= 1 && st[0].numUnmappedRealigned == 0);
+        CHECK(dindel_b200::deviceStats(*eng, jobs, reads.size(), st) == (dindel_b200::statsPolicy() > 0)); // 4 reads: below the size threshold
     }
     { // a haplotype shorter than maxLengthDel: "hapSize error." (ObservationModelFB.cpp:47)
         std::vector<MockHap> bad(2);
