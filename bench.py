@@ -687,9 +687,10 @@ def main():
 
 
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per cell of the dominant K1 launch, from one `ncu --set full`
-# capture of `python bench.py --windows 3000 --steps 1 --warmup 1` (hpos rows included): 302 MB for 8.9 G cells.
-TRAFFIC = {2: 301.8e6 / 8.9e9}
-TRAFFIC_SOURCE = "profiles/r1_k1_tiled_v4_k4.md (k1_tiled_kernel<4,6>, ncu --set full), scaled to this step's cells"
+# capture of `python bench.py --windows 3000 --steps 2 --warmup 3 --no-cpu-baseline --no-extra --no-strong` (hpos rows
+# included): 118.1 MB read + 185.5 MB written for the launch's 8.9 G cells (round 1's capture: 302 MB).
+TRAFFIC = {2: 303.6e6 / 8.9e9}
+TRAFFIC_SOURCE = "profiles/r2_k1_j6_v5_ncu_raw.csv (k1_tiled_kernel<4,6>, ncu --set full, round 2), scaled to this step's cells"
 
 
 if __name__ == "__main__":
