@@ -35,6 +35,8 @@ extern "C" cudaError_t k2_launch(const K2Args *a, int max_npairs, cudaStream_t s
 extern "C" cudaError_t k3_launch(const K3Args *a, int max_nh, int max_nr, size_t smem_optin, cudaStream_t st);
 extern "C" int k3_max_haps(void);
 extern "C" size_t k4_smem_bytes(int ne, int nk, int nr, int nh);
+extern "C" size_t k4_smem_bytes_big(int ne, int nk, int nh);
+extern "C" size_t k4_cov_words(int ne, int nr);
 extern "C" cudaError_t k4_launch(const K4Args *a, int n_windows, size_t smem, cudaStream_t st);
 extern "C" size_t k5_smem_bytes(int pitch);
 extern "C" int k5_pitch(int max_R);
@@ -1607,7 +1609,13 @@ static int coverage_resident(dindel_ctx *ctx, const dindel_cover_in *in, dindel_
     const int nwt = ctx->idx_windows;
     if (in->win_entry[0] != 0 || in->win_key[0] != 0 || in->win_entry[nwt] != in->n_entries || in->win_key[nwt] != in->n_keys)
         return fail(ctx, DINDEL_E_INVALID, "win_entry / win_key do not span the entries / keys");
-    size_t smem = 0;
+    // Windows are served by one CTA each with their bit sets in shared memory; the few whose sets would take more than
+    // K4_SMEM_SMALL (one such window would otherwise size every CTA's shared memory, or not fit at all) go to a second
+    // launch with the sets in a global scratch.
+    const size_t K4_SMEM_SMALL = 48 * 1024;
+    size_t smem = 0, smem_big = 0, cov_words = 0;
+    std::vector<int32_t> big;
+    std::vector<long long> big_off;
     for (int w = b.w0; w < b.w1; w++) {
         const long long ne = in->win_entry[w + 1] - in->win_entry[w], nk = in->win_key[w + 1] - in->win_key[w];
         if (ne < 0 || nk < 0) return fail(ctx, DINDEL_E_INVALID, "win_entry / win_key not monotone");
@@ -1621,9 +1629,16 @@ static int coverage_resident(dindel_ctx *ctx, const dindel_cover_in *in, dindel_
             prev_h = in->entry_hap[e];
         }
         const size_t s = k4_smem_bytes((int)ne, (int)nk, nr, nh);
-        if (s > smem) smem = s;
+        if (s > K4_SMEM_SMALL || s > ctx->smem_optin) {
+            // deep window (thousands of reads x hundreds of entries): its covering-read bit sets go to global memory
+            const size_t sb = k4_smem_bytes_big((int)ne, (int)nk, nh);
+            if (sb > ctx->smem_optin) return fail(ctx, DINDEL_E_UNSUPPORTED, "window has too many variant entries for one CTA's shared memory");
+            if (sb > smem_big) smem_big = sb;
+            big.push_back(w);
+            big_off.push_back((long long)cov_words);
+            cov_words += k4_cov_words((int)ne, nr);
+        } else if (s > smem) smem = s;
     }
-    if (smem > ctx->smem_optin) return fail(ctx, DINDEL_E_UNSUPPORTED, "window has too many (variant entries x reads) for one CTA's shared memory");
     CU(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     const size_t nw = (size_t)(b.w1 - b.w0), nh = (size_t)(b.h1 - b.h0), nr = (size_t)(b.r1 - b.r0);
@@ -1651,7 +1666,7 @@ static int coverage_resident(dindel_ctx *ctx, const dindel_cover_in *in, dindel_
     if (nr) CU(cudaMemcpyAsync(d_in + o_rs, in->read_strand + b.r0, nr, cudaMemcpyHostToDevice, st));
     K4Args a;
     a.maxMismatch = in->maxMismatch; a.doFilter = in->doFilter;
-    a.w_begin = b.w0;
+    a.w_begin = b.w0; a.win_list = nullptr; a.cov_global = nullptr; a.cov_off = nullptr;
     // win_entry / win_key values stay absolute: the arrays they index are rebased by e0 / k0
     a.win_entry = (const long long *)(d_in + o_we) - b.w0; a.win_key = (const long long *)(d_in + o_wk) - b.w0;
     a.entry_hap = (const int32_t *)(d_in + o_eh) - e0; a.entry_key = (const int32_t *)(d_in + o_ek) - e0;
@@ -1662,7 +1677,35 @@ static int coverage_resident(dindel_ctx *ctx, const dindel_cover_in *in, dindel_
     a.win_hap = B.win_hap; a.win_read = B.win_read; a.win_pair = B.win_pair; a.hap_off = B.hap_off; a.read_off = B.read_off;
     a.hap_seq = B.hap_seq; a.read_seq = B.read_seq; a.pairs = B.pairs; a.hpos = B.hpos; a.hpos_stride = B.hpos_stride;
     CU(cudaEventRecord(ctx->ev_k[0], st));
-    CU(k4_launch(&a, (int)nw, smem, st));
+    if (big.empty()) {
+        CU(k4_launch(&a, (int)nw, smem, st));
+    } else {
+        // lists: [small windows | big windows] (int32), then the big windows' offsets into the scratch (int64)
+        std::vector<int32_t> lists;
+        lists.reserve(nw);
+        size_t ib = 0;
+        for (int w = b.w0; w < b.w1; w++) {
+            if (ib < big.size() && big[ib] == w) ib++;
+            else lists.push_back(w);
+        }
+        const size_t n_small = lists.size(), n_big = big.size();
+        lists.insert(lists.end(), big.begin(), big.end());
+        const size_t o_off = (nw * 4 + 7) & ~(size_t)7, o_cov = o_off + n_big * 8;
+        CU(ctx->d_x[2].ensure(o_cov + cov_words * 4 + 16));
+        char *d_l = (char *)ctx->d_x[2].p;
+        CU(cudaMemcpyAsync(d_l, lists.data(), nw * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_l + o_off, big_off.data(), n_big * 8, cudaMemcpyHostToDevice, st));
+        CU(cudaMemsetAsync(d_l + o_cov, 0, cov_words * 4, st));
+        if (n_small) {
+            a.win_list = (const int32_t *)d_l;
+            CU(k4_launch(&a, (int)n_small, smem, st));
+        }
+        a.win_list = (const int32_t *)d_l + n_small;
+        a.cov_global = (uint32_t *)(d_l + o_cov);
+        a.cov_off = (const long long *)(d_l + o_off);
+        CU(k4_launch(&a, (int)n_big, smem_big, st));
+        CU(cudaStreamSynchronize(st)); // `lists` / `big_off` are pageable host vectors: done before they go out of scope
+    }
     CU(cudaEventRecord(ctx->ev_k[1], st));
     if (nk) {
         CU(cudaMemcpyAsync(out->key_nf + k0, d_out + r_nf, nk * 4, cudaMemcpyDeviceToHost, st));

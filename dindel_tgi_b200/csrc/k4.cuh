@@ -4,7 +4,12 @@
 
 struct K4Args {
     int maxMismatch, doFilter;
-    int w_begin; // CTA b works on window w_begin + b (the resident range; every pointer below is rebased)
+    int w_begin; // CTA b works on window w_begin + b (the resident range; every pointer below is rebased) ...
+    const int32_t *win_list;      // ... or on window win_list[b] when not null
+    // windows whose covering-read bit sets (entries x 2 strands x ceil(reads / 32) words) do not fit shared memory keep
+    // them in global memory: CTA b's sets start at cov_global + cov_off[b] (zeroed by the host); null = shared memory
+    uint32_t *cov_global;
+    const long long *cov_off;
     const long long *win_entry, *win_key;
     const int32_t *entry_hap, *entry_key, *entry_left, *entry_right;
     const uint8_t *entry_type, *read_strand;

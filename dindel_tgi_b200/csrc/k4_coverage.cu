@@ -18,7 +18,7 @@
 __global__ void __launch_bounds__(K4_THREADS) k4_coverage_kernel(K4Args a)
 {
     extern __shared__ uint32_t sm[];
-    const int w = a.w_begin + blockIdx.x;
+    const int w = a.win_list ? a.win_list[blockIdx.x] : a.w_begin + blockIdx.x;
     const long long e0 = a.win_entry[w], e1 = a.win_entry[w + 1];
     const long long k0 = a.win_key[w], k1 = a.win_key[w + 1];
     const int ne = (int)(e1 - e0), nk = (int)(k1 - k0);
@@ -26,13 +26,15 @@ __global__ void __launch_bounds__(K4_THREADS) k4_coverage_kernel(K4Args a)
     const int r0 = a.win_read[w], nr = a.win_read[w + 1] - r0;
     const int words = (nr + 31) >> 5;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    // shared: cov[ne][2][words] | any[ne] | active[ne] | cnt[nk][2] | filt[nh]
-    uint32_t *cov = sm;
-    uint32_t *any = cov + (size_t)ne * 2 * words;
+    // shared: cov[ne][2][words] | any[ne] | active[ne] | cnt[nk][2] | filt[nh]; cov in global memory for the windows
+    // it would not fit (deep pooled windows: thousands of reads x hundreds of entries)
+    const bool big = a.cov_global != nullptr;
+    uint32_t *cov = big ? a.cov_global + a.cov_off[blockIdx.x] : sm;
+    uint32_t *any = big ? sm : cov + (size_t)ne * 2 * words;
     uint32_t *active = any + ne;
     uint32_t *cnt = active + ne;
     uint32_t *filt = cnt + 2 * nk;
-    for (int i = threadIdx.x; i < ne * 2 * words + 2 * ne + 2 * nk + nh; i += blockDim.x) sm[i] = 0;
+    for (int i = threadIdx.x; i < (big ? 0 : ne * 2 * words) + 2 * ne + 2 * nk + nh; i += blockDim.x) sm[i] = 0;
     __syncthreads();
 
     // ---- phase 1: which reads cover which entry ----
@@ -113,6 +115,9 @@ extern "C" size_t k4_smem_bytes(int ne, int nk, int nr, int nh)
     const size_t words = (size_t)((nr + 31) >> 5);
     return ((size_t)ne * 2 * words + 2 * (size_t)ne + 2 * (size_t)nk + (size_t)nh) * sizeof(uint32_t);
 }
+// the same with the covering-read bit sets in global memory: what stays in shared memory, and the words of the sets
+extern "C" size_t k4_smem_bytes_big(int ne, int nk, int nh) { return (2 * (size_t)ne + 2 * (size_t)nk + (size_t)nh) * sizeof(uint32_t); }
+extern "C" size_t k4_cov_words(int ne, int nr) { return (size_t)ne * 2 * (size_t)((nr + 31) >> 5); }
 
 extern "C" cudaError_t k4_launch(const K4Args *a, int n_windows, size_t smem, cudaStream_t st)
 {

@@ -60,13 +60,13 @@ def test_oracle_break_and_n_exemption(port_oracle):
     assert (nf[0], nr[0]) == (0, 1)                     # INS: 3 mismatches > 2
 
 
-def _random_entries(rng, batch, w):
+def _random_entries(rng, batch, w, per_hap=None):
     h0, h1 = int(batch.win_hap[w]), int(batch.win_hap[w + 1])
-    nk = int(rng.integers(1, 6))
+    nk = int(rng.integers(1, 6)) if per_hap is None else int(rng.integers(20, 60))
     ents = []
     for h in range(h1 - h0):
         H = int(batch.hap_off[h0 + h + 1] - batch.hap_off[h0 + h])
-        for _ in range(int(rng.integers(0, 4))):
+        for _ in range(int(rng.integers(0, 4)) if per_hap is None else per_hap):
             ty = int(rng.choice([0, 1, 1, 0, 2]))
             kind = rng.random()
             if kind < 0.75:
@@ -106,6 +106,34 @@ def test_k4_matches_oracle(engine_cli, port_oracle, cfg, nwin, keep_only, do_fil
         assert (nf[w] == onf).all() and (nr[w] == onr).all(), (w, nf[w], onf, nr[w], onr)
         n_hits += int((onf + onr).sum()); n_filt += int(ou.sum())
     assert n_hits > 0 and n_filt > 0
+
+
+@pytest.mark.gpu
+def test_k4_deep_windows_keep_their_bit_sets_in_global_memory(engine_cli, port_oracle):
+    """Deep pooled windows (configs[2]: 1000 reads x 16 haplotypes) with many variant entries: the covering-read bit sets
+    (entries x 2 x ceil(reads/32) words) of a window no longer fit one CTA's shared memory (960 entries: 245 KB; the call
+    used to refuse the whole batch).  Such windows run in a second launch with their sets in a global scratch, in the
+    same call as ordinary windows; results against the oracle, window by window."""
+    from dindel_tgi_b200 import synth
+    rng = np.random.default_rng(99)
+    batch = synth.make_batch(3, 4, seed=77)
+    res = engine_cli.compute_likelihoods(batch, want_hpos=True)
+    ents, nks = zip(*[_random_entries(rng, batch, w, per_hap) for w, per_hap in enumerate((None, 14, 60, None))])
+    assert len(ents[2]) * 2 * 32 * 4 > 227 * 1024 and len(ents[1]) * 2 * 32 * 4 > 48 * 1024 and len(ents[0]) < 64
+    strand = rng.integers(0, 2, batch.n_reads).astype(np.uint8)
+    for do_filter in (1, 0):
+        filt, unc, nf, nr = engine_cli.coverage(list(ents), list(nks), strand, max_mismatch=2, do_filter=do_filter)
+        hits = 0
+        for w in range(batch.n_windows):
+            haps, reads, _ = batch.window(w)
+            h0, r0, p0, p1 = int(batch.win_hap[w]), int(batch.win_read[w]), int(res.win_pair[w]), int(res.win_pair[w + 1])
+            of, ou, onf, onr = port_oracle.filter_haplotypes(
+                haps, [r[0] for r in reads], res.hpos[p0:p1].astype(np.int32), res.pairs["offHapHMQ"][p0:p1],
+                res.pairs["numIndels"][p0:p1].astype(np.int32), strand[r0:r0 + len(reads)], ents[w], nks[w], 2, do_filter)
+            assert (filt[h0:h0 + len(haps)] == of).all() and (unc[h0:h0 + len(haps)] == ou).all(), w
+            assert (nf[w] == onf).all() and (nr[w] == onr).all(), w
+            hits += int((onf + onr).sum())
+        assert hits > 1000
 
 
 @pytest.mark.gpu
