@@ -362,8 +362,8 @@ private:
 class Inference {
 public:
     enum Mode { IDLE, GPU, CPU };
-    Inference() : nWindows(0), nRecheck(0), nEmSets(0), nEmMismatch(0), enabled_(false), mode_(IDLE), risky_(false), S_(0),
-                  nh_(0), nr_(0), G_(0), gsize_(0), eps_(0.0), emErr_(0.0), emSets_(0) {}
+    Inference() : nWindows(0), nRecheck(0), nEmSets(0), nEmMismatch(0), nEmUnsupported(0), enabled_(false), mode_(IDLE), risky_(false), S_(0),
+                  nh_(0), nr_(0), G_(0), gsize_(0), eps_(0.0), emErr_(0.0), emSets_(0), emUnavailable_(false) {}
     void enable(bool on) { enabled_ = on; }
     bool enabled() const { return enabled_; }
     bool enter() { if (!enabled_ || mode_ != IDLE) return false; mode_ = GPU; risky_ = false; eps_ = 0.0; emErr_ = 0.0; nWindows++; return true; }
@@ -440,9 +440,15 @@ public:
     template <class Provider>
     void emBegin(Provider &e, const std::vector<uint8_t> &compatible, size_t nSets, double a0, double tol)
     {
-        emCompat_ = compatible; emSets_ = nSets;
+        emCompat_ = compatible; emSets_ = nSets; emUnavailable_ = false;
         if (mode_ != GPU) return;
-        e.windowEM(compatible, nSets, a0, tol, emLoglik_, emIters_, emPi_, emMargin_);
+        // A window the kernel is not built for (more haplotypes than K3's 64: deep pooled data with many candidate
+        // variants) is not an error of the window: its EM runs in the reference's own loop, like an undecided one.
+        try { e.windowEM(compatible, nSets, a0, tol, emLoglik_, emIters_, emPi_, emMargin_); }
+        catch (std::string &why) {
+            if (why.find("shape not supported") == std::string::npos && why.find("more than 64 haplotypes") == std::string::npos) throw;
+            emUnavailable_ = true; risky_ = true; nEmUnsupported++;
+        }
     }
     // returns true (converged) and fills loglik / pi / iter when the GPU's EM of set th stands; else the reference's
     // own while-loop runs (returns false)
@@ -450,6 +456,7 @@ public:
     bool em(int th, const IntVec &compatible, double tol, double &loglik, DblVec &pi, int &iter)
     {
         if (mode_ != GPU) return false;
+        if (emUnavailable_) { risky_ = true; return false; }
         nEmSets++;
         const size_t nh = compatible.size();
         if ((size_t)th >= emSets_ || emCompat_.size() != emSets_ * nh) { nEmMismatch++; risky_ = true; return false; }
@@ -476,7 +483,7 @@ public:
         double diff = l1 - l2; return l2 + log(1.0 + exp(diff));
     }
     static double phred(double ref, double alt) { return -10.0 * (ref - addLogsHost(alt, ref)) / log(10.0); }
-    long nWindows, nRecheck, nEmSets, nEmMismatch;
+    long nWindows, nRecheck, nEmSets, nEmMismatch, nEmUnsupported;
 private:
     void widen(double e) { if (e > eps_) eps_ = e; }
     bool enabled_;
@@ -489,6 +496,7 @@ private:
     double eps_, emErr_;
     std::vector<uint8_t> emCompat_;
     size_t emSets_;
+    bool emUnavailable_;
     std::vector<double> emLoglik_, emPi_, emMargin_;
     std::vector<int32_t> emIters_;
 };

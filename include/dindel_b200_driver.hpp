@@ -393,6 +393,7 @@ struct dindel_b200_driver {
         for (size_t k = 0; k < workers.size(); k++) {
             totals.nWindows += workers[k].replay.inf.nWindows; totals.nRecheck += workers[k].replay.inf.nRecheck;
             totals.nEmSets += workers[k].replay.inf.nEmSets; totals.nEmMismatch += workers[k].replay.inf.nEmMismatch;
+            totals.nEmUnsupported += workers[k].replay.inf.nEmUnsupported;
         }
         double tp = 0.0, tf = 0.0, trd = 0.0, thp = 0.0;
         for (size_t k = 0; k < workers.size(); k++) { tp += workers[k].tPrepare; tf += workers[k].tFinish; trd += workers[k].tReads; thp += workers[k].tHaps; }
@@ -400,8 +401,8 @@ struct dindel_b200_driver {
         fprintf(stderr, "dindel_b200 batched: windows %ld batches %ld threads %d late_failures %ld; wall: read %.3f s, flush(GPU) %.3f s, write %.3f s; "
                         "thread-seconds: prepare %.3f finish %.3f; engine created in %.3f s (under the first prepare)\n", nWindows, nBatches, (int)workers.size(), nLateFail, tRead, tFlush, tWrite, tp, tf, tEngine);
         if (totals.nWindows)
-            fprintf(stderr, "dindel_b200 inference: windows %ld rechecked_on_host %ld em_sets %ld em_set_mismatch %ld\n",
-                    totals.nWindows, totals.nRecheck, totals.nEmSets, totals.nEmMismatch);
+            fprintf(stderr, "dindel_b200 inference: windows %ld rechecked_on_host %ld em_sets %ld em_set_mismatch %ld em_unsupported_windows %ld\n",
+                    totals.nWindows, totals.nRecheck, totals.nEmSets, totals.nEmMismatch, totals.nEmUnsupported);
         if (gpu && gpu->nStatsCalls)
             { fprintf(stderr, "dindel_b200 read stats: device_calls %ld jobs %ld\n", gpu->nStatsCalls, gpu->nStatsJobs); gpu->nStatsCalls = 0; }
     }

@@ -27,8 +27,8 @@ if not (len(sys.argv) > 3 and sys.argv[3] == "--dump"):
                         '#define DINDEL_B200_STATS(JOBS, NREADS, OUT) (dindel_b200_replay ? dindel_b200::deviceStats(*dindel_b200_replay, JOBS, NREADS, OUT) : (dindel_b200_gpu ? dindel_b200::deviceStats(*dindel_b200_gpu, JOBS, NREADS, OUT) : false))\n'
                         'static std::string dindel_b200_bam_arg; static int dindel_b200_multiple_files = 0; // main() -> batched driver\n'
                         'static struct dindel_b200_report_t { ~dindel_b200_report_t() { if (dindel_b200_inf.nWindows) '
-                        'fprintf(stderr, "dindel_b200 inference: windows %ld rechecked_on_host %ld em_sets %ld em_set_mismatch %ld\\n", '
-                        'dindel_b200_inf.nWindows, dindel_b200_inf.nRecheck, dindel_b200_inf.nEmSets, dindel_b200_inf.nEmMismatch); '
+                        'fprintf(stderr, "dindel_b200 inference: windows %ld rechecked_on_host %ld em_sets %ld em_set_mismatch %ld em_unsupported_windows %ld\\n", '
+                        'dindel_b200_inf.nWindows, dindel_b200_inf.nRecheck, dindel_b200_inf.nEmSets, dindel_b200_inf.nEmMismatch, dindel_b200_inf.nEmUnsupported); '
                         'if (dindel_b200_gpu && dindel_b200_gpu->nStatsCalls) fprintf(stderr, "dindel_b200 read stats: device_calls %ld jobs %ld\\n", dindel_b200_gpu->nStatsCalls, dindel_b200_gpu->nStatsJobs); } } dindel_b200_report;\n'
                         '// the one engine of the process; K2 / K3 (the read sums of diploidGLF / the EM of estimateHaplotypeFrequenciesBayesEM) on the GPU too\n'
                         'static dindel_b200::Engine *dindel_b200_engine(const DetInDel::Parameters & params, size_t nBams)\n{\n'

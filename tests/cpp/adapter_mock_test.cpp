@@ -87,8 +87,35 @@ static MockRead mk(const std::string &s, uint32_t start)
 }
 #define CHECK(c) do { if (!(c)) { fprintf(stderr, "adapter_mock_test: check failed at line %d: %s\n", __LINE__, #c); return 1; } } while (0)
 
+// a K3 provider that refuses the window the way the library does for more than 64 haplotypes / another error
+struct RefusingEM {
+    std::string why;
+    void windowEM(const std::vector<uint8_t> &, size_t, double, double, std::vector<double> &, std::vector<int32_t> &,
+                  std::vector<double> &, std::vector<double> &) { throw why; }
+};
+
 int main()
 {
+    { // host logic only: a window the EM kernel is not built for goes to the caller's own loop, other errors propagate
+        dindel_b200::Inference inf;
+        inf.enable(true);
+        CHECK(inf.enter() && inf.gpu());
+        RefusingEM r;
+        r.why = "dindel_b200: batch shape not supported by the compiled kernels (more than 64 haplotypes in a window)";
+        std::vector<uint8_t> comp(2 * 70, 1);
+        inf.emBegin(r, comp, 2, 0.001, 1e-4);
+        std::vector<int> c70(70, 1);
+        std::vector<double> pi(70, 0.0);
+        double ll = 0.0; int it = 0;
+        CHECK(inf.risky() && inf.nEmUnsupported == 1 && !inf.em(0, c70, 1e-4, ll, pi, it) && inf.risky());
+        inf.leave();
+        CHECK(inf.enter());
+        r.why = "dindel_b200: CUDA runtime error (an illegal memory access was encountered)";
+        bool thrown = false;
+        try { inf.emBegin(r, comp, 2, 0.001, 1e-4); } catch (std::string &) { thrown = true; }
+        CHECK(thrown && inf.nEmUnsupported == 1);
+        inf.leave();
+    }
     Params p = {5e-4, 1e-5, 100.0, 0.01, 0.95, 5, 2, -1, false, false};
     dindel_b200::Engine *eng = 0;
     try {
