@@ -1523,7 +1523,7 @@ static int em_sets(dindel_ctx *ctx, const dindel_em_in *in, dindel_em_out *out, 
         const int w = in->set_window[s];
         const long long nh = ctx->win_nh[w];
         if (in->set_off[s + 1] - in->set_off[s] != nh) return fail(ctx, DINDEL_E_INVALID, "set_off does not match nh");
-        if (nh > k3_max_haps()) return fail(ctx, DINDEL_E_UNSUPPORTED, "more than 64 haplotypes in a window");
+        if (nh > k3_max_haps()) return fail(ctx, DINDEL_E_UNSUPPORTED, "more than 256 haplotypes in a window (K3)");
         const long long np = ctx->win_pair[w + 1] - ctx->win_pair[w];
         const int nr = nh ? (int)(np / nh) : 0;
         if (nh > max_nh) max_nh = (int)nh;

@@ -257,6 +257,134 @@ __global__ void __launch_bounds__(32 * K3_MAX_WARPS) k3_bayes_em(K3Args A)
     }
 }
 
+// K3 for windows with more than K3_MAXH haplotypes (deep pooled data: 70-90 candidate haplotypes per window, thousands
+// of reads).  A read's responsibilities no longer fit one thread's registers, so the roles turn: a WARP owns a read, its
+// lanes hold the haplotypes h = lane, lane + 32, ... (K3W_KH slots); max / sum of the log-sum-exp by warp shuffles, the
+// counts nk[h] accumulate per lane over the warp's reads, then the warps are summed in a fixed order (deterministic).
+// The ll values come straight from the pair records (L2) every pass: 2 500 x 92 doubles do not fit shared memory.
+// Same arithmetic per read as k3_bayes_em, another reduction order: inside the same error bound.
+#define K3W_MAXH 256
+#define K3W_KH (K3W_MAXH / 32)
+__global__ void __launch_bounds__(32 * K3_MAX_WARPS) k3_bayes_em_wide(K3Args A)
+{
+    __shared__ double s_lpi[K3W_MAXH], s_pi[K3W_MAXH], s_nk[K3W_MAXH];
+    __shared__ double s_wpart[K3_MAX_WARPS][K3W_MAXH + 2];
+    __shared__ double s_scal[4];
+    const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarps = blockDim.x >> 5;
+    if (s >= A.n_sets) return;
+    const int w = A.set_window[s];
+    const int nh = A.win_hap[w + 1] - A.win_hap[w];
+    const int nr = A.win_read[w + 1] - A.win_read[w];
+    const dindel_pair_out *p = A.pairs + A.win_pair[w];
+    const uint8_t *compat = A.compatible + A.set_off[s];
+    int numah = 0;
+    for (int h = 0; h < nh; h++) numah += compat[h] ? 1 : 0;
+    for (int h = tid; h < nh; h += blockDim.x) s_lpi[h] = compat[h] ? log(1.0 / (double)numah) : -100.0; // DInDel.cpp:2418
+    __syncthreads();
+    double eOld = K1_NEG_INF, margin = __longlong_as_double(0x7ff0000000000000LL), loglik = 0.0;
+    int iter = 0;
+    for (;;) {
+        // ---- E-step: this warp's reads (DInDel.cpp:2439-2457) ----
+        double nkp[K3W_KH];
+#pragma unroll
+        for (int k = 0; k < K3W_KH; k++) nkp[k] = 0.0;
+        double ll = 0.0, Bp = 0.0;
+        for (int r = wid; r < nr; r += nwarps) {
+            double e[K3W_KH], rl[K3W_KH];
+            double m = K1_NEG_INF;
+#pragma unroll
+            for (int k = 0; k < K3W_KH; k++) {
+                const int h = lane + 32 * k;
+                if (h < nh) {
+                    rl[k] = p[(long long)r * nh + h].ll;
+                    e[k] = s_lpi[h] + rl[k];
+                    m = fmax(m, e[k]);
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+            double sum = 0.0;
+#pragma unroll
+            for (int k = 0; k < K3W_KH; k++) {
+                if (lane + 32 * k < nh) {
+                    e[k] = exp(e[k] - m);
+                    sum += e[k];
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            const double inv = 1.0 / sum;
+#pragma unroll
+            for (int k = 0; k < K3W_KH; k++) {
+                if (lane + 32 * k < nh) {
+                    const double zz = e[k] * inv;
+                    nkp[k] += zz;
+                    Bp += zz * rl[k];
+                }
+            }
+            if (lane == 0) ll += m + log(sum);
+        }
+        // ---- reductions: Bp over the lanes, then everything over the warps in order ----
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) Bp += __shfl_xor_sync(0xffffffffu, Bp, o);
+#pragma unroll
+        for (int k = 0; k < K3W_KH; k++)
+            if (lane + 32 * k < nh) s_wpart[wid][lane + 32 * k] = nkp[k];
+        if (lane == 0) { s_wpart[wid][K3W_MAXH] = ll; s_wpart[wid][K3W_MAXH + 1] = Bp; }
+        __syncthreads();
+        for (int h = tid; h < nh; h += blockDim.x) {
+            double v = 0.0;
+            for (int k = 0; k < nwarps; k++) v += s_wpart[k][h];
+            s_nk[h] = v;
+        }
+        if (tid == 0) {
+            double v0 = 0.0, v1 = 0.0;
+            for (int k = 0; k < nwarps; k++) { v0 += s_wpart[k][K3W_MAXH]; v1 += s_wpart[k][K3W_MAXH + 1]; }
+            s_scal[0] = v0; s_scal[1] = v1;
+        }
+        __syncthreads();
+        // ---- M-step (DInDel.cpp:2461-2480) ----
+        double ahat = 0.0;
+        for (int h = 0; h < nh; h++)
+            if (compat[h]) ahat += s_nk[h] + A.a0;
+        __syncthreads(); // every thread has read s_nk before s_lpi / s_pi change (they are not read above, kept for clarity)
+        for (int h = tid; h < nh; h += blockDim.x) {
+            if (compat[h]) {
+                s_lpi[h] = digamma_pos(s_nk[h] + A.a0) - digamma_pos(ahat);
+                s_pi[h] = log((A.a0 + s_nk[h]) / ((double)numah * A.a0 + (double)nr));
+            } else {
+                s_lpi[h] = -100.0;
+                s_pi[h] = -100.0;
+            }
+        }
+        __syncthreads();
+        // ---- energy and stopping rule (:2484-2492, :2515), every thread on the same shared values ----
+        double eNew = s_scal[1];
+        for (int h = 0; h < nh; h++) eNew += s_pi[h] * s_nk[h];
+        loglik = s_scal[0];
+        const double dE = fabs(eOld - eNew);
+        if (iter <= 25) margin = fmin(margin, fabs(dE - A.tol));
+        const bool done = (dE < A.tol) || (iter > 25);
+        eOld = eNew;
+        iter++;
+        if (done) break;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        double zs = 0.0;
+        for (int h = 0; h < nh; h++) zs += exp(s_pi[h]);
+        const long long off = A.set_off[s];
+        for (int h = 0; h < nh; h++) {
+            A.pi[off + h] = s_pi[h];
+            A.freqs[off + h] = exp(s_pi[h]) / zs;
+        }
+        A.loglik[s] = loglik;
+        A.iters[s] = iter;
+        if (A.margin) A.margin[s] = margin;
+        if (A.energy) A.energy[s] = eOld;
+    }
+}
+
 extern "C" cudaError_t k2_launch(const K2Args *a, int max_npairs, cudaStream_t st)
 {
     if (a->n_jobs <= 0) return cudaSuccess;
@@ -293,6 +421,8 @@ extern "C" cudaError_t k3_launch(const K3Args *a, int max_nh, int max_nr, size_t
     if (max_nh <= 8) return k3_launch_nhp<8>(a, threads, need, stage, st);
     if (max_nh <= 16) return k3_launch_nhp<16>(a, threads, need, stage, st);
     if (max_nh <= 32) return k3_launch_nhp<32>(a, threads, need, stage, st);
-    return k3_launch_nhp<64>(a, threads, need, stage, st);
+    if (max_nh <= K3_MAXH) return k3_launch_nhp<64>(a, threads, need, stage, st);
+    k3_bayes_em_wide<<<a->n_sets, 32 * K3_MAX_WARPS, 0, st>>>(*a); // a warp per read
+    return cudaGetLastError();
 }
-extern "C" int k3_max_haps(void) { return K3_MAXH; }
+extern "C" int k3_max_haps(void) { return K3W_MAXH; }

@@ -442,11 +442,11 @@ public:
     {
         emCompat_ = compatible; emSets_ = nSets; emUnavailable_ = false;
         if (mode_ != GPU) return;
-        // A window the kernel is not built for (more haplotypes than K3's 64: deep pooled data with many candidate
-        // variants) is not an error of the window: its EM runs in the reference's own loop, like an undecided one.
+        // A window the kernel is not built for (more haplotypes than K3 takes: 256) is not an error of the window: its EM
+        // runs in the reference's own loop, like an undecided one.
         try { e.windowEM(compatible, nSets, a0, tol, emLoglik_, emIters_, emPi_, emMargin_); }
         catch (std::string &why) {
-            if (why.find("shape not supported") == std::string::npos && why.find("more than 64 haplotypes") == std::string::npos) throw;
+            if (why.find("shape not supported") == std::string::npos) throw;
             emUnavailable_ = true; risky_ = true; nEmUnsupported++;
         }
     }

@@ -121,6 +121,42 @@ def test_gpu_bayes_em(port_oracle):
     e.close()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("nh,nr", [(80, 700), (65, 40), (200, 1300)])
+def test_gpu_bayes_em_wide_windows(port_oracle, nh, nr):
+    """More than 64 haplotypes per window (1000x pooled data has windows with 72-92): the warp-per-read kernel
+    (k3_bayes_em_wide) against the oracle on a loaded likelihood matrix: identical pass counts, 1e-9 relative."""
+    from dindel_tgi_b200 import engine
+    rng = np.random.default_rng(nh * 1000 + nr)
+    # reads drawn from a few true haplotypes: ll close to 0 on them, penalties elsewhere (the shape of a real matrix)
+    truth = rng.integers(0, nh, nr)
+    rl = -rng.gamma(2.0, 6.0, (nr, nh)) - 3.0
+    rl[np.arange(nr), truth] = -rng.gamma(1.0, 0.3, nr)
+    rl[:, : nh // 3] += 2.5                                   # a block of near-equivalent haplotypes: slow EM convergence
+    e = engine.Engine(engine.cli_params(), 0)
+    e.load_likelihoods([rl.ravel(), rl[:50, :8].ravel().copy()], [nh, 8])
+    sets, comps = [], []
+    for k in range(6):
+        c = (rng.random(nh) < (0.3 + 0.1 * k)).astype(np.uint8)
+        c[int(truth[0])] = 1
+        sets.append(0); comps.append(c)
+    sets.append(0); comps.append(np.ones(nh, dtype=np.uint8))
+    sets.append(1); comps.append(np.ones(8, dtype=np.uint8))    # a narrow window in the same call
+    ll, it, pi, fr = e.bayes_em(sets, comps, 0.001, 1e-4)
+    mats = {0: (rl.ravel(), nh), 1: (rl[:50, :8].ravel(), 8)}
+    its = []
+    for j, w in enumerate(sets):
+        m, n = mats[w]
+        wll, wit, wpi, wfr = port_oracle.bayes_em(m, n, comps[j], 0.001, 1e-4)
+        assert it[j] == wit, (j, it[j], wit)
+        assert abs(ll[j] - wll) <= RTOL * abs(wll)
+        assert np.allclose(pi[j], wpi, rtol=RTOL, atol=0)
+        assert np.allclose(fr[j], wfr, rtol=1e-8, atol=1e-300)
+        its.append(wit)
+    assert len(set(its)) >= 2
+    e.close()
+
+
 def test_oracle_digamma_against_cephes(port_oracle):
     """boost::math::digamma (DInDel.cpp:2466, 2472) is third party and absent here, so `ora_digamma` cannot be pinned
     against it; it is cross-checked against an independent published implementation instead (Cephes psi through
