@@ -52,11 +52,11 @@ def sh(cmd, log, env=None):
         raise RuntimeError("%s failed (rc %d), see %s:\n%s" % (cmd[0], rc, log, open(log).read()[-2000:]))
 
 
-def prepare(work, length, seed, coverage=30.0, per_file=1000, min_count=2):
+def prepare(work, length, seed, coverage=30.0, per_file=1000, min_count=2, read_len=100):
     """synthetic genome -> BAM -> candidates -> window files.  Returns dict of paths."""
     os.makedirs(work, exist_ok=True)
     sh([sys.executable, os.path.join(HERE, "synth_genome.py"), "--out", work, "--length", str(length),
-        "--coverage", str(coverage), "--seed", str(seed)], os.path.join(work, "synth.log"))
+        "--coverage", str(coverage), "--seed", str(seed), "--read-len", str(read_len)], os.path.join(work, "synth.log"))
     ref, sam, bam = (os.path.join(work, n) for n in ("ref.fa", "sample.sam", "sample.bam"))
     sh([BAMTOOL, "faidx", ref], os.path.join(work, "faidx.log"))
     sh([BAMTOOL, "sam2bam", sam, bam], os.path.join(work, "sam2bam.log"))
@@ -274,11 +274,13 @@ def main():
     ap.add_argument("--gpu-no-batch", action="store_true", help="gpu arm: the window-at-a-time loop (DINDEL_B200_NO_BATCH)")
     ap.add_argument("--gpu-device-stats", default="", help="DINDEL_B200_DEVICE_STATS of the gpu arm: 1 = the read statistics of every "
                     "called site from K6, 0 = always the reference's host loops (default: by size)")
+    ap.add_argument("--read-len", type=int, default=100, help="read length of the synthetic BAM (configs[3]: 250)")
+    ap.add_argument("--stage3-args", default="", help="extra arguments for stage 3 of every arm, e.g. '--maxLengthIndel 10 --maxHap 32'")
     ap.add_argument("--host-inference", action="store_true", help="gpu arm: diploidGLF / EM sums on the host (DINDEL_B200_HOST_INFERENCE)")
     a = ap.parse_args()
     arms = a.arms.split(",")
     procs = a.procs or len(os.sched_getaffinity(0))
-    prep = prepare(a.work, a.length, a.seed, a.coverage, a.windows_per_file)
+    prep = prepare(a.work, a.length, a.seed, a.coverage, a.windows_per_file, read_len=a.read_len)
     res = {"length": a.length, "coverage": a.coverage, "n_candidates": prep["n_candidates"],
            "n_windows": prep["n_windows"], "window_files": len(prep["window_files"]), "procs": procs, "gpu_procs": a.gpu_procs,
            "filterHaplotypes": a.filter_haplotypes, "libFile": a.lib_file, "pooled": a.pooled}
@@ -305,7 +307,7 @@ def main():
             glfs, vcf, wall, n_calls = run_arm(arm, prep, a.work, procs if arm == "cpu" else a.gpu_procs,
                                                extra=(["--filterHaplotypes"] if a.filter_haplotypes else []) +
                                                (["--libFile", prep["libraries"]] if a.lib_file else []) +
-                                               (["--outputRealignedBAM"] if a.realigned_bam else []), env=aenv or None, tag=tag,
+                                               (["--outputRealignedBAM"] if a.realigned_bam else []) + a.stage3_args.split(), env=aenv or None, tag=tag,
                                                mode="--doPooled" if a.pooled else "--doDiploid",
                                                one_file=a.gpu_one_file and arm == "gpu")
             ok, err = glf_stats(glfs)

@@ -275,6 +275,26 @@ def test_device_read_stats_identical(tmp_path, extra):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("pooled", [False, True])
+def test_long_reads_pipeline_identical(tmp_path, pooled):
+    """configs[3] through the real binary: 250-bp reads (longer than most candidate haplotypes: long LO / RO overhangs),
+    --maxLengthIndel 10 (the J = 11 kernel classes) and up to 32 haplotypes per window; glf (and VCF) byte-identical to the
+    stock CPU binary."""
+    if not run_e2e.have_binaries(("cpu", "gpu")):
+        pytest.skip("oracle/_ref binaries not built (reference sources absent at build time)")
+    r = subprocess.run([sys.executable, os.path.join(E2E, "run_e2e.py"), "--work", str(tmp_path), "--length", "30000",
+                        "--coverage", "40", "--seed", "9", "--read-len", "250", "--stage3-args", "--maxLengthIndel 10 --maxHap 32",
+                        "--arms", "cpu,gpu", "--windows-per-file", "3", "--heap-neutral", "--gpu-one-file"] +
+                       (["--pooled"] if pooled else []), capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout + r.stderr
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    hn = res["heap_neutral"]
+    assert hn["glf_identical"] and hn["cpu"]["windows_ok"] >= 10 and hn["gpu"]["inference"]["windows"] >= 10, res
+    if not pooled:
+        assert hn["vcf_identical"] and hn["cpu"]["vcf_calls"] >= 8, res
+
+
+@pytest.mark.gpu
 def test_batched_driver_over_several_devices(tmp_path):
     """configs[4] in the small: the patched binary's batched driver shards every batch of windows over several CUDA
     devices through the in-process scheduler (DINDEL_B200_DEVICES -> Engine::enableMulti -> dindel_b200_multi_process);
