@@ -25,7 +25,9 @@
 extern "C" {
 #endif
 
-#define DINDEL_B200_ABI_VERSION 4
+/* 4: dindel_b200_process / dindel_job, the multi-device calls, margins of the EM.  5 (additive: no existing struct or entry
+ * changed): dindel_b200_read_stats (K6), dindel_b200_load_records, dindel_b200_run_static. */
+#define DINDEL_B200_ABI_VERSION 5
 
 /* error codes (batch-fatal) */
 #define DINDEL_OK 0

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(engine.EXPORTS) == names
-    assert lib.dindel_b200_abi_version() == 4
+    assert lib.dindel_b200_abi_version() == 5
 
 
 def test_struct_layouts_match_header():
