@@ -363,7 +363,7 @@ class Inference {
 public:
     enum Mode { IDLE, GPU, CPU };
     Inference() : nWindows(0), nRecheck(0), nEmSets(0), nEmMismatch(0), nEmUnsupported(0), enabled_(false), mode_(IDLE), risky_(false), S_(0),
-                  nh_(0), nr_(0), G_(0), gsize_(0), eps_(0.0), emErr_(0.0), emSets_(0), emUnavailable_(false) {}
+                  nh_(0), nr_(0), G_(0), gsize_(0), eps_(0.0), emErr_(0.0), emSets_(0), emUnavailable_(false) { for (int i = 0; i < 6; i++) nTrip[i] = 0; }
     void enable(bool on) { enabled_ = on; }
     bool enabled() const { return enabled_; }
     bool enter() { if (!enabled_ || mode_ != IDLE) return false; mode_ = GPU; risky_ = false; eps_ = 0.0; emErr_ = 0.0; nWindows++; return true; }
@@ -396,12 +396,12 @@ public:
     // (sums, log-likelihoods: absolute bound); gtLin: probabilities / frequencies derived from the EM (relative bound)
     bool gt(double a, double b)
     {
-        if (mode_ == GPU && fabs(a - b) <= 2.0 * eps_ + 2.0 * emErr_) risky_ = true;
+        if (mode_ == GPU && fabs(a - b) <= 2.0 * eps_ + 2.0 * emErr_) trip(0);
         return a > b;
     }
     bool gtLin(double a, double b)
     {
-        if (mode_ == GPU && fabs(a - b) <= 4.0 * emErr_ * (fabs(a) > fabs(b) ? fabs(a) : fabs(b))) risky_ = true;
+        if (mode_ == GPU && fabs(a - b) <= 4.0 * emErr_ * (fabs(a) > fabs(b) ? fabs(a) : fabs(b))) trip(1);
         return a > b;
     }
     // a value about to be printed: its text must not depend on where inside the bound the true value lies
@@ -409,7 +409,7 @@ public:
     {
         if (mode_ == GPU) {
             const double e = 2.0 * eps_ + 2.0 * emErr_;
-            if (text(v - e) != text(v + e)) risky_ = true;
+            if (text(v - e) != text(v + e)) trip(2);
         }
         return v;
     }
@@ -417,7 +417,7 @@ public:
     {
         if (mode_ == GPU) {
             const double e = 4.0 * emErr_ * fabs(v);
-            if (text(v - e) != text(v + e)) risky_ = true;
+            if (text(v - e) != text(v + e)) trip(3);
         }
         return v;
     }
@@ -430,7 +430,7 @@ public:
         const double e = 2.0 * eps_;
         const std::string t = text(phred(ref, alt));
         for (int i = 0; i < 4; i++)
-            if (text(phred(ref + ((i & 1) ? e : -e), alt + ((i & 2) ? e : -e))) != t) { risky_ = true; return; }
+            if (text(phred(ref + ((i & 1) ? e : -e), alt + ((i & 2) ? e : -e))) != t) { trip(4); return; }
     }
     // ---- Bayes EM (K3) ----
     // All EM runs of the window in one launch; em() then hands them out set by set and checks that the set it was
@@ -466,7 +466,7 @@ public:
         // relative (measured 1e-15, tools/k23_deviation.py -> profiles/r2_k23_deviation.json); a pass that came closer to
         // tol than 1e-10 * (1 + |loglik|) could have gone the other way on the CPU
         const double guard = emGuardRel() * (1.0 + fabs(emLoglik_[th]));
-        if (emMargin_[th] < guard) { risky_ = true; return false; }
+        if (emMargin_[th] < guard) { trip(5); return false; }
         loglik = emLoglik_[th];
         for (size_t h = 0; h < nh; h++) pi[h] = emPi_[th * nh + h];
         iter = emIters_[th];
@@ -484,8 +484,10 @@ public:
     }
     static double phred(double ref, double alt) { return -10.0 * (ref - addLogsHost(alt, ref)) / log(10.0); }
     long nWindows, nRecheck, nEmSets, nEmMismatch, nEmUnsupported;
+    long nTrip[6]; // which guard marked a window undecided: 0 gt, 1 gtLin, 2 printed, 3 printedLin, 4 checkPhred, 5 EM stop-rule margin
 private:
     void widen(double e) { if (e > eps_) eps_ = e; }
+    void trip(int which) { if (!risky_) nTrip[which]++; risky_ = true; } // counts the FIRST guard that tripped in a window
     bool enabled_;
     Mode mode_;
     bool risky_;

@@ -394,6 +394,7 @@ struct dindel_b200_driver {
             totals.nWindows += workers[k].replay.inf.nWindows; totals.nRecheck += workers[k].replay.inf.nRecheck;
             totals.nEmSets += workers[k].replay.inf.nEmSets; totals.nEmMismatch += workers[k].replay.inf.nEmMismatch;
             totals.nEmUnsupported += workers[k].replay.inf.nEmUnsupported;
+            for (int i = 0; i < 6; i++) totals.nTrip[i] += workers[k].replay.inf.nTrip[i];
         }
         double tp = 0.0, tf = 0.0, trd = 0.0, thp = 0.0;
         for (size_t k = 0; k < workers.size(); k++) { tp += workers[k].tPrepare; tf += workers[k].tFinish; trd += workers[k].tReads; thp += workers[k].tHaps; }
@@ -403,6 +404,9 @@ struct dindel_b200_driver {
         if (totals.nWindows)
             fprintf(stderr, "dindel_b200 inference: windows %ld rechecked_on_host %ld em_sets %ld em_set_mismatch %ld em_unsupported_windows %ld\n",
                     totals.nWindows, totals.nRecheck, totals.nEmSets, totals.nEmMismatch, totals.nEmUnsupported);
+        if (totals.nRecheck)
+            fprintf(stderr, "dindel_b200 guard band, first guard that tripped per rechecked window: compare %ld compare_lin %ld printed %ld printed_lin %ld phred %ld em_stop_margin %ld\n",
+                    totals.nTrip[0], totals.nTrip[1], totals.nTrip[2], totals.nTrip[3], totals.nTrip[4], totals.nTrip[5]);
         if (gpu && gpu->nStatsCalls)
             { fprintf(stderr, "dindel_b200 read stats: device_calls %ld jobs %ld\n", gpu->nStatsCalls, gpu->nStatsJobs); gpu->nStatsCalls = 0; }
     }
