@@ -94,6 +94,13 @@ struct RefusingEM {
                   std::vector<double> &, std::vector<double> &) { throw why; }
 };
 
+// a K6 provider that only counts its calls
+struct FakeStats {
+    bool resident; int calls;
+    bool statsResident() const { return resident; }
+    void windowStats(const std::vector<dindel_b200::StatsJob> &jobs, std::vector<dindel_read_stats> &out) { calls++; out.resize(jobs.size()); }
+};
+
 int main()
 {
     { // host logic only: a window the EM kernel is not built for goes to the caller's own loop, other errors propagate
@@ -115,6 +122,21 @@ int main()
         try { inf.emBegin(r, comp, 2, 0.001, 1e-4); } catch (std::string &) { thrown = true; }
         CHECK(thrown && inf.nEmUnsupported == 1);
         inf.leave();
+    }
+    { // host logic only: the K6 policy (by size unless $DINDEL_B200_DEVICE_STATS says otherwise; never when not resident)
+        FakeStats fs = {true, 0};
+        std::vector<dindel_b200::StatsJob> jobs(1, dindel_b200::StatsJob(DINDEL_STATS_SITE, -1));
+        jobs[0].cands.resize(2);
+        std::vector<dindel_read_stats> out;
+        const int pol = dindel_b200::statsPolicy();
+        const bool small = dindel_b200::deviceStats(fs, jobs, 50, out);            // 100 records
+        const bool large = dindel_b200::deviceStats(fs, jobs, 5000, out);          // 10 000 records
+        CHECK(small == (pol > 0) && large == (pol != 0) && fs.calls == (small ? 1 : 0) + (large ? 1 : 0));
+        fs.resident = false;
+        CHECK(!dindel_b200::deviceStats(fs, jobs, 5000, out));
+        std::vector<dindel_b200::StatsJob> none;
+        fs.resident = true;
+        CHECK(!dindel_b200::deviceStats(fs, none, 5000, out));
     }
     Params p = {5e-4, 1e-5, 100.0, 0.01, 0.95, 5, 2, -1, false, false};
     dindel_b200::Engine *eng = 0;
