@@ -530,7 +530,7 @@ int dindel_b200_set_libraries(dindel_ctx *ctx, int n_libs, const int64_t *lib_of
 
 int64_t dindel_b200_count_pairs(const dindel_batch_in *in)
 {
-    if (validate(in) != DINDEL_OK) return -1;
+    if (validate_parallel(in, 4) != DINDEL_OK) return -1; // the same check the compute entries run (sliced above 200 k reads)
     int64_t n = 0;
     for (int w = 0; w < in->n_windows; w++)
         n += (int64_t)(in->win_hap[w + 1] - in->win_hap[w]) * (in->win_read[w + 1] - in->win_read[w]);

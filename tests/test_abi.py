@@ -75,6 +75,28 @@ def test_count_pairs_and_cells_host_logic():
     assert lib.dindel_b200_count_pairs(C.byref(bad._c())) == -1
 
 
+def test_large_batches_are_validated_in_slices():
+    """Above 200 k reads the CSR checks run on several host threads (validate_parallel in csrc/api.cu): a defect anywhere in
+    any slice still refuses the batch.  Host only, through dindel_b200_count_pairs."""
+    from dindel_tgi_b200 import synth
+    batch = synth.make_batch(2, 4000, seed=12)
+    assert batch.n_reads >= 200000
+    lib = engine.load_library()
+    assert lib.dindel_b200_count_pairs(C.byref(batch._c())) == batch.n_pairs()
+    for field in ("read_off", "hap_off", "win_read", "win_hap"):
+        for pos in (0.02, 0.26, 0.5, 0.74, 0.98):
+            arr = getattr(batch, field).copy()
+            k = int(len(arr) * pos)
+            arr[k], arr[k + 1] = arr[k + 1], arr[k]
+            if arr[k] == arr[k + 1]:
+                continue
+            kw = dict(win_hap=batch.win_hap, win_read=batch.win_read, hap_off=batch.hap_off, read_off=batch.read_off)
+            kw[field] = arr
+            bad = engine.Batch(batch.hap_start, kw["win_hap"], kw["win_read"], kw["hap_off"], batch.hap_seq, kw["read_off"],
+                               batch.read_seq, batch.read_qual, batch.read_mapq, batch.read_start, batch.read_flags)
+            assert lib.dindel_b200_count_pairs(C.byref(bad._c())) == -1, (field, pos)
+
+
 def test_no_cpu_fallback_without_device():
     import torch
     if torch.cuda.is_available():
